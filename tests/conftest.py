@@ -1,0 +1,29 @@
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (B200); run with -m gpu on the GPU box")
+
+
+@pytest.fixture(scope="session")
+def golden_unet():
+    return np.load(os.path.join(GOLDEN, "unet.npz"))
+
+
+@pytest.fixture(scope="session")
+def golden_schedule():
+    return np.load(os.path.join(GOLDEN, "schedule.npz"))
+
+
+@pytest.fixture(scope="session")
+def golden_traj():
+    return np.load(os.path.join(GOLDEN, "trajectory.npz"))

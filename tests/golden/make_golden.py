@@ -1,0 +1,162 @@
+"""Generate the committed golden vectors from the REAL reference (run in the build container only).
+
+    python tests/golden/make_golden.py        # writes tests/golden/*.npz
+
+The reference ships no tests or golden vectors for this path, so these files are what
+pins the oracle: every array here is an output of the unmodified reference modules
+(``/root/reference/{face_reenactment,talking_face}/ldm``: ``UNetModel``, ``DDIMSampler``,
+``timestep_embedding``, ``make_beta_schedule``) run on CPU fp32 with the synthetic weights of
+``oracle.ldm_oracle.init_state_dict`` (loaded with ``strict=True`` — which also proves the 626
+parameter names/shapes).  ``/root/reference`` does not exist on the GPU box; the tests there read
+only the ``.npz`` files.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.abspath(os.path.join(HERE, "..", "..")))
+
+from oracle import ldm_oracle as O  # noqa: E402
+from oracle import ref_shim as R  # noqa: E402
+
+
+def synth_inputs(cfg, B, hw, seed, ctx_len=1):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(B, cfg["in_channels"], hw, hw, generator=g)
+    ctx = torch.randn(B, ctx_len, cfg["context_dim"], generator=g)
+    return x, ctx
+
+
+def unet_goldens():
+    out = {}
+    cases = [  # name, cfg, flavour, B, hw, ctx_len, timesteps
+        ("tiny_c1", O.TINY_UNET, "face_reenactment", 2, 8, 1, [981, 501, 21]),
+        ("tiny_c3", O.TINY_UNET, "face_reenactment", 2, 8, 3, [981, 21]),
+        ("tiny_hw16", O.TINY_UNET, "face_reenactment", 3, 16, 1, [501]),
+        ("fr_32", O.FR_UNET, "face_reenactment", 1, 32, 1, [981]),
+        ("tf_32", O.TF_UNET, "talking_face", 1, 32, 1, [501]),
+    ]
+    for name, cfg, flavour, B, hw, cl, tsteps in cases:
+        sd = O.init_state_dict(cfg, seed=0)
+        ref = R.reference_unet(cfg, flavour).eval()
+        ref.load_state_dict(sd, strict=True)
+        assert len(list(ref.buffers())) == 0
+        x, ctx = synth_inputs(cfg, B, hw, seed=1, ctx_len=cl)
+        out[f"{name}/checksum"] = np.asarray(O.state_dict_checksum(sd), dtype=np.float64)
+        out[f"{name}/n_params"] = np.asarray([len(sd), sum(v.numel() for v in sd.values())], dtype=np.int64)
+        for t in tsteps:
+            tt = torch.tensor([t] * B, dtype=torch.long)
+            with torch.no_grad():
+                eps = ref(x, tt, context=ctx)
+            out[f"{name}/eps_t{t}"] = eps.numpy()
+        # per-sample distinct timesteps (training-style call, ddpm.py:1015)
+        tt = torch.tensor([(37 * (i + 1)) % 1000 for i in range(B)], dtype=torch.long)
+        with torch.no_grad():
+            out[f"{name}/eps_tmixed"] = ref(x, tt, context=ctx).numpy()
+        out[f"{name}/tmixed"] = tt.numpy()
+        if name == "tiny_c1":
+            # block-level taps through forward hooks on the reference module
+            taps = {}
+            hooks = []
+            for bn, mod in [(f"input_blocks.{i}", m) for i, m in enumerate(ref.input_blocks)] + \
+                           [("middle_block", ref.middle_block)] + \
+                           [(f"output_blocks.{i}", m) for i, m in enumerate(ref.output_blocks)]:
+                hooks.append(mod.register_forward_hook(lambda m, a, o, bn=bn: taps.__setitem__(bn, o.detach())))
+            with torch.no_grad():
+                ref(x, torch.tensor([981] * B), context=ctx)
+            for h in hooks:
+                h.remove()
+            for bn, v in taps.items():
+                out[f"{name}/tap/{bn}"] = v.numpy()
+    return out
+
+
+def schedule_goldens():
+    out = {}
+    R.import_reference("face_reenactment")
+    from ldm.modules.diffusionmodules.util import timestep_embedding
+    unet = torch.nn.Identity()
+    model = R.LatentDiffusionStandIn(unet)
+    out["ddpm/betas"] = model.betas.numpy()
+    out["ddpm/alphas_cumprod"] = model.alphas_cumprod.numpy()
+    out["ddpm/alphas_cumprod_prev"] = model.alphas_cumprod_prev.numpy()
+    for S in (50, 200, 7):
+        for eta in (0.0, 1.0):
+            smp = R.cpu_ddim_sampler(model)
+            smp.make_schedule(S, ddim_eta=eta, verbose=False)
+            n = smp.ddim_timesteps.shape[0]
+            # values exactly as p_sample_ddim materialises them: torch.full(..., v) in fp32 (ddim.py:188-191)
+            f = lambda arr: np.asarray([torch.full((1,), arr[i]).item() for i in range(n)], dtype=np.float32)
+            k = f"ddim/S{S}_eta{int(eta)}"
+            out[k + "/timesteps"] = np.asarray(smp.ddim_timesteps, dtype=np.int64)
+            out[k + "/a_t"] = f(smp.ddim_alphas)
+            out[k + "/a_prev"] = f(smp.ddim_alphas_prev)
+            out[k + "/sigma_t"] = f(smp.ddim_sigmas)
+            out[k + "/sqrt_one_minus_at"] = f(smp.ddim_sqrt_one_minus_alphas)
+    t = torch.tensor([0, 1, 21, 501, 981, 999])
+    out["temb/t"] = t.numpy()
+    out["temb/dim160"] = timestep_embedding(t, 160).numpy()
+    out["temb/dim32"] = timestep_embedding(t, 32).numpy()
+    return out
+
+
+def trajectory_goldens():
+    """Full DDIM trajectories of the reference sampler on the tiny UNet (seconds on CPU)."""
+    out = {}
+    cfg = O.TINY_UNET
+    sd = O.init_state_dict(cfg, seed=0)
+    B, hw = 2, 8
+    # ---- FR flavour: ddim.py, eta 0 / eta 1 / CFG -------------------------------------------
+    ref = R.reference_unet(cfg, "face_reenactment").eval()
+    ref.load_state_dict(sd, strict=True)
+    model = R.LatentDiffusionStandIn(ref)
+    x_T, ctx = synth_inputs(cfg, B, hw, seed=2)
+    g = torch.Generator().manual_seed(3)
+    uc = torch.randn(B, 1, cfg["context_dim"], generator=g)
+    for tag, S, eta, scale in [("fr_S10_eta0", 10, 0.0, 1.0), ("fr_S50_eta0", 50, 0.0, 1.0),
+                               ("fr_S10_eta1", 10, 1.0, 1.0), ("fr_S10_cfg3", 10, 0.0, 3.0)]:
+        smp = R.cpu_ddim_sampler(model)
+        torch.manual_seed(1234)  # the per-step torch.randn draws of noise_like (util.py:264-267)
+        samples, inter = smp.sample(S, batch_size=B, shape=[3, hw, hw], conditioning=ctx, eta=eta, x_T=x_T,
+                                    verbose=False, log_every_t=3, unconditional_guidance_scale=scale,
+                                    unconditional_conditioning=uc if scale != 1.0 else None)
+        out[f"traj/{tag}/samples"] = samples.numpy()
+        out[f"traj/{tag}/x_inter"] = torch.stack(inter["x_inter"]).numpy()
+        out[f"traj/{tag}/pred_x0"] = torch.stack(inter["pred_x0"]).numpy()
+    out["traj/x_T"] = x_T.numpy()
+    out["traj/ctx"] = ctx.numpy()
+    out["traj/uc"] = uc.numpy()
+    # ---- TF flavour: ddim2cond.py with the 2-key dict conditioning --------------------------
+    cfg9 = dict(cfg, in_channels=9)
+    sd9 = O.init_state_dict(cfg9, seed=0)
+    ref9 = R.reference_unet(cfg9, "talking_face").eval()
+    ref9.load_state_dict(sd9, strict=True)
+    model9 = R.LatentDiffusionStandIn(ref9, two_cond=True)
+    g = torch.Generator().manual_seed(4)
+    c34 = torch.randn(B, 6, hw, hw, generator=g)
+    smp = R.cpu_ddim_sampler(model9, "talking_face")
+    torch.manual_seed(1234)
+    samples, x_inter = smp.sample(10, batch_size=B, shape=[3, hw, hw],
+                                  conditioning={"class_label_&_audio": ctx, "motion_&_id": c34},
+                                  eta=1.0, x_T=x_T, verbose=False, log_every_t=3)
+    out["traj/tf_S10_eta1/samples"] = samples.numpy()
+    out["traj/tf_S10_eta1/x_inter"] = torch.stack(x_inter).numpy()
+    out["traj/c34"] = c34.numpy()
+    return out
+
+
+def main():
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    for fn, gen in (("unet.npz", unet_goldens), ("schedule.npz", schedule_goldens),
+                    ("trajectory.npz", trajectory_goldens)):
+        data = gen()
+        path = os.path.join(HERE, fn)
+        np.savez_compressed(path, **data)
+        print(fn, len(data), "arrays", os.path.getsize(path) // 1024, "KiB")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,129 @@
+"""Pins the oracle restatement (oracle/ldm_oracle.py) to the committed golden vectors, which are
+outputs of the REAL reference (tests/golden/make_golden.py).  CPU only."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ldm_oracle as O
+from oracle import ref_shim as R
+
+CASES = {  # name -> (cfg, B, hw, ctx_len, timesteps)
+    "tiny_c1": (O.TINY_UNET, 2, 8, 1, [981, 501, 21]),
+    "tiny_c3": (O.TINY_UNET, 2, 8, 3, [981, 21]),
+    "tiny_hw16": (O.TINY_UNET, 3, 16, 1, [501]),
+    "fr_32": (O.FR_UNET, 1, 32, 1, [981]),
+    "tf_32": (O.TF_UNET, 1, 32, 1, [501]),
+}
+
+
+def synth_inputs(cfg, B, hw, seed, ctx_len=1):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(B, cfg["in_channels"], hw, hw, generator=g)
+    ctx = torch.randn(B, ctx_len, cfg["context_dim"], generator=g)
+    return x, ctx
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_unet_eps_matches_reference_golden(name, golden_unet):
+    cfg, B, hw, cl, tsteps = CASES[name]
+    sd = O.init_state_dict(cfg, 0)
+    np.testing.assert_allclose(np.asarray(O.state_dict_checksum(sd)), golden_unet[f"{name}/checksum"], rtol=1e-12)
+    assert [len(sd), sum(v.numel() for v in sd.values())] == golden_unet[f"{name}/n_params"].tolist()
+    x, ctx = synth_inputs(cfg, B, hw, 1, cl)
+    for t in tsteps:
+        eps = O.unet_forward(sd, cfg, x, torch.tensor([t] * B), ctx)
+        # same ATen ops in the same order: the restatement is bit-exact here; 2e-6 is the fp32
+        # thread-count noise floor measured in SURVEY §4 for a differently-threaded host
+        assert O.rel_l2(eps, torch.from_numpy(golden_unet[f"{name}/eps_t{t}"])) <= 2e-6
+    tm = torch.from_numpy(golden_unet[f"{name}/tmixed"])
+    assert O.rel_l2(O.unet_forward(sd, cfg, x, tm, ctx), torch.from_numpy(golden_unet[f"{name}/eps_tmixed"])) <= 2e-6
+
+
+def test_param_inventory_is_626():
+    # 626 tensors, 156.76 M (FR) / 163.16 M (TF) parameters
+    for cfg, n in ((O.FR_UNET, 156_760_483), (O.TF_UNET, None)):
+        shapes = O.param_shapes(cfg)
+        assert len(shapes) == 626
+        if n:
+            assert sum(int(np.prod(s)) for s in shapes.values()) == n
+
+
+def test_block_taps(golden_unet):
+    cfg, B, hw, cl, _ = CASES["tiny_c1"]
+    sd = O.init_state_dict(cfg, 0)
+    x, ctx = synth_inputs(cfg, B, hw, 1, cl)
+    taps = {}
+    O.unet_forward(sd, cfg, x, torch.tensor([981] * B), ctx, taps=taps)
+    keys = [k for k in golden_unet.files if k.startswith("tiny_c1/tap/")]
+    assert len(keys) == len(taps) == 13
+    for k in keys:
+        assert O.rel_l2(taps[k.split("/tap/")[1]], torch.from_numpy(golden_unet[k])) <= 2e-6
+
+
+def test_schedules_bit_exact(golden_schedule):
+    buf = O.ddpm_buffers()
+    for k in ("betas", "alphas_cumprod", "alphas_cumprod_prev"):
+        assert np.array_equal(buf[k].numpy(), golden_schedule[f"ddpm/{k}"]), k
+    for S in (50, 200, 7):
+        for eta in (0.0, 1.0):
+            sch = O.ddim_schedule(buf["alphas_cumprod"], S, eta)
+            key = f"ddim/S{S}_eta{int(eta)}"
+            assert np.array_equal(sch["timesteps"], golden_schedule[key + "/timesteps"])
+            for f in ("a_t", "a_prev", "sigma_t", "sqrt_one_minus_at"):
+                assert np.array_equal(sch[f], golden_schedule[f"{key}/{f}"]), (S, eta, f)
+    # S=50 -> [1,21,...,981]; S=200 -> [1,6,...,996]
+    assert O.make_ddim_timesteps(50)[[0, 1, -1]].tolist() == [1, 21, 981]
+    assert O.make_ddim_timesteps(200)[[0, 1, -1]].tolist() == [1, 6, 996]
+
+
+def test_timestep_embedding(golden_schedule):
+    t = torch.from_numpy(golden_schedule["temb/t"])
+    assert np.array_equal(O.timestep_embedding(t, 160).numpy(), golden_schedule["temb/dim160"])
+    assert np.array_equal(O.timestep_embedding(t, 32).numpy(), golden_schedule["temb/dim32"])
+
+
+@pytest.mark.parametrize("tag,S,eta,scale", [("fr_S10_eta0", 10, 0.0, 1.0), ("fr_S50_eta0", 50, 0.0, 1.0),
+                                             ("fr_S10_eta1", 10, 1.0, 1.0), ("fr_S10_cfg3", 10, 0.0, 3.0)])
+def test_ddim_trajectory_fr(tag, S, eta, scale, golden_traj):
+    cfg = O.TINY_UNET
+    sd = O.init_state_dict(cfg, 0)
+    x_T = torch.from_numpy(golden_traj["traj/x_T"])
+    ctx = torch.from_numpy(golden_traj["traj/ctx"])
+    uc = torch.from_numpy(golden_traj["traj/uc"])
+    torch.manual_seed(1234)
+    noises = [torch.randn(x_T.shape) for _ in range(S)]
+    apply_model = lambda x, t, c: O.unet_forward(sd, cfg, x, t, c)
+    img, inter, _ = O.ddim_sample(apply_model, O.ddpm_buffers()["alphas_cumprod"], S, x_T, ctx, eta=eta,
+                                  unconditional_guidance_scale=scale,
+                                  unconditional_conditioning=uc if scale != 1.0 else None,
+                                  noises=noises, log_every_t=3)
+    assert O.rel_l2(img, torch.from_numpy(golden_traj[f"traj/{tag}/samples"])) <= 1e-5
+    assert O.rel_l2(torch.stack(inter["x_inter"]), torch.from_numpy(golden_traj[f"traj/{tag}/x_inter"])) <= 1e-5
+    assert O.rel_l2(torch.stack(inter["pred_x0"]), torch.from_numpy(golden_traj[f"traj/{tag}/pred_x0"])) <= 1e-5
+
+
+def test_ddim_trajectory_tf_two_cond(golden_traj):
+    cfg = dict(O.TINY_UNET, in_channels=9)
+    sd = O.init_state_dict(cfg, 0)
+    x_T = torch.from_numpy(golden_traj["traj/x_T"])
+    ctx = torch.from_numpy(golden_traj["traj/ctx"])
+    c34 = torch.from_numpy(golden_traj["traj/c34"])
+    torch.manual_seed(1234)
+    noises = [torch.randn(x_T.shape) for _ in range(10)]
+    apply_model = lambda x, t, c: O.unet_forward(sd, cfg, torch.cat([x, c34], 1), t, c)
+    img, inter, _ = O.ddim_sample(apply_model, O.ddpm_buffers()["alphas_cumprod"], 10, x_T, ctx, eta=1.0,
+                                  noises=noises, log_every_t=3)
+    assert O.rel_l2(img, torch.from_numpy(golden_traj["traj/tf_S10_eta1/samples"])) <= 1e-5
+    assert O.rel_l2(torch.stack(inter["x_inter"]), torch.from_numpy(golden_traj["traj/tf_S10_eta1/x_inter"])) <= 1e-5
+
+
+@pytest.mark.skipif(not R.available(), reason="reference tree only exists in the build container")
+def test_oracle_bit_exact_vs_live_reference():
+    cfg = O.TINY_UNET
+    sd = O.init_state_dict(cfg, 0)
+    ref = R.reference_unet(cfg).eval()
+    ref.load_state_dict(sd, strict=True)
+    x, ctx = synth_inputs(cfg, 2, 8, 7, 2)
+    t = torch.tensor([3, 777])
+    with torch.no_grad():
+        assert torch.equal(ref(x, t, context=ctx), O.unet_forward(sd, cfg, x, t, ctx))

@@ -1,0 +1,574 @@
+// HBM-bound kernels of the denoising path: fused DDIM update (K13), timestep embedding + small dense layers
+// (K12), GroupNorm+SiLU over (virtually concatenated) channels-last maps (K7/K11), LayerNorm (K9), layout
+// changes, and the one-launch weight packer for the tensor-core path.
+#include "common.cuh"
+
+namespace ldm {
+
+template <typename T>
+struct Store4;
+template <>
+struct Store4<float> {
+  static __device__ __forceinline__ void st(float* p, float a, float b, float c, float d) {
+    *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+  }
+};
+template <>
+struct Store4<__nv_bfloat16> {
+  static __device__ __forceinline__ void st(__nv_bfloat16* p, float a, float b, float c, float d) {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
+    uint2 u;
+    u.x = *reinterpret_cast<uint32_t*>(&lo);
+    u.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(p) = u;
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// K13 DDIM update.  Each product/sum is a separate rounded fp32 op (no FMA contraction) so the result
+// is bit-identical to the reference's chain of elementwise torch ops (ddim.py:177,194-202).
+// ---------------------------------------------------------------------------------------------
+struct DdimCoef {
+  float s1;        // sqrt_one_minus_at
+  float sqrt_at;   // sqrtf(a_t)
+  float sqrt_ap;   // sqrtf(a_prev)
+  float dir;       // sqrtf(1 - a_prev - sigma^2)
+  float sigma, temperature, cfg;
+};
+
+__device__ __forceinline__ void ddim_one(float x, float ec, float eu, float nz, bool has_u, bool has_n,
+                                         const DdimCoef& k, float& xp, float& p0) {
+  float e = has_u ? __fadd_rn(eu, __fmul_rn(k.cfg, __fsub_rn(ec, eu))) : ec;
+  p0 = __fdiv_rn(__fsub_rn(x, __fmul_rn(k.s1, e)), k.sqrt_at);
+  float dir = __fmul_rn(k.dir, e);
+  float noise = has_n ? __fmul_rn(__fmul_rn(k.sigma, nz), k.temperature) : 0.0f;
+  xp = __fadd_rn(__fadd_rn(__fmul_rn(k.sqrt_ap, p0), dir), noise);
+}
+
+__global__ void __launch_bounds__(256) ddim_step_kernel(const float* __restrict__ x, const float* __restrict__ ec,
+                                                        const float* __restrict__ eu,
+                                                        const float* __restrict__ nz, float* __restrict__ xp,
+                                                        float* __restrict__ p0, int64_t n, float a_t, float a_prev,
+                                                        float sigma, float s1, float cfg, float temperature) {
+  DdimCoef k;
+  k.s1 = s1;
+  k.sqrt_at = __fsqrt_rn(a_t);
+  k.sqrt_ap = __fsqrt_rn(a_prev);
+  k.dir = __fsqrt_rn(__fsub_rn(__fsub_rn(1.0f, a_prev), __fmul_rn(sigma, sigma)));
+  k.sigma = sigma;
+  k.temperature = temperature;
+  k.cfg = cfg;
+  const bool has_u = eu != nullptr, has_n = nz != nullptr;
+  const int64_t n4 = n >> 2;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 vx = reinterpret_cast<const float4*>(x)[i];
+    float4 ve = reinterpret_cast<const float4*>(ec)[i];
+    float4 vu = has_u ? reinterpret_cast<const float4*>(eu)[i] : make_float4(0, 0, 0, 0);
+    float4 vn = has_n ? reinterpret_cast<const float4*>(nz)[i] : make_float4(0, 0, 0, 0);
+    float4 ox, op;
+    ddim_one(vx.x, ve.x, vu.x, vn.x, has_u, has_n, k, ox.x, op.x);
+    ddim_one(vx.y, ve.y, vu.y, vn.y, has_u, has_n, k, ox.y, op.y);
+    ddim_one(vx.z, ve.z, vu.z, vn.z, has_u, has_n, k, ox.z, op.z);
+    ddim_one(vx.w, ve.w, vu.w, vn.w, has_u, has_n, k, ox.w, op.w);
+    reinterpret_cast<float4*>(xp)[i] = ox;
+    reinterpret_cast<float4*>(p0)[i] = op;
+  }
+  // scalar tail
+  for (int64_t i = (n4 << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    float ox, op;
+    ddim_one(x[i], ec[i], has_u ? eu[i] : 0.f, has_n ? nz[i] : 0.f, has_u, has_n, k, ox, op);
+    xp[i] = ox;
+    p0[i] = op;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K12 timestep embedding.  The fp32 argument chain matches torch's (scalar*arange, /half); exp and
+// cos/sin are evaluated in double and rounded once so the result sits within 1 ulp of torch's fp32 ops.
+// ---------------------------------------------------------------------------------------------
+__global__ void timestep_embedding_kernel(const int64_t* __restrict__ t, float* __restrict__ out, int batch, int dim,
+                                          float neg_log_period) {
+  const int half = dim / 2;
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= batch * half) return;
+  int b = idx / half, i = idx % half;
+  float a = __fdiv_rn(__fmul_rn(neg_log_period, (float)i), (float)half);
+  float freq = (float)exp((double)a);
+  float arg = __fmul_rn((float)t[b], freq);
+  out[(size_t)b * dim + i] = (float)cos((double)arg);
+  out[(size_t)b * dim + half + i] = (float)sin((double)arg);
+}
+
+// ---------------------------------------------------------------------------------------------
+// small dense layer on per-sample vectors (fp32).  Block: 8 warps x 4 outputs; rows in chunks of 16;
+// act(in) staged once per block in shared memory.
+// ---------------------------------------------------------------------------------------------
+constexpr int SL_RT = 16, SL_KC = 256, SL_NPW = 4, SL_WARPS = 8;
+
+__global__ void __launch_bounds__(SL_WARPS * 32) small_linear_kernel(const float* __restrict__ in, int in_ld,
+                                                                     const float* __restrict__ w,
+                                                                     const float* __restrict__ bias,
+                                                                     float* __restrict__ out, int out_ld, int rows,
+                                                                     int K, int N, int silu_in) {
+  __shared__ float tile[SL_RT][SL_KC];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = (blockIdx.x * SL_WARPS + warp) * SL_NPW;
+  for (int r0 = 0; r0 < rows; r0 += SL_RT) {
+    float acc[SL_NPW][SL_RT];
+#pragma unroll
+    for (int j = 0; j < SL_NPW; ++j)
+#pragma unroll
+      for (int r = 0; r < SL_RT; ++r) acc[j][r] = 0.f;
+    for (int k0 = 0; k0 < K; k0 += SL_KC) {
+      __syncthreads();
+      for (int e = threadIdx.x; e < SL_RT * SL_KC; e += blockDim.x) {
+        int r = e / SL_KC, kk = e % SL_KC;
+        float v = 0.f;
+        if (r0 + r < rows && k0 + kk < K) {
+          v = in[(size_t)(r0 + r) * in_ld + k0 + kk];
+          if (silu_in) v = silu_f(v);
+        }
+        tile[r][kk] = v;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < SL_NPW; ++j) {
+        int n = n0 + j;
+        if (n >= N) continue;
+        const float* wr = w + (size_t)n * K + k0;
+        for (int kk = lane; kk < SL_KC && k0 + kk < K; kk += 32) {
+          float wv = wr[kk];
+#pragma unroll
+          for (int r = 0; r < SL_RT; ++r) acc[j][r] = fmaf(tile[r][kk], wv, acc[j][r]);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < SL_NPW; ++j) {
+      int n = n0 + j;
+#pragma unroll
+      for (int r = 0; r < SL_RT; ++r) {
+        float v = warp_sum(acc[j][r]);
+        if (lane == 0 && n < N && r0 + r < rows) out[(size_t)(r0 + r) * out_ld + n] = v + (bias ? bias[n] : 0.f);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// layout changes
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__ y, int batch, int C, int HW,
+                                    int c_pad) {
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)batch * HW) return;
+  int b = idx / HW, p = idx % HW;
+  T* dst = y + idx * c_pad;
+  for (int c = 0; c < c_pad; ++c) {
+    float v = c < C ? x[((size_t)b * C + c) * HW + p] : 0.f;
+    dst[c] = (T)v;
+  }
+}
+
+__global__ void nhwc_to_nchw_kernel(const float* __restrict__ y, int ld, float* __restrict__ x, int batch, int C,
+                                    int HW) {
+  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (int64_t)batch * HW) return;
+  int b = idx / HW, p = idx % HW;
+  for (int c = 0; c < C; ++c) x[((size_t)b * C + c) * HW + p] = y[idx * ld + c];
+}
+
+// x fp32 [B,H,W,C] -> y [B,4,H/2,W/2,C], plane = (h&1)*2 + (w&1)
+template <typename T>
+__global__ void space_to_depth2_kernel(const float* __restrict__ x, T* __restrict__ y, int batch, int H, int W,
+                                       int C) {
+  const int c4n = C >> 2, Ho = H >> 1, Wo = W >> 1;
+  int64_t total = (int64_t)batch * H * W * c4n;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    int c4 = idx % c4n;
+    int64_t pix = idx / c4n;  // destination pixel index over [B,4,Ho,Wo]
+    int wo = pix % Wo;
+    int64_t t = pix / Wo;
+    int ho = t % Ho;
+    t /= Ho;
+    int plane = t & 3;
+    int b = t >> 2;
+    int h = ho * 2 + (plane >> 1), w = wo * 2 + (plane & 1);
+    float4 v = *reinterpret_cast<const float4*>(x + (((size_t)b * H + h) * W + w) * C + c4 * 4);
+    Store4<T>::st(y + pix * C + c4 * 4, v.x, v.y, v.z, v.w);
+  }
+}
+
+// x fp32 [B,H,W,C] -> y [B,2H,2W,C] nearest
+template <typename T>
+__global__ void upsample2x_kernel(const float* __restrict__ x, T* __restrict__ y, int batch, int H, int W, int C) {
+  const int c4n = C >> 2, Ho = H * 2, Wo = W * 2;
+  int64_t total = (int64_t)batch * Ho * Wo * c4n;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (int64_t)gridDim.x * blockDim.x) {
+    int c4 = idx % c4n;
+    int64_t pix = idx / c4n;
+    int wo = pix % Wo;
+    int64_t t = pix / Wo;
+    int ho = t % Ho;
+    int b = t / Ho;
+    float4 v = *reinterpret_cast<const float4*>(x + (((size_t)b * H + (ho >> 1)) * W + (wo >> 1)) * C + c4 * 4);
+    Store4<T>::st(y + pix * C + c4 * 4, v.x, v.y, v.z, v.w);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K7 GroupNorm (+SiLU) over channels-last [B, HW, C1 (+C2)].  Two launches:
+//   stats: grid (S, B); thread owns one channel quad, sums x and x^2 over its rows; block reduces channel
+//          partials to 32 group partials -> ws[b][s][g][2]   (deterministic, no atomics)
+//   apply: grid (T, B); combines the S partials in float64, folds gamma/beta into per-channel (scale, shift)
+//          registers, streams the slab once: y = silu(x*scale + shift)  (+ raw cast copy)
+// ---------------------------------------------------------------------------------------------
+constexpr int GN_MAX_SPLITS = 64;
+
+static inline int gn_rows_per_block(int C) {
+  int q = C / 4;
+  int r = 256 / q;
+  return r < 1 ? 1 : r;
+}
+static inline int gn_splits(int hw, int C) {
+  int R = gn_rows_per_block(C);
+  int s = hw / (R * 8);
+  if (s < 1) s = 1;
+  if (s > GN_MAX_SPLITS) s = GN_MAX_SPLITS;
+  return s;
+}
+
+__device__ __forceinline__ float4 gn_load(const float* __restrict__ x1, int c1, const float* __restrict__ x2, int c2,
+                                          int64_t row, int c) {
+  if (c < c1) return *reinterpret_cast<const float4*>(x1 + row * c1 + c);
+  return *reinterpret_cast<const float4*>(x2 + row * c2 + (c - c1));
+}
+
+__global__ void gn_stats_kernel(const float* __restrict__ x1, int c1, const float* __restrict__ x2, int c2, int hw,
+                                int groups, int R, float* __restrict__ ws) {
+  extern __shared__ float sm[];  // [2][R][C]
+  const int C = c1 + c2, q = C >> 2;
+  const int cq = threadIdx.x % q, rl = threadIdx.x / q;
+  const int S = gridDim.x, s = blockIdx.x, b = blockIdx.y;
+  const int rows_per = (hw + S - 1) / S;
+  const int r0 = s * rows_per, r1 = min(hw, r0 + rows_per);
+  float sx[4] = {0, 0, 0, 0}, sq[4] = {0, 0, 0, 0};
+  for (int r = r0 + rl; r < r1; r += R) {
+    float4 v = gn_load(x1, c1, x2, c2, (int64_t)b * hw + r, cq * 4);
+    sx[0] += v.x; sx[1] += v.y; sx[2] += v.z; sx[3] += v.w;
+    sq[0] = fmaf(v.x, v.x, sq[0]); sq[1] = fmaf(v.y, v.y, sq[1]);
+    sq[2] = fmaf(v.z, v.z, sq[2]); sq[3] = fmaf(v.w, v.w, sq[3]);
+  }
+  float* ps = sm;
+  float* pq = sm + R * C;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    ps[rl * C + cq * 4 + j] = sx[j];
+    pq[rl * C + cq * 4 + j] = sq[j];
+  }
+  __syncthreads();
+  const int cpg = C / groups;
+  for (int g = threadIdx.x; g < groups; g += blockDim.x) {
+    float a = 0.f, c = 0.f;
+    for (int r = 0; r < R; ++r)
+      for (int j = 0; j < cpg; ++j) {
+        a += ps[r * C + g * cpg + j];
+        c += pq[r * C + g * cpg + j];
+      }
+    float* o = ws + (((size_t)b * S + s) * groups + g) * 2;
+    o[0] = a;
+    o[1] = c;
+  }
+}
+
+template <typename T>
+__global__ void gn_apply_kernel(const float* __restrict__ x1, int c1, const float* __restrict__ x2, int c2,
+                                const float* __restrict__ gamma, const float* __restrict__ beta, T* __restrict__ y,
+                                T* __restrict__ raw, int hw, int groups, int R, int S, float eps, int silu,
+                                const float* __restrict__ ws) {
+  __shared__ float s_mean[64], s_rstd[64];
+  const int C = c1 + c2, q = C >> 2, cpg = C / groups;
+  const int b = blockIdx.y;
+  for (int g = threadIdx.x; g < groups; g += blockDim.x) {
+    double a = 0.0, c = 0.0;
+    for (int s = 0; s < S; ++s) {
+      const float* p = ws + (((size_t)b * S + s) * groups + g) * 2;
+      a += (double)p[0];
+      c += (double)p[1];
+    }
+    double n = (double)cpg * (double)hw;
+    double mean = a / n;
+    double var = c / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    s_mean[g] = (float)mean;
+    s_rstd[g] = (float)(1.0 / sqrt(var + (double)eps));
+  }
+  __syncthreads();
+  const int cq = threadIdx.x % q, rl = threadIdx.x / q;
+  float sc[4], sh[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    int c = cq * 4 + j;
+    int g = c / cpg;
+    float ga = gamma[c] * s_rstd[g];
+    sc[j] = ga;
+    sh[j] = beta[c] - s_mean[g] * ga;
+  }
+  const int T_ = gridDim.x;
+  const int rows_per = (hw + T_ - 1) / T_;
+  const int r0 = blockIdx.x * rows_per, r1 = min(hw, r0 + rows_per);
+  for (int r = r0 + rl; r < r1; r += R) {
+    int64_t row = (int64_t)b * hw + r;
+    float4 v = gn_load(x1, c1, x2, c2, row, cq * 4);
+    float o0 = fmaf(v.x, sc[0], sh[0]), o1 = fmaf(v.y, sc[1], sh[1]);
+    float o2 = fmaf(v.z, sc[2], sh[2]), o3 = fmaf(v.w, sc[3], sh[3]);
+    if (silu) {
+      o0 = silu_f(o0); o1 = silu_f(o1); o2 = silu_f(o2); o3 = silu_f(o3);
+    }
+    Store4<T>::st(y + row * C + cq * 4, o0, o1, o2, o3);
+    if (raw) Store4<T>::st(raw + row * C + cq * 4, v.x, v.y, v.z, v.w);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K9 LayerNorm: one warp per row, two-pass statistics on register-resident values.
+// ---------------------------------------------------------------------------------------------
+template <typename T, int MAXV>
+__global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                        const float* __restrict__ beta, T* __restrict__ y,
+                                                        int64_t rows, int C, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int q = C >> 2;
+  const float4* xr = reinterpret_cast<const float4*>(x + row * C);
+  float4 v[MAXV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    int idx = lane + i * 32;
+    if (idx < q) {
+      v[i] = xr[idx];
+      s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+    }
+  }
+  const float mean = warp_sum(s) / (float)C;
+  float d = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    int idx = lane + i * 32;
+    if (idx < q) {
+      float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, e = v[i].w - mean;
+      d += (a * a + b * b) + (c * c + e * e);
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(d) / (float)C + eps);
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    int idx = lane + i * 32;
+    if (idx < q) {
+      float4 g = reinterpret_cast<const float4*>(gamma)[idx];
+      float4 bb = reinterpret_cast<const float4*>(beta)[idx];
+      Store4<T>::st(y + row * C + idx * 4, (v[i].x - mean) * rstd * g.x + bb.x, (v[i].y - mean) * rstd * g.y + bb.y,
+                    (v[i].z - mean) * rstd * g.z + bb.z, (v[i].w - mean) * rstd * g.w + bb.w);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// weight packer: fp32 nn.Parameter -> bf16 [n_pad, taps, c_pad] (K-major), optional GEGLU row permutation
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int geglu_src_row(int rp, int n_total, int block_n) {
+  int t = rp / block_n, rem = rp % block_n;
+  int qd = rem >> 5, i = rem & 31;
+  int col = t * (block_n >> 1) + qd * 16 + (i & 15);
+  return (i < 16) ? col : (n_total >> 1) + col;
+}
+
+__global__ void __launch_bounds__(256) pack_weights_kernel(const ldmb200_pack_job* __restrict__ jobs) {
+  const ldmb200_pack_job j = jobs[blockIdx.y];
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j.kind == 2) {
+    float* dst = reinterpret_cast<float*>(j.dst);
+    for (int64_t i = i0; i < j.n_pad; i += stride) {
+      int src = geglu_src_row((int)i, j.n, j.block_n);
+      dst[j.row_offset + i] = src < j.n ? j.src[src] : 0.f;
+    }
+    return;
+  }
+  const int taps = j.ksize * j.ksize;
+  const int64_t kp = (int64_t)taps * j.c_pad;
+  const int64_t total = (int64_t)j.n_pad * kp;
+  __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(j.dst);
+  for (int64_t i = i0; i < total; i += stride) {
+    int rp = (int)(i / kp);
+    int rem = (int)(i % kp);
+    int tap = rem / j.c_pad, c = rem % j.c_pad;
+    int src_row = j.kind == 1 ? geglu_src_row(rp, j.n, j.block_n) : rp;
+    float v = 0.f;
+    if (src_row < j.n && c < j.c) v = j.src[((size_t)src_row * j.c + c) * taps + tap];
+    dst[(size_t)(j.row_offset + rp) * kp + rem] = __float2bfloat16_rn(v);
+  }
+}
+
+}  // namespace ldm
+
+using namespace ldm;
+
+extern "C" {
+
+int ldmb200_ddim_step(const float* x, const float* e_cond, const float* e_uncond, const float* noise, float* x_prev,
+                      float* pred_x0, int64_t n, float a_t, float a_prev, float sigma_t, float sqrt_one_minus_at,
+                      float cfg_scale, float temperature, void* stream) {
+  LDM_CHECK_ARG(x && e_cond && x_prev && pred_x0 && n > 0, "ddim_step: null pointer or n <= 0");
+  LDM_CHECK_ARG((((uintptr_t)x | (uintptr_t)e_cond | (uintptr_t)e_uncond | (uintptr_t)noise | (uintptr_t)x_prev |
+                  (uintptr_t)pred_x0) & 15) == 0, "ddim_step: pointers must be 16-byte aligned");
+  int64_t n4 = (n + 3) / 4;
+  int blocks = (int)((n4 + 255) / 256);
+  int cap = sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  ddim_step_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, e_cond, e_uncond, noise, x_prev, pred_x0, n, a_t,
+                                                             a_prev, sigma_t, sqrt_one_minus_at, cfg_scale,
+                                                             temperature);
+  LDM_CHECK_LAUNCH("ddim_step");
+  return 0;
+}
+
+int ldmb200_timestep_embedding(const int64_t* t, float* out, int batch, int dim, float max_period, void* stream) {
+  LDM_CHECK_ARG(t && out && batch > 0 && dim > 0 && dim % 2 == 0, "timestep_embedding: bad arguments");
+  int total = batch * (dim / 2);
+  // -math.log(max_period) is a python float rounded to fp32 when it multiplies the fp32 arange (util.py:162-164)
+  float neg_log = (float)(-log((double)max_period));
+  timestep_embedding_kernel<<<ceil_div(total, 128), 128, 0, (cudaStream_t)stream>>>(t, out, batch, dim, neg_log);
+  LDM_CHECK_LAUNCH("timestep_embedding");
+  return 0;
+}
+
+int ldmb200_small_linear(const float* in, int in_ld, const float* w, const float* bias, float* out, int out_ld,
+                         int rows, int k, int n, int silu_in, void* stream) {
+  LDM_CHECK_ARG(in && w && out && rows > 0 && k > 0 && n > 0, "small_linear: bad arguments");
+  int blocks = ceil_div(n, SL_WARPS * SL_NPW);
+  small_linear_kernel<<<blocks, SL_WARPS * 32, 0, (cudaStream_t)stream>>>(in, in_ld, w, bias, out, out_ld, rows, k,
+                                                                          n, silu_in);
+  LDM_CHECK_LAUNCH("small_linear");
+  return 0;
+}
+
+int ldmb200_nchw_to_nhwc(const float* x, void* y, int batch, int c, int hw, int c_pad, int out_dtype, void* stream) {
+  LDM_CHECK_ARG(x && y && batch > 0 && c > 0 && hw > 0 && c_pad >= c, "nchw_to_nhwc: bad arguments");
+  int64_t total = (int64_t)batch * hw;
+  int blocks = (int)ceil_div64(total, 256);
+  if (out_dtype == LDMB200_BF16)
+    nchw_to_nhwc_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (__nv_bfloat16*)y, batch, c, hw, c_pad);
+  else
+    nchw_to_nhwc_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (float*)y, batch, c, hw, c_pad);
+  LDM_CHECK_LAUNCH("nchw_to_nhwc");
+  return 0;
+}
+
+int ldmb200_nhwc_to_nchw(const float* y, int ld, float* x, int batch, int c, int hw, void* stream) {
+  LDM_CHECK_ARG(x && y && batch > 0 && c > 0 && hw > 0 && ld >= c, "nhwc_to_nchw: bad arguments");
+  int64_t total = (int64_t)batch * hw;
+  nhwc_to_nchw_kernel<<<(int)ceil_div64(total, 256), 256, 0, (cudaStream_t)stream>>>(y, ld, x, batch, c, hw);
+  LDM_CHECK_LAUNCH("nhwc_to_nchw");
+  return 0;
+}
+
+int ldmb200_space_to_depth2(const float* x, void* y, int out_dtype, int batch, int h, int w, int c, void* stream) {
+  LDM_CHECK_ARG(x && y && batch > 0 && h > 0 && w > 0 && h % 2 == 0 && w % 2 == 0 && c % 4 == 0,
+                "space_to_depth2: bad arguments (h, w even; c %% 4 == 0)");
+  int64_t total = (int64_t)batch * h * w * (c / 4);
+  int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), (int64_t)sm_count() * 16);
+  if (out_dtype == LDMB200_BF16)
+    space_to_depth2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (__nv_bfloat16*)y, batch, h, w, c);
+  else
+    space_to_depth2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (float*)y, batch, h, w, c);
+  LDM_CHECK_LAUNCH("space_to_depth2");
+  return 0;
+}
+
+int ldmb200_upsample2x(const float* x, void* y, int out_dtype, int batch, int h, int w, int c, void* stream) {
+  LDM_CHECK_ARG(x && y && batch > 0 && h > 0 && w > 0 && c % 4 == 0, "upsample2x: bad arguments (c %% 4 == 0)");
+  int64_t total = (int64_t)batch * h * w * 4 * (c / 4);
+  int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), (int64_t)sm_count() * 16);
+  if (out_dtype == LDMB200_BF16)
+    upsample2x_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (__nv_bfloat16*)y, batch, h, w, c);
+  else
+    upsample2x_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (float*)y, batch, h, w, c);
+  LDM_CHECK_LAUNCH("upsample2x");
+  return 0;
+}
+
+int64_t ldmb200_groupnorm_ws_floats(int batch, int hw, int c) {
+  (void)hw;
+  (void)c;
+  return (int64_t)batch * GN_MAX_SPLITS * 64 * 2;
+}
+
+int ldmb200_groupnorm(const float* x1, int c1, const float* x2, int c2, const float* gamma, const float* beta, void* y,
+                      void* raw_copy, int out_dtype, int batch, int hw, int groups, float eps, int silu,
+                      float* stats_ws, void* stream) {
+  const int C = c1 + (x2 ? c2 : 0);
+  if (!x2) c2 = 0;
+  LDM_CHECK_ARG(x1 && gamma && beta && y && stats_ws && batch > 0 && hw > 0, "groupnorm: null pointer / empty");
+  LDM_CHECK_ARG(groups > 0 && groups <= 64 && C % groups == 0, "groupnorm: C=%d not divisible by groups=%d", C, groups);
+  LDM_CHECK_ARG(c1 % 4 == 0 && c2 % 4 == 0 && C / 4 <= 1024, "groupnorm: channel counts must be multiples of 4");
+  const int R = gn_rows_per_block(C);
+  const int S = gn_splits(hw, C);
+  const int threads = (C / 4) * R;
+  size_t smem = (size_t)2 * R * C * sizeof(float);
+  cudaStream_t st = (cudaStream_t)stream;
+  gn_stats_kernel<<<dim3(S, batch), threads, smem, st>>>(x1, c1, x2, c2, hw, groups, R, stats_ws);
+  LDM_CHECK_LAUNCH("groupnorm stats");
+  int T = hw / (R * 4);
+  int want = ceil_div(sm_count() * 4, batch);
+  if (T > want) T = want;
+  if (T < 1) T = 1;
+  if (out_dtype == LDMB200_BF16)
+    gn_apply_kernel<<<dim3(T, batch), threads, 0, st>>>(x1, c1, x2, c2, gamma, beta, (__nv_bfloat16*)y,
+                                                        (__nv_bfloat16*)raw_copy, hw, groups, R, S, eps, silu,
+                                                        stats_ws);
+  else
+    gn_apply_kernel<<<dim3(T, batch), threads, 0, st>>>(x1, c1, x2, c2, gamma, beta, (float*)y, (float*)raw_copy, hw,
+                                                        groups, R, S, eps, silu, stats_ws);
+  LDM_CHECK_LAUNCH("groupnorm apply");
+  return 0;
+}
+
+int ldmb200_layernorm(const float* x, const float* gamma, const float* beta, void* y, int out_dtype, int64_t rows,
+                      int c, float eps, void* stream) {
+  LDM_CHECK_ARG(x && gamma && beta && y && rows > 0, "layernorm: null pointer / empty");
+  LDM_CHECK_ARG(c % 4 == 0 && c <= 2048, "layernorm: C=%d must be a multiple of 4 and <= 2048", c);
+  const int warps = 8;
+  int blocks = (int)ceil_div64(rows, warps);
+  cudaStream_t st = (cudaStream_t)stream;
+#define LN_LAUNCH(T, MAXV) layernorm_kernel<T, MAXV><<<blocks, warps * 32, 0, st>>>(x, gamma, beta, (T*)y, rows, c, eps)
+  const int need = ceil_div(c / 4, 32);
+  if (out_dtype == LDMB200_BF16) {
+    if (need <= 2) LN_LAUNCH(__nv_bfloat16, 2);
+    else if (need <= 5) LN_LAUNCH(__nv_bfloat16, 5);
+    else LN_LAUNCH(__nv_bfloat16, 16);
+  } else {
+    if (need <= 2) LN_LAUNCH(float, 2);
+    else if (need <= 5) LN_LAUNCH(float, 5);
+    else LN_LAUNCH(float, 16);
+  }
+#undef LN_LAUNCH
+  LDM_CHECK_LAUNCH("layernorm");
+  return 0;
+}
+
+int ldmb200_pack_weights(const ldmb200_pack_job* jobs, int n_jobs, void* stream) {
+  LDM_CHECK_ARG(jobs && n_jobs > 0 && n_jobs <= 65535, "pack_weights: bad job table");
+  pack_weights_kernel<<<dim3(48, n_jobs), 256, 0, (cudaStream_t)stream>>>(jobs);
+  LDM_CHECK_LAUNCH("pack_weights");
+  return 0;
+}
+
+}  // extern "C"

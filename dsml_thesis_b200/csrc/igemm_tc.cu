@@ -1,0 +1,385 @@
+// tcgen05 / TMEM / TMA implicit GEMM for the convolutions and linears of the UNet (K1-K4, K8, K11).
+//
+//   acc[m, n] = sum_{tap, c} A(m, tap, c) * W[n, tap, c]       bf16 x bf16 -> fp32 in tensor memory
+//
+// * persistent CTAs (one per SM), static round-robin over (m-tile, n-tile); tile = 128 x BN
+// * warp 0: TMA producer   — A tiles come straight from the channels-last activation map through a 5-D
+//           tensor map {C, W, H, plane, B}: a 3x3 tap is a coordinate shift, the padding halo is TMA
+//           out-of-bounds zero fill, stride 2 reads the space-to-depth planes, the virtual channel concat
+//           (K11) is a second tensor map; B tiles from the packed K-major weight matrix
+// * warp 1: MMA issuer     — tcgen05.mma cta_group::1 kind::f16, M=128, N=BN, K=16 per instruction,
+//           accumulators double-buffered in TMEM (2 x BN columns) so the epilogue overlaps the next tile
+// * warps 2-5: epilogue    — tcgen05.ld 32x32b, fused bias / per-sample row vector (K8) / residual / GEGLU,
+//           transposed through shared memory so global loads and stores are 128-byte coalesced
+// smem operand tiles are K-major with the hardware 64B (BK=32) or 128B (BK=64) swizzle, written by TMA and
+// read by the UMMA descriptors (cute/arch/mma_sm100_desc.hpp bit layout).
+#include <algorithm>
+#include <stdlib.h>
+
+#include "common.cuh"
+
+namespace ldm {
+
+struct TcParams {
+  int64_t M;
+  int tiles_m, tiles_n;
+  int taps, ks, stride, is_conv;
+  int c1_chunks, c2_chunks, ctot;
+  int hw_out, w_out, rows_per_sample;
+  const float* bias;
+  const float* rowvec;
+  int rowvec_ld;
+  const float* residual;
+  int residual_ld;
+  int geglu;
+  void* out;
+  int out_bf16, out_ld, out_nchw, n_valid;
+};
+
+template <int BN, int BK>
+struct TcCfg {
+  static constexpr int BM = 128;
+  static constexpr int SW = BK * 2;  // swizzle span in bytes == one K-major row
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = ((BN * BK * 2 + 1023) / 1024) * 1024;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN >= 128) ? (BK == 32 ? 8 : 5) : 8;
+  static constexpr int TX_BYTES = BM * BK * 2 + BN * BK * 2;
+  static constexpr int EPI_PITCH = 36;  // floats; 144 B row pitch: conflict-free 16 B row-owner writes + row reads
+  static constexpr int EPI_BYTES = 4 * 32 * EPI_PITCH * 4;
+  static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + (2 * STAGES + 4) * 8 + 16 + 1024;
+  static constexpr int CH = BN >= 32 ? 32 : 16;  // epilogue column chunk
+};
+
+constexpr int TC_THREADS = 192;
+
+template <int BN, int BK>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
+                const __grid_constant__ CUtensorMap tmB, const TcParams p) {
+  using Cfg = TcCfg<BN, BK>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + Cfg::STAGES * Cfg::A_BYTES;
+  float* epi = reinterpret_cast<float*>(sB + Cfg::STAGES * Cfg::B_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(epi) + Cfg::EPI_BYTES);
+  uint64_t* empty = full + Cfg::STAGES;
+  uint64_t* tfull = empty + Cfg::STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int k_iters = p.taps * (p.c1_chunks + p.c2_chunks);
+  const int ntiles = p.tiles_m * p.tiles_n;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA1);
+    prefetch_tmap(&tmB);
+    if (p.c2_chunks) prefetch_tmap(&tmA2);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < Cfg::STAGES; ++s) {
+        mbar_init(&full[s], 1);
+        mbar_init(&empty[s], 1);
+      }
+      for (int b = 0; b < 2; ++b) {
+        mbar_init(&tfull[b], 1);
+        mbar_init(&tempty[b], 4);
+      }
+      fence_mbar_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
+        const int64_t m0 = (int64_t)tm * Cfg::BM;
+        int n_img = 0, h0 = 0;
+        if (p.is_conv) {
+          n_img = (int)(m0 / p.hw_out);
+          h0 = (int)(m0 % p.hw_out) / p.w_out;
+        }
+        for (int tap = 0; tap < p.taps; ++tap) {
+          int dh = 0, dw = 0, plane = 0;
+          if (p.ks == 3) {
+            const int kh = tap / 3, kw = tap % 3;
+            if (p.stride == 1) {
+              dh = kh - 1;
+              dw = kw - 1;
+            } else {  // stride 2 on space-to-depth planes: row 2*oh+kh-1 -> (parity, index)
+              const int ph = (kh == 1) ? 0 : 1, pw = (kw == 1) ? 0 : 1;
+              dh = (kh == 0) ? -1 : 0;
+              dw = (kw == 0) ? -1 : 0;
+              plane = ph * 2 + pw;
+            }
+          }
+          const int nchunks = p.c1_chunks + p.c2_chunks;
+          for (int j = 0; j < nchunks; ++j, ++it) {
+            const int s = it % Cfg::STAGES;
+            const uint32_t ph_ = (it / Cfg::STAGES) & 1;
+            mbar_wait(&empty[s], ph_ ^ 1);
+            mbar_expect_tx(&full[s], Cfg::TX_BYTES);
+            const bool second = j >= p.c1_chunks;
+            const CUtensorMap* tm_a = second ? &tmA2 : &tmA1;
+            const int c0 = (second ? j - p.c1_chunks : j) * BK;
+            if (p.is_conv)
+              tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, dw, h0 + dh, plane, n_img);
+            else
+              tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, 0, (int)m0, 0, 0);
+            tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &full[s], tap * p.ctot + j * BK, tn * BN);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(Cfg::BM, BN);
+      uint32_t it = 0, t_iter = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
+        const uint32_t buf = t_iter & 1;
+        mbar_wait(&tempty[buf], ((t_iter >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * BN;
+        for (int k = 0; k < k_iters; ++k, ++it) {
+          const int s = it % Cfg::STAGES;
+          const uint32_t ph_ = (it / Cfg::STAGES) & 1;
+          mbar_wait(&full[s], ph_);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(sA + s * Cfg::A_BYTES);
+          const uint32_t b_addr = smem_u32(sB + s * Cfg::B_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < BK / 16; ++kk) {
+            umma_bf16_ss(d_tmem, umma_desc_kmajor(a_addr + kk * 32, Cfg::SW), umma_desc_kmajor(b_addr + kk * 32, Cfg::SW),
+                         idesc, (k > 0 || kk > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty[s]);  // frees the smem stage once these MMAs retire
+        }
+        umma_commit(&tfull[buf]);  // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ===================== epilogue (4 warps) =====================
+    const int qw = warp & 3;  // TMEM lane quarter accessible to this warp
+    float* st = epi + qw * 32 * Cfg::EPI_PITCH;
+    uint32_t t_iter = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
+      const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
+      const int64_t m0 = (int64_t)tm * Cfg::BM + qw * 32;
+      const int n0 = tn * BN;
+      const uint32_t buf = t_iter & 1;
+      mbar_wait(&tfull[buf], (t_iter >> 1) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int cc = 0; cc < BN / Cfg::CH; ++cc) {
+        float v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16) + buf * BN + cc * Cfg::CH;
+        if (Cfg::CH == 32)
+          tmem_ld_32x32(taddr, v);
+        else
+          tmem_ld_32x16(taddr, v);
+        tmem_ld_wait();
+        if (p.out_nchw) {
+          // UNetModel.out conv: thread owns pixel m, writes the n_valid real channels as fp32 NCHW
+          const int64_t m = m0 + lane;
+          if (m < p.M) {
+            const int b = (int)(m / p.hw_out), pix = (int)(m % p.hw_out);
+            float* o = reinterpret_cast<float*>(p.out);
+#pragma unroll
+            for (int j = 0; j < Cfg::CH; ++j) {
+              const int n = n0 + cc * Cfg::CH + j;
+              if (n < p.n_valid) o[((size_t)b * p.n_valid + n) * p.hw_out + pix] = v[j] + (p.bias ? p.bias[n] : 0.f);
+            }
+          }
+          continue;
+        }
+        int ncols = Cfg::CH;
+        int col0 = n0 + cc * Cfg::CH;
+        if (p.geglu) {  // chunk = [16 value | 16 gate] columns (packed order), biases in the same order
+          const float* bp = p.bias + n0 + cc * 32;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float val = v[j] + bp[j];
+            const float gate = v[16 + j] + bp[16 + j];
+            v[j] = val * gelu_erf_f(gate);
+          }
+          ncols = 16;
+          col0 = (n0 >> 1) + cc * 16;
+        }
+#pragma unroll
+        for (int j = 0; j < Cfg::CH / 4; ++j)
+          if (j * 4 < ncols)
+            *reinterpret_cast<float4*>(&st[lane * Cfg::EPI_PITCH + j * 4]) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+        __syncwarp();
+        const int lpr = ncols >> 2;       // lanes per row
+        const int rpi = 32 / lpr;         // rows per iteration
+        const int c4 = (lane % lpr) * 4;
+        const int col = col0 + c4;
+        float4 bq = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (!p.geglu && p.bias && col < p.n_valid) bq = *reinterpret_cast<const float4*>(p.bias + col);
+        for (int r = lane / lpr; r < 32; r += rpi) {
+          const int64_t m = m0 + r;
+          if (m < p.M && col < p.n_valid) {
+            float4 t = *reinterpret_cast<const float4*>(&st[r * Cfg::EPI_PITCH + c4]);
+            t.x += bq.x; t.y += bq.y; t.z += bq.z; t.w += bq.w;
+            if (p.rowvec) {
+              const float4 rv = *reinterpret_cast<const float4*>(p.rowvec + (size_t)(m / p.rows_per_sample) * p.rowvec_ld + col);
+              t.x += rv.x; t.y += rv.y; t.z += rv.z; t.w += rv.w;
+            }
+            if (p.residual) {
+              const float4 rs = *reinterpret_cast<const float4*>(p.residual + (size_t)m * p.residual_ld + col);
+              t.x += rs.x; t.y += rs.y; t.z += rs.z; t.w += rs.w;
+            }
+            if (p.out_bf16) {
+              __nv_bfloat162 lo = __floats2bfloat162_rn(t.x, t.y), hi = __floats2bfloat162_rn(t.z, t.w);
+              uint2 u;
+              u.x = *reinterpret_cast<uint32_t*>(&lo);
+              u.y = *reinterpret_cast<uint32_t*>(&hi);
+              *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)m * p.out_ld + col) = u;
+            } else {
+              *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)m * p.out_ld + col) = t;
+            }
+          }
+        }
+        __syncwarp();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[buf]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+template <int BN, int BK>
+static int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b, const TcParams& p,
+                     cudaStream_t st) {
+  using Cfg = TcCfg<BN, BK>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) {
+      set_error("igemm_tc: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
+      return LDMB200_ERR_CUDA;
+    }
+    attr_set = true;
+  }
+  int grid = std::min(p.tiles_m * p.tiles_n, sm_count());
+  igemm_tc_kernel<BN, BK><<<grid, TC_THREADS, Cfg::SMEM_BYTES, st>>>(a1, a2, b, p);
+  LDM_CHECK_LAUNCH("igemm_tc");
+  return 0;
+}
+
+static bool is_pow2(int x) { return x > 0 && (x & (x - 1)) == 0; }
+
+}  // namespace ldm
+
+using namespace ldm;
+
+extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
+  LDM_CHECK_ARG(d && d->a && d->w && d->out, "igemm_tc: null pointer");
+  LDM_CHECK_ARG(d->a_dtype == LDMB200_BF16, "igemm_tc: A operand must be bf16");
+  LDM_CHECK_ARG(!d->upsample, "igemm_tc: upsample must be materialised (ldmb200_upsample2x) on the tensor-core path");
+  LDM_CHECK_ARG(d->ksize == 1 || d->ksize == 3, "igemm_tc: ksize must be 1 or 3");
+  LDM_CHECK_ARG(d->stride == 1 || (d->stride == 2 && d->ksize == 3), "igemm_tc: stride 2 only for 3x3");
+  const int c1 = d->c1, c2 = d->a2 ? d->c2 : 0;
+  LDM_CHECK_ARG(c1 > 0 && c1 % 32 == 0 && c2 % 32 == 0, "igemm_tc: channel counts must be multiples of 32 (c1=%d c2=%d)", c1, c2);
+  LDM_CHECK_ARG(d->n > 0 && d->n % 16 == 0, "igemm_tc: n=%d must be a multiple of 16 (pad the packed weights)", d->n);
+  const int h_out = d->stride == 2 ? d->h_in / 2 : d->h_in, w_out = d->stride == 2 ? d->w_in / 2 : d->w_in;
+  const int hw_out = h_out * w_out;
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = (int64_t)d->batch * hw_out;
+  p.ks = d->ksize;
+  p.taps = d->ksize * d->ksize;
+  p.stride = d->stride;
+  p.is_conv = d->ksize == 3;
+  p.ctot = c1 + c2;
+  p.hw_out = hw_out;
+  p.w_out = w_out;
+  p.rows_per_sample = hw_out;
+  p.bias = d->bias;
+  p.rowvec = d->rowvec;
+  p.rowvec_ld = d->rowvec_ld;
+  p.residual = d->residual;
+  p.residual_ld = d->residual_ld;
+  p.geglu = d->geglu;
+  p.out = d->out;
+  p.out_bf16 = d->out_dtype == LDMB200_BF16;
+  p.out_ld = d->out_ld;
+  p.out_nchw = d->out_nchw;
+  const int n_cols = d->geglu ? d->n / 2 : d->n;
+  p.n_valid = d->n_valid > 0 ? d->n_valid : n_cols;
+  LDM_CHECK_ARG(d->out_nchw || p.n_valid % 4 == 0, "igemm_tc: n_valid must be a multiple of 4 unless out_nchw");
+  LDM_CHECK_ARG(!(d->out_nchw && (p.out_bf16 || d->geglu || d->rowvec || d->residual)), "igemm_tc: out_nchw is a plain fp32 store");
+  LDM_CHECK_ARG(!(d->geglu && (!d->bias || d->rowvec || d->residual)), "igemm_tc: geglu epilogue takes the packed bias only");
+  LDM_CHECK_ARG(p.M > 0 && p.M < (1ll << 31), "igemm_tc: M out of range");
+
+  int BK = (c1 % 64 == 0 && c2 % 64 == 0) ? 64 : 32;
+  if (const char* e = getenv("LDMB200_TC_BK")) {
+    int v = atoi(e);
+    if (v == 32 || (v == 64 && BK == 64)) BK = v;
+  }
+  int BN = (d->n % 160 == 0) ? 160 : (d->n % 32 == 0) ? 32 : 16;
+  LDM_CHECK_ARG(BN != 16 || d->n == 16, "igemm_tc: n=%d unsupported (need multiple of 32, or exactly 16)", d->n);
+  LDM_CHECK_ARG(!(d->geglu && BN == 16), "igemm_tc: geglu needs n %% 32 == 0");
+  p.c1_chunks = c1 / BK;
+  p.c2_chunks = c2 / BK;
+  p.tiles_m = (int)ceil_div64(p.M, 128);
+  p.tiles_n = d->n / BN;
+
+  // ---- A tensor maps: {C, W, H, plane, B}, box {BK, bw, bh, 1, bn} with bw*bh*bn = 128 rows
+  CUtensorMap tA1, tA2, tB;
+  const int planes = d->stride == 2 ? 4 : 1;
+  for (int which = 0; which < (c2 ? 2 : 1); ++which) {
+    const void* base = which ? d->a2 : d->a;
+    const uint64_t C = which ? c2 : c1;
+    uint64_t dims[5], str[4];
+    uint32_t box[5];
+    if (p.is_conv) {
+      LDM_CHECK_ARG(is_pow2(w_out) && is_pow2(h_out) && w_out <= 128,
+                    "igemm_tc: 3x3 conv needs power-of-two output H,W with W <= 128 (got %dx%d)", h_out, w_out);
+      const int bw = w_out, bh = std::min(h_out, 128 / bw), bn = 128 / (bw * bh);
+      dims[0] = C; dims[1] = w_out; dims[2] = h_out; dims[3] = planes; dims[4] = d->batch;
+      str[0] = C * 2; str[1] = (uint64_t)w_out * C * 2; str[2] = (uint64_t)hw_out * C * 2; str[3] = (uint64_t)planes * hw_out * C * 2;
+      box[0] = BK; box[1] = bw; box[2] = bh; box[3] = 1; box[4] = bn;
+    } else {
+      dims[0] = C; dims[1] = 1; dims[2] = (uint64_t)p.M; dims[3] = 1; dims[4] = 1;
+      str[0] = C * 2; str[1] = C * 2; str[2] = (uint64_t)p.M * C * 2; str[3] = (uint64_t)p.M * C * 2;
+      box[0] = BK; box[1] = 1; box[2] = 128; box[3] = 1; box[4] = 1;
+    }
+    int rc = make_tensor_map_bf16(which ? &tA2 : &tA1, base, 5, dims, str, box, BK * 2);
+    if (rc) return rc;
+  }
+  if (!c2) tA2 = tA1;
+  {
+    uint64_t dims[2] = {(uint64_t)p.taps * p.ctot, (uint64_t)d->n};
+    uint64_t str[1] = {(uint64_t)p.taps * p.ctot * 2};
+    uint32_t box[2] = {(uint32_t)BK, (uint32_t)BN};
+    int rc = make_tensor_map_bf16(&tB, d->w, 2, dims, str, box, BK * 2);
+    if (rc) return rc;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (BN == 160) return BK == 64 ? launch_tc<160, 64>(tA1, tA2, tB, p, st) : launch_tc<160, 32>(tA1, tA2, tB, p, st);
+  if (BN == 32) return BK == 64 ? launch_tc<32, 64>(tA1, tA2, tB, p, st) : launch_tc<32, 32>(tA1, tA2, tB, p, st);
+  return BK == 64 ? launch_tc<16, 64>(tA1, tA2, tB, p, st) : launch_tc<16, 32>(tA1, tA2, tB, p, st);
+}

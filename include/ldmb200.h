@@ -1,0 +1,185 @@
+/*
+ * ldmb200 — C-ABI of the B200-native latent-diffusion denoising path (sm_100a).
+ *
+ * This is the drop-in boundary.  The reference (GiannisPikoulis/dsml-thesis) is pure
+ * Python/PyTorch and has no FFI of its own, so each entry point below replaces the ATen call sites of one
+ * kernel family on the hot path; the reference file:line each one stands for is cited per function
+ * (paths relative to face_reenactment/; the UNet files are byte-identical under talking_face/).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; no torch / C++ types cross the boundary.
+ *   - Every pointer is a DEVICE pointer owned by the caller; nothing is allocated, freed or retained.
+ *   - All work is enqueued on `stream` (a cudaStream_t passed as void*; NULL = legacy default stream);
+ *     calls are stateless, re-entrant and CUDA-Graph capturable.
+ *   - Return value: 0 on success, negative LDMB200_ERR_* otherwise; ldmb200_last_error() returns a
+ *     thread-local message.  Nothing throws.
+ *   - Activations are channels-last: a feature map is a row-major matrix [B*H*W, C] ("pixels x channels").
+ *   - dtype codes: LDMB200_F32 = 0, LDMB200_BF16 = 1.
+ */
+#ifndef LDMB200_H_
+#define LDMB200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LDMB200_ABI_VERSION 1
+
+#define LDMB200_F32 0
+#define LDMB200_BF16 1
+
+#define LDMB200_ERR_INVALID (-1) /* bad argument / unsupported shape */
+#define LDMB200_ERR_CUDA (-2)    /* CUDA runtime / driver error     */
+
+int ldmb200_abi_version(void);
+const char* ldmb200_last_error(void);
+/* number of SMs of the current device (grid sizing); negative on error */
+int ldmb200_sm_count(void);
+
+/* ---------------------------------------------------------------------------------------------------
+ * K13  DDIM x_{t-1} update — DDIMSampler.p_sample_ddim, ldm/models/diffusion/ddim.py:173-203
+ * (talking_face: ldm/models/diffusion/ddim2cond.py:167-194).  One fused pass:
+ *   e      = e_uncond ? e_uncond + cfg_scale*(e_cond - e_uncond) : e_cond                 (ddim.py:177)
+ *   pred_x0 = (x - sqrt_one_minus_at*e) / sqrtf(a_t)                                        (ddim.py:194)
+ *   x_prev  = sqrtf(a_prev)*pred_x0 + sqrtf(1 - a_prev - sigma_t^2)*e + sigma_t*noise*temperature
+ * Coefficients are the fp32-rounded per-step scalars of torch.full (ddim.py:188-191); the three square
+ * roots are evaluated in fp32 on the device like the reference.  noise may be NULL (treated as 0).
+ * n = number of elements.  x_prev may alias x.
+ */
+int ldmb200_ddim_step(const float* x, const float* e_cond, const float* e_uncond, const float* noise,
+                      float* x_prev, float* pred_x0, int64_t n, float a_t, float a_prev, float sigma_t,
+                      float sqrt_one_minus_at, float cfg_scale, float temperature, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * K12  timestep_embedding — ldm/modules/diffusionmodules/util.py:151-171:  out[b] = [cos(t_b f) | sin(t_b f)],
+ * f_i = exp(-ln(max_period) * i / (dim/2)), fp32.  t is int64 [B]; out is fp32 [B, dim] (dim even).
+ */
+int ldmb200_timestep_embedding(const int64_t* t, float* out, int batch, int dim, float max_period, void* stream);
+
+/* Small dense layer for per-sample vectors (time_embed MLP openaimodel.py:506-511,724; ResBlock emb_layers
+ * 218-224,264; cross-attention to_k/to_v/to_out on a length-1 context attention.py:175-176,193):
+ *   out[r, n] = bias[n] + sum_k act(in[r, k]) * W[n, k]      fp32 throughout, act = SiLU if silu_in else id.
+ * in [R, K] (row stride in_ld), W [N, K] row-major (nn.Linear layout), out [R, N] (row stride out_ld).
+ */
+int ldmb200_small_linear(const float* in, int in_ld, const float* w, const float* bias, float* out, int out_ld,
+                         int rows, int k, int n, int silu_in, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * Layout changes at the UNet boundary (openaimodel.py:730,738-742: NCHW fp32 in, NCHW fp32 out).
+ *   nchw_to_nhwc: x fp32 [B, C, HW] -> y [B, HW, c_pad] (dtype out_dtype), channels >= C zero-filled.
+ *   nhwc_to_nchw: y fp32 [B, HW, ld] (first C columns) -> x fp32 [B, C, HW].
+ */
+int ldmb200_nchw_to_nhwc(const float* x, void* y, int batch, int c, int hw, int c_pad, int out_dtype, void* stream);
+int ldmb200_nhwc_to_nchw(const float* y, int ld, float* x, int batch, int c, int hw, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * K7 (+K11)  GroupNorm(32 groups) [+ SiLU] over a channels-last map that may be the virtual channel
+ * concat of two maps — GroupNorm32 util.py:214-216 / normalization 199-205 (eps 1e-5) followed by nn.SiLU
+ * in ResBlock.in_layers/out_layers (openaimodel.py:201-203,226-227) and UNetModel.out (683-684); Normalize
+ * attention.py:76-77 (eps 1e-6, no SiLU); th.cat([h, hs.pop()], 1) openaimodel.py:736.
+ * x1 [B, HW, c1], x2 [B, HW, c2] (x2 NULL / c2 = 0 for no concat), both fp32.  Statistics in fp32 with a
+ * float64 combine.  y [B, HW, c1+c2] (out_dtype).  raw_copy (nullable) receives the un-normalised concat
+ * cast to out_dtype (operand of ResBlock.skip_connection, openaimodel.py:241,275).
+ * stats_ws: caller workspace of ldmb200_groupnorm_ws_floats(batch, hw, c) floats.
+ */
+int64_t ldmb200_groupnorm_ws_floats(int batch, int hw, int c);
+int ldmb200_groupnorm(const float* x1, int c1, const float* x2, int c2, const float* gamma, const float* beta,
+                      void* y, void* raw_copy, int out_dtype, int batch, int hw, int groups, float eps, int silu,
+                      float* stats_ws, void* stream);
+
+/* K9  LayerNorm over the last dim — nn.LayerNorm(dim) attention.py:203-205 (eps 1e-5, affine).
+ * x fp32 [M, C] -> y [M, C] (out_dtype). */
+int ldmb200_layernorm(const float* x, const float* gamma, const float* beta, void* y, int out_dtype, int64_t rows,
+                      int c, float eps, void* stream);
+
+/* fp32 -> out_dtype helpers feeding the strided / upsampled convolutions on the tensor-core path:
+ *   space_to_depth2: x fp32 [B, H, W, C] -> y [B, 4, H/2, W/2, C], plane p = (h&1)*2 + (w&1)
+ *                    (input re-ordering for Downsample.op, conv 3x3 stride 2, openaimodel.py:151-160)
+ *   upsample2x:      x fp32 [B, H, W, C] -> y [B, 2H, 2W, C] nearest  (F.interpolate, openaimodel.py:116)
+ */
+int ldmb200_space_to_depth2(const float* x, void* y, int out_dtype, int batch, int h, int w, int c, void* stream);
+int ldmb200_upsample2x(const float* x, void* y, int out_dtype, int batch, int h, int w, int c, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * K1-K4 (+K8,K10,K11)  Convolution / linear as (implicit) GEMM with fused epilogue.
+ *   conv_nd(2,..,3,padding=1) openaimodel.py:204,230,519,685,107 ; Downsample.op stride 2 151-153 ;
+ *   1x1 skip_connection 241, proj_in/proj_out attention.py:233-248 ; nn.Linear attention.py:40,60,161-166.
+ *
+ *   acc[m, n] = sum_{tap, c} A(m, tap, c) * W[n, tap, c]
+ *   v         = acc + bias[n] + rowvec[sample(m), n] + residual[m, n]
+ *   out[m, j] = geglu ? v[value col] * gelu_erf(v[gate col]) : v           (attention.py:43-44)
+ *
+ * A is read from one or two channels-last maps (virtual concat, c1 + c2 channels per tap) of spatial size
+ * h_in x w_in; ksize 1 or 3 (padding 1); stride 1 or 2; upsample=1 reads the nearest-2x upsampled map
+ * (SIMT path only — the tensor-core path takes a materialised ldmb200_upsample2x / space_to_depth2 input).
+ */
+typedef struct ldmb200_gemm_desc {
+  const void* a;         /* first map  [B, h_in, w_in, c1] (plain GEMM: [M, c1] with h_in = M/batch, w_in = 1) */
+  const void* a2;        /* second map [B, h_in, w_in, c2] or NULL                                    */
+  int32_t c1, c2;
+  int32_t a_dtype;       /* LDMB200_F32 | LDMB200_BF16                                                */
+  int32_t batch, h_in, w_in;
+  int32_t ksize;         /* 1 | 3                                                                     */
+  int32_t stride;        /* 1 | 2  (tensor-core path, stride 2: `a` is the space_to_depth2 layout)    */
+  int32_t upsample;      /* 0 | 1                                                                     */
+  const void* w;         /* SIMT: fp32 native nn layout [n, c1+c2, k, k] ; TC: packed bf16 (ldmb200_pack_weights) */
+  int32_t n;             /* GEMM N = rows of w (for geglu: 2 x output width)                          */
+  const float* bias;     /* [n] or NULL (TC + geglu: packed order)                                    */
+  const float* rowvec;   /* [batch, rowvec_ld] per-sample broadcast add or NULL (K8: emb_out; K6: M=1 cross-attn) */
+  int32_t rowvec_ld;
+  const float* residual; /* fp32 [M, residual_ld] or NULL                                             */
+  int32_t residual_ld;
+  int32_t geglu;         /* 0 | 1                                                                     */
+  void* out;             /* [M, out_ld]                                                               */
+  int32_t out_dtype;
+  int32_t out_ld;
+  int32_t out_nchw;      /* 1: out is fp32 NCHW [B, n_valid, H_out*W_out]  (UNetModel.out conv)       */
+  int32_t n_valid;       /* columns actually stored (<= n; TC path pads n to a multiple of 16)        */
+} ldmb200_gemm_desc;
+
+/* fp32-exact SIMT path (precision mode "fp32": per-step eps rel-L2 <= 1e-4 vs the fp32 reference). */
+int ldmb200_igemm_simt(const ldmb200_gemm_desc* d, void* stream);
+/* tcgen05 / TMEM / TMA path: bf16 operands, fp32 accumulation in tensor memory.
+ * Requirements: a_dtype bf16, c1 % 32 == 0, c2 % 32 == 0, w packed, upsample == 0. */
+int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream);
+
+/* Weight packing for the tensor-core path (one launch for the whole model, re-run whenever weights change —
+ * LitEma.copy_to/restore write param.data in place, ldm/modules/ema.py:46-76).
+ * Each job converts one fp32 nn.Parameter into the bf16 K-major layout ldmb200_igemm_tc expects:
+ *   kind 0  conv/linear weight [n, c, k, k] -> [n_pad, k, k, c_pad]   (zero padded)
+ *   kind 1  same, rows permuted for the GEGLU epilogue (value/gate interleaved in groups of 16)
+ *   kind 2  fp32 vector copy with the GEGLU permutation (bias of ff.net.0.proj)
+ * jobs is a DEVICE array of n_jobs ldmb200_pack_job.
+ */
+typedef struct ldmb200_pack_job {
+  const float* src;
+  void* dst;
+  int32_t kind;
+  int32_t n, c, ksize;   /* source shape [n, c, ksize, ksize] (vectors: n)            */
+  int32_t n_pad, c_pad;  /* destination padding (>= n, >= c)                          */
+  int32_t row_offset;    /* destination row offset (fused QKV: q rows, k rows, v rows) */
+  int32_t block_n;       /* GEGLU permutation tile (kind 1/2)                          */
+} ldmb200_pack_job;
+int ldmb200_pack_weights(const ldmb200_pack_job* jobs, int n_jobs, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * K5/K6  Attention — CrossAttention.forward attention.py:170-193: softmax(q k^T * d^-0.5) v per head,
+ * head index = outer factor of the channel dim ('b n (h d) -> (b h) n d', attention.py:178), d_head = 32.
+ *   q  [B, Nq,  q_ld ] (+q_off ), k [B, Nkv, kv_ld] (+k_off), v [B, Nkv, kv_ld] (+v_off): element (b,i,h,d) of q is
+ *   q[(b*Nq + i)*q_ld + q_off + h*32 + d]; out [B, Nq, out_ld].  Self-attention passes the fused QKV matrix
+ *   [B*N, 3C] as all three with offsets 0, C, 2C.
+ * _simt: fp32 in/out (precision mode fp32, and the general cross-attention path with a short context);
+ * _tc:   bf16 in/out, flash-style on tcgen05 (S and PV in tensor memory, online softmax in fp32).
+ */
+int ldmb200_attention_simt(const float* q, int q_ld, int q_off, const float* k, int k_off, const float* v, int v_off,
+                           int kv_ld, float* out, int out_ld, int batch, int heads, int nq, int nkv, float scale,
+                           void* stream);
+int ldmb200_attention_tc(const void* qkv, int ld, int q_off, int k_off, int v_off, void* out, int out_ld, int batch,
+                         int heads, int n_tokens, float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LDMB200_H_ */

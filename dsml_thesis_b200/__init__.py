@@ -1,0 +1,22 @@
+"""B200-native (sm_100a) latent-diffusion denoising path of GiannisPikoulis/dsml-thesis.
+
+Public surface = the reference's own plugin interface for this path:
+
+  * ``UNetModel``       — drop-in for ``ldm.modules.diffusionmodules.openaimodel.UNetModel``
+  * ``DDIMSampler``     — drop-in for ``ldm.models.diffusion.ddim.DDIMSampler``
+  * ``DDIMSampler2Cond`` / ``DDIMSampler2CondFR`` — drop-ins for the two ``ddim2cond.DDIMSampler`` flavours
+  * ``install()``       — patches those dotted targets after ``import ldm`` so ``main.py``, the YAML configs and
+                          the sampling scripts pick the new classes up with no file edited
+  * ``ddim_step``       — the fused x_{t-1} update as a function
+
+All compute goes through ``libldmb200.so`` (C-ABI in ``include/ldmb200.h``); there is no CPU or PyTorch
+fallback — importing works anywhere, running needs the built library and a B200.
+"""
+from ._cabi import Ldmb200Error, load as load_library  # noqa: F401
+from .unet import UNetModel  # noqa: F401
+from .sampler import DDIMSampler, DDIMSampler2Cond, DDIMSampler2CondFR, ddim_step  # noqa: F401
+from .handle import DiffusionHandle  # noqa: F401
+from .install import install, uninstall  # noqa: F401
+
+__all__ = ["UNetModel", "DDIMSampler", "DDIMSampler2Cond", "DDIMSampler2CondFR", "ddim_step", "install",
+           "uninstall", "DiffusionHandle", "load_library", "Ldmb200Error"]

@@ -1,0 +1,265 @@
+"""Per-kernel parity through the C-ABI (``-m gpu``): each sm_100a kernel against a plain PyTorch fp32/fp64
+reference of the same op on the same seeded inputs, on the shape classes of SURVEY Appendix A.
+
+Tolerances (rel-L2 = ||a-b||/||b||):
+  * fp32 SIMT kernels and norms: 2e-6 .. 1e-5 (summation-order floor);
+  * tensor-core kernels: operands are bf16-rounded BEFORE the reference is computed, so what remains is fp32
+    accumulation order (<= 1e-5) plus the bf16 rounding of the output when it is stored as bf16 (<= 4e-3);
+  * DDIM update: bit-exact.
+"""
+import math
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from dsml_thesis_b200 import _cabi  # noqa: E402
+from dsml_thesis_b200._cabi import BF16, F32  # noqa: E402
+
+import kernel_harness as K  # noqa: E402
+from oracle import ldm_oracle as O  # noqa: E402
+
+
+@pytest.fixture(autouse=True)
+def _seed():
+    torch.manual_seed(0)
+    yield
+    torch.cuda.synchronize()
+
+
+def rnd(*shape, scale=1.0):
+    return torch.randn(*shape, device="cuda") * scale
+
+
+def bf(x):
+    return x.to(torch.bfloat16).float()
+
+
+# ------------------------------------------------------------------------------------------ elementwise
+@pytest.mark.parametrize("n", [4, 1000, 2 * 3 * 64 * 64, 64 * 3 * 64 * 64 + 3])
+@pytest.mark.parametrize("cfg,noise", [(False, False), (True, False), (False, True), (True, True)])
+def test_elementwise_ddim_step_bit_exact(n, cfg, noise):
+    from dsml_thesis_b200 import ddim_step
+    sch = O.ddim_schedule(O.ddpm_buffers()["alphas_cumprod"], 50, 1.0)
+    for index in (49, 25, 0):
+        x, ec = rnd(n), rnd(n)
+        eu = rnd(n) if cfg else None
+        nz = rnd(n) if noise else None
+        a_t, a_prev, sg, s1 = (float(sch[k][index]) for k in ("a_t", "a_prev", "sigma_t", "sqrt_one_minus_at"))
+        xp, p0 = ddim_step(x, ec, eu, nz, a_t, a_prev, sg, s1, 3.0, 0.7)
+        e = ec.cpu() if eu is None else eu.cpu() + 3.0 * (ec.cpu() - eu.cpu())
+        rx, rp = O.ddim_update(x.cpu().reshape(1, 1, 1, n), e.reshape(1, 1, 1, n), a_t, a_prev, sg, s1,
+                               nz.cpu().reshape(1, 1, 1, n) if nz is not None else None, 0.7)
+        assert torch.equal(p0.cpu(), rp.reshape(n)), "pred_x0 not bit-exact"
+        assert torch.equal(xp.cpu(), rx.reshape(n)), "x_prev not bit-exact"
+
+
+def test_elementwise_ddim_step_empty_is_an_error():
+    with pytest.raises(_cabi.Ldmb200Error):
+        _cabi.call("ldmb200_ddim_step", None, None, None, None, None, None, 0, 1., 1., 0., 0., 1., 1., K.stream())
+
+
+def test_elementwise_timestep_embedding():
+    t = torch.tensor([0, 1, 21, 501, 981, 999], device="cuda")
+    for dim in (160, 32):
+        out = torch.empty(t.numel(), dim, device="cuda")
+        _cabi.call("ldmb200_timestep_embedding", t.data_ptr(), out.data_ptr(), t.numel(), dim, 10000.0, K.stream())
+        ref = O.timestep_embedding(t.cpu(), dim)
+        # arguments reach ~1e3 rad: one fp32 ulp of the argument is 6e-5, torch's own fp32 sin/cos sit within that
+        assert (out.cpu() - ref).abs().max() <= 1.5e-4
+        assert K.rel_l2(out, ref) <= 2e-5
+
+
+@pytest.mark.parametrize("rows,k,n,silu", [(2, 160, 640, 0), (64, 640, 640, 1), (3, 1024, 320, 0), (17, 512, 160, 1),
+                                           (33, 64, 100, 0)])
+def test_elementwise_small_linear(rows, k, n, silu):
+    x, w, b = rnd(rows, k), rnd(n, k, scale=k ** -0.5), rnd(n)
+    out = torch.empty(rows, n, device="cuda")
+    _cabi.call("ldmb200_small_linear", x.data_ptr(), k, w.data_ptr(), b.data_ptr(), out.data_ptr(), n, rows, k, n,
+               silu, K.stream())
+    ref = F.linear((F.silu(x) if silu else x).double(), w.double(), b.double()).float()
+    assert K.rel_l2(out, ref) <= 2e-6
+
+
+@pytest.mark.parametrize("B,Cc,H,cpad,dt", [(2, 3, 8, 32, BF16), (2, 9, 16, 32, BF16), (3, 3, 8, 3, F32)])
+def test_elementwise_layout_roundtrip(B, Cc, H, cpad, dt):
+    x = rnd(B, Cc, H, H)
+    y = torch.full((B * H * H, cpad), float("nan"), dtype=torch.bfloat16 if dt == BF16 else torch.float32, device="cuda")
+    _cabi.call("ldmb200_nchw_to_nhwc", x.data_ptr(), y.data_ptr(), B, Cc, H * H, cpad, dt, K.stream())
+    ref = K.to_cl(x)
+    assert torch.equal(y[:, :Cc].float(), bf(ref) if dt == BF16 else ref)
+    assert (y[:, Cc:] == 0).all()
+    if dt == F32:
+        back = torch.empty_like(x)
+        _cabi.call("ldmb200_nhwc_to_nchw", y.data_ptr(), cpad, back.data_ptr(), B, Cc, H * H, K.stream())
+        assert torch.equal(back, x)
+
+
+@pytest.mark.parametrize("B,c1,c2,H,eps,silu,dt,raw", [
+    (2, 160, 0, 64, 1e-5, 1, BF16, False), (2, 320, 160, 32, 1e-5, 1, BF16, True), (1, 640, 640, 16, 1e-5, 1, F32, True),
+    (3, 640, 0, 16, 1e-6, 0, F32, False), (2, 32, 0, 8, 1e-6, 0, BF16, False), (2, 64, 32, 4, 1e-5, 1, F32, True),
+    (2, 128, 0, 2, 1e-5, 1, F32, False), (1, 960, 0, 32, 1e-5, 1, BF16, False)])
+def test_elementwise_groupnorm(B, c1, c2, H, eps, silu, dt, raw):
+    hw = H * H
+    x1 = rnd(B * hw, c1) * 2 + 0.5
+    x2 = rnd(B * hw, c2) - 1 if c2 else None
+    c = c1 + c2
+    g, b = 1 + 0.1 * rnd(c), 0.1 * rnd(c)
+    y, r = K.groupnorm(x1, x2, g, b, B, hw, eps, silu, dt, raw)
+    xc = torch.cat([x1, x2], 1) if c2 else x1
+    ref = F.group_norm(K.from_cl(xc, B, H, H).double(), 32, g.double(), b.double(), eps)
+    ref = K.to_cl(F.silu(ref) if silu else ref)
+    assert K.rel_l2(y, ref) <= (4e-3 if dt == BF16 else 3e-6)
+    if raw:
+        assert torch.equal(r.float(), bf(xc) if dt == BF16 else xc)
+
+
+@pytest.mark.parametrize("rows,c,dt", [(4096, 160, BF16), (1024, 320, F32), (256, 640, BF16), (5, 32, F32), (77, 1280, F32)])
+def test_elementwise_layernorm(rows, c, dt):
+    x, g, b = rnd(rows, c) * 3 + 1, 1 + 0.1 * rnd(c), 0.1 * rnd(c)
+    y = torch.empty(rows, c, dtype=torch.bfloat16 if dt == BF16 else torch.float32, device="cuda")
+    _cabi.call("ldmb200_layernorm", x.data_ptr(), g.data_ptr(), b.data_ptr(), y.data_ptr(), dt, rows, c, 1e-5, K.stream())
+    ref = F.layer_norm(x.double(), (c,), g.double(), b.double(), 1e-5)
+    assert K.rel_l2(y, ref) <= (4e-3 if dt == BF16 else 2e-6)
+
+
+def test_elementwise_resample_layouts():
+    B, Cc, H = 2, 32, 8
+    x = rnd(B, Cc, H, H)
+    up = torch.empty(B * 4 * H * H, Cc, device="cuda")
+    _cabi.call("ldmb200_upsample2x", K.to_cl(x).data_ptr(), up.data_ptr(), F32, B, H, H, Cc, K.stream())
+    assert torch.equal(up, K.to_cl(F.interpolate(x, scale_factor=2, mode="nearest")))
+    s2d = K.space_to_depth(x, torch.float32).reshape(B, 2, 2, H // 2, H // 2, Cc)
+    ref = x.permute(0, 2, 3, 1).reshape(B, H // 2, 2, H // 2, 2, Cc).permute(0, 2, 4, 1, 3, 5)
+    assert torch.equal(s2d, ref.contiguous())
+
+
+# ------------------------------------------------------------------------------------------ weight packer
+@pytest.mark.parametrize("n,c,ks,kind", [(160, 160, 3, 0), (3, 160, 3, 0), (160, 3, 3, 0), (320, 480, 1, 0),
+                                         (1280, 160, 1, 1), (256, 32, 1, 1)])
+def test_pack_weights(n, c, ks, kind):
+    w = rnd(n, c, ks, ks)
+    bias = rnd(n)
+    wp, fb, n_pad, c_pad = K.pack_weight(w, kind=kind, bias=bias)
+    ref = torch.zeros(n_pad, ks * ks, c_pad, device="cuda")
+    src = w
+    if kind == 1:
+        perm = K.geglu_perm(n, 160 if n % 160 == 0 else 32)
+        src = w[perm]
+        assert torch.equal(fb, bias[perm])
+    ref[:n, :, :c] = src.permute(0, 2, 3, 1).reshape(n, ks * ks, c)
+    assert torch.equal(wp.float(), bf(ref))
+
+
+def test_pack_weights_fused_rows():
+    q, k, v = rnd(64, 64), rnd(64, 64), rnd(64, 64)
+    wp, _, n_pad, _ = K.pack_weight(None, parts=[q, k, v])
+    assert n_pad == 192
+    assert torch.equal(wp[:, 0, :].float(), bf(torch.cat([q, k, v])))
+
+
+# ------------------------------------------------------------------------------------------ SIMT implicit GEMM
+@pytest.mark.parametrize("B,cin,cout,H,ks,stride,up", [
+    (2, 3, 160, 16, 3, 1, 0), (1, 160, 160, 16, 3, 1, 0), (2, 64, 64, 8, 3, 2, 0), (2, 64, 32, 4, 3, 1, 1),
+    (2, 96, 64, 8, 1, 1, 0), (1, 160, 3, 16, 3, 1, 0), (3, 32, 70, 6, 3, 1, 0)])
+def test_simt_conv(B, cin, cout, H, ks, stride, up):
+    x, w, b = rnd(B, cin, H, H), rnd(cout, cin, ks, ks, scale=(cin * ks * ks) ** -0.5), rnd(cout)
+    out = K.igemm("simt", K.to_cl(x), B, H, H, w, b, ksize=ks, stride=stride, upsample=up)
+    ref = K.igemm_reference(x, w, b, stride=stride, upsample=up)
+    assert K.rel_l2(K.from_cl(out, B, ref.shape[2], ref.shape[3]), ref) <= 2e-6
+
+
+def test_simt_epilogues_and_concat():
+    B, c1, c2, cout, H = 2, 64, 32, 96, 8
+    x1, x2 = rnd(B, c1, H, H), rnd(B, c2, H, H)
+    w, b = rnd(cout, c1 + c2, 3, 3, scale=0.05), rnd(cout)
+    rv, res = rnd(B, cout), rnd(B, cout, H, H)
+    out = K.igemm("simt", K.to_cl(x1), B, H, H, w, b, ksize=3, a2=K.to_cl(x2), rowvec=rv, residual=K.to_cl(res))
+    ref = K.igemm_reference(torch.cat([x1, x2], 1), w, b, rowvec=rv, residual_nchw=res)
+    assert K.rel_l2(K.from_cl(out, B, H, H), ref) <= 2e-6
+    # GEGLU linear (attention.py:43-44) and the NCHW store of UNetModel.out
+    wg, bg = rnd(256, c1, 1, 1, scale=0.1), rnd(256)
+    out = K.igemm("simt", K.to_cl(x1), B, H * H, 1, wg, bg, geglu=True)
+    ref = K.igemm_reference(x1, wg, bg, geglu=True)
+    assert K.rel_l2(K.from_cl(out, B, H, H), ref) <= 3e-6
+    wo, bo = rnd(3, c1, 3, 3, scale=0.05), rnd(3)
+    out = K.igemm("simt", K.to_cl(x1), B, H, H, wo, bo, ksize=3, out_nchw=True)
+    assert K.rel_l2(out, K.igemm_reference(x1, wo, bo)) <= 2e-6
+
+
+# ------------------------------------------------------------------------------------------ tcgen05 implicit GEMM
+@pytest.mark.parametrize("M,k,n", [(128, 32, 32), (256, 64, 32), (128, 64, 160), (4096, 160, 160), (1024, 320, 960),
+                                   (256, 2560, 640), (300, 96, 64), (8192, 160, 1280)])
+def test_tc_gemm_plain(M, k, n):
+    a = rnd(M, k).to(torch.bfloat16)
+    w, b = rnd(n, k, 1, 1, scale=k ** -0.5), rnd(n)
+    out = K.igemm("tc", a, 1, M, 1, w, b)
+    ref = F.linear(a.double(), bf(w.reshape(n, k)).double(), b.double()).float()
+    assert K.rel_l2(out, ref) <= 1e-5
+
+
+@pytest.mark.parametrize("B,cin,cout,H", [(2, 32, 32, 16), (1, 160, 160, 64), (2, 320, 320, 32), (4, 64, 64, 8),
+                                          (3, 64, 32, 4), (5, 128, 64, 2), (1, 480, 160, 16), (1, 32, 16, 128)])
+def test_tc_conv3x3(B, cin, cout, H):
+    x = bf(rnd(B, cin, H, H))
+    w, b = rnd(cout, cin, 3, 3, scale=(9 * cin) ** -0.5), rnd(cout)
+    out = K.igemm("tc", K.to_cl(x, torch.bfloat16), B, H, H, w, b, ksize=3)
+    ref = K.igemm_reference(x, bf(w), b)
+    assert K.rel_l2(K.from_cl(out, B, H, H), ref) <= 1e-5
+
+
+@pytest.mark.parametrize("B,c,H", [(2, 64, 16), (1, 160, 64), (3, 320, 8)])
+def test_tc_conv3x3_stride2(B, c, H):
+    x = bf(rnd(B, c, H, H))
+    w, b = rnd(c, c, 3, 3, scale=(9 * c) ** -0.5), rnd(c)
+    out = K.igemm("tc", K.space_to_depth(x, torch.bfloat16), B, H, H, w, b, ksize=3, stride=2)
+    ref = K.igemm_reference(x, bf(w), b, stride=2)
+    assert K.rel_l2(K.from_cl(out, B, H // 2, H // 2), ref) <= 1e-5
+
+
+def test_tc_epilogues():
+    B, c, H, n = 2, 64, 16, 96
+    x = bf(rnd(B, c, H, H))
+    a = K.to_cl(x, torch.bfloat16)
+    w, b = rnd(n, c, 3, 3, scale=0.05), rnd(n)
+    rv, res = rnd(B, n), rnd(B, n, H, H)
+    out = K.igemm("tc", a, B, H, H, w, b, ksize=3, rowvec=rv, residual=K.to_cl(res))
+    ref = K.igemm_reference(x, bf(w), b, rowvec=rv, residual_nchw=res)
+    assert K.rel_l2(K.from_cl(out, B, H, H), ref) <= 1e-5
+    out = K.igemm("tc", a, B, H, H, w, b, ksize=3, rowvec=rv, residual=K.to_cl(res), out_dtype=BF16)
+    assert K.rel_l2(K.from_cl(out, B, H, H), ref) <= 4e-3
+    # GEGLU with both N tiles (160: C = 160 -> n = 1280; 32: C = 32 -> n = 256)
+    for cc in (160, 32):
+        xg = bf(rnd(512, cc))
+        wg, bg = rnd(8 * cc, cc, 1, 1, scale=cc ** -0.5), rnd(8 * cc)
+        out = K.igemm("tc", xg.to(torch.bfloat16), 1, 512, 1, wg, bg, geglu=True, out_dtype=BF16)
+        y = F.linear(xg.double(), bf(wg.reshape(8 * cc, cc)).double(), bg.double())
+        va, ga = y.chunk(2, dim=1)
+        assert K.rel_l2(out, (va * F.gelu(ga)).float()) <= 4e-3
+    # UNetModel.out: n = 3 padded to 16, fp32 NCHW store
+    wo, bo = rnd(3, c, 3, 3, scale=0.05), rnd(3)
+    out = K.igemm("tc", a, B, H, H, wo, bo, ksize=3, out_nchw=True)
+    assert K.rel_l2(out, K.igemm_reference(x, bf(wo), bo)) <= 1e-5
+
+
+# ------------------------------------------------------------------------------------------ attention
+@pytest.mark.parametrize("B,N,M,heads", [(2, 64, 64, 2), (1, 256, 256, 5), (2, 100, 7, 3), (1, 130, 1, 1), (2, 16, 77, 4)])
+def test_attn_simt(B, N, M, heads):
+    c = heads * 32
+    q, k, v = rnd(B, N, c), rnd(B, M, c), rnd(B, M, c)
+    out = K.attention("simt", q, k, v, heads, 32 ** -0.5)
+    assert K.rel_l2(out, K.attention_reference(q, k, v, heads, 32 ** -0.5)) <= 3e-6
+
+
+@pytest.mark.parametrize("B,N,heads,scale_in", [(1, 128, 1, 1.0), (2, 256, 2, 1.0), (1, 1024, 10, 1.0), (2, 64, 4, 1.0),
+                                                (3, 16, 1, 1.0), (1, 4, 20, 1.0), (1, 4096, 5, 1.0), (2, 320, 2, 3.0)])
+def test_attn_tc(B, N, heads, scale_in):
+    c = heads * 32
+    q, k, v = (bf(rnd(B, N, c) * scale_in) for _ in range(3))
+    out = K.attention("tc", q, k, v, heads, 32 ** -0.5)
+    ref = K.attention_reference(q, k, v, heads, 32 ** -0.5)
+    # P is rounded to bf16 before PV and the output is stored as bf16
+    assert K.rel_l2(out, ref) <= 6e-3

@@ -1,0 +1,198 @@
+"""End-to-end parity of the drop-in ``UNetModel`` / ``DDIMSampler`` on a B200 (``-m gpu``) against
+
+  * the committed golden vectors = outputs of the REAL reference modules (tests/golden/make_golden.py), and
+  * the CPU oracle (oracle/ldm_oracle.py) on freshly seeded inputs.
+
+Tolerances are BASELINE.json's: per-step eps rel-L2 <= 1e-4 in fp32 mode and <= 1e-2 in bf16 mode; final
+latents after a full DDIM trajectory within the bounds stated at each test.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import dsml_thesis_b200 as P  # noqa: E402
+from oracle import ldm_oracle as O  # noqa: E402
+
+TOL = {"fp32": 1e-4, "bf16": 1e-2}
+
+CASES = {  # name -> (cfg, B, hw, ctx_len, timesteps)   (same table as tests/test_oracle_golden.py)
+    "tiny_c1": (O.TINY_UNET, 2, 8, 1, [981, 501, 21]),
+    "tiny_c3": (O.TINY_UNET, 2, 8, 3, [981, 21]),
+    "tiny_hw16": (O.TINY_UNET, 3, 16, 1, [501]),
+    "fr_32": (O.FR_UNET, 1, 32, 1, [981]),
+    "tf_32": (O.TF_UNET, 1, 32, 1, [501]),
+}
+
+
+def synth_inputs(cfg, B, hw, seed, ctx_len=1):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(B, cfg["in_channels"], hw, hw, generator=g)
+    ctx = torch.randn(B, ctx_len, cfg["context_dim"], generator=g)
+    return x, ctx
+
+
+_models = {}
+
+
+def build(cfg, precision):
+    key = (tuple(sorted((k, str(v)) for k, v in cfg.items())), precision)
+    if key not in _models:
+        m = P.UNetModel(**cfg)
+        m.load_state_dict(O.init_state_dict(cfg, 0), strict=True)
+        m = m.cuda().eval()
+        m.precision = precision
+        _models.clear()  # one resident model at a time
+        _models[key] = m
+    return _models[key]
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("name", list(CASES))
+def test_unet_eps_vs_reference_golden(name, precision, golden_unet):
+    cfg, B, hw, cl, tsteps = CASES[name]
+    m = build(cfg, precision)
+    x, ctx = synth_inputs(cfg, B, hw, 1, cl)
+    with torch.no_grad():
+        for t in tsteps:
+            eps = m(x.cuda(), torch.tensor([t] * B).cuda(), context=ctx.cuda())
+            assert eps.shape == x[:, :3].shape and eps.dtype == torch.float32
+            err = O.rel_l2(eps, torch.from_numpy(golden_unet[f"{name}/eps_t{t}"]))
+            assert err <= TOL[precision], (name, t, err)
+        tm = torch.from_numpy(golden_unet[f"{name}/tmixed"])
+        err = O.rel_l2(m(x.cuda(), tm.cuda(), context=ctx.cuda()), torch.from_numpy(golden_unet[f"{name}/eps_tmixed"]))
+        assert err <= TOL[precision], (name, "tmixed", err)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_unet_cuda_graph_replay_matches_eager(precision):
+    cfg = O.TINY_UNET
+    m = build(cfg, precision)
+    x, ctx = synth_inputs(cfg, 2, 8, 5)
+    t = torch.tensor([400, 30]).cuda()
+    with torch.no_grad():
+        ref = m(x.cuda(), t, context=ctx.cuda())
+        m.use_cuda_graph = True
+        try:
+            m._plans.clear()
+            outs = [m(x.cuda(), t, context=ctx.cuda()) for _ in range(3)]   # eager, capture+replay, replay
+            x2, ctx2 = synth_inputs(cfg, 2, 8, 6)
+            other = m(x2.cuda(), t, context=ctx2.cuda())
+        finally:
+            m.use_cuda_graph = False
+            m._plans.clear()
+    for o in outs:
+        assert torch.equal(o, ref)
+    assert not torch.equal(other, ref)
+
+
+def test_unet_sees_in_place_weight_swaps():
+    """LitEma.copy_to writes param.data in place (ema.py:46-53): neither _version nor data_ptr changes."""
+    cfg = O.TINY_UNET
+    m = build(cfg, "bf16")
+    x, ctx = synth_inputs(cfg, 2, 8, 5)
+    t = torch.tensor([400, 30]).cuda()
+    with torch.no_grad():
+        a = m(x.cuda(), t, context=ctx.cuda())
+        w = m.out[2].weight
+        saved = w.data.clone()
+        w.data.copy_(saved * 2.0)
+        b = m(x.cuda(), t, context=ctx.cuda())
+        with m.frozen_weights():
+            c = m(x.cuda(), t, context=ctx.cuda())
+            w.data.copy_(saved)
+            m.invalidate_weight_cache()
+            d = m(x.cuda(), t, context=ctx.cuda())
+    assert not torch.equal(a, b)
+    assert torch.equal(b, c)
+    assert torch.equal(a, d)
+
+
+def test_unet_rejects_what_it_cannot_run():
+    cfg = O.TINY_UNET
+    m = build(cfg, "bf16")
+    x, ctx = synth_inputs(cfg, 2, 8, 5)
+    with pytest.raises(P.Ldmb200Error):
+        m(x, torch.tensor([1, 2]), context=ctx)            # CPU tensors: no fallback
+    with pytest.raises(NotImplementedError):
+        m.train()
+        try:
+            m(x.cuda(), torch.tensor([1, 2]).cuda(), context=ctx.cuda())
+        finally:
+            m.eval()
+    with pytest.raises(AssertionError):
+        with torch.no_grad():
+            m(x.cuda(), torch.tensor([1, 2]).cuda(), context=ctx.cuda(), y=torch.tensor([0, 1]).cuda())
+
+
+# ------------------------------------------------------------------------------------------ DDIM trajectories
+def handle_for(cfg, precision, two_cond=False):
+    return P.DiffusionHandle(build(cfg, precision), two_cond=two_cond).cuda()
+
+
+# final-latent bounds: fp32 mode tracks the reference to summation-order noise amplified over the trajectory;
+# bf16 mode accumulates per-step eps errors of <= 1e-2 (reference's own bf16 autocast: 1.5e-3 over 50 steps at 32^2)
+TRAJ_TOL = {"fp32": 1e-3, "bf16": 3e-2}
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("tag,S,eta,scale", [("fr_S10_eta0", 10, 0.0, 1.0), ("fr_S50_eta0", 50, 0.0, 1.0),
+                                             ("fr_S10_eta1", 10, 1.0, 1.0), ("fr_S10_cfg3", 10, 0.0, 3.0)])
+def test_ddim_trajectory_fr_vs_reference_golden(tag, S, eta, scale, precision, golden_traj):
+    model = handle_for(O.TINY_UNET, precision)
+    x_T = torch.from_numpy(golden_traj["traj/x_T"]).cuda()
+    ctx = torch.from_numpy(golden_traj["traj/ctx"]).cuda()
+    uc = torch.from_numpy(golden_traj["traj/uc"]).cuda()
+    # the reference drew its per-step noise from the CPU generator; feed the same draws through torch.randn
+    torch.manual_seed(1234)
+    noises = [torch.randn(x_T.shape) for _ in range(S)]
+    smp = P.DDIMSampler(model)
+    it = iter(noises)
+    orig = torch.randn
+    torch.randn = lambda *a, **k: next(it).to(k.get("device", "cpu"))
+    try:
+        samples, inter = smp.sample(S, batch_size=2, shape=[3, 8, 8], conditioning=ctx, eta=eta, x_T=x_T,
+                                    verbose=False, log_every_t=3, unconditional_guidance_scale=scale,
+                                    unconditional_conditioning=uc if scale != 1.0 else None)
+    finally:
+        torch.randn = orig
+    tol = TRAJ_TOL[precision]
+    assert O.rel_l2(samples, torch.from_numpy(golden_traj[f"traj/{tag}/samples"])) <= tol
+    assert O.rel_l2(torch.stack(inter["x_inter"]), torch.from_numpy(golden_traj[f"traj/{tag}/x_inter"])) <= tol
+    assert O.rel_l2(torch.stack(inter["pred_x0"]), torch.from_numpy(golden_traj[f"traj/{tag}/pred_x0"])) <= tol
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_ddim_trajectory_tf_two_cond_vs_reference_golden(precision, golden_traj):
+    cfg = dict(O.TINY_UNET, in_channels=9)
+    model = handle_for(cfg, precision, two_cond=True)
+    x_T = torch.from_numpy(golden_traj["traj/x_T"]).cuda()
+    cond = {"class_label_&_audio": torch.from_numpy(golden_traj["traj/ctx"]).cuda(),
+            "motion_&_id": torch.from_numpy(golden_traj["traj/c34"]).cuda()}
+    torch.manual_seed(1234)
+    noises = [torch.randn(x_T.shape) for _ in range(10)]
+    it = iter(noises)
+    orig = torch.randn
+    torch.randn = lambda *a, **k: next(it).to(k.get("device", "cpu"))
+    try:
+        samples, x_inter = P.DDIMSampler2Cond(model).sample(10, batch_size=2, shape=[3, 8, 8], conditioning=cond,
+                                                            eta=1.0, x_T=x_T, verbose=False, log_every_t=3)
+    finally:
+        torch.randn = orig
+    tol = TRAJ_TOL[precision]
+    assert isinstance(x_inter, list)
+    assert O.rel_l2(samples, torch.from_numpy(golden_traj["traj/tf_S10_eta1/samples"])) <= tol
+    assert O.rel_l2(torch.stack(x_inter), torch.from_numpy(golden_traj["traj/tf_S10_eta1/x_inter"])) <= tol
+
+
+def test_batch_sharding_is_result_invariant():
+    """Sampling shards the batch across GPUs: a sample's eps must not depend on its batch-mates."""
+    cfg = O.TINY_UNET
+    m = build(cfg, "bf16")
+    x, ctx = synth_inputs(cfg, 4, 8, 9)
+    t = torch.tensor([981, 981, 981, 981]).cuda()
+    with torch.no_grad():
+        full = m(x.cuda(), t, context=ctx.cuda())
+        halves = torch.cat([m(x[:2].cuda(), t[:2], context=ctx[:2].cuda()), m(x[2:].cuda(), t[2:], context=ctx[2:].cuda())])
+    assert torch.equal(full, halves)

@@ -27,3 +27,17 @@ def golden_schedule():
 @pytest.fixture(scope="session")
 def golden_traj():
     return np.load(os.path.join(GOLDEN, "trajectory.npz"))
+
+
+@pytest.fixture(scope="session")
+def golden_unet64():
+    return np.load(os.path.join(GOLDEN, "unet64.npz"))
+
+
+def record_parity(key, value):
+    """Appends one measured parity figure to gpurun_out/parity_report.jsonl (kept as evidence under profiles/)."""
+    import json
+    d = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(d, exist_ok=True)
+    with open(os.path.join(d, "parity_report.jsonl"), "a") as f:
+        f.write(json.dumps({"key": key, "value": value}) + "\n")

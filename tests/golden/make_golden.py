@@ -74,6 +74,21 @@ def unet_goldens():
     return out
 
 
+def unet64_goldens():
+    """BASELINE configs 1-3 run 64x64 latents: one eval of the real FR / TF UNets at that size (B=1)."""
+    out = {}
+    for name, cfg, flavour, B, hw, cl, tsteps in [("fr_64", O.FR_UNET, "face_reenactment", 1, 64, 1, [981, 21]),
+                                                  ("tf_64", O.TF_UNET, "talking_face", 1, 64, 1, [501])]:
+        sd = O.init_state_dict(cfg, seed=0)
+        ref = R.reference_unet(cfg, flavour).eval()
+        ref.load_state_dict(sd, strict=True)
+        x, ctx = synth_inputs(cfg, B, hw, seed=1, ctx_len=cl)
+        for t in tsteps:
+            with torch.no_grad():
+                out[f"{name}/eps_t{t}"] = ref(x, torch.tensor([t] * B, dtype=torch.long), context=ctx).numpy()
+    return out
+
+
 def schedule_goldens():
     out = {}
     R.import_reference("face_reenactment")
@@ -150,8 +165,11 @@ def trajectory_goldens():
 
 def main():
     torch.set_num_threads(max(1, os.cpu_count() or 1))
+    only = sys.argv[1:]
     for fn, gen in (("unet.npz", unet_goldens), ("schedule.npz", schedule_goldens),
-                    ("trajectory.npz", trajectory_goldens)):
+                    ("trajectory.npz", trajectory_goldens), ("unet64.npz", unet64_goldens)):
+        if only and fn not in only:
+            continue
         data = gen()
         path = os.path.join(HERE, fn)
         np.savez_compressed(path, **data)

@@ -39,6 +39,15 @@ def test_unet_eps_matches_reference_golden(name, golden_unet):
     assert O.rel_l2(O.unet_forward(sd, cfg, x, tm, ctx), torch.from_numpy(golden_unet[f"{name}/eps_tmixed"])) <= 2e-6
 
 
+@pytest.mark.parametrize("name,cfg,t", [("fr_64", O.FR_UNET, 981), ("tf_64", O.TF_UNET, 501)])
+def test_unet_eps_64_matches_reference_golden(name, cfg, t, golden_unet64):
+    """BASELINE's 64x64 latent size: one eval of the full-size UNets (a few seconds on CPU)."""
+    sd = O.init_state_dict(cfg, 0)
+    x, ctx = synth_inputs(cfg, 1, 64, 1, 1)
+    eps = O.unet_forward(sd, cfg, x, torch.tensor([t]), ctx)
+    assert O.rel_l2(eps, torch.from_numpy(golden_unet64[f"{name}/eps_t{t}"])) <= 2e-6
+
+
 def test_param_inventory_is_626():
     # SURVEY Appendix C: 626 tensors, 156.76 M (FR) / 163.16 M (TF) parameters
     for cfg, n in ((O.FR_UNET, 156_760_483), (O.TF_UNET, None)):

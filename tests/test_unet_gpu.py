@@ -13,6 +13,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 import dsml_thesis_b200 as P  # noqa: E402
+from conftest import record_parity  # noqa: E402
 from oracle import ldm_oracle as O  # noqa: E402
 
 TOL = {"fp32": 1e-4, "bf16": 1e-2}
@@ -59,10 +60,25 @@ def test_unet_eps_vs_reference_golden(name, precision, golden_unet):
             eps = m(x.cuda(), torch.tensor([t] * B).cuda(), context=ctx.cuda())
             assert eps.shape == x[:, :3].shape and eps.dtype == torch.float32
             err = O.rel_l2(eps, torch.from_numpy(golden_unet[f"{name}/eps_t{t}"]))
+            record_parity(f"eps/{name}/t{t}/{precision}", err)
             assert err <= TOL[precision], (name, t, err)
         tm = torch.from_numpy(golden_unet[f"{name}/tmixed"])
         err = O.rel_l2(m(x.cuda(), tm.cuda(), context=ctx.cuda()), torch.from_numpy(golden_unet[f"{name}/eps_tmixed"]))
         assert err <= TOL[precision], (name, "tmixed", err)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("name,cfg,tsteps", [("fr_64", O.FR_UNET, [981, 21]), ("tf_64", O.TF_UNET, [501])])
+def test_unet_eps_64_vs_reference_golden(name, cfg, tsteps, precision, golden_unet64):
+    """The latent size BASELINE.json quotes (64x64x3), full-size FR / TF UNets, vs the real reference's eps."""
+    m = build(cfg, precision)
+    x, ctx = synth_inputs(cfg, 1, 64, 1, 1)
+    with torch.no_grad():
+        for t in tsteps:
+            eps = m(x.cuda(), torch.tensor([t]).cuda(), context=ctx.cuda())
+            err = O.rel_l2(eps, torch.from_numpy(golden_unet64[f"{name}/eps_t{t}"]))
+            record_parity(f"eps/{name}/t{t}/{precision}", err)
+            assert err <= TOL[precision], (name, t, err)
 
 
 @pytest.mark.parametrize("precision", ["fp32", "bf16"])

@@ -276,7 +276,7 @@ def main():
         plan.run_timed(torch.cuda.current_stream())
         per_op = plan.run_timed(torch.cuda.current_stream())
     fam = {}
-    for name, t_ms, fl, by in per_op:
+    for name, t_ms, fl, by, _what in per_op:
         f = fam.setdefault(name, [0.0, 0.0, 0.0, 0])
         f[0] += t_ms
         f[1] += fl

@@ -1,6 +1,8 @@
 // HBM-bound kernels of the denoising path: fused DDIM update (K13), timestep embedding + small dense layers
 // (K12), GroupNorm+SiLU over (virtually concatenated) channels-last maps (K7/K11), LayerNorm (K9), layout
 // changes, and the one-launch weight packer for the tensor-core path.
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace ldm {
@@ -114,7 +116,7 @@ __global__ void __launch_bounds__(SL_WARPS * 32) small_linear_kernel(const float
   __shared__ float tile[SL_RT][SL_KC];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = (blockIdx.x * SL_WARPS + warp) * SL_NPW;
-  for (int r0 = 0; r0 < rows; r0 += SL_RT) {
+  for (int r0 = blockIdx.y * SL_RT; r0 < rows; r0 += gridDim.y * SL_RT) {
     float acc[SL_NPW][SL_RT];
 #pragma unroll
     for (int j = 0; j < SL_NPW; ++j)
@@ -453,7 +455,7 @@ int ldmb200_timestep_embedding(const int64_t* t, float* out, int batch, int dim,
 int ldmb200_small_linear(const float* in, int in_ld, const float* w, const float* bias, float* out, int out_ld,
                          int rows, int k, int n, int silu_in, void* stream) {
   LDM_CHECK_ARG(in && w && out && rows > 0 && k > 0 && n > 0, "small_linear: bad arguments");
-  int blocks = ceil_div(n, SL_WARPS * SL_NPW);
+  dim3 blocks(ceil_div(n, SL_WARPS * SL_NPW), std::min(ceil_div(rows, SL_RT), 64));
   small_linear_kernel<<<blocks, SL_WARPS * 32, 0, (cudaStream_t)stream>>>(in, in_ld, w, bias, out, out_ld, rows, k,
                                                                           n, silu_in);
   LDM_CHECK_LAUNCH("small_linear");

@@ -326,11 +326,11 @@ class _Plan:
             if a is not None and id(a) not in self.pinned:
                 self.arena.release(a.buf)
 
-    def emit(self, name: str, *args, flops: float = 0.0, bytes_: float = 0.0):
+    def emit(self, name: str, *args, flops: float = 0.0, bytes_: float = 0.0, what: str = ""):
         """Appends one launch.  ``flops`` / ``bytes_`` are the ALGORITHMIC work of the launch (no padding, no
         re-reads) used by ``bench.py`` for the roofline; they do not influence execution."""
         self.ops.append((getattr(self.lib, name), args, name))
-        self.meta.append((name, float(flops), float(bytes_)))
+        self.meta.append((name, float(flops), float(bytes_), what))
 
     def view_f32(self, a: _Act) -> torch.Tensor:
         return a.buf.t[: a.rows * a.c * 4].view(torch.float32).view(a.rows, a.c)
@@ -340,7 +340,8 @@ class _Plan:
         n, k = lin.weight.shape
         o = self.new(rows, n, F32)
         self.emit("ldmb200_small_linear", in_ptr, in_ld, lin.weight.data_ptr(),
-                  lin.bias.data_ptr() if lin.bias is not None else None, o.ptr, n, rows, k, n, silu_in)
+                  lin.bias.data_ptr() if lin.bias is not None else None, o.ptr, n, rows, k, n, silu_in,
+                  what=f"R{rows} K{k} N{n}")
         return o
 
     def groupnorm(self, x1: _Act, x2: Optional[_Act], gn: nn.GroupNorm, hw: int, silu: int, want_raw: bool):
@@ -351,13 +352,14 @@ class _Plan:
                   x2.c if x2 is not None else 0, gn.weight.data_ptr(), gn.bias.data_ptr(), y.ptr,
                   raw.ptr if raw is not None else None, self.act, self.B, hw, gn.num_groups, float(gn.eps), silu,
                   self.gn_ws.data_ptr(),
-                  bytes_=x1.rows * c * (4 + (2 if self.tc else 4) * (2 if want_raw else 1)))
+                  bytes_=x1.rows * c * (4 + (2 if self.tc else 4) * (2 if want_raw else 1)),
+                  what=f"rows{x1.rows} C{c}" + (" cat" if x2 is not None else "") + (" raw" if want_raw else ""))
         return y, raw
 
     def layernorm(self, x: _Act, ln: nn.LayerNorm) -> _Act:
         y = self.new(x.rows, x.c, self.act)
         self.emit("ldmb200_layernorm", x.ptr, ln.weight.data_ptr(), ln.bias.data_ptr(), y.ptr, self.act, x.rows, x.c,
-                  float(ln.eps), bytes_=x.rows * x.c * (4 + (2 if self.tc else 4)))
+                  float(ln.eps), bytes_=x.rows * x.c * (4 + (2 if self.tc else 4)), what=f"rows{x.rows} C{x.c}")
         return y
 
     def gemm(self, a: _Act, key: str, weight: torch.Tensor, bias: Optional[torch.Tensor], h_in: int, w_in: int,
@@ -401,7 +403,9 @@ class _Plan:
             d.out, d.out_dtype, d.out_ld, d.out_nchw, d.n_valid = res.ptr, out_dtype, n_cols, 0, n_cols
         self.keep.append(d)
         k_true = weight.shape[1] * ksize * ksize if weight.dim() >= 2 and n_true == weight.shape[0] else a.c
-        self.emit("ldmb200_igemm_tc" if tc else "ldmb200_igemm_simt", C.byref(d), flops=2.0 * rows * n_true * k_true)
+        self.emit("ldmb200_igemm_tc" if tc else "ldmb200_igemm_simt", C.byref(d), flops=2.0 * rows * n_true * k_true,
+                  what=f"M{rows} N{n_true} K{k_true} ks{ksize} s{stride}" + (" geglu" if geglu else "")
+                  + (" res" if residual is not None else "") + (" bf16out" if out_dtype == BF16 else ""))
         return res
 
     # ---- blocks ------------------------------------------------------------------------
@@ -450,7 +454,7 @@ class _Plan:
         o = self.new(t0.rows, Cc, self.act)
         if self.tc:
             self.emit("ldmb200_attention_tc", qkv.ptr, 3 * Cc, 0, Cc, 2 * Cc, o.ptr, Cc, B, heads, hw, scale,
-                      flops=4.0 * B * heads * hw * hw * dh)
+                      flops=4.0 * B * heads * hw * hw * dh, what=f"B{B} h{heads} N{hw}")
         else:
             self.emit("ldmb200_attention_simt", qkv.ptr, 3 * Cc, 0, qkv.ptr, Cc, qkv.ptr, 2 * Cc, 3 * Cc, o.ptr, Cc, B,
                       heads, hw, hw, scale, flops=4.0 * B * heads * hw * hw * dh)
@@ -606,7 +610,7 @@ class _Plan:
                 _cabi.check(rc, name)
             evs.append((e0, e1))
         stream_obj.synchronize()
-        return [(m[0], e0.elapsed_time(e1), m[1], m[2]) for m, (e0, e1) in zip(self.meta, evs)]
+        return [(m[0], e0.elapsed_time(e1), m[1], m[2], m[3]) for m, (e0, e1) in zip(self.meta, evs)]
 
     def run(self, stream: int):
         py = self.py_ops

@@ -10,7 +10,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 
-F32, BF16 = 0, 1
+F32, BF16, F16 = 0, 1, 2
 ABI_VERSION = 1
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -48,6 +48,17 @@ class PackJob(C.Structure):
         ("n", C.c_int32), ("c", C.c_int32), ("ksize", C.c_int32),
         ("n_pad", C.c_int32), ("c_pad", C.c_int32),
         ("row_offset", C.c_int32), ("block_n", C.c_int32),
+        ("dst_dtype", C.c_int32), ("pad_", C.c_int32),
+    ]
+
+
+class LinearJob(C.Structure):
+    """``ldmb200_linear_job`` (include/ldmb200.h)."""
+    _fields_ = [
+        ("in_", C.c_void_p), ("w", C.c_void_p), ("bias", C.c_void_p), ("out", C.c_void_p),
+        ("in_ld", C.c_int32), ("out_ld", C.c_int32),
+        ("rows", C.c_int32), ("k", C.c_int32), ("n", C.c_int32),
+        ("silu_in", C.c_int32), ("first_block", C.c_int32), ("pad_", C.c_int32),
     ]
 
 
@@ -60,6 +71,8 @@ SIGNATURES = {
     "ldmb200_ddim_step": (_i, [_p, _p, _p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _f, _p]),
     "ldmb200_timestep_embedding": (_i, [_p, _p, _i, _i, _f, _p]),
     "ldmb200_small_linear": (_i, [_p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
+    "ldmb200_small_linear_blocks": (_i, [_i, _i]),
+    "ldmb200_small_linear_batched": (_i, [_p, _i, _i, _p]),
     "ldmb200_nchw_to_nhwc": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "ldmb200_nhwc_to_nchw": (_i, [_p, _i, _p, _i, _i, _i, _p]),
     "ldmb200_groupnorm_ws_floats": (_i64, [_i, _i, _i]),
@@ -71,7 +84,7 @@ SIGNATURES = {
     "ldmb200_igemm_tc": (_i, [C.POINTER(GemmDesc), _p]),
     "ldmb200_pack_weights": (_i, [_p, _i, _p]),
     "ldmb200_attention_simt": (_i, [_p, _i, _i, _p, _i, _p, _i, _i, _p, _i, _i, _i, _i, _i, _f, _p]),
-    "ldmb200_attention_tc": (_i, [_p, _i, _i, _i, _i, _p, _i, _i, _i, _i, _f, _p]),
+    "ldmb200_attention_tc": (_i, [_p, _i, _i, _i, _i, _p, _i, _i, _i, _i, _i, _f, _p]),
 }
 
 _lib = None

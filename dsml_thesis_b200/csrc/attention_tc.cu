@@ -1,31 +1,55 @@
 // Fused flash-style self-attention for d_head = 32 on tcgen05 (K5): softmax(q k^T * scale) v per (sample, head)
 // without materialising the [N, N] score matrix the reference builds (attention.py:180-191).
 //
-// One CTA per (128-query tile, head, sample); 2 CTAs per SM so one CTA's softmax (MUFU-bound: one exp per
-// score vs 128 tensor flops) hides the other's MMA/TMA latency.
-//   warp 4 : TMA producer  — Q tile once, then K/V tiles (128 keys x 32) double-buffered, all from the fused
-//            QKV matrix [B*N, 3C] through one 2-D tensor map (64B-swizzled K-major rows of 32 bf16)
-//   warp 5 : MMA issuer    — S = Q K^T (M128 N128 K32) into TMEM cols [0,128); O_j = P V (M128 N32 K128, V as
-//            MN-major B operand straight from the row-major tile) into TMEM cols [128,160)
-//   warps 0-3 : softmax    — thread r owns query row r: two passes over S in TMEM (row max, then exp2 + row
-//            sum), P written as bf16 into a 128B-swizzled K-major smem tile for the PV MMA; the running
-//            output lives in registers (32 fp32) and is rescaled online.
+// The op is MUFU-bound, not tensor-bound: every score needs one ex2 (16/clk/SM) but only 128 tensor flops, so
+// the design goal is to keep the exponent pipe busy all the time.  One CTA per (256-query block, head, sample),
+// one CTA per SM, two 128-query tiles per CTA that ping-pong: while warpgroup 0 runs the softmax of its tile,
+// the tensor pipe computes the scores / P.V of the other tile, and K/V tiles are shared by both.
+//   warps 0-3 : softmax warpgroup of query tile 0     (thread r <-> query row r <-> TMEM lane r)
+//   warps 4-7 : softmax warpgroup of query tile 1
+//   warp  8   : TMA producer — both Q tiles once, then K/V tiles (128 keys x 32) through a 3-stage ring, all from
+//               the fused QKV matrix [B*N, 3C] through one 2-D tensor map (64B-swizzled K-major rows of 32 x 16 bit)
+//   warp  9   : MMA issuer   — S_q = Q_q K^T (M128 N128 K32) into TMEM cols [128q, 128q+128);
+//               O_q = P_q V (M128 N32 K128, V as MN-major B operand straight from the row-major tile) into
+//               TMEM cols [256+32q, +32).  Issue order per KV tile j:  PV0(j) S0(j+1) | PV1(j) S1(j+1)
+// Softmax: two passes over S in TMEM with the next 32-column chunk prefetched (row max with 3-input max on
+// 4 independent chains, then ex2 + row sum on 4 chains); P is written as bf16 into a 128B-swizzled K-major smem
+// tile for the PV MMA; the running output lives in registers (32 fp32) and is rescaled online.
 #include <algorithm>
 
 #include "common.cuh"
 
 namespace ldm {
 
-constexpr int AT_THREADS = 192;
-constexpr int AT_TILE_BYTES = 128 * 32 * 2;  // 8 KiB: 128 rows x 32 bf16
+constexpr int AT_THREADS = 320;
+constexpr int AT_STAGES = 3;
+constexpr int AT_TILE_BYTES = 128 * 32 * 2;  // 8 KiB: 128 rows x 32 16-bit values
 constexpr int AT_P_BYTES = 2 * 128 * 128;    // two K-major chunks of [128 x 64] bf16, 128B swizzle
-constexpr int AT_SMEM = AT_TILE_BYTES * 5 + AT_P_BYTES + 16 * 8 + 16 + 1024;
-constexpr int AT_TMEM_COLS = 256;
+constexpr int AT_SMEM = 2 * AT_TILE_BYTES + 2 * AT_STAGES * AT_TILE_BYTES + 2 * AT_P_BYTES + 16 * 8 + 16 + 1024;
+constexpr int AT_TMEM_COLS = 512;
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float y;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(y) : "f"(a), "f"(b), "f"(c));
+  return y;
+}
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ uint32_t pack_out16(float lo, float hi, int dt) {
+  uint32_t r;
+  if (dt == LDMB200_F16)
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  else
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
 }
 
 // MN-major B operand (V tile: rows = keys (K dim), 32 contiguous d = N dim), 64B swizzle:
@@ -40,40 +64,141 @@ __device__ __forceinline__ uint64_t umma_desc_mnmajor_sw64(uint32_t smem_addr) {
   return d;
 }
 
-__global__ void __launch_bounds__(AT_THREADS, 2)
-attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __restrict__ out, int out_ld, int n_tok,
-                    int q_off, int k_off, int v_off, float scale_log2e) {
+// row max of one 32-column chunk on 4 independent chains; MASK: columns >= valid are ignored
+template <bool MASK>
+__device__ __forceinline__ void chunk_max(const float (&v)[32], float (&mx)[4], int col0, int valid) {
+  if (MASK) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      if (col0 + i < valid) mx[i & 3] = fmaxf(mx[i & 3], v[i]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 32; i += 8) {
+      mx[0] = fmax3(mx[0], v[i], v[i + 1]);
+      mx[1] = fmax3(mx[1], v[i + 2], v[i + 3]);
+      mx[2] = fmax3(mx[2], v[i + 4], v[i + 5]);
+      mx[3] = fmax3(mx[3], v[i + 6], v[i + 7]);
+    }
+  }
+}
+
+// p = exp2(s*c - mb) for one 32-column chunk, row sum on 4 chains, bf16 pack and swizzled store of the
+// thread's 64 bytes: chunk c of the row -> 64-key half (c>>1), 16-byte units (c&1)*4 .. +3
+template <bool MASK>
+__device__ __forceinline__ void chunk_exp_store(const float (&v)[32], float (&ls)[4], float c_, float mb, int c,
+                                                int valid, uint8_t* sP, int r) {
+  uint8_t* rowp = sP + (c >> 1) * (128 * 128) + r * 128;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {  // 8 columns -> one 16-byte unit
+    uint32_t pk[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int i = u * 8 + e * 2;
+      float p0 = ex2_approx(fmaf(v[i], c_, -mb));
+      float p1 = ex2_approx(fmaf(v[i + 1], c_, -mb));
+      if (MASK) {
+        if (c * 32 + i >= valid) p0 = 0.f;
+        if (c * 32 + i + 1 >= valid) p1 = 0.f;
+      }
+      ls[e] += p0 + p1;
+      pk[e] = pack_bf16x2(p0, p1);
+    }
+    const int unit = (c & 1) * 4 + u;
+    *reinterpret_cast<uint4*>(rowp + ((unit ^ (r & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+  }
+}
+
+// tcgen05.wait::ld that also names the destination registers of the load it completes, so the compiler cannot
+// schedule a use of them above the wait (the asynchronous write is invisible to it otherwise)
+#define LDM_R8(v, o) "+f"(v[o]), "+f"(v[o + 1]), "+f"(v[o + 2]), "+f"(v[o + 3]), "+f"(v[o + 4]), "+f"(v[o + 5]), "+f"(v[o + 6]), "+f"(v[o + 7])
+__device__ __forceinline__ void tmem_wait_regs(float (&v)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : LDM_R8(v, 0), LDM_R8(v, 8), LDM_R8(v, 16), LDM_R8(v, 24)::"memory");
+}
+__device__ __forceinline__ void reg_fence(float (&v)[32]) {
+  asm volatile("" : LDM_R8(v, 0), LDM_R8(v, 8), LDM_R8(v, 16), LDM_R8(v, 24)::"memory");
+}
+
+// One KV tile of the online softmax for query row r: reads S (128 fp32 columns at tS) twice, folds the previous
+// tile's P.V (32 columns at tO) into the running output, writes P (bf16) to the swizzled smem tile.
+template <bool MASK>
+__device__ __forceinline__ void softmax_tile(uint32_t tS, uint32_t tO, bool have_prev, int valid, float c_, float& m,
+                                             float& l, float (&o)[32], uint8_t* sP, int r) {
+  float a[32], b[32];
+  float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  // ---- pass 1: row max, next chunk in flight while the current one is reduced
+  tmem_ld_32x32(tS, a);
+  tmem_wait_regs(a);
+  tmem_ld_32x32(tS + 32, b);
+  chunk_max<MASK>(a, mx, 0, valid);
+  tmem_wait_regs(b);
+  tmem_ld_32x32(tS + 64, a);
+  chunk_max<MASK>(b, mx, 32, valid);
+  tmem_wait_regs(a);
+  tmem_ld_32x32(tS + 96, b);
+  chunk_max<MASK>(a, mx, 64, valid);
+  tmem_wait_regs(b);
+  chunk_max<MASK>(b, mx, 96, valid);
+  if (have_prev) tmem_ld_32x32(tO, b);  // previous tile's P.V (b is free again)
+  tmem_ld_32x32(tS, a);
+  const float m_new = fmaxf(m, fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])));
+  const float corr = ex2_approx((m - m_new) * c_);  // m = -inf on the first tile -> 0
+  const float mb = m_new * c_;
+  m = m_new;
+  tmem_wait_regs(a);
+  if (have_prev) {
+    reg_fence(b);
+#pragma unroll
+    for (int d = 0; d < 32; ++d) o[d] = (o[d] + b[d]) * corr;
+  }
+  // ---- pass 2: p = exp2(s*c - m*c), row sum, bf16 P tile
+  float ls[4] = {0.f, 0.f, 0.f, 0.f};
+  tmem_ld_32x32(tS + 32, b);
+  chunk_exp_store<MASK>(a, ls, c_, mb, 0, valid, sP, r);
+  tmem_wait_regs(b);
+  tmem_ld_32x32(tS + 64, a);
+  chunk_exp_store<MASK>(b, ls, c_, mb, 1, valid, sP, r);
+  tmem_wait_regs(a);
+  tmem_ld_32x32(tS + 96, b);
+  chunk_exp_store<MASK>(a, ls, c_, mb, 2, valid, sP, r);
+  tmem_wait_regs(b);
+  chunk_exp_store<MASK>(b, ls, c_, mb, 3, valid, sP, r);
+  l = l * corr + ((ls[0] + ls[1]) + (ls[2] + ls[3]));
+}
+
+__global__ void __launch_bounds__(AT_THREADS, 1)
+attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict__ out, int out_ld, int out_dtype,
+                    int n_tok, int q_off, int k_off, int v_off, float scale_log2e) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* sQ = smem;
-  uint8_t* sK = sQ + AT_TILE_BYTES;       // 2 stages
-  uint8_t* sV = sK + 2 * AT_TILE_BYTES;   // 2 stages
-  uint8_t* sP = sV + 2 * AT_TILE_BYTES;   // 32 KiB, 1024-aligned (5 * 8 KiB offset)
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + AT_P_BYTES);
+  uint8_t* sQ = smem;                               // 2 tiles (256 rows), one TMA box
+  uint8_t* sK = sQ + 2 * AT_TILE_BYTES;             // AT_STAGES tiles
+  uint8_t* sV = sK + AT_STAGES * AT_TILE_BYTES;     // AT_STAGES tiles
+  uint8_t* sP = sV + AT_STAGES * AT_TILE_BYTES;     // 2 x 32 KiB, 1024-aligned (8 x 8 KiB offset)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * AT_P_BYTES);
   uint64_t* q_full = bars;
-  uint64_t* kv_full = bars + 1;   // [2]
-  uint64_t* kv_empty = bars + 3;  // [2]
-  uint64_t* s_full = bars + 5;
-  uint64_t* p_full = bars + 6;
-  uint64_t* o_full = bars + 7;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* kv_full = bars + 1;                     // [AT_STAGES]
+  uint64_t* kv_empty = kv_full + AT_STAGES;         // [AT_STAGES]
+  uint64_t* s_full = kv_empty + AT_STAGES;          // [2]  S_q(j) ready (and everything issued before it: P.V(j-1))
+  uint64_t* p_full = s_full + 2;                    // [2]  P_q(j) written, S_q(j) and O_q(j-1) consumed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_full + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
-  const int n_kv_tiles = (n_tok + 127) / 128;
+  const int qb = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int n_kv = (n_tok + 127) / 128;
   const int row_base = b * n_tok;  // first row of this sample in the [B*N, ld] matrix
 
-  if (warp == 4 && lane == 0) prefetch_tmap(&tm);
-  if (warp == 5) {
+  if (warp == 8 && lane == 0) prefetch_tmap(&tm);
+  if (warp == 9) {
     if (lane == 0) {
       mbar_init(q_full, 1);
-      for (int s = 0; s < 2; ++s) {
+      for (int s = 0; s < AT_STAGES; ++s) {
         mbar_init(&kv_full[s], 1);
         mbar_init(&kv_empty[s], 1);
       }
-      mbar_init(s_full, 1);
-      mbar_init(p_full, 128);
-      mbar_init(o_full, 1);
+      for (int q = 0; q < 2; ++q) {
+        mbar_init(&s_full[q], 1);
+        mbar_init(&p_full[q], 128);
+      }
       fence_mbar_init();
     }
     __syncwarp();
@@ -83,132 +208,109 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_S = tmem_base, tmem_O = tmem_base + 128;
 
-  if (warp == 4) {
+  if (warp == 8) {
+    // ===================== TMA producer =====================
     if (lane == 0) {
-      mbar_expect_tx(q_full, AT_TILE_BYTES);
-      tma_load_2d(sQ, &tm, q_full, q_off + h * 32, row_base + qt * 128);
-      for (int j = 0; j < n_kv_tiles; ++j) {
-        const int s = j & 1;
-        mbar_wait(&kv_empty[s], ((j >> 1) & 1) ^ 1);
+      mbar_expect_tx(q_full, 2 * AT_TILE_BYTES);
+      tma_load_2d(sQ, &tm, q_full, q_off + h * 32, row_base + qb * 256);
+      tma_load_2d(sQ + AT_TILE_BYTES, &tm, q_full, q_off + h * 32, row_base + qb * 256 + 128);
+      for (int j = 0; j < n_kv; ++j) {
+        const int s = j % AT_STAGES;
+        mbar_wait(&kv_empty[s], ((j / AT_STAGES) & 1) ^ 1);
         mbar_expect_tx(&kv_full[s], 2 * AT_TILE_BYTES);
         tma_load_2d(sK + s * AT_TILE_BYTES, &tm, &kv_full[s], k_off + h * 32, row_base + j * 128);
         tma_load_2d(sV + s * AT_TILE_BYTES, &tm, &kv_full[s], v_off + h * 32, row_base + j * 128);
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
+    // ===================== MMA issuer =====================
     if (lane == 0) {
       constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 128, 0, 0);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 32, 0, 1);  // B = V is MN-major
-      mbar_wait(q_full, 0);
       const uint32_t q_addr = smem_u32(sQ), p_addr = smem_u32(sP);
-      for (int j = 0; j < n_kv_tiles; ++j) {
-        const int s = j & 1;
-        mbar_wait(&kv_full[s], (j >> 1) & 1);
-        tc_fence_after();
-        const uint32_t k_addr = smem_u32(sK + s * AT_TILE_BYTES), v_addr = smem_u32(sV + s * AT_TILE_BYTES);
+      auto issue_s = [&](int q, int s) {
+        const uint32_t k_addr = smem_u32(sK + s * AT_TILE_BYTES);
 #pragma unroll
         for (int kk = 0; kk < 2; ++kk)
-          umma_bf16_ss(tmem_S, umma_desc_kmajor(q_addr + kk * 32, 64), umma_desc_kmajor(k_addr + kk * 32, 64), idesc_qk,
-                       kk > 0);
-        umma_commit(s_full);
-        mbar_wait(p_full, j & 1);
-        tc_fence_after();
+          umma_bf16_ss(tmem_base + q * 128, umma_desc_kmajor(q_addr + q * AT_TILE_BYTES + kk * 32, 64),
+                       umma_desc_kmajor(k_addr + kk * 32, 64), idesc_qk, kk > 0);
+      };
+      auto issue_pv = [&](int q, int s) {
+        const uint32_t v_addr = smem_u32(sV + s * AT_TILE_BYTES);
 #pragma unroll
         for (int t = 0; t < 8; ++t)
-          umma_bf16_ss(tmem_O, umma_desc_kmajor(p_addr + (t >> 2) * (128 * 128) + (t & 3) * 32, 128),
+          umma_bf16_ss(tmem_base + 256 + q * 32,
+                       umma_desc_kmajor(p_addr + q * AT_P_BYTES + (t >> 2) * (128 * 128) + (t & 3) * 32, 128),
                        umma_desc_mnmajor_sw64(v_addr + t * 1024), idesc_pv, t > 0);
-        umma_commit(&kv_empty[s]);
-        if (j == n_kv_tiles - 1) umma_commit(o_full);
+      };
+      mbar_wait(q_full, 0);
+      mbar_wait(&kv_full[0], 0);
+      tc_fence_after();
+      issue_s(0, 0);
+      umma_commit(&s_full[0]);
+      issue_s(1, 0);
+      umma_commit(&s_full[1]);
+      for (int j = 0; j < n_kv; ++j) {
+        const int s = j % AT_STAGES, sn = (j + 1) % AT_STAGES;
+        const bool more = j + 1 < n_kv;
+        mbar_wait(&p_full[0], j & 1);
+        tc_fence_after();
+        issue_pv(0, s);
+        if (more) {
+          mbar_wait(&kv_full[sn], ((j + 1) / AT_STAGES) & 1);
+          tc_fence_after();
+          issue_s(0, sn);
+        }
+        umma_commit(&s_full[0]);
+        mbar_wait(&p_full[1], j & 1);
+        tc_fence_after();
+        issue_pv(1, s);
+        umma_commit(&kv_empty[s]);  // K_j / V_j are dead once both P.V of tile j have retired
+        if (more) issue_s(1, sn);
+        umma_commit(&s_full[1]);
       }
     }
   } else {
-    // ===================== softmax warps: thread r <-> query row r =====================
-    const int r = threadIdx.x;  // 0..127 == TMEM lane
-    const uint32_t lane_sel = (uint32_t)(warp * 32) << 16;
+    // ===================== softmax warpgroups: thread r <-> query row r of tile q =====================
+    const int q = warp >> 2;
+    const int r = threadIdx.x & 127;  // == TMEM lane
+    const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
+    const uint32_t tS = tmem_base + lane_sel + q * 128, tO = tmem_base + lane_sel + 256 + q * 32;
+    uint8_t* myP = sP + q * AT_P_BYTES;
     float o[32];
 #pragma unroll
     for (int d = 0; d < 32; ++d) o[d] = 0.f;
     float m = -INFINITY, l = 0.f;
-    const bool ragged = (n_tok & 127) != 0;
-    for (int j = 0; j < n_kv_tiles; ++j) {
-      mbar_wait(s_full, j & 1);
+    const int last_valid = n_tok - (n_kv - 1) * 128;  // keys in the last tile (1..128)
+    for (int j = 0; j < n_kv; ++j) {
+      mbar_wait(&s_full[q], j & 1);
       tc_fence_after();
-      float tmp[32];
-      if (j > 0) {  // S_j complete implies P V of tile j-1 complete (in-order tensor pipe): fetch it
-        tmem_ld_32x32(tmem_O + lane_sel, tmp);
-      }
-      const int valid = ragged ? min(128, n_tok - j * 128) : 128;
-      // ---- pass 1: row max
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        float v[32];
-        tmem_ld_32x32(tmem_S + lane_sel + c * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i < valid) ? v[i] : -INFINITY);
-      }
-      const float m_new = fmaxf(m, mx);
-      const float corr = ex2_approx((m - m_new) * scale_log2e);  // m = -inf on the first tile -> 0
-      const float mb = m_new * scale_log2e;
-      l *= corr;
-      if (j > 0) {
-        tmem_ld_wait();
-#pragma unroll
-        for (int d = 0; d < 32; ++d) o[d] = (o[d] + tmp[d]) * corr;
-      }
-      // ---- pass 2: p = exp2(s*c - m*c), row sum, bf16 P tile (K-major, 128B swizzle)
-      float lsum = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        float v[32];
-        tmem_ld_32x32(tmem_S + lane_sel + c * 32, v);
-        tmem_ld_wait();
-        uint32_t pk[16];
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float p0 = (c * 32 + i < valid) ? ex2_approx(fmaf(v[i], scale_log2e, -mb)) : 0.f;
-          float p1 = (c * 32 + i + 1 < valid) ? ex2_approx(fmaf(v[i + 1], scale_log2e, -mb)) : 0.f;
-          lsum += p0 + p1;
-          __nv_bfloat162 t = __floats2bfloat162_rn(p0, p1);
-          pk[i >> 1] = *reinterpret_cast<uint32_t*>(&t);
-        }
-        // 32 keys = 64 B = 4 units of 16 B; chunk (c>>1) of 64 keys, units (c&1)*4 .. +3 of row r
-        uint8_t* rowp = sP + (c >> 1) * (128 * 128) + r * 128;
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int unit = (c & 1) * 4 + u;
-          *reinterpret_cast<uint4*>(rowp + ((unit ^ (r & 7)) << 4)) =
-              make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
-        }
-      }
-      l += lsum;
-      m = m_new;
+      if (j == n_kv - 1 && last_valid < 128)
+        softmax_tile<true>(tS, tO, j > 0, last_valid, scale_log2e, m, l, o, myP, r);
+      else
+        softmax_tile<false>(tS, tO, j > 0, 128, scale_log2e, m, l, o, myP, r);
       fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the UMMA (async proxy)
       tc_fence_before();
-      mbar_arrive(p_full);
+      mbar_arrive(&p_full[q]);
     }
-    mbar_wait(o_full, 0);
+    mbar_wait(&s_full[q], n_kv & 1);  // the commit after the last P.V
     tc_fence_after();
     {
       float tmp[32];
-      tmem_ld_32x32(tmem_O + lane_sel, tmp);
-      tmem_ld_wait();
+      tmem_ld_32x32(tO, tmp);
+      tmem_wait_regs(tmp);
       const float inv = 1.0f / l;
-      const int qi = qt * 128 + r;
+      const int qi = qb * 256 + q * 128 + r;
       if (qi < n_tok) {
-        __nv_bfloat16* op = out + (size_t)(row_base + qi) * out_ld + h * 32;
+        uint16_t* op = out + (size_t)(row_base + qi) * out_ld + h * 32;
 #pragma unroll
         for (int d = 0; d < 32; d += 8) {
           uint32_t w[4];
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            __nv_bfloat162 t = __floats2bfloat162_rn((o[d + 2 * e] + tmp[d + 2 * e]) * inv,
-                                                     (o[d + 2 * e + 1] + tmp[d + 2 * e + 1]) * inv);
-            w[e] = *reinterpret_cast<uint32_t*>(&t);
-          }
+          for (int e = 0; e < 4; ++e)
+            w[e] = pack_out16((o[d + 2 * e] + tmp[d + 2 * e]) * inv, (o[d + 2 * e + 1] + tmp[d + 2 * e + 1]) * inv,
+                              out_dtype);
           *reinterpret_cast<uint4*>(op + d) = make_uint4(w[0], w[1], w[2], w[3]);
         }
       }
@@ -217,7 +319,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) {
+  if (warp == 9) {
     tc_fence_after();
     tmem_dealloc(tmem_base, AT_TMEM_COLS);
   }
@@ -228,10 +330,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, __nv_bfloat16* __res
 using namespace ldm;
 
 extern "C" int ldmb200_attention_tc(const void* qkv, int ld, int q_off, int k_off, int v_off, void* out, int out_ld,
-                                    int batch, int heads, int n_tokens, float scale, void* stream) {
+                                    int out_dtype, int batch, int heads, int n_tokens, float scale, void* stream) {
   LDM_CHECK_ARG(qkv && out && batch > 0 && heads > 0 && n_tokens > 0, "attention_tc: bad arguments");
   LDM_CHECK_ARG(ld % 8 == 0 && out_ld % 8 == 0 && q_off % 8 == 0 && k_off % 8 == 0 && v_off % 8 == 0,
-                "attention_tc: leading dims / offsets must be multiples of 8 bf16 (16 bytes)");
+                "attention_tc: leading dims / offsets must be multiples of 8 elements (16 bytes)");
+  LDM_CHECK_ARG(out_dtype == LDMB200_BF16 || out_dtype == LDMB200_F16, "attention_tc: out_dtype must be bf16 or f16");
   LDM_CHECK_ARG(batch <= 65535 && heads <= 65535, "attention_tc: batch/heads exceed grid limits");
   LDM_CHECK_ARG((int64_t)batch * n_tokens < (1ll << 31), "attention_tc: too many rows");
   static bool attr_set = false;
@@ -249,10 +352,10 @@ extern "C" int ldmb200_attention_tc(const void* qkv, int ld, int q_off, int k_of
   uint32_t box[2] = {32, 128};
   int rc = make_tensor_map_bf16(&tm, qkv, 2, dims, str, box, 64);
   if (rc) return rc;
-  dim3 grid(ceil_div(n_tokens, 128), heads, batch);
+  dim3 grid(ceil_div(n_tokens, 256), heads, batch);
   const float scale_log2e = scale * 1.4426950408889634f;
-  attention_tc_kernel<<<grid, AT_THREADS, AT_SMEM, (cudaStream_t)stream>>>(tm, (__nv_bfloat16*)out, out_ld, n_tokens,
-                                                                           q_off, k_off, v_off, scale_log2e);
+  attention_tc_kernel<<<grid, AT_THREADS, AT_SMEM, (cudaStream_t)stream>>>(tm, (uint16_t*)out, out_ld, out_dtype,
+                                                                           n_tokens, q_off, k_off, v_off, scale_log2e);
   LDM_CHECK_LAUNCH("attention_tc");
   return 0;
 }

@@ -195,10 +195,13 @@ __device__ __forceinline__ uint64_t umma_desc_kmajor(uint32_t smem_addr, uint32_
   d |= layout << 61;                                       // swizzle mode        bits [61,64)
   return d;
 }
-// instruction descriptor for kind::f16, A/B bf16 (format 1), D fp32 (format 1)
+// instruction descriptor for kind::f16: A/B format fmt (0 = f16, 1 = bf16), D fp32 (format 1)
+__host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N, int fmt, int a_mn_major = 0, int b_mn_major = 0) {
+  return (1u << 4) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)a_mn_major << 15) |
+         ((uint32_t)b_mn_major << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, int a_mn_major = 0, int b_mn_major = 0) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
-         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+  return umma_idesc_f16(M, N, 1, a_mn_major, b_mn_major);
 }
 
 // ---- small math ----

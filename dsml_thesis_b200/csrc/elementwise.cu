@@ -3,6 +3,8 @@
 // changes, and the one-launch weight packer for the tensor-core path.
 #include <algorithm>
 
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace ldm {
@@ -25,6 +27,36 @@ struct Store4<__nv_bfloat16> {
     *reinterpret_cast<uint2*>(p) = u;
   }
 };
+
+template <>
+struct Store4<__half> {  // conversions saturate to +-65504 instead of overflowing to inf
+  static __device__ __forceinline__ void st(__half* p, float a, float b, float c, float d) {
+    uint2 u;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(u.x) : "f"(b), "f"(a));
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(u.y) : "f"(d), "f"(c));
+    *reinterpret_cast<uint2*>(p) = u;
+  }
+};
+__device__ __forceinline__ void cvt_store(float* p, float v) { *p = v; }
+__device__ __forceinline__ void cvt_store(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+__device__ __forceinline__ void cvt_store(__half* p, float v) {
+  *p = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
+}
+
+// launches `call` with T = the C type of an LDMB200_* dtype code
+#define LDM_DISPATCH_DTYPE(dt, call)                   \
+  do {                                                 \
+    if ((dt) == LDMB200_BF16) {                        \
+      using T = __nv_bfloat16;                         \
+      call;                                            \
+    } else if ((dt) == LDMB200_F16) {                  \
+      using T = __half;                                \
+      call;                                            \
+    } else {                                           \
+      using T = float;                                 \
+      call;                                            \
+    }                                                  \
+  } while (0)
 
 // ---------------------------------------------------------------------------------------------
 // K13 DDIM update.  Each product/sum is a separate rounded fp32 op (no FMA contraction) so the result
@@ -103,59 +135,83 @@ __global__ void timestep_embedding_kernel(const int64_t* __restrict__ t, float* 
 }
 
 // ---------------------------------------------------------------------------------------------
-// small dense layer on per-sample vectors (fp32).  Block: 8 warps x 4 outputs; rows in chunks of 16;
-// act(in) staged once per block in shared memory.
+// small dense layers on per-sample vectors (fp32 FMA, exact-parity path): out = act(in) W^T + bias.
+// Block = 256 threads, output tile 64 rows x 32 columns, K in chunks of 32 staged in shared memory with the
+// next chunk prefetched into registers; thread (ty, tx) owns rows 4ty..4ty+3, columns 2tx..2tx+1.
+// One launch serves a whole table of independent layers (all ResBlock emb projections of a UNet eval, or all
+// cross-attention value projections): block -> job by the job's first block index.
 // ---------------------------------------------------------------------------------------------
-constexpr int SL_RT = 16, SL_KC = 256, SL_NPW = 4, SL_WARPS = 8;
+constexpr int SL_BM = 64, SL_BN = 32, SL_BK = 32, SL_XP = 68, SL_WP = 34;
 
-__global__ void __launch_bounds__(SL_WARPS * 32) small_linear_kernel(const float* __restrict__ in, int in_ld,
-                                                                     const float* __restrict__ w,
-                                                                     const float* __restrict__ bias,
-                                                                     float* __restrict__ out, int out_ld, int rows,
-                                                                     int K, int N, int silu_in) {
-  __shared__ float tile[SL_RT][SL_KC];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = (blockIdx.x * SL_WARPS + warp) * SL_NPW;
-  for (int r0 = blockIdx.y * SL_RT; r0 < rows; r0 += gridDim.y * SL_RT) {
-    float acc[SL_NPW][SL_RT];
+__device__ __forceinline__ void small_linear_tile(const ldmb200_linear_job& j, int blk) {
+  __shared__ __align__(16) float xs[SL_BK][SL_XP];
+  __shared__ __align__(16) float ws[SL_BK][SL_WP];
+  const int nb = (j.n + SL_BN - 1) / SL_BN;
+  const int r0 = (blk / nb) * SL_BM, n0 = (blk % nb) * SL_BN;
+  const int tid = threadIdx.x, lk = tid & 31, lr = tid >> 5;  // loader: k = lk, rows / columns lr + 8i
+  const int ty = tid >> 4, tx = tid & 15;
+  float acc[4][2] = {};
+  float xr[8], wr[4];
+  auto fetch = [&](int k0) {
+    const int k = k0 + lk;
 #pragma unroll
-    for (int j = 0; j < SL_NPW; ++j)
-#pragma unroll
-      for (int r = 0; r < SL_RT; ++r) acc[j][r] = 0.f;
-    for (int k0 = 0; k0 < K; k0 += SL_KC) {
-      __syncthreads();
-      for (int e = threadIdx.x; e < SL_RT * SL_KC; e += blockDim.x) {
-        int r = e / SL_KC, kk = e % SL_KC;
-        float v = 0.f;
-        if (r0 + r < rows && k0 + kk < K) {
-          v = in[(size_t)(r0 + r) * in_ld + k0 + kk];
-          if (silu_in) v = silu_f(v);
-        }
-        tile[r][kk] = v;
+    for (int i = 0; i < 8; ++i) {
+      const int r = r0 + lr + 8 * i;
+      float v = 0.f;
+      if (r < j.rows && k < j.k) {
+        v = j.in[(size_t)r * j.in_ld + k];
+        if (j.silu_in) v = silu_f(v);
       }
-      __syncthreads();
-#pragma unroll
-      for (int j = 0; j < SL_NPW; ++j) {
-        int n = n0 + j;
-        if (n >= N) continue;
-        const float* wr = w + (size_t)n * K + k0;
-        for (int kk = lane; kk < SL_KC && k0 + kk < K; kk += 32) {
-          float wv = wr[kk];
-#pragma unroll
-          for (int r = 0; r < SL_RT; ++r) acc[j][r] = fmaf(tile[r][kk], wv, acc[j][r]);
-        }
-      }
+      xr[i] = v;
     }
 #pragma unroll
-    for (int j = 0; j < SL_NPW; ++j) {
-      int n = n0 + j;
+    for (int i = 0; i < 4; ++i) {
+      const int n = n0 + lr + 8 * i;
+      wr[i] = (n < j.n && k < j.k) ? j.w[(size_t)n * j.k + k] : 0.f;
+    }
+  };
+  fetch(0);
+  for (int k0 = 0; k0 < j.k; k0 += SL_BK) {
+    __syncthreads();
 #pragma unroll
-      for (int r = 0; r < SL_RT; ++r) {
-        float v = warp_sum(acc[j][r]);
-        if (lane == 0 && n < N && r0 + r < rows) out[(size_t)(r0 + r) * out_ld + n] = v + (bias ? bias[n] : 0.f);
-      }
+    for (int i = 0; i < 8; ++i) xs[lk][lr + 8 * i] = xr[i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) ws[lk][lr + 8 * i] = wr[i];
+    __syncthreads();
+    if (k0 + SL_BK < j.k) fetch(k0 + SL_BK);
+#pragma unroll
+    for (int kk = 0; kk < SL_BK; ++kk) {
+      const float4 xv = *reinterpret_cast<const float4*>(&xs[kk][ty * 4]);
+      const float2 wv = *reinterpret_cast<const float2*>(&ws[kk][tx * 2]);
+      acc[0][0] = fmaf(xv.x, wv.x, acc[0][0]); acc[0][1] = fmaf(xv.x, wv.y, acc[0][1]);
+      acc[1][0] = fmaf(xv.y, wv.x, acc[1][0]); acc[1][1] = fmaf(xv.y, wv.y, acc[1][1]);
+      acc[2][0] = fmaf(xv.z, wv.x, acc[2][0]); acc[2][1] = fmaf(xv.z, wv.y, acc[2][1]);
+      acc[3][0] = fmaf(xv.w, wv.x, acc[3][0]); acc[3][1] = fmaf(xv.w, wv.y, acc[3][1]);
     }
   }
+#pragma unroll
+  for (int a = 0; a < 4; ++a) {
+    const int r = r0 + ty * 4 + a;
+    if (r >= j.rows) continue;
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      const int n = n0 + tx * 2 + b;
+      if (n < j.n) j.out[(size_t)r * j.out_ld + n] = acc[a][b] + (j.bias ? j.bias[n] : 0.f);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) small_linear_kernel(const __grid_constant__ ldmb200_linear_job job) {
+  small_linear_tile(job, blockIdx.x);
+}
+
+__global__ void __launch_bounds__(256) small_linear_batched_kernel(const ldmb200_linear_job* __restrict__ jobs,
+                                                                   int n_jobs) {
+  int lo = 0;  // last job whose first_block <= blockIdx.x (tables are a few dozen entries)
+  for (int i = 1; i < n_jobs; ++i)
+    if (jobs[i].first_block <= (int)blockIdx.x) lo = i;
+  const ldmb200_linear_job j = jobs[lo];
+  small_linear_tile(j, blockIdx.x - j.first_block);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -170,7 +226,7 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__
   T* dst = y + idx * c_pad;
   for (int c = 0; c < c_pad; ++c) {
     float v = c < C ? x[((size_t)b * C + c) * HW + p] : 0.f;
-    dst[c] = (T)v;
+    cvt_store(dst + c, v);
   }
 }
 
@@ -406,7 +462,7 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const ldmb200_pack_jo
   const int taps = j.ksize * j.ksize;
   const int64_t kp = (int64_t)taps * j.c_pad;
   const int64_t total = (int64_t)j.n_pad * kp;
-  __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(j.dst);
+  uint16_t* dst = reinterpret_cast<uint16_t*>(j.dst);
   for (int64_t i = i0; i < total; i += stride) {
     int rp = (int)(i / kp);
     int rem = (int)(i % kp);
@@ -414,7 +470,9 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const ldmb200_pack_jo
     int src_row = j.kind == 1 ? geglu_src_row(rp, j.n, j.block_n) : rp;
     float v = 0.f;
     if (src_row < j.n && c < j.c) v = j.src[((size_t)src_row * j.c + c) * taps + tap];
-    dst[(size_t)(j.row_offset + rp) * kp + rem] = __float2bfloat16_rn(v);
+    dst[(size_t)(j.row_offset + rp) * kp + rem] =
+        j.dst_dtype == LDMB200_F16 ? __half_as_ushort(__float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f)))
+                                   : __bfloat16_as_ushort(__float2bfloat16_rn(v));
   }
 }
 
@@ -455,10 +513,21 @@ int ldmb200_timestep_embedding(const int64_t* t, float* out, int batch, int dim,
 int ldmb200_small_linear(const float* in, int in_ld, const float* w, const float* bias, float* out, int out_ld,
                          int rows, int k, int n, int silu_in, void* stream) {
   LDM_CHECK_ARG(in && w && out && rows > 0 && k > 0 && n > 0, "small_linear: bad arguments");
-  dim3 blocks(ceil_div(n, SL_WARPS * SL_NPW), std::min(ceil_div(rows, SL_RT), 64));
-  small_linear_kernel<<<blocks, SL_WARPS * 32, 0, (cudaStream_t)stream>>>(in, in_ld, w, bias, out, out_ld, rows, k,
-                                                                          n, silu_in);
+  ldmb200_linear_job j;
+  j.in = in; j.w = w; j.bias = bias; j.out = out;
+  j.in_ld = in_ld; j.out_ld = out_ld; j.rows = rows; j.k = k; j.n = n; j.silu_in = silu_in; j.first_block = 0;
+  const int blocks = ceil_div(n, SL_BN) * ceil_div(rows, SL_BM);
+  small_linear_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(j);
   LDM_CHECK_LAUNCH("small_linear");
+  return 0;
+}
+
+int ldmb200_small_linear_blocks(int rows, int n) { return ceil_div(n, SL_BN) * ceil_div(rows, SL_BM); }
+
+int ldmb200_small_linear_batched(const ldmb200_linear_job* jobs, int n_jobs, int total_blocks, void* stream) {
+  LDM_CHECK_ARG(jobs && n_jobs > 0 && total_blocks > 0, "small_linear_batched: bad arguments");
+  small_linear_batched_kernel<<<total_blocks, 256, 0, (cudaStream_t)stream>>>(jobs, n_jobs);
+  LDM_CHECK_LAUNCH("small_linear_batched");
   return 0;
 }
 
@@ -466,10 +535,7 @@ int ldmb200_nchw_to_nhwc(const float* x, void* y, int batch, int c, int hw, int 
   LDM_CHECK_ARG(x && y && batch > 0 && c > 0 && hw > 0 && c_pad >= c, "nchw_to_nhwc: bad arguments");
   int64_t total = (int64_t)batch * hw;
   int blocks = (int)ceil_div64(total, 256);
-  if (out_dtype == LDMB200_BF16)
-    nchw_to_nhwc_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (__nv_bfloat16*)y, batch, c, hw, c_pad);
-  else
-    nchw_to_nhwc_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (float*)y, batch, c, hw, c_pad);
+  LDM_DISPATCH_DTYPE(out_dtype, (nchw_to_nhwc_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (T*)y, batch, c, hw, c_pad)));
   LDM_CHECK_LAUNCH("nchw_to_nhwc");
   return 0;
 }
@@ -487,10 +553,7 @@ int ldmb200_space_to_depth2(const float* x, void* y, int out_dtype, int batch, i
                 "space_to_depth2: bad arguments (h, w even; c %% 4 == 0)");
   int64_t total = (int64_t)batch * h * w * (c / 4);
   int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), (int64_t)sm_count() * 16);
-  if (out_dtype == LDMB200_BF16)
-    space_to_depth2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (__nv_bfloat16*)y, batch, h, w, c);
-  else
-    space_to_depth2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (float*)y, batch, h, w, c);
+  LDM_DISPATCH_DTYPE(out_dtype, (space_to_depth2_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (T*)y, batch, h, w, c)));
   LDM_CHECK_LAUNCH("space_to_depth2");
   return 0;
 }
@@ -499,10 +562,7 @@ int ldmb200_upsample2x(const float* x, void* y, int out_dtype, int batch, int h,
   LDM_CHECK_ARG(x && y && batch > 0 && h > 0 && w > 0 && c % 4 == 0, "upsample2x: bad arguments (c %% 4 == 0)");
   int64_t total = (int64_t)batch * h * w * 4 * (c / 4);
   int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), (int64_t)sm_count() * 16);
-  if (out_dtype == LDMB200_BF16)
-    upsample2x_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (__nv_bfloat16*)y, batch, h, w, c);
-  else
-    upsample2x_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (float*)y, batch, h, w, c);
+  LDM_DISPATCH_DTYPE(out_dtype, (upsample2x_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (T*)y, batch, h, w, c)));
   LDM_CHECK_LAUNCH("upsample2x");
   return 0;
 }
@@ -532,13 +592,10 @@ int ldmb200_groupnorm(const float* x1, int c1, const float* x2, int c2, const fl
   int want = ceil_div(sm_count() * 4, batch);
   if (T > want) T = want;
   if (T < 1) T = 1;
-  if (out_dtype == LDMB200_BF16)
-    gn_apply_kernel<<<dim3(T, batch), threads, 0, st>>>(x1, c1, x2, c2, gamma, beta, (__nv_bfloat16*)y,
-                                                        (__nv_bfloat16*)raw_copy, hw, groups, R, S, eps, silu,
-                                                        stats_ws);
-  else
-    gn_apply_kernel<<<dim3(T, batch), threads, 0, st>>>(x1, c1, x2, c2, gamma, beta, (float*)y, (float*)raw_copy, hw,
-                                                        groups, R, S, eps, silu, stats_ws);
+  const int nblk = T;
+  LDM_DISPATCH_DTYPE(out_dtype, (gn_apply_kernel<T><<<dim3(nblk, batch), threads, 0, st>>>(
+                                    x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw_copy, hw, groups, R, S, eps, silu,
+                                    stats_ws)));
   LDM_CHECK_LAUNCH("groupnorm apply");
   return 0;
 }
@@ -552,15 +609,11 @@ int ldmb200_layernorm(const float* x, const float* gamma, const float* beta, voi
   cudaStream_t st = (cudaStream_t)stream;
 #define LN_LAUNCH(T, MAXV) layernorm_kernel<T, MAXV><<<blocks, warps * 32, 0, st>>>(x, gamma, beta, (T*)y, rows, c, eps)
   const int need = ceil_div(c / 4, 32);
-  if (out_dtype == LDMB200_BF16) {
-    if (need <= 2) LN_LAUNCH(__nv_bfloat16, 2);
-    else if (need <= 5) LN_LAUNCH(__nv_bfloat16, 5);
-    else LN_LAUNCH(__nv_bfloat16, 16);
-  } else {
-    if (need <= 2) LN_LAUNCH(float, 2);
-    else if (need <= 5) LN_LAUNCH(float, 5);
-    else LN_LAUNCH(float, 16);
-  }
+  LDM_DISPATCH_DTYPE(out_dtype, {
+    if (need <= 2) LN_LAUNCH(T, 2);
+    else if (need <= 5) LN_LAUNCH(T, 5);
+    else LN_LAUNCH(T, 16);
+  });
 #undef LN_LAUNCH
   LDM_CHECK_LAUNCH("layernorm");
   return 0;

@@ -21,7 +21,7 @@
 namespace ldm {
 
 struct TcParams {
-  int64_t M;
+  int M;
   int tiles_m, tiles_n;
   int taps, ks, stride, is_conv;
   int c1_chunks, c2_chunks, ctot;
@@ -29,12 +29,17 @@ struct TcParams {
   const float* bias;
   const float* rowvec;
   int rowvec_ld;
+  int rowvec_uniform;  // rows_per_sample % 128 == 0: every row of a tile belongs to one sample
   const float* residual;
   int residual_ld;
   int geglu;
   void* out;
-  int out_bf16, out_ld, out_nchw, n_valid;
+  int out_dtype, out_ld, out_nchw, n_valid;
+  uint32_t idesc;  // tcgen05 instruction descriptor (operand format bf16 or f16, M = 128, N = BN)
 };
+
+constexpr int TC_EPI_WARPS = 8;  // two warps per TMEM lane quarter, alternating 32-column chunks
+constexpr int TC_THREADS = 64 + TC_EPI_WARPS * 32;
 
 template <int BN, int BK>
 struct TcCfg {
@@ -46,13 +51,96 @@ struct TcCfg {
   static constexpr int STAGES = (BN >= 128) ? (BK == 32 ? 8 : 5) : 8;
   static constexpr int TX_BYTES = BM * BK * 2 + BN * BK * 2;
   static constexpr int EPI_PITCH = 36;  // floats; 144 B row pitch: conflict-free 16 B row-owner writes + row reads
-  static constexpr int EPI_BYTES = 4 * 32 * EPI_PITCH * 4;
+  static constexpr int EPI_BYTES = TC_EPI_WARPS * 32 * EPI_PITCH * 4;
   static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + (2 * STAGES + 4) * 8 + 16 + 1024;
   static constexpr int CH = BN >= 32 ? 32 : 16;  // epilogue column chunk
 };
 
-constexpr int TC_THREADS = 192;
+// two fp32 -> one packed pair of 16-bit floats (lo in the low half); f16 saturates instead of overflowing to inf
+__device__ __forceinline__ uint32_t pack16(float lo, float hi, int dt) {
+  uint32_t r;
+  if (dt == LDMB200_F16)
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  else
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
+// ---- epilogue, coalesced phase --------------------------------------------------------------------
+// A warp owns 32 accumulator rows.  tcgen05.ld hands thread i row i; the chunk is transposed through a
+// warp-private smem tile so that global traffic is row-contiguous: LPR lanes cover one row's COLS columns
+// (CPL = 4 fp32 or 8 16-bit columns per lane), 32/LPR rows per instruction.
+template <bool OUT16>
+__device__ __forceinline__ void epi_load_residual(const TcParams& p, float4 (&res)[8], int m0, int col0, int lane) {
+  constexpr int CPL = OUT16 ? 8 : 4, LPR = 32 / CPL, RPI = 32 / LPR;
+  const int lr = lane / LPR, lc = (lane % LPR) * CPL;
+  const bool col_ok = col0 + lc < p.n_valid;
+#pragma unroll
+  for (int it = 0; it < LPR; ++it) {
+    const int m = m0 + it * RPI + lr;
+    const float* src = p.residual + (size_t)m * p.residual_ld + col0 + lc;
+#pragma unroll
+    for (int q = 0; q < CPL / 4; ++q)
+      res[it * (CPL / 4) + q] = (col_ok && m < p.M) ? *reinterpret_cast<const float4*>(src + 4 * q)
+                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
+template <bool OUT16, int COLS>
+__device__ __forceinline__ void epi_store(const TcParams& p, const float* st, int pitch, int m0, int col0, int lane,
+                                          const float4 (&res)[8], bool has_res, bool add_bias, int tile_sample) {
+  constexpr int CPL = OUT16 ? 8 : 4, LPR = COLS / CPL, RPI = 32 / LPR, NQ = CPL / 4;
+  const int lr = lane / LPR, lc = (lane % LPR) * CPL;
+  const int col = col0 + lc;
+  if (col >= p.n_valid) return;
+  float4 add[NQ];
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+    add[q] = (add_bias && p.bias) ? *reinterpret_cast<const float4*>(p.bias + col + 4 * q) : make_float4(0.f, 0.f, 0.f, 0.f);
+    if (p.rowvec && p.rowvec_uniform) {
+      const float4 rv = *reinterpret_cast<const float4*>(p.rowvec + (size_t)tile_sample * p.rowvec_ld + col + 4 * q);
+      add[q].x += rv.x; add[q].y += rv.y; add[q].z += rv.z; add[q].w += rv.w;
+    }
+  }
+#pragma unroll
+  for (int it = 0; it < LPR; ++it) {
+    const int r = it * RPI + lr;
+    const int m = m0 + r;
+    if (m >= p.M) continue;
+    float4 t[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+      t[q] = *reinterpret_cast<const float4*>(&st[r * pitch + lc + 4 * q]);
+      t[q].x += add[q].x; t[q].y += add[q].y; t[q].z += add[q].z; t[q].w += add[q].w;
+    }
+    if (p.rowvec && !p.rowvec_uniform) {
+      const float* rvp = p.rowvec + (size_t)(m / p.rows_per_sample) * p.rowvec_ld + col;
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) {
+        const float4 rv = *reinterpret_cast<const float4*>(rvp + 4 * q);
+        t[q].x += rv.x; t[q].y += rv.y; t[q].z += rv.z; t[q].w += rv.w;
+      }
+    }
+    if (has_res) {
+#pragma unroll
+      for (int q = 0; q < NQ; ++q) {
+        const float4 rs = res[it * NQ + q];
+        t[q].x += rs.x; t[q].y += rs.y; t[q].z += rs.z; t[q].w += rs.w;
+      }
+    }
+    if (OUT16) {
+      uint4 u;
+      u.x = pack16(t[0].x, t[0].y, p.out_dtype);
+      u.y = pack16(t[0].z, t[0].w, p.out_dtype);
+      u.z = pack16(t[NQ - 1].x, t[NQ - 1].y, p.out_dtype);
+      u.w = pack16(t[NQ - 1].z, t[NQ - 1].w, p.out_dtype);
+      *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out) + (size_t)m * p.out_ld + col) = u;
+    } else {
+      *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)m * p.out_ld + col) = t[0];
+    }
+  }
+}
 
 template <int BN, int BK>
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -87,7 +175,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       }
       for (int b = 0; b < 2; ++b) {
         mbar_init(&tfull[b], 1);
-        mbar_init(&tempty[b], 4);
+        mbar_init(&tempty[b], TC_EPI_WARPS);
       }
       fence_mbar_init();
     }
@@ -105,11 +193,11 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       uint32_t it = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
-        const int64_t m0 = (int64_t)tm * Cfg::BM;
+        const int m0 = tm * Cfg::BM;
         int n_img = 0, h0 = 0;
         if (p.is_conv) {
-          n_img = (int)(m0 / p.hw_out);
-          h0 = (int)(m0 % p.hw_out) / p.w_out;
+          n_img = m0 / p.hw_out;
+          h0 = (m0 % p.hw_out) / p.w_out;
         }
         for (int tap = 0; tap < p.taps; ++tap) {
           int dh = 0, dw = 0, plane = 0;
@@ -137,7 +225,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
             if (p.is_conv)
               tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, dw, h0 + dh, plane, n_img);
             else
-              tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, 0, (int)m0, 0, 0);
+              tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, 0, m0, 0, 0);
             tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &full[s], tap * p.ctot + j * BK, tn * BN);
           }
         }
@@ -146,7 +234,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(Cfg::BM, BN);
+      const uint32_t idesc = p.idesc;
       uint32_t it = 0, t_iter = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
         const uint32_t buf = t_iter & 1;
@@ -171,31 +259,56 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       }
     }
   } else {
-    // ===================== epilogue (4 warps) =====================
-    const int qw = warp & 3;  // TMEM lane quarter accessible to this warp
-    float* st = epi + qw * 32 * Cfg::EPI_PITCH;
+    // ===================== epilogue (TC_EPI_WARPS warps) =====================
+    const int ew = warp - 2;
+    const int qw = warp & 3;          // TMEM lane quarter accessible to this warp (hardware: warp id % 4)
+    const int par = ew >> 2;          // which of the quarter's two warps: takes chunks cc % 2 == par
+    constexpr int NCH = BN / Cfg::CH;
+    constexpr int PITCH = Cfg::EPI_PITCH;
+    float* st = epi + ew * 32 * PITCH;
+    const bool out16 = p.out_dtype != LDMB200_F32;
+    const bool has_res = p.residual != nullptr;
     uint32_t t_iter = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
       const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
-      const int64_t m0 = (int64_t)tm * Cfg::BM + qw * 32;
+      const int m0 = tm * Cfg::BM + qw * 32;
       const int n0 = tn * BN;
       const uint32_t buf = t_iter & 1;
+      const int tile_sample = (tm * Cfg::BM) / p.rows_per_sample;
+      float4 res[8];
+      const int cc_first = par;
+      // the residual tile does not depend on the accumulator: fetch it while the MMAs are still running
+      if (has_res && cc_first < NCH) {
+        if (out16) epi_load_residual<true>(p, res, m0, n0 + cc_first * Cfg::CH, lane);
+        else epi_load_residual<false>(p, res, m0, n0 + cc_first * Cfg::CH, lane);
+      }
       mbar_wait(&tfull[buf], (t_iter >> 1) & 1);
       tc_fence_after();
 #pragma unroll 1
-      for (int cc = 0; cc < BN / Cfg::CH; ++cc) {
+      for (int cc = cc_first; cc < NCH; cc += 2) {
         float v[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16) + buf * BN + cc * Cfg::CH;
         if (Cfg::CH == 32)
           tmem_ld_32x32(taddr, v);
         else
           tmem_ld_32x16(taddr, v);
+        float4 res_next[8];
+        const bool more = cc + 2 < NCH;
+        if (has_res && more) {
+          if (out16) epi_load_residual<true>(p, res_next, m0, n0 + (cc + 2) * Cfg::CH, lane);
+          else epi_load_residual<false>(p, res_next, m0, n0 + (cc + 2) * Cfg::CH, lane);
+        }
         tmem_ld_wait();
+        if (!more) {  // last TMEM read of this warp for this tile: hand the accumulator buffer back early
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[buf]);
+        }
         if (p.out_nchw) {
           // UNetModel.out conv: thread owns pixel m, writes the n_valid real channels as fp32 NCHW
-          const int64_t m = m0 + lane;
+          const int m = m0 + lane;
           if (m < p.M) {
-            const int b = (int)(m / p.hw_out), pix = (int)(m % p.hw_out);
+            const int b = m / p.hw_out, pix = m % p.hw_out;
             float* o = reinterpret_cast<float*>(p.out);
 #pragma unroll
             for (int j = 0; j < Cfg::CH; ++j) {
@@ -205,59 +318,48 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
           }
           continue;
         }
-        int ncols = Cfg::CH;
-        int col0 = n0 + cc * Cfg::CH;
         if (p.geglu) {  // chunk = [16 value | 16 gate] columns (packed order), biases in the same order
-          const float* bp = p.bias + n0 + cc * 32;
+          if (Cfg::CH == 32) {
+            const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + cc * 32);
+            float bv[32];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const float val = v[j] + bp[j];
-            const float gate = v[16 + j] + bp[16 + j];
-            v[j] = val * gelu_erf_f(gate);
+            for (int j = 0; j < 8; ++j) {
+              const float4 t = bp[j];
+              bv[4 * j] = t.x; bv[4 * j + 1] = t.y; bv[4 * j + 2] = t.z; bv[4 * j + 3] = t.w;
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = (v[j] + bv[j]) * gelu_erf_f(v[16 + j] + bv[16 + j]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              *reinterpret_cast<float4*>(&st[lane * PITCH + j * 4]) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+            __syncwarp();
+            const int col0 = (n0 >> 1) + cc * 16;
+            if (out16) epi_store<true, 16>(p, st, PITCH, m0, col0, lane, res, false, false, tile_sample);
+            else epi_store<false, 16>(p, st, PITCH, m0, col0, lane, res, false, false, tile_sample);
+            __syncwarp();
           }
-          ncols = 16;
-          col0 = (n0 >> 1) + cc * 16;
+          continue;
         }
 #pragma unroll
         for (int j = 0; j < Cfg::CH / 4; ++j)
-          if (j * 4 < ncols)
-            *reinterpret_cast<float4*>(&st[lane * Cfg::EPI_PITCH + j * 4]) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+          *reinterpret_cast<float4*>(&st[lane * PITCH + j * 4]) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
         __syncwarp();
-        const int lpr = ncols >> 2;       // lanes per row
-        const int rpi = 32 / lpr;         // rows per iteration
-        const int c4 = (lane % lpr) * 4;
-        const int col = col0 + c4;
-        float4 bq = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (!p.geglu && p.bias && col < p.n_valid) bq = *reinterpret_cast<const float4*>(p.bias + col);
-        for (int r = lane / lpr; r < 32; r += rpi) {
-          const int64_t m = m0 + r;
-          if (m < p.M && col < p.n_valid) {
-            float4 t = *reinterpret_cast<const float4*>(&st[r * Cfg::EPI_PITCH + c4]);
-            t.x += bq.x; t.y += bq.y; t.z += bq.z; t.w += bq.w;
-            if (p.rowvec) {
-              const float4 rv = *reinterpret_cast<const float4*>(p.rowvec + (size_t)(m / p.rows_per_sample) * p.rowvec_ld + col);
-              t.x += rv.x; t.y += rv.y; t.z += rv.z; t.w += rv.w;
-            }
-            if (p.residual) {
-              const float4 rs = *reinterpret_cast<const float4*>(p.residual + (size_t)m * p.residual_ld + col);
-              t.x += rs.x; t.y += rs.y; t.z += rs.z; t.w += rs.w;
-            }
-            if (p.out_bf16) {
-              __nv_bfloat162 lo = __floats2bfloat162_rn(t.x, t.y), hi = __floats2bfloat162_rn(t.z, t.w);
-              uint2 u;
-              u.x = *reinterpret_cast<uint32_t*>(&lo);
-              u.y = *reinterpret_cast<uint32_t*>(&hi);
-              *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)m * p.out_ld + col) = u;
-            } else {
-              *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)m * p.out_ld + col) = t;
-            }
-          }
+        {
+          const int col0 = n0 + cc * Cfg::CH;
+          if (out16) epi_store<true, Cfg::CH>(p, st, PITCH, m0, col0, lane, res, has_res, true, tile_sample);
+          else epi_store<false, Cfg::CH>(p, st, PITCH, m0, col0, lane, res, has_res, true, tile_sample);
         }
         __syncwarp();
+        if (has_res && more) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) res[j] = res_next[j];
+        }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[buf]);
+      if (cc_first >= NCH) {  // this warp had no chunk in the tile (BN == CH): still release the buffer
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[buf]);
+      }
     }
   }
 
@@ -297,7 +399,8 @@ using namespace ldm;
 
 extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   LDM_CHECK_ARG(d && d->a && d->w && d->out, "igemm_tc: null pointer");
-  LDM_CHECK_ARG(d->a_dtype == LDMB200_BF16, "igemm_tc: A operand must be bf16");
+  LDM_CHECK_ARG(d->a_dtype == LDMB200_BF16 || d->a_dtype == LDMB200_F16,
+                "igemm_tc: A operand must be bf16 or f16 (and the packed weights of the same type)");
   LDM_CHECK_ARG(!d->upsample, "igemm_tc: upsample must be materialised (ldmb200_upsample2x) on the tensor-core path");
   LDM_CHECK_ARG(d->ksize == 1 || d->ksize == 3, "igemm_tc: ksize must be 1 or 3");
   LDM_CHECK_ARG(d->stride == 1 || (d->stride == 2 && d->ksize == 3), "igemm_tc: stride 2 only for 3x3");
@@ -308,7 +411,8 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   const int hw_out = h_out * w_out;
   TcParams p;
   memset(&p, 0, sizeof(p));
-  p.M = (int64_t)d->batch * hw_out;
+  LDM_CHECK_ARG((int64_t)d->batch * hw_out > 0 && (int64_t)d->batch * hw_out < (1ll << 31), "igemm_tc: M out of range");
+  p.M = d->batch * hw_out;
   p.ks = d->ksize;
   p.taps = d->ksize * d->ksize;
   p.stride = d->stride;
@@ -324,15 +428,22 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   p.residual_ld = d->residual_ld;
   p.geglu = d->geglu;
   p.out = d->out;
-  p.out_bf16 = d->out_dtype == LDMB200_BF16;
+  p.out_dtype = d->out_dtype;
+  p.rowvec_uniform = hw_out % 128 == 0;
   p.out_ld = d->out_ld;
   p.out_nchw = d->out_nchw;
   const int n_cols = d->geglu ? d->n / 2 : d->n;
   p.n_valid = d->n_valid > 0 ? d->n_valid : n_cols;
-  LDM_CHECK_ARG(d->out_nchw || p.n_valid % 4 == 0, "igemm_tc: n_valid must be a multiple of 4 unless out_nchw");
-  LDM_CHECK_ARG(!(d->out_nchw && (p.out_bf16 || d->geglu || d->rowvec || d->residual)), "igemm_tc: out_nchw is a plain fp32 store");
+  LDM_CHECK_ARG(d->out_dtype == LDMB200_F32 || d->out_dtype == LDMB200_BF16 || d->out_dtype == LDMB200_F16,
+                "igemm_tc: bad out_dtype");
+  const bool out16 = d->out_dtype != LDMB200_F32;
+  LDM_CHECK_ARG(d->out_nchw || p.n_valid % (out16 ? 8 : 4) == 0,
+                "igemm_tc: n_valid must be a multiple of 4 (fp32 out) / 8 (16-bit out) unless out_nchw");
+  LDM_CHECK_ARG(d->out_nchw || d->out_ld % (out16 ? 8 : 4) == 0, "igemm_tc: out_ld must keep rows 16-byte aligned");
+  LDM_CHECK_ARG(!d->residual || d->residual_ld % 4 == 0, "igemm_tc: residual_ld must be a multiple of 4");
+  LDM_CHECK_ARG(!d->rowvec || d->rowvec_ld % 4 == 0, "igemm_tc: rowvec_ld must be a multiple of 4");
+  LDM_CHECK_ARG(!(d->out_nchw && (out16 || d->geglu || d->rowvec || d->residual)), "igemm_tc: out_nchw is a plain fp32 store");
   LDM_CHECK_ARG(!(d->geglu && (!d->bias || d->rowvec || d->residual)), "igemm_tc: geglu epilogue takes the packed bias only");
-  LDM_CHECK_ARG(p.M > 0 && p.M < (1ll << 31), "igemm_tc: M out of range");
 
   int BK = (c1 % 64 == 0 && c2 % 64 == 0) ? 64 : 32;
   if (const char* e = getenv("LDMB200_TC_BK")) {
@@ -344,8 +455,9 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   LDM_CHECK_ARG(!(d->geglu && BN == 16), "igemm_tc: geglu needs n %% 32 == 0");
   p.c1_chunks = c1 / BK;
   p.c2_chunks = c2 / BK;
-  p.tiles_m = (int)ceil_div64(p.M, 128);
+  p.tiles_m = ceil_div(p.M, 128);
   p.tiles_n = d->n / BN;
+  p.idesc = umma_idesc_f16(128, BN, d->a_dtype == LDMB200_F16 ? 0 : 1);
 
   // ---- A tensor maps: {C, W, H, plane, B}, box {BK, bw, bh, 1, bn} with bw*bh*bn = 128 rows
   CUtensorMap tA1, tA2, tB;

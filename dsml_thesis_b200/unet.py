@@ -17,8 +17,13 @@ What is different: the modules below only HOLD parameters.  ``forward`` compiles
 activation arena (``_Plan``) and replays it; optionally through a CUDA graph.
 
 Precision modes (``LDMB200_PRECISION`` or ``model.precision``):
-  * ``"bf16"`` (default) — tcgen05 implicit GEMM + flash attention, bf16 operands, fp32 accumulation,
-    fp32 residual stream and fp32 norm statistics;
+  * ``"f16"`` (default) — tcgen05 implicit GEMM + flash attention with 16-bit operands, fp32 accumulation in
+    tensor memory, fp32 residual stream, fp32 norm statistics and softmax.  GEMM operands (weights, GroupNorm /
+    LayerNorm / GEGLU / attention outputs) are IEEE fp16 with saturating conversions: same tensor-core rate as
+    bf16 but 3 more mantissa bits, which is what brings the per-step eps error from ~1.2e-2 (pure bf16 — also
+    what the reference's own bf16 autocast gives, SURVEY hard part 2) down to ~1e-3.  Attention internals
+    (q, k, v, P) stay bf16 so that scores keep the fp32 exponent range;
+  * ``"bf16"`` — the same kernels with every 16-bit operand in bf16;
   * ``"fp32"`` — fp32 SIMT kernels (parity mode, per-step eps rel-L2 <= 1e-4).
 """
 from __future__ import annotations
@@ -33,7 +38,7 @@ import torch
 import torch.nn as nn
 
 from . import _cabi
-from ._cabi import BF16, F32, GemmDesc, PackJob
+from ._cabi import BF16, F16, F32, GemmDesc, LinearJob, PackJob
 
 
 # ----------------------------------------------------------------------------------------------
@@ -172,8 +177,9 @@ class _WeightPack:
     """bf16 K-major copies of the UNet's weights for ``ldmb200_igemm_tc`` plus the device job table that
     (re)fills them in ONE launch (``ldmb200_pack_weights``).  Layout depends on the model only."""
 
-    def __init__(self, model: "UNetModel"):
+    def __init__(self, model: "UNetModel", dtype: int = BF16):
         dev = model._device()
+        self.dtype = dtype
         self.entries: Dict[str, Tuple[int, int, int]] = {}   # key -> (byte offset, n_pad, c_pad)
         self.f32_entries: Dict[str, int] = {}                 # key -> float offset (GEGLU biases)
         jobs: List[tuple] = []
@@ -224,6 +230,7 @@ class _WeightPack:
                 j.dst = self.bf16.data_ptr() + dst
             j.kind, j.n, j.c, j.ksize = kind, n, c, ks
             j.n_pad, j.c_pad, j.row_offset, j.block_n = n_pad, c_pad, row_off, bn
+            j.dst_dtype = dtype
         host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
         self.jobs_dev = host.to(dev)
         self.n_jobs = len(jobs)
@@ -296,8 +303,9 @@ class _Act:
 class _Plan:
     def __init__(self, model: "UNetModel", B: int, H: int, W: int, L: int, mode: str):
         self.model, self.B, self.H, self.W, self.L, self.mode = model, B, H, W, L, mode
-        self.tc = mode == "bf16"
-        self.act = BF16 if self.tc else F32
+        self.tc = mode in ("bf16", "f16")
+        self.act = {"bf16": BF16, "f16": F16, "fp32": F32}[mode]   # dtype of GEMM A operands
+        self.qkv_dt = BF16 if self.tc else F32                     # attention_tc takes bf16 q/k/v
         dev = model._device()
         self.lib = _cabi.load()
         self.ops: List[tuple] = []       # (c function, args without the trailing stream)
@@ -305,7 +313,7 @@ class _Plan:
         self.py_ops: Dict[int, object] = {}  # op index -> python callable run before that op
         self.keep: List[object] = []     # ctypes structs referenced by pointer from ops
         self.arena = _Arena(dev)
-        self.pack = model._weight_pack() if self.tc else None
+        self.pack = model._weight_pack(self.act) if self.tc else None
         f32 = dict(dtype=torch.float32, device=dev)
         self.x_in = torch.empty(B, model.in_channels, H, W, **f32)
         self.t_in = torch.empty(B, dtype=torch.int64, device=dev)
@@ -319,7 +327,7 @@ class _Plan:
 
     # ---- small helpers -------------------------------------------------------------------
     def new(self, rows: int, c: int, dtype: int) -> _Act:
-        return _Act(self.arena.alloc(rows * c * (2 if dtype == BF16 else 4)), rows, c, dtype)
+        return _Act(self.arena.alloc(rows * c * (4 if dtype == F32 else 2)), rows, c, dtype)
 
     def free(self, *acts):
         for a in acts:
@@ -344,6 +352,73 @@ class _Plan:
                   what=f"R{rows} K{k} N{n}")
         return o
 
+    def small_linear_batched(self, jobs: List[tuple], what: str):
+        """One launch for a table of independent small dense layers.  jobs: (in_ptr, in_ld, weight, bias, out_ptr,
+        out_ld, rows, silu_in).  The device job table is built once per plan (all addresses are static)."""
+        if not jobs:
+            return
+        arr = (LinearJob * len(jobs))()
+        first = 0
+        for j, (in_ptr, in_ld, w, b, out_ptr, out_ld, rows, silu) in zip(arr, jobs):
+            n, k = w.shape
+            j.in_, j.w, j.bias, j.out = in_ptr, w.data_ptr(), (b.data_ptr() if b is not None else None), out_ptr
+            j.in_ld, j.out_ld, j.rows, j.k, j.n, j.silu_in, j.first_block = in_ld, out_ld, rows, k, n, silu, first
+            first += int(self.lib.ldmb200_small_linear_blocks(rows, n))
+        table = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(self.model._device())
+        self.keep.append(table)
+        self.emit("ldmb200_small_linear_batched", table.data_ptr(), len(jobs), first, what=what)
+
+    def _prepass_vectors(self, emb: _Act, ctx: _Act):
+        """Everything that depends only on (emb, context) and not on x, for the whole network, in three launches:
+        all ResBlock emb projections (openaimodel.py:264) and — for a length-1 context, where softmax over one key
+        is 1 and attn2(x) == to_out(to_v(ctx)) for every token — all cross-attention outputs."""
+        m, B, L = self.model, self.B, self.L
+        res = [(n, mod) for n, mod in m.named_modules() if isinstance(mod, ResBlock)]
+        tbs = [(n, mod) for n, mod in m.named_modules() if isinstance(mod, BasicTransformerBlock)]
+        self.vec: Dict[int, Tuple[int, int]] = {}   # id(module) -> (pointer, leading dim) of its per-sample row vector
+        tot = sum(mod.out_channels for _, mod in res)
+        ev = self.new(B, tot, F32)
+        self.pinned.add(id(ev))
+        jobs, off = [], 0
+        for _, mod in res:
+            lin = mod.emb_layers[1]
+            jobs.append((emb.ptr, emb.c, lin.weight, lin.bias, ev.ptr + 4 * off, tot, B, 1))
+            self.vec[id(mod)] = (ev.ptr + 4 * off, tot)
+            off += mod.out_channels
+        self.small_linear_batched(jobs, f"emb_layers x{len(jobs)}")
+        tot = sum(mod.attn2.to_v.weight.shape[0] for _, mod in tbs)
+        rows = B * max(L, 1)
+        vall = self.new(rows, tot, F32)
+        self.pinned.add(id(vall))
+        jobs, off = [], 0
+        for _, mod in tbs:
+            w = mod.attn2.to_v.weight
+            jobs.append((ctx.ptr, ctx.c, w, None, vall.ptr + 4 * off, tot, rows, 0))
+            self.vec[("v", id(mod))] = (vall.ptr + 4 * off, tot)
+            off += w.shape[0]
+        self.small_linear_batched(jobs, f"attn2.to_v x{len(jobs)}")
+        if L == 1:
+            cv = self.new(B, tot, F32)
+            self.pinned.add(id(cv))
+            jobs, off = [], 0
+            for _, mod in tbs:
+                lo = mod.attn2.to_out[0]
+                vp, vld = self.vec[("v", id(mod))]
+                jobs.append((vp, vld, lo.weight, lo.bias, cv.ptr + 4 * off, tot, B, 0))
+                self.vec[id(mod)] = (cv.ptr + 4 * off, tot)
+                off += lo.weight.shape[0]
+            self.small_linear_batched(jobs, f"attn2.to_out x{len(jobs)}")
+        else:
+            kall = self.new(rows, tot, F32)
+            self.pinned.add(id(kall))
+            jobs, off = [], 0
+            for _, mod in tbs:
+                w = mod.attn2.to_k.weight
+                jobs.append((ctx.ptr, ctx.c, w, None, kall.ptr + 4 * off, tot, rows, 0))
+                self.vec[("k", id(mod))] = (kall.ptr + 4 * off, tot)
+                off += w.shape[0]
+            self.small_linear_batched(jobs, f"attn2.to_k x{len(jobs)}")
+
     def groupnorm(self, x1: _Act, x2: Optional[_Act], gn: nn.GroupNorm, hw: int, silu: int, want_raw: bool):
         c = x1.c + (x2.c if x2 is not None else 0)
         y = self.new(x1.rows, c, self.act)
@@ -363,7 +438,7 @@ class _Plan:
         return y
 
     def gemm(self, a: _Act, key: str, weight: torch.Tensor, bias: Optional[torch.Tensor], h_in: int, w_in: int,
-             ksize: int = 1, stride: int = 1, upsample: int = 0, rowvec: Optional[_Act] = None,
+             ksize: int = 1, stride: int = 1, upsample: int = 0, rowvec: Optional[Tuple[int, int]] = None,
              residual: Optional[_Act] = None, geglu: bool = False, out_dtype: int = F32,
              out: Optional[Tuple[int, int]] = None, out_nchw_ptr: Optional[int] = None,
              force_simt: bool = False, n_true: Optional[int] = None) -> Optional[_Act]:
@@ -386,7 +461,7 @@ class _Plan:
             d.w = weight.data_ptr()
             d.n = n_true
             d.bias = bias.data_ptr() if bias is not None else None
-        d.rowvec, d.rowvec_ld = (rowvec.ptr, rowvec.c) if rowvec is not None else (None, 0)
+        d.rowvec, d.rowvec_ld = rowvec if rowvec is not None else (None, 0)
         d.residual, d.residual_ld = (residual.ptr, residual.c) if residual is not None else (None, 0)
         d.geglu = 1 if geglu else 0
         n_cols = n_true // 2 if geglu else n_true
@@ -405,7 +480,7 @@ class _Plan:
         k_true = weight.shape[1] * ksize * ksize if weight.dim() >= 2 and n_true == weight.shape[0] else a.c
         self.emit("ldmb200_igemm_tc" if tc else "ldmb200_igemm_simt", C.byref(d), flops=2.0 * rows * n_true * k_true,
                   what=f"M{rows} N{n_true} K{k_true} ks{ksize} s{stride}" + (" geglu" if geglu else "")
-                  + (" res" if residual is not None else "") + (" bf16out" if out_dtype == BF16 else ""))
+                  + (" res" if residual is not None else "") + ({BF16: " bf16out", F16: " f16out"}.get(out_dtype, "")))
         return res
 
     # ---- blocks ------------------------------------------------------------------------
@@ -415,10 +490,9 @@ class _Plan:
         if x2 is not None and not has_skip:
             raise NotImplementedError("identity skip over a concatenated input is not reachable from UNetModel")
         y1, raw = self.groupnorm(x1, x2, m.in_layers[0], H * W, 1, has_skip)
-        ev = self.small_linear(emb.ptr, emb.c, m.emb_layers[1], self.B, 1)
         c0 = m.in_layers[2]
-        h1 = self.gemm(y1, name + ".in_layers.2", c0.weight, c0.bias, H, W, ksize=3, rowvec=ev)
-        self.free(y1, ev)
+        h1 = self.gemm(y1, name + ".in_layers.2", c0.weight, c0.bias, H, W, ksize=3, rowvec=self.vec[id(m)])
+        self.free(y1)
         y2, _ = self.groupnorm(h1, None, m.out_layers[0], H * W, 1, False)
         self.free(h1)
         if has_skip:
@@ -443,7 +517,7 @@ class _Plan:
             raise NotImplementedError(f"attention kernels are built for d_head = 32 (got {dh})")
         scale = float(m.attn1.scale)
         a = self.layernorm(t0, m.norm1)
-        qkv = self.new(t0.rows, 3 * Cc, self.act)
+        qkv = self.new(t0.rows, 3 * Cc, self.qkv_dt)
         if self.tc:
             self.gemm(a, name + ".attn1.qkv", m.attn1.to_q.weight, None, hw, 1, out_dtype=BF16,
                       out=(qkv.ptr, 3 * Cc), n_true=3 * Cc)
@@ -453,7 +527,7 @@ class _Plan:
         self.free(a)
         o = self.new(t0.rows, Cc, self.act)
         if self.tc:
-            self.emit("ldmb200_attention_tc", qkv.ptr, 3 * Cc, 0, Cc, 2 * Cc, o.ptr, Cc, B, heads, hw, scale,
+            self.emit("ldmb200_attention_tc", qkv.ptr, 3 * Cc, 0, Cc, 2 * Cc, o.ptr, Cc, self.act, B, heads, hw, scale,
                       flops=4.0 * B * heads * hw * hw * dh, what=f"B{B} h{heads} N{hw}")
         else:
             self.emit("ldmb200_attention_simt", qkv.ptr, 3 * Cc, 0, qkv.ptr, Cc, qkv.ptr, 2 * Cc, 3 * Cc, o.ptr, Cc, B,
@@ -464,23 +538,20 @@ class _Plan:
         if L == 1:
             # one key: softmax == 1, attn2(x) == to_out(to_v(ctx)) for every token -> a per-sample
             # row vector added in the epilogue of attn1's output projection
-            v = self.small_linear(ctx.ptr, ctx.c, a2m.to_v, B, 0)
-            cv = self.small_linear(v.ptr, v.c, a2m.to_out[0], B, 0)
-            self.free(v)
-            t2 = self.gemm(o, name + ".attn1.to_out.0", lo.weight, lo.bias, hw, 1, rowvec=cv, residual=t0)
-            self.free(o, cv, t0)
+            t2 = self.gemm(o, name + ".attn1.to_out.0", lo.weight, lo.bias, hw, 1, rowvec=self.vec[id(m)],
+                           residual=t0)
+            self.free(o, t0)
         else:
             t1 = self.gemm(o, name + ".attn1.to_out.0", lo.weight, lo.bias, hw, 1, residual=t0)
             self.free(o, t0)
             a2 = self.layernorm(t1, m.norm2)
             q = self.gemm(a2, name + ".attn2.to_q", a2m.to_q.weight, None, hw, 1)
             self.free(a2)
-            k = self.small_linear(ctx.ptr, ctx.c, a2m.to_k, B * L, 0)
-            v = self.small_linear(ctx.ptr, ctx.c, a2m.to_v, B * L, 0)
+            (kp, kld), (vp, _) = self.vec[("k", id(m))], self.vec[("v", id(m))]
             o2 = self.new(t1.rows, Cc, F32)
-            self.emit("ldmb200_attention_simt", q.ptr, Cc, 0, k.ptr, 0, v.ptr, 0, Cc, o2.ptr, Cc, B, a2m.heads, hw, L,
+            self.emit("ldmb200_attention_simt", q.ptr, Cc, 0, kp, 0, vp, 0, kld, o2.ptr, Cc, B, a2m.heads, hw, L,
                       float(a2m.scale), flops=4.0 * B * a2m.heads * hw * L * dh)
-            self.free(q, k, v)
+            self.free(q)
             lo2 = a2m.to_out[0]
             t2 = self.gemm(o2, "", lo2.weight, lo2.bias, hw, 1, residual=t1, force_simt=True)
             self.free(o2, t1)
@@ -509,8 +580,8 @@ class _Plan:
     def downsample(self, m: Downsample, name: str, x: _Act, H: int, W: int) -> _Act:
         """openaimodel.py:151-160: conv 3x3 stride 2 pad 1."""
         if self.tc:
-            s = self.new(x.rows, x.c, BF16)
-            self.emit("ldmb200_space_to_depth2", x.ptr, s.ptr, BF16, self.B, H, W, x.c)
+            s = self.new(x.rows, x.c, self.act)
+            self.emit("ldmb200_space_to_depth2", x.ptr, s.ptr, self.act, self.B, H, W, x.c)
             out = self.gemm(s, name + ".op", m.op.weight, m.op.bias, H, W, ksize=3, stride=2)
             self.free(s)
             return out
@@ -519,8 +590,8 @@ class _Plan:
     def upsample(self, m: Upsample, name: str, x: _Act, H: int, W: int) -> _Act:
         """openaimodel.py:109-119: nearest 2x, then conv 3x3."""
         if self.tc:
-            u = self.new(4 * x.rows, x.c, BF16)
-            self.emit("ldmb200_upsample2x", x.ptr, u.ptr, BF16, self.B, H, W, x.c)
+            u = self.new(4 * x.rows, x.c, self.act)
+            self.emit("ldmb200_upsample2x", x.ptr, u.ptr, self.act, self.B, H, W, x.c)
             out = self.gemm(u, name + ".conv", m.conv.weight, m.conv.bias, 2 * H, 2 * W, ksize=3)
             self.free(u)
             return out
@@ -572,6 +643,7 @@ class _Plan:
         self.pinned.add(id(emb))
         ctx = _Act(_Buf(self.ctx_in.view(torch.uint8).view(-1)), B * max(self.L, 1), self.ctx_in.shape[-1], F32)
         self.pinned.add(id(ctx))
+        self._prepass_vectors(emb, ctx)
         # --- input layout: NCHW fp32 -> channels-last (zero padded to 32 channels on the tensor-core path)
         cin = m.in_channels
         cpad = _tc_cpad(cin) if self.tc else cin
@@ -738,12 +810,12 @@ class UNetModel(nn.Module):
                                  _zero(nn.Conv2d(model_channels, out_channels, 3, padding=1)))
 
         # ---- runtime state (not parameters / buffers: state_dict stays identical to the reference)
-        self.precision = os.environ.get("LDMB200_PRECISION", "bf16")
+        self.precision = os.environ.get("LDMB200_PRECISION", "f16")
         self.use_cuda_graph = os.environ.get("LDMB200_CUDA_GRAPH", "0") == "1"
         self._plans: Dict[tuple, _Plan] = {}
-        self._pack: Optional[_WeightPack] = None
+        self._packs: Dict[int, _WeightPack] = {}   # operand dtype -> packed weights
         self._frozen = 0
-        self._pack_valid = False
+        self._pack_valid: set = set()              # dtypes whose pack matches the current parameters
         self.launches = 0   # kernels launched by forward() so far (bench.py's gpu_launches)
 
     # ---- reference API stubs (openaimodel.py:694-708): the fp16 conversion is a no-op there too -------
@@ -760,20 +832,20 @@ class UNetModel(nn.Module):
     def _apply(self, fn, *a, **k):
         # .to()/.cuda()/.float() may move parameter storage: drop everything that holds raw pointers
         self._plans = {}
-        self._pack = None
-        self._pack_valid = False
+        self._packs = {}
+        self._pack_valid = set()
         return super()._apply(fn, *a, **k)
 
-    def _weight_pack(self) -> _WeightPack:
-        if self._pack is None:
-            self._pack = _WeightPack(self)
-            self._pack_valid = False
-        return self._pack
+    def _weight_pack(self, dtype: int) -> _WeightPack:
+        if dtype not in self._packs:
+            self._packs[dtype] = _WeightPack(self, dtype)
+            self._pack_valid.discard(dtype)
+        return self._packs[dtype]
 
     def invalidate_weight_cache(self):
         """Call after writing parameters in place through ``.data`` while the weights are frozen (``LitEma.copy_to``
         / ``restore``, ema.py:46-76, bump neither ``_version`` nor ``data_ptr``)."""
-        self._pack_valid = False
+        self._pack_valid = set()
 
     @contextlib.contextmanager
     def frozen_weights(self):
@@ -781,7 +853,7 @@ class UNetModel(nn.Module):
         forward.  ``DDIMSampler.sample`` wraps its loop in it; weights cannot change inside a sampling loop."""
         self._frozen += 1
         if self._frozen == 1:
-            self._pack_valid = False
+            self._pack_valid = set()
         try:
             yield self
         finally:
@@ -814,8 +886,8 @@ class UNetModel(nn.Module):
         if timesteps is None or timesteps.dtype.is_floating_point:
             raise ValueError("timesteps must be an integer tensor of shape [N]")
         mode = self.precision
-        if mode not in ("bf16", "fp32"):
-            raise ValueError(f"precision must be 'bf16' or 'fp32', got {mode!r}")
+        if mode not in ("f16", "bf16", "fp32"):
+            raise ValueError(f"precision must be 'f16', 'bf16' or 'fp32', got {mode!r}")
         B, Cin, H, W = x.shape
         assert Cin == self.in_channels, f"expected {self.in_channels} input channels, got {Cin}"
         assert context.dim() == 3 and context.shape[0] == B and context.shape[2] == self.context_dim, \
@@ -831,7 +903,7 @@ class UNetModel(nn.Module):
             if y is not None:
                 assert y.shape == (B,)
                 plan.y_in.copy_(y)
-            need_pack = plan.tc and not (self._frozen and self._pack_valid)
+            need_pack = plan.tc and not (self._frozen and plan.act in self._pack_valid)
             self.launches += len(plan.ops) + (1 if need_pack else 0)
             if self.use_cuda_graph and plan.runs >= 1:
                 if plan.graph is None:
@@ -840,14 +912,14 @@ class UNetModel(nn.Module):
                         plan.run(torch.cuda.current_stream().cuda_stream)
                     plan.graph = g
                 if need_pack:
-                    self._pack.run(torch.cuda.current_stream().cuda_stream)
-                    self._pack_valid = True
+                    plan.pack.run(torch.cuda.current_stream().cuda_stream)
+                    self._pack_valid.add(plan.act)
                 plan.graph.replay()
             else:
                 stream = torch.cuda.current_stream().cuda_stream
                 if need_pack:
-                    self._pack.run(stream)
-                    self._pack_valid = True
+                    plan.pack.run(stream)
+                    self._pack_valid.add(plan.act)
                 plan.run(stream)
             out = plan.out
             if out.dtype != x.dtype:

@@ -14,7 +14,7 @@
  *   - Return value: 0 on success, negative LDMB200_ERR_* otherwise; ldmb200_last_error() returns a
  *     thread-local message.  Nothing throws.
  *   - Activations are channels-last: a feature map is a row-major matrix [B*H*W, C] ("pixels x channels").
- *   - dtype codes: LDMB200_F32 = 0, LDMB200_BF16 = 1.
+ *   - dtype codes: LDMB200_F32 = 0, LDMB200_BF16 = 1, LDMB200_F16 = 2 (IEEE half; conversions saturate).
  */
 #ifndef LDMB200_H_
 #define LDMB200_H_
@@ -29,6 +29,7 @@ extern "C" {
 
 #define LDMB200_F32 0
 #define LDMB200_BF16 1
+#define LDMB200_F16 2
 
 #define LDMB200_ERR_INVALID (-1) /* bad argument / unsupported shape */
 #define LDMB200_ERR_CUDA (-2)    /* CUDA runtime / driver error     */
@@ -65,6 +66,24 @@ int ldmb200_timestep_embedding(const int64_t* t, float* out, int batch, int dim,
  */
 int ldmb200_small_linear(const float* in, int in_ld, const float* w, const float* bias, float* out, int out_ld,
                          int rows, int k, int n, int silu_in, void* stream);
+
+/* The same layer for a whole table of independent (in, W, bias, out) problems in ONE launch: all 17 ResBlock
+ * emb projections of a UNet eval depend only on emb (openaimodel.py:264), all 16 cross-attention value paths only
+ * on the context (attention.py:175-176,193), so each group is one launch.  jobs is a DEVICE array; first_block is
+ * the exclusive prefix sum of ldmb200_small_linear_blocks(rows, n) over the table, total_blocks its total. */
+typedef struct ldmb200_linear_job {
+  const float* in;
+  const float* w;    /* [n, k] row-major (nn.Linear layout) */
+  const float* bias; /* [n] or NULL */
+  float* out;
+  int32_t in_ld, out_ld;
+  int32_t rows, k, n;
+  int32_t silu_in;
+  int32_t first_block;
+  int32_t pad_;
+} ldmb200_linear_job;
+int ldmb200_small_linear_blocks(int rows, int n);
+int ldmb200_small_linear_batched(const ldmb200_linear_job* jobs, int n_jobs, int total_blocks, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * Layout changes at the UNet boundary (openaimodel.py:730,738-742: NCHW fp32 in, NCHW fp32 out).
@@ -161,6 +180,8 @@ typedef struct ldmb200_pack_job {
   int32_t n_pad, c_pad;  /* destination padding (>= n, >= c)                          */
   int32_t row_offset;    /* destination row offset (fused QKV: q rows, k rows, v rows) */
   int32_t block_n;       /* GEGLU permutation tile (kind 1/2)                          */
+  int32_t dst_dtype;     /* LDMB200_BF16 | LDMB200_F16 (kinds 0/1)                      */
+  int32_t pad_;
 } ldmb200_pack_job;
 int ldmb200_pack_weights(const ldmb200_pack_job* jobs, int n_jobs, void* stream);
 
@@ -171,13 +192,14 @@ int ldmb200_pack_weights(const ldmb200_pack_job* jobs, int n_jobs, void* stream)
  *   q[(b*Nq + i)*q_ld + q_off + h*32 + d]; out [B, Nq, out_ld].  Self-attention passes the fused QKV matrix
  *   [B*N, 3C] as all three with offsets 0, C, 2C.
  * _simt: fp32 in/out (precision mode fp32, and the general cross-attention path with a short context);
- * _tc:   bf16 in/out, flash-style on tcgen05 (S and PV in tensor memory, online softmax in fp32).
+ * _tc:   bf16 q/k/v in, out_dtype (bf16 | f16) out, flash-style on tcgen05 (S and PV in tensor memory, online
+ *        softmax in fp32, P in bf16 so the exponent range of fp32 scores is kept).
  */
 int ldmb200_attention_simt(const float* q, int q_ld, int q_off, const float* k, int k_off, const float* v, int v_off,
                            int kv_ld, float* out, int out_ld, int batch, int heads, int nq, int nkv, float scale,
                            void* stream);
-int ldmb200_attention_tc(const void* qkv, int ld, int q_off, int k_off, int v_off, void* out, int out_ld, int batch,
-                         int heads, int n_tokens, float scale, void* stream);
+int ldmb200_attention_tc(const void* qkv, int ld, int q_off, int k_off, int v_off, void* out, int out_ld,
+                         int out_dtype, int batch, int heads, int n_tokens, float scale, void* stream);
 
 #ifdef __cplusplus
 }

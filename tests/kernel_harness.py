@@ -7,7 +7,7 @@ import torch
 import torch.nn.functional as F
 
 from dsml_thesis_b200 import _cabi
-from dsml_thesis_b200._cabi import BF16, F32, GemmDesc, PackJob
+from dsml_thesis_b200._cabi import BF16, F16, F32, GemmDesc, LinearJob, PackJob
 from dsml_thesis_b200.unet import _tc_bn, _tc_cpad, _tc_npad
 
 DEV = "cuda"
@@ -36,8 +36,17 @@ def ptr(t):
     return t.data_ptr() if t is not None else None
 
 
+TORCH_DT = {F32: torch.float32, BF16: torch.bfloat16, F16: torch.float16}
+CODE_DT = {v: k for k, v in TORCH_DT.items()}
+
+
+def rnd16(x, dt):
+    """fp32 -> rounded through the 16-bit operand type dt -> fp32 (what the tensor core sees)."""
+    return x.to(TORCH_DT[dt]).float()
+
+
 # ---------------------------------------------------------------------------------------------
-def pack_weight(w, kind=0, bias=None, parts=None):
+def pack_weight(w, kind=0, bias=None, parts=None, dtype=BF16):
     """fp32 [n, c, k, k] (or [n, c]) -> packed bf16 [n_pad, k*k, c_pad] through ldmb200_pack_weights.
     Returns (packed tensor, packed fp32 bias or None, n_pad, c_pad)."""
     parts = parts or [w]
@@ -46,7 +55,7 @@ def pack_weight(w, kind=0, bias=None, parts=None):
     c = ws[0].shape[1]
     n_tot = sum(p.shape[0] for p in ws)
     n_pad, c_pad = _tc_npad(n_tot), _tc_cpad(c)
-    dst = torch.full((n_pad, ks * ks, c_pad), float("nan"), dtype=torch.bfloat16, device=DEV)
+    dst = torch.full((n_pad, ks * ks, c_pad), float("nan"), dtype=TORCH_DT[dtype], device=DEV)
     fb = torch.full((n_tot,), float("nan"), dtype=torch.float32, device=DEV) if (kind == 1 and bias is not None) else None
     jobs = []
     row = 0
@@ -59,6 +68,7 @@ def pack_weight(w, kind=0, bias=None, parts=None):
     arr = (PackJob * len(jobs))()
     for j, v in zip(arr, jobs):
         (j.src, j.dst, j.kind, j.n, j.c, j.ksize, j.n_pad, j.c_pad, j.row_offset, j.block_n) = v
+        j.dst_dtype = dtype
     dev_jobs = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(DEV)
     _cabi.call("ldmb200_pack_weights", dev_jobs.data_ptr(), len(jobs), stream())
     torch.cuda.synchronize()
@@ -85,11 +95,11 @@ def igemm(mode, a, B, h_in, w_in, w, bias=None, ksize=1, stride=1, upsample=0, a
     n_true = w.shape[0]
     d.a, d.a2 = a.data_ptr(), ptr(a2)
     d.c1, d.c2 = a.shape[1], (a2.shape[1] if a2 is not None else 0)
-    d.a_dtype = BF16 if a.dtype == torch.bfloat16 else F32
+    d.a_dtype = CODE_DT[a.dtype]
     d.batch, d.h_in, d.w_in = B, h_in, w_in
     d.ksize, d.stride, d.upsample = ksize, stride, upsample
     if mode == "tc":
-        wp, fb, n_pad, c_pad = pack_weight(w, kind=1 if geglu else 0, bias=bias)
+        wp, fb, n_pad, c_pad = pack_weight(w, kind=1 if geglu else 0, bias=bias, dtype=d.a_dtype)
         assert c_pad == d.c1 + d.c2 or d.c2 == 0, "test harness: concat inputs must be multiples of 32"
         keep += [wp, fb]
         d.w, d.n = wp.data_ptr(), n_pad
@@ -105,7 +115,7 @@ def igemm(mode, a, B, h_in, w_in, w, bias=None, ksize=1, stride=1, upsample=0, a
     h_eff, w_eff = (2 * h_in, 2 * w_in) if upsample else (h_in, w_in)
     h_out, w_out = (h_eff // 2, w_eff // 2) if stride == 2 else (h_eff, w_eff)
     M = B * h_out * w_out
-    tdt = torch.bfloat16 if out_dtype == BF16 else torch.float32
+    tdt = TORCH_DT[out_dtype]
     if out_nchw:
         out = torch.full((B, n_true, h_out, w_out), float("nan"), dtype=torch.float32, device=DEV)
         d.out, d.out_dtype, d.out_ld, d.out_nchw, d.n_valid = out.data_ptr(), F32, 0, 1, n_true
@@ -141,21 +151,20 @@ def space_to_depth(x_nchw, dtype):
     B, Cc, H, W = x_nchw.shape
     src = to_cl(x_nchw)
     out = torch.empty(B * H * W, Cc, dtype=dtype, device=DEV)
-    _cabi.call("ldmb200_space_to_depth2", src.data_ptr(), out.data_ptr(), BF16 if dtype == torch.bfloat16 else F32, B,
-               H, W, Cc, stream())
+    _cabi.call("ldmb200_space_to_depth2", src.data_ptr(), out.data_ptr(), CODE_DT[dtype], B, H, W, Cc, stream())
     return out
 
 
-def attention(mode, q, k, v, heads, scale):
+def attention(mode, q, k, v, heads, scale, out_dtype=BF16):
     """q [B,Nq,C], k/v [B,Nkv,C] fp32 -> out [B,Nq,C].  tc: self-attention layout (fused QKV, bf16)."""
     B, Nq, Cc = q.shape
     Nkv = k.shape[1]
     if mode == "tc":
         assert Nq == Nkv
         qkv = torch.cat([q, k, v], dim=2).reshape(B * Nq, 3 * Cc).to(torch.bfloat16).contiguous()
-        out = torch.full((B * Nq, Cc), float("nan"), dtype=torch.bfloat16, device=DEV)
-        _cabi.call("ldmb200_attention_tc", qkv.data_ptr(), 3 * Cc, 0, Cc, 2 * Cc, out.data_ptr(), Cc, B, heads, Nq,
-                   float(scale), stream())
+        out = torch.full((B * Nq, Cc), float("nan"), dtype=TORCH_DT[out_dtype], device=DEV)
+        _cabi.call("ldmb200_attention_tc", qkv.data_ptr(), 3 * Cc, 0, Cc, 2 * Cc, out.data_ptr(), Cc, out_dtype, B,
+                   heads, Nq, float(scale), stream())
     else:
         q2, k2, v2 = (t.reshape(-1, Cc).contiguous() for t in (q, k, v))
         out = torch.full((B * Nq, Cc), float("nan"), dtype=torch.float32, device=DEV)
@@ -177,7 +186,7 @@ def attention_reference(q, k, v, heads, scale):
 def groupnorm(x1, x2, gamma, beta, B, hw, eps, silu, out_dtype, want_raw=False):
     """x1/x2 channels-last fp32 matrices.  Returns (y, raw)."""
     c = x1.shape[1] + (x2.shape[1] if x2 is not None else 0)
-    tdt = torch.bfloat16 if out_dtype == BF16 else torch.float32
+    tdt = TORCH_DT[out_dtype]
     y = torch.full((B * hw, c), float("nan"), dtype=tdt, device=DEV)
     raw = torch.full((B * hw, c), float("nan"), dtype=tdt, device=DEV) if want_raw else None
     lib = _cabi.load()
@@ -187,3 +196,22 @@ def groupnorm(x1, x2, gamma, beta, B, hw, eps, silu, out_dtype, want_raw=False):
                ws.data_ptr(), stream())
     torch.cuda.synchronize()
     return y, raw
+
+
+def small_linear_batched(problems):
+    """problems: list of (x [R,K], w [N,K], bias [N] or None, silu).  One launch; returns the outputs."""
+    lib = _cabi.load()
+    arr = (LinearJob * len(problems))()
+    outs, first = [], 0
+    for j, (x, w, b, silu) in zip(arr, problems):
+        rows, k = x.shape
+        n = w.shape[0]
+        o = torch.full((rows, n), float("nan"), device=DEV)
+        outs.append(o)
+        j.in_, j.w, j.bias, j.out = x.data_ptr(), w.data_ptr(), ptr(b), o.data_ptr()
+        j.in_ld, j.out_ld, j.rows, j.k, j.n, j.silu_in, j.first_block = k, n, rows, k, n, int(silu), first
+        first += int(lib.ldmb200_small_linear_blocks(rows, n))
+    table = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(DEV)
+    _cabi.call("ldmb200_small_linear_batched", table.data_ptr(), len(problems), first, stream())
+    torch.cuda.synchronize()
+    return outs

@@ -17,7 +17,7 @@ import torch.nn.functional as F
 pytestmark = pytest.mark.gpu
 
 from dsml_thesis_b200 import _cabi  # noqa: E402
-from dsml_thesis_b200._cabi import BF16, F32  # noqa: E402
+from dsml_thesis_b200._cabi import BF16, F16, F32  # noqa: E402
 
 import kernel_harness as K  # noqa: E402
 from oracle import ldm_oracle as O  # noqa: E402
@@ -36,6 +36,14 @@ def rnd(*shape, scale=1.0):
 
 def bf(x):
     return x.to(torch.bfloat16).float()
+
+
+def r16(x, dt):
+    return K.rnd16(x, dt)
+
+
+#: rel-L2 bound of storing an fp32 result in a 16-bit type (half an ulp, uniformly distributed)
+OUT_TOL = {F32: 1e-5, BF16: 4e-3, F16: 5e-4}
 
 
 # ------------------------------------------------------------------------------------------ elementwise
@@ -84,13 +92,25 @@ def test_elementwise_small_linear(rows, k, n, silu):
     assert K.rel_l2(out, ref) <= 2e-6
 
 
-@pytest.mark.parametrize("B,Cc,H,cpad,dt", [(2, 3, 8, 32, BF16), (2, 9, 16, 32, BF16), (3, 3, 8, 3, F32)])
+def test_elementwise_small_linear_batched():
+    """One launch over a ragged table of layers (the emb / cross-attention pre-pass of the UNet plan)."""
+    shapes = [(64, 640, 160, 1), (64, 640, 640, 1), (2, 512, 320, 0), (64, 320, 320, 0), (1, 64, 32, 0),
+              (130, 96, 70, 1), (64, 1024, 640, 0)]
+    probs = [(rnd(r, k), rnd(n, k, scale=k ** -0.5), rnd(n) if i % 2 == 0 else None, s)
+             for i, (r, k, n, s) in enumerate(shapes)]
+    outs = K.small_linear_batched(probs)
+    for (x, w, b, s), o in zip(probs, outs):
+        ref = F.linear((F.silu(x) if s else x).double(), w.double(), b.double() if b is not None else None).float()
+        assert K.rel_l2(o, ref) <= 2e-6
+
+
+@pytest.mark.parametrize("B,Cc,H,cpad,dt", [(2, 3, 8, 32, BF16), (2, 9, 16, 32, BF16), (3, 3, 8, 3, F32), (2, 3, 8, 32, F16)])
 def test_elementwise_layout_roundtrip(B, Cc, H, cpad, dt):
     x = rnd(B, Cc, H, H)
-    y = torch.full((B * H * H, cpad), float("nan"), dtype=torch.bfloat16 if dt == BF16 else torch.float32, device="cuda")
+    y = torch.full((B * H * H, cpad), float("nan"), dtype=K.TORCH_DT[dt], device="cuda")
     _cabi.call("ldmb200_nchw_to_nhwc", x.data_ptr(), y.data_ptr(), B, Cc, H * H, cpad, dt, K.stream())
     ref = K.to_cl(x)
-    assert torch.equal(y[:, :Cc].float(), bf(ref) if dt == BF16 else ref)
+    assert torch.equal(y[:, :Cc].float(), r16(ref, dt))
     assert (y[:, Cc:] == 0).all()
     if dt == F32:
         back = torch.empty_like(x)
@@ -101,7 +121,8 @@ def test_elementwise_layout_roundtrip(B, Cc, H, cpad, dt):
 @pytest.mark.parametrize("B,c1,c2,H,eps,silu,dt,raw", [
     (2, 160, 0, 64, 1e-5, 1, BF16, False), (2, 320, 160, 32, 1e-5, 1, BF16, True), (1, 640, 640, 16, 1e-5, 1, F32, True),
     (3, 640, 0, 16, 1e-6, 0, F32, False), (2, 32, 0, 8, 1e-6, 0, BF16, False), (2, 64, 32, 4, 1e-5, 1, F32, True),
-    (2, 128, 0, 2, 1e-5, 1, F32, False), (1, 960, 0, 32, 1e-5, 1, BF16, False)])
+    (2, 128, 0, 2, 1e-5, 1, F32, False), (1, 960, 0, 32, 1e-5, 1, BF16, False), (2, 320, 160, 32, 1e-5, 1, F16, True),
+    (2, 160, 0, 64, 1e-6, 0, F16, False)])
 def test_elementwise_groupnorm(B, c1, c2, H, eps, silu, dt, raw):
     hw = H * H
     x1 = rnd(B * hw, c1) * 2 + 0.5
@@ -112,18 +133,30 @@ def test_elementwise_groupnorm(B, c1, c2, H, eps, silu, dt, raw):
     xc = torch.cat([x1, x2], 1) if c2 else x1
     ref = F.group_norm(K.from_cl(xc, B, H, H).double(), 32, g.double(), b.double(), eps)
     ref = K.to_cl(F.silu(ref) if silu else ref)
-    assert K.rel_l2(y, ref) <= (4e-3 if dt == BF16 else 3e-6)
+    assert K.rel_l2(y, ref) <= (OUT_TOL[dt] if dt != F32 else 3e-6)
     if raw:
-        assert torch.equal(r.float(), bf(xc) if dt == BF16 else xc)
+        assert torch.equal(r.float(), r16(xc, dt))
 
 
-@pytest.mark.parametrize("rows,c,dt", [(4096, 160, BF16), (1024, 320, F32), (256, 640, BF16), (5, 32, F32), (77, 1280, F32)])
+@pytest.mark.parametrize("rows,c,dt", [(4096, 160, BF16), (1024, 320, F32), (256, 640, BF16), (5, 32, F32), (77, 1280, F32),
+                                       (4096, 160, F16), (300, 640, F16)])
 def test_elementwise_layernorm(rows, c, dt):
     x, g, b = rnd(rows, c) * 3 + 1, 1 + 0.1 * rnd(c), 0.1 * rnd(c)
-    y = torch.empty(rows, c, dtype=torch.bfloat16 if dt == BF16 else torch.float32, device="cuda")
+    y = torch.empty(rows, c, dtype=K.TORCH_DT[dt], device="cuda")
     _cabi.call("ldmb200_layernorm", x.data_ptr(), g.data_ptr(), b.data_ptr(), y.data_ptr(), dt, rows, c, 1e-5, K.stream())
     ref = F.layer_norm(x.double(), (c,), g.double(), b.double(), 1e-5)
-    assert K.rel_l2(y, ref) <= (4e-3 if dt == BF16 else 2e-6)
+    assert K.rel_l2(y, ref) <= (OUT_TOL[dt] if dt != F32 else 2e-6)
+
+
+def test_elementwise_f16_conversions_saturate():
+    """fp16 stores clamp to +-65504 instead of producing inf (LayerNorm with a huge gain as the generator)."""
+    rows, c = 8, 64
+    x = rnd(rows, c)
+    g, b = torch.full((c,), 1e6, device="cuda"), torch.zeros(c, device="cuda")
+    y = torch.empty(rows, c, dtype=torch.float16, device="cuda")
+    _cabi.call("ldmb200_layernorm", x.data_ptr(), g.data_ptr(), b.data_ptr(), y.data_ptr(), F16, rows, c, 1e-5, K.stream())
+    torch.cuda.synchronize()
+    assert torch.isfinite(y.float()).all() and y.float().abs().max() == 65504.0
 
 
 def test_elementwise_resample_layouts():
@@ -138,12 +171,13 @@ def test_elementwise_resample_layouts():
 
 
 # ------------------------------------------------------------------------------------------ weight packer
+@pytest.mark.parametrize("dt", [BF16, F16])
 @pytest.mark.parametrize("n,c,ks,kind", [(160, 160, 3, 0), (3, 160, 3, 0), (160, 3, 3, 0), (320, 480, 1, 0),
                                          (1280, 160, 1, 1), (256, 32, 1, 1)])
-def test_pack_weights(n, c, ks, kind):
+def test_pack_weights(n, c, ks, kind, dt):
     w = rnd(n, c, ks, ks)
     bias = rnd(n)
-    wp, fb, n_pad, c_pad = K.pack_weight(w, kind=kind, bias=bias)
+    wp, fb, n_pad, c_pad = K.pack_weight(w, kind=kind, bias=bias, dtype=dt)
     ref = torch.zeros(n_pad, ks * ks, c_pad, device="cuda")
     src = w
     if kind == 1:
@@ -151,7 +185,7 @@ def test_pack_weights(n, c, ks, kind):
         src = w[perm]
         assert torch.equal(fb, bias[perm])
     ref[:n, :, :c] = src.permute(0, 2, 3, 1).reshape(n, ks * ks, c)
-    assert torch.equal(wp.float(), bf(ref))
+    assert torch.equal(wp.float(), r16(ref, dt))
 
 
 def test_pack_weights_fused_rows():
@@ -193,12 +227,31 @@ def test_simt_epilogues_and_concat():
 # ------------------------------------------------------------------------------------------ tcgen05 implicit GEMM
 @pytest.mark.parametrize("M,k,n", [(128, 32, 32), (256, 64, 32), (128, 64, 160), (4096, 160, 160), (1024, 320, 960),
                                    (256, 2560, 640), (300, 96, 64), (8192, 160, 1280)])
-def test_tc_gemm_plain(M, k, n):
-    a = rnd(M, k).to(torch.bfloat16)
+@pytest.mark.parametrize("dt", [BF16, F16])
+def test_tc_gemm_plain(M, k, n, dt):
+    a = rnd(M, k).to(K.TORCH_DT[dt])
     w, b = rnd(n, k, 1, 1, scale=k ** -0.5), rnd(n)
     out = K.igemm("tc", a, 1, M, 1, w, b)
-    ref = F.linear(a.double(), bf(w.reshape(n, k)).double(), b.double()).float()
+    ref = F.linear(a.double(), r16(w.reshape(n, k), dt).double(), b.double()).float()
     assert K.rel_l2(out, ref) <= 1e-5
+
+
+@pytest.mark.parametrize("M,k,n,odt", [(4096, 160, 160, F32), (4096, 160, 160, F16), (1000, 320, 320, BF16),
+                                       (8192, 640, 160, F32), (260, 64, 480, F16)])
+def test_tc_gemm_residual_rowvec_every_out_dtype(M, k, n, odt):
+    """The coalesced epilogue: bias + per-sample row vector + fp32 residual, fp32 / bf16 / f16 stores, M not a
+    multiple of the tile, samples of 4 / 100 / 4096 rows (uniform and per-row row-vector lookup)."""
+    for rows_per_sample in (4096, 100, 4):
+        if M % rows_per_sample:
+            continue
+        Bn = M // rows_per_sample
+        a = rnd(M, k).to(torch.float16)
+        w, b = rnd(n, k, 1, 1, scale=k ** -0.5), rnd(n)
+        rv, res = rnd(Bn, n), rnd(M, n)
+        out = K.igemm("tc", a, Bn, rows_per_sample, 1, w, b, rowvec=rv, residual=res, out_dtype=odt)
+        ref = F.linear(a.double(), r16(w.reshape(n, k), F16).double(), b.double()).float()
+        ref = ref + rv.repeat_interleave(rows_per_sample, 0) + res
+        assert K.rel_l2(out, ref) <= OUT_TOL[odt], rows_per_sample
 
 
 @pytest.mark.parametrize("B,cin,cout,H", [(2, 32, 32, 16), (1, 160, 160, 64), (2, 320, 320, 32), (4, 64, 64, 8),
@@ -229,16 +282,18 @@ def test_tc_epilogues():
     out = K.igemm("tc", a, B, H, H, w, b, ksize=3, rowvec=rv, residual=K.to_cl(res))
     ref = K.igemm_reference(x, bf(w), b, rowvec=rv, residual_nchw=res)
     assert K.rel_l2(K.from_cl(out, B, H, H), ref) <= 1e-5
-    out = K.igemm("tc", a, B, H, H, w, b, ksize=3, rowvec=rv, residual=K.to_cl(res), out_dtype=BF16)
-    assert K.rel_l2(K.from_cl(out, B, H, H), ref) <= 4e-3
+    for odt in (BF16, F16):
+        out = K.igemm("tc", a, B, H, H, w, b, ksize=3, rowvec=rv, residual=K.to_cl(res), out_dtype=odt)
+        assert K.rel_l2(K.from_cl(out, B, H, H), ref) <= OUT_TOL[odt]
     # GEGLU with both N tiles (160: C = 160 -> n = 1280; 32: C = 32 -> n = 256)
     for cc in (160, 32):
         xg = bf(rnd(512, cc))
         wg, bg = rnd(8 * cc, cc, 1, 1, scale=cc ** -0.5), rnd(8 * cc)
-        out = K.igemm("tc", xg.to(torch.bfloat16), 1, 512, 1, wg, bg, geglu=True, out_dtype=BF16)
         y = F.linear(xg.double(), bf(wg.reshape(8 * cc, cc)).double(), bg.double())
         va, ga = y.chunk(2, dim=1)
-        assert K.rel_l2(out, (va * F.gelu(ga)).float()) <= 4e-3
+        for odt in (BF16, F16, F32):
+            out = K.igemm("tc", xg.to(torch.bfloat16), 1, 512, 1, wg, bg, geglu=True, out_dtype=odt)
+            assert K.rel_l2(out, (va * F.gelu(ga)).float()) <= OUT_TOL[odt]
     # UNetModel.out: n = 3 padded to 16, fp32 NCHW store
     wo, bo = rnd(3, c, 3, 3, scale=0.05), rnd(3)
     out = K.igemm("tc", a, B, H, H, wo, bo, ksize=3, out_nchw=True)
@@ -255,11 +310,13 @@ def test_attn_simt(B, N, M, heads):
 
 
 @pytest.mark.parametrize("B,N,heads,scale_in", [(1, 128, 1, 1.0), (2, 256, 2, 1.0), (1, 1024, 10, 1.0), (2, 64, 4, 1.0),
-                                                (3, 16, 1, 1.0), (1, 4, 20, 1.0), (1, 4096, 5, 1.0), (2, 320, 2, 3.0)])
-def test_attn_tc(B, N, heads, scale_in):
+                                                (3, 16, 1, 1.0), (1, 4, 20, 1.0), (1, 4096, 5, 1.0), (2, 320, 2, 3.0),
+                                                (2, 512, 3, 1.0), (3, 200, 2, 2.0), (1, 129, 1, 1.0)])
+@pytest.mark.parametrize("odt", [BF16, F16])
+def test_attn_tc(B, N, heads, scale_in, odt):
     c = heads * 32
     q, k, v = (bf(rnd(B, N, c) * scale_in) for _ in range(3))
-    out = K.attention("tc", q, k, v, heads, 32 ** -0.5)
+    out = K.attention("tc", q, k, v, heads, 32 ** -0.5, out_dtype=odt)
     ref = K.attention_reference(q, k, v, heads, 32 ** -0.5)
-    # P is rounded to bf16 before PV and the output is stored as bf16
-    assert K.rel_l2(out, ref) <= 6e-3
+    # P is rounded to bf16 before PV; the output is stored as bf16 / f16
+    assert K.rel_l2(out, ref) <= (6e-3 if odt == BF16 else 4e-3)

@@ -17,7 +17,7 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--hw", type=int, default=64)
     ap.add_argument("--reps", type=int, default=3)
-    ap.add_argument("--precision", default="bf16")
+    ap.add_argument("--precision", default="f16")
     a = ap.parse_args()
     torch.cuda.set_device(0)
     unet = P.UNetModel(**FR_UNET)

@@ -11,7 +11,7 @@ import ctypes as C
 import os
 
 F32, BF16, F16 = 0, 1, 2
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("LDMB200_LIB", os.path.join(_HERE, "libldmb200.so"))
@@ -37,6 +37,7 @@ class GemmDesc(C.Structure):
         ("geglu", C.c_int32),
         ("out", C.c_void_p),
         ("out_dtype", C.c_int32), ("out_ld", C.c_int32), ("out_nchw", C.c_int32), ("n_valid", C.c_int32),
+        ("colstats", C.c_void_p),
     ]
 
 
@@ -77,6 +78,7 @@ SIGNATURES = {
     "ldmb200_nhwc_to_nchw": (_i, [_p, _i, _p, _i, _i, _i, _p]),
     "ldmb200_groupnorm_ws_floats": (_i64, [_i, _i, _i]),
     "ldmb200_groupnorm": (_i, [_p, _i, _p, _i, _p, _p, _p, _p, _i, _i, _i, _i, _f, _i, _p, _p]),
+    "ldmb200_groupnorm_fused": (_i, [_p, _i, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _i, _i, _f, _i, _p, _p]),
     "ldmb200_layernorm": (_i, [_p, _p, _p, _p, _i, _i64, _i, _f, _p]),
     "ldmb200_space_to_depth2": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "ldmb200_upsample2x": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),

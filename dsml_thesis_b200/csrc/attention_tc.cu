@@ -12,9 +12,11 @@
 //   warp  9   : MMA issuer   — S_q = Q_q K^T (M128 N128 K32) into TMEM cols [128q, 128q+128);
 //               O_q = P_q V (M128 N32 K128, V as MN-major B operand straight from the row-major tile) into
 //               TMEM cols [256+32q, +32).  Issue order per KV tile j:  PV0(j) S0(j+1) | PV1(j) S1(j+1)
-// Softmax: two passes over S in TMEM with the next 32-column chunk prefetched (row max with 3-input max on
-// 4 independent chains, then ex2 + row sum on 4 chains); P is written as bf16 into a 128B-swizzled K-major smem
-// tile for the PV MMA; the running output lives in registers (32 fp32) and is rescaled online.
+// Softmax: ONE pass over S in TMEM per KV tile (TMEM read bandwidth, ~64 B/clk/SM, and the ex2 pipe bound the
+// kernel): p = exp2(s*c - ref) against a per-row reference that is only re-based when a tile's row max outgrows it
+// by more than 2^8 (any finite reference is exact after normalisation); the running output accumulates in TMEM
+// across KV tiles (no per-tile read-back / rescale) and is re-based in place (tcgen05.ld/st) on that rare path.
+// P is written as bf16 into a 128B-swizzled K-major smem tile for the PV MMA.
 #include <algorithm>
 
 #include "common.cuh"
@@ -50,18 +52,6 @@ __device__ __forceinline__ uint32_t pack_out16(float lo, float hi, int dt) {
   else
     asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
   return r;
-}
-
-// MN-major B operand (V tile: rows = keys (K dim), 32 contiguous d = N dim), 64B swizzle:
-// 8-key groups are SBO = 512 B apart; N = 32 spans a single 64 B atom so LBO is unused.
-__device__ __forceinline__ uint64_t umma_desc_mnmajor_sw64(uint32_t smem_addr) {
-  uint64_t d = 0;
-  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
-  d |= (uint64_t)1 << 16;
-  d |= (uint64_t)(512u >> 4) << 32;
-  d |= (uint64_t)1 << 46;
-  d |= (uint64_t)4 << 61;
-  return d;
 }
 
 // row max of one 32-column chunk on 4 independent chains; MASK: columns >= valid are ignored
@@ -118,52 +108,55 @@ __device__ __forceinline__ void reg_fence(float (&v)[32]) {
   asm volatile("" : LDM_R8(v, 0), LDM_R8(v, 8), LDM_R8(v, 16), LDM_R8(v, 24)::"memory");
 }
 
-// One KV tile of the online softmax for query row r: reads S (128 fp32 columns at tS) twice, folds the previous
-// tile's P.V (32 columns at tO) into the running output, writes P (bf16) to the swizzled smem tile.
-template <bool MASK>
-__device__ __forceinline__ void softmax_tile(uint32_t tS, uint32_t tO, bool have_prev, int valid, float c_, float& m,
-                                             float& l, float (&o)[32], uint8_t* sP, int r) {
+// One KV tile for query row r, ONE pass over S (128 fp32 columns at tS; TMEM reads are the scarce resource):
+// p = exp2(s*c - mb) against the row's current reference mb (= m_ref*c), the tile's row max and row sum on the
+// side, P (bf16) into the swizzled smem tile.  FIRST: the reference is not known yet — take the max of the
+// first 32 keys (any finite reference is exact after normalisation; the caller re-references on overflow risk).
+template <bool MASK, bool FIRST>
+__device__ __forceinline__ void score_pass(uint32_t tS, int valid, float c_, float& mb, float& tmax, float& lsum,
+                                           uint8_t* sP, int r) {
   float a[32], b[32];
   float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-  // ---- pass 1: row max, next chunk in flight while the current one is reduced
+  float ls[4] = {0.f, 0.f, 0.f, 0.f};
   tmem_ld_32x32(tS, a);
   tmem_wait_regs(a);
   tmem_ld_32x32(tS + 32, b);
   chunk_max<MASK>(a, mx, 0, valid);
-  tmem_wait_regs(b);
-  tmem_ld_32x32(tS + 64, a);
-  chunk_max<MASK>(b, mx, 32, valid);
-  tmem_wait_regs(a);
-  tmem_ld_32x32(tS + 96, b);
-  chunk_max<MASK>(a, mx, 64, valid);
-  tmem_wait_regs(b);
-  chunk_max<MASK>(b, mx, 96, valid);
-  if (have_prev) tmem_ld_32x32(tO, b);  // previous tile's P.V (b is free again)
-  tmem_ld_32x32(tS, a);
-  const float m_new = fmaxf(m, fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])));
-  const float corr = ex2_approx((m - m_new) * c_);  // m = -inf on the first tile -> 0
-  const float mb = m_new * c_;
-  m = m_new;
-  tmem_wait_regs(a);
-  if (have_prev) {
-    reg_fence(b);
-#pragma unroll
-    for (int d = 0; d < 32; ++d) o[d] = (o[d] + b[d]) * corr;
-  }
-  // ---- pass 2: p = exp2(s*c - m*c), row sum, bf16 P tile
-  float ls[4] = {0.f, 0.f, 0.f, 0.f};
-  tmem_ld_32x32(tS + 32, b);
+  if (FIRST) mb = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * c_;
   chunk_exp_store<MASK>(a, ls, c_, mb, 0, valid, sP, r);
   tmem_wait_regs(b);
   tmem_ld_32x32(tS + 64, a);
+  chunk_max<MASK>(b, mx, 32, valid);
   chunk_exp_store<MASK>(b, ls, c_, mb, 1, valid, sP, r);
   tmem_wait_regs(a);
   tmem_ld_32x32(tS + 96, b);
+  chunk_max<MASK>(a, mx, 64, valid);
   chunk_exp_store<MASK>(a, ls, c_, mb, 2, valid, sP, r);
   tmem_wait_regs(b);
+  chunk_max<MASK>(b, mx, 96, valid);
   chunk_exp_store<MASK>(b, ls, c_, mb, 3, valid, sP, r);
-  l = l * corr + ((ls[0] + ls[1]) + (ls[2] + ls[3]));
+  tmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+  lsum = (ls[0] + ls[1]) + (ls[2] + ls[3]);
 }
+
+// 32 fp32 columns of this thread's TMEM lane <- registers (the rare re-referencing of the running output)
+__device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const float* v) {
+  const uint32_t* r = reinterpret_cast<const uint32_t*>(v);
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+        "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+        "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+// how far (in exp2 units) a tile's row max may exceed the row's reference before the row is re-referenced:
+// p <= 2^8 per score, sums stay far inside the fp32 / bf16 exponent range
+constexpr float AT_REREF = 8.0f;
 
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict__ out, int out_ld, int out_dtype,
@@ -210,66 +203,83 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 8) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+    // ===================== TMA producer (warp converged, one elected lane issues) =====================
+    if (elect_one()) {
       mbar_expect_tx(q_full, 2 * AT_TILE_BYTES);
       tma_load_2d(sQ, &tm, q_full, q_off + h * 32, row_base + qb * 256);
       tma_load_2d(sQ + AT_TILE_BYTES, &tm, q_full, q_off + h * 32, row_base + qb * 256 + 128);
-      for (int j = 0; j < n_kv; ++j) {
-        const int s = j % AT_STAGES;
-        mbar_wait(&kv_empty[s], ((j / AT_STAGES) & 1) ^ 1);
+    }
+    __syncwarp();
+    for (int j = 0; j < n_kv; ++j) {
+      const int s = j % AT_STAGES;
+      mbar_wait(&kv_empty[s], ((j / AT_STAGES) & 1) ^ 1);
+      if (elect_one()) {
         mbar_expect_tx(&kv_full[s], 2 * AT_TILE_BYTES);
         tma_load_2d(sK + s * AT_TILE_BYTES, &tm, &kv_full[s], k_off + h * 32, row_base + j * 128);
         tma_load_2d(sV + s * AT_TILE_BYTES, &tm, &kv_full[s], v_off + h * 32, row_base + j * 128);
       }
+      __syncwarp();
     }
   } else if (warp == 9) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 128, 0, 0);
-      constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 32, 0, 1);  // B = V is MN-major
-      const uint32_t q_addr = smem_u32(sQ), p_addr = smem_u32(sP);
-      auto issue_s = [&](int q, int s) {
-        const uint32_t k_addr = smem_u32(sK + s * AT_TILE_BYTES);
+    // ===================== MMA issuer (warp converged, one elected lane issues) =====================
+    // Smem descriptors: constant high word (SBO, version, swizzle mode), low word = (address >> 4) | LBO.
+    constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 128, 0, 0);
+    constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 32, 0, 1);  // B = V is MN-major
+    constexpr uint32_t hi_sw64 = (512u >> 4) | (1u << 14) | (4u << 29);    // Q, K (K-major) and V (MN-major) tiles
+    constexpr uint32_t hi_sw128 = (1024u >> 4) | (1u << 14) | (2u << 29);  // P tile
+    const uint32_t q_lo = ((smem_u32(sQ) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t k_lo = ((smem_u32(sK) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t v_lo = ((smem_u32(sV) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t p_lo = ((smem_u32(sP) & 0x3FFFFu) >> 4) | (1u << 16);
+    auto issue_s = [&](int q, int s) {
 #pragma unroll
-        for (int kk = 0; kk < 2; ++kk)
-          umma_bf16_ss(tmem_base + q * 128, umma_desc_kmajor(q_addr + q * AT_TILE_BYTES + kk * 32, 64),
-                       umma_desc_kmajor(k_addr + kk * 32, 64), idesc_qk, kk > 0);
-      };
-      auto issue_pv = [&](int q, int s) {
-        const uint32_t v_addr = smem_u32(sV + s * AT_TILE_BYTES);
+      for (int kk = 0; kk < 2; ++kk)
+        umma_bf16_ss(tmem_base + q * 128, ((uint64_t)hi_sw64 << 32) | (q_lo + q * (AT_TILE_BYTES >> 4) + kk * 2),
+                     ((uint64_t)hi_sw64 << 32) | (k_lo + s * (AT_TILE_BYTES >> 4) + kk * 2), idesc_qk, kk > 0);
+    };
+    auto issue_pv = [&](int q, int s, bool acc) {
 #pragma unroll
-        for (int t = 0; t < 8; ++t)
-          umma_bf16_ss(tmem_base + 256 + q * 32,
-                       umma_desc_kmajor(p_addr + q * AT_P_BYTES + (t >> 2) * (128 * 128) + (t & 3) * 32, 128),
-                       umma_desc_mnmajor_sw64(v_addr + t * 1024), idesc_pv, t > 0);
-      };
-      mbar_wait(q_full, 0);
-      mbar_wait(&kv_full[0], 0);
-      tc_fence_after();
+      for (int t = 0; t < 8; ++t)
+        umma_bf16_ss(tmem_base + 256 + q * 32,
+                     ((uint64_t)hi_sw128 << 32) | (p_lo + q * (AT_P_BYTES >> 4) + (t >> 2) * ((128 * 128) >> 4) + (t & 3) * 2),
+                     ((uint64_t)hi_sw64 << 32) | (v_lo + s * (AT_TILE_BYTES >> 4) + t * (1024 >> 4)), idesc_pv,
+                     (acc || t > 0) ? 1u : 0u);
+    };
+    mbar_wait(q_full, 0);
+    mbar_wait(&kv_full[0], 0);
+    tc_fence_after();
+    if (elect_one()) {
       issue_s(0, 0);
       umma_commit(&s_full[0]);
       issue_s(1, 0);
       umma_commit(&s_full[1]);
-      for (int j = 0; j < n_kv; ++j) {
-        const int s = j % AT_STAGES, sn = (j + 1) % AT_STAGES;
-        const bool more = j + 1 < n_kv;
-        mbar_wait(&p_full[0], j & 1);
+    }
+    __syncwarp();
+    for (int j = 0; j < n_kv; ++j) {
+      const int s = j % AT_STAGES, sn = (j + 1) % AT_STAGES;
+      const bool more = j + 1 < n_kv;
+      mbar_wait(&p_full[0], j & 1);
+      tc_fence_after();
+      if (elect_one()) issue_pv(0, s, j > 0);
+      __syncwarp();
+      if (more) {
+        mbar_wait(&kv_full[sn], ((j + 1) / AT_STAGES) & 1);
         tc_fence_after();
-        issue_pv(0, s);
-        if (more) {
-          mbar_wait(&kv_full[sn], ((j + 1) / AT_STAGES) & 1);
-          tc_fence_after();
-          issue_s(0, sn);
-        }
+      }
+      if (elect_one()) {
+        if (more) issue_s(0, sn);
         umma_commit(&s_full[0]);
-        mbar_wait(&p_full[1], j & 1);
-        tc_fence_after();
-        issue_pv(1, s);
+      }
+      __syncwarp();
+      mbar_wait(&p_full[1], j & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        issue_pv(1, s, j > 0);
         umma_commit(&kv_empty[s]);  // K_j / V_j are dead once both P.V of tile j have retired
         if (more) issue_s(1, sn);
         umma_commit(&s_full[1]);
       }
+      __syncwarp();
     }
   } else {
     // ===================== softmax warpgroups: thread r <-> query row r of tile q =====================
@@ -278,18 +288,39 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
     const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t tS = tmem_base + lane_sel + q * 128, tO = tmem_base + lane_sel + 256 + q * 32;
     uint8_t* myP = sP + q * AT_P_BYTES;
-    float o[32];
-#pragma unroll
-    for (int d = 0; d < 32; ++d) o[d] = 0.f;
-    float m = -INFINITY, l = 0.f;
+    float mb = 0.f, l = 0.f;  // mb = (row reference) * c: the running output and l are relative to 2^mb
     const int last_valid = n_tok - (n_kv - 1) * 128;  // keys in the last tile (1..128)
     for (int j = 0; j < n_kv; ++j) {
-      mbar_wait(&s_full[q], j & 1);
+      const bool masked = (j == n_kv - 1) && last_valid < 128;
+      mbar_wait(&s_full[q], j & 1);  // S_q(j) complete, and with it P_q.V(j-1): O_q in TMEM is quiescent
       tc_fence_after();
-      if (j == n_kv - 1 && last_valid < 128)
-        softmax_tile<true>(tS, tO, j > 0, last_valid, scale_log2e, m, l, o, myP, r);
-      else
-        softmax_tile<false>(tS, tO, j > 0, 128, scale_log2e, m, l, o, myP, r);
+      float tmax, lsum;
+      if (j == 0) {
+        if (masked) score_pass<true, true>(tS, last_valid, scale_log2e, mb, tmax, lsum, myP, r);
+        else score_pass<false, true>(tS, 128, scale_log2e, mb, tmax, lsum, myP, r);
+      } else {
+        if (masked) score_pass<true, false>(tS, last_valid, scale_log2e, mb, tmax, lsum, myP, r);
+        else score_pass<false, false>(tS, 128, scale_log2e, mb, tmax, lsum, myP, r);
+      }
+      // lazy re-referencing: only when some row's scores outgrew its reference by more than 2^AT_REREF
+      const bool need = fmaf(tmax, scale_log2e, -mb) > AT_REREF;
+      if (__any_sync(0xffffffffu, need)) {
+        const float mb_new = need ? tmax * scale_log2e : mb;
+        const float f = ex2_approx(mb - mb_new);  // 1 for the rows that keep their reference
+        if (j > 0) {
+          float t[32];
+          tmem_ld_32x32(tO, t);
+          tmem_wait_regs(t);
+#pragma unroll
+          for (int d = 0; d < 32; ++d) t[d] *= f;
+          tmem_st_32x32(tO, t);
+        }
+        l *= f;
+        mb = mb_new;
+        if (masked) score_pass<true, false>(tS, last_valid, scale_log2e, mb, tmax, lsum, myP, r);
+        else score_pass<false, false>(tS, 128, scale_log2e, mb, tmax, lsum, myP, r);
+      }
+      l += lsum;
       fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the UMMA (async proxy)
       tc_fence_before();
       mbar_arrive(&p_full[q]);
@@ -297,9 +328,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
     mbar_wait(&s_full[q], n_kv & 1);  // the commit after the last P.V
     tc_fence_after();
     {
-      float tmp[32];
-      tmem_ld_32x32(tO, tmp);
-      tmem_wait_regs(tmp);
+      float o[32];
+      tmem_ld_32x32(tO, o);
+      tmem_wait_regs(o);
       const float inv = 1.0f / l;
       const int qi = qb * 256 + q * 128 + r;
       if (qi < n_tok) {
@@ -308,9 +339,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
         for (int d = 0; d < 32; d += 8) {
           uint32_t w[4];
 #pragma unroll
-          for (int e = 0; e < 4; ++e)
-            w[e] = pack_out16((o[d + 2 * e] + tmp[d + 2 * e]) * inv, (o[d + 2 * e + 1] + tmp[d + 2 * e + 1]) * inv,
-                              out_dtype);
+          for (int e = 0; e < 4; ++e) w[e] = pack_out16(o[d + 2 * e] * inv, o[d + 2 * e + 1] * inv, out_dtype);
           *reinterpret_cast<uint4*>(op + d) = make_uint4(w[0], w[1], w[2], w[3]);
         }
       }

@@ -343,6 +343,45 @@ __global__ void gn_stats_kernel(const float* __restrict__ x1, int c1, const floa
   }
 }
 
+// Fused-statistics path: the GEMM epilogues that wrote x1 / x2 left {sum, sum of squares} per column per 32-row block
+// (ldmb200_gemm_desc.colstats).  One block per (group, sample) folds them in float64 -> ws[b][g] = {mean, rstd}.
+__global__ void __launch_bounds__(128) gn_finalize_kernel(const float* __restrict__ cs1, int c1,
+                                                          const float* __restrict__ cs2, int c2, int hw, int groups,
+                                                          float eps, float* __restrict__ ws) {
+  __shared__ double red[2][4];
+  const int g = blockIdx.x, b = blockIdx.y;
+  const int C = c1 + c2, cpg = C / groups, nrb = hw >> 5;
+  double a = 0.0, q = 0.0;
+  for (int i = threadIdx.x; i < nrb * cpg; i += blockDim.x) {
+    const int rb = i / cpg, c = g * cpg + i % cpg;
+    const size_t blk = (size_t)b * nrb + rb;
+    const float2 v = (c < c1) ? reinterpret_cast<const float2*>(cs1)[blk * c1 + c]
+                              : reinterpret_cast<const float2*>(cs2)[blk * c2 + (c - c1)];
+    a += (double)v.x;
+    q += (double)v.y;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    red[0][threadIdx.x >> 5] = a;
+    red[1][threadIdx.x >> 5] = q;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    a = (red[0][0] + red[0][1]) + (red[0][2] + red[0][3]);
+    q = (red[1][0] + red[1][1]) + (red[1][2] + red[1][3]);
+    const double n = (double)cpg * (double)hw;
+    const double mean = a / n;
+    double var = q / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    ws[((size_t)b * groups + g) * 2] = (float)mean;
+    ws[((size_t)b * groups + g) * 2 + 1] = (float)(1.0 / sqrt(var + (double)eps));
+  }
+}
+
 template <typename T>
 __global__ void gn_apply_kernel(const float* __restrict__ x1, int c1, const float* __restrict__ x2, int c2,
                                 const float* __restrict__ gamma, const float* __restrict__ beta, T* __restrict__ y,
@@ -352,6 +391,11 @@ __global__ void gn_apply_kernel(const float* __restrict__ x1, int c1, const floa
   const int C = c1 + c2, q = C >> 2, cpg = C / groups;
   const int b = blockIdx.y;
   for (int g = threadIdx.x; g < groups; g += blockDim.x) {
+    if (S == 0) {  // fused path: gn_finalize_kernel already reduced the producers' column statistics
+      s_mean[g] = ws[((size_t)b * groups + g) * 2];
+      s_rstd[g] = ws[((size_t)b * groups + g) * 2 + 1];
+      continue;
+    }
     double a = 0.0, c = 0.0;
     for (int s = 0; s < S; ++s) {
       const float* p = ws + (((size_t)b * S + s) * groups + g) * 2;
@@ -595,6 +639,33 @@ int ldmb200_groupnorm(const float* x1, int c1, const float* x2, int c2, const fl
   const int nblk = T;
   LDM_DISPATCH_DTYPE(out_dtype, (gn_apply_kernel<T><<<dim3(nblk, batch), threads, 0, st>>>(
                                     x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw_copy, hw, groups, R, S, eps, silu,
+                                    stats_ws)));
+  LDM_CHECK_LAUNCH("groupnorm apply");
+  return 0;
+}
+
+int ldmb200_groupnorm_fused(const float* x1, int c1, const float* colstats1, const float* x2, int c2,
+                            const float* colstats2, const float* gamma, const float* beta, void* y, void* raw_copy,
+                            int out_dtype, int batch, int hw, int groups, float eps, int silu, float* stats_ws,
+                            void* stream) {
+  const int C = c1 + (x2 ? c2 : 0);
+  if (!x2) c2 = 0;
+  LDM_CHECK_ARG(x1 && colstats1 && (!x2 || colstats2) && gamma && beta && y && stats_ws && batch > 0 && hw > 0,
+                "groupnorm_fused: null pointer / empty");
+  LDM_CHECK_ARG(hw % 32 == 0, "groupnorm_fused: hw=%d must be a multiple of 32 (column statistics are per 32-row block)", hw);
+  LDM_CHECK_ARG(groups > 0 && groups <= 64 && C % groups == 0, "groupnorm_fused: C=%d not divisible by groups=%d", C, groups);
+  LDM_CHECK_ARG(c1 % 4 == 0 && c2 % 4 == 0 && C / 4 <= 1024, "groupnorm_fused: channel counts must be multiples of 4");
+  cudaStream_t st = (cudaStream_t)stream;
+  gn_finalize_kernel<<<dim3(groups, batch), 128, 0, st>>>(colstats1, c1, colstats2, c2, hw, groups, eps, stats_ws);
+  LDM_CHECK_LAUNCH("groupnorm finalize");
+  const int R = gn_rows_per_block(C);
+  const int threads = (C / 4) * R;
+  int T = hw / (R * 4);
+  int want = ceil_div(sm_count() * 4, batch);
+  if (T > want) T = want;
+  if (T < 1) T = 1;
+  LDM_DISPATCH_DTYPE(out_dtype, (gn_apply_kernel<T><<<dim3(T, batch), threads, 0, st>>>(
+                                    x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw_copy, hw, groups, R, 0, eps, silu,
                                     stats_ws)));
   LDM_CHECK_LAUNCH("groupnorm apply");
   return 0;

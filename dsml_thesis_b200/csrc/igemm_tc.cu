@@ -24,7 +24,8 @@ struct TcParams {
   int M;
   int tiles_m, tiles_n;
   int taps, ks, stride, is_conv;
-  int c1_chunks, c2_chunks, ctot;
+  int c1_chunks, c2_chunks, ctot, c1;
+  int c1_tail_k, c2_tail_k;  // MMAs (K = 16 each) of the last chunk of each channel range
   int hw_out, w_out, rows_per_sample;
   const float* bias;
   const float* rowvec;
@@ -35,6 +36,7 @@ struct TcParams {
   int geglu;
   void* out;
   int out_dtype, out_ld, out_nchw, n_valid;
+  float* colstats;  // optional [M/32][n_valid][2]: per 32-row block column sums / sums of squares of the stored values
   uint32_t idesc;  // tcgen05 instruction descriptor (operand format bf16 or f16, M = 128, N = BN)
 };
 
@@ -87,13 +89,15 @@ __device__ __forceinline__ void epi_load_residual(const TcParams& p, float4 (&re
   }
 }
 
-template <bool OUT16, int COLS>
+template <bool OUT16, int COLS, bool STATS = false>
 __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, int pitch, int m0, int col0, int lane,
                                           const float4 (&res)[8], bool has_res, bool add_bias, int tile_sample) {
+  static_assert(!(STATS && OUT16), "column statistics are taken of fp32 outputs only");
+  float sx[4] = {0.f, 0.f, 0.f, 0.f}, sq[4] = {0.f, 0.f, 0.f, 0.f};
   constexpr int CPL = OUT16 ? 8 : 4, LPR = COLS / CPL, RPI = 32 / LPR, NQ = CPL / 4;
   const int lr = lane / LPR, lc = (lane % LPR) * CPL;
   const int col = col0 + lc;
-  if (col >= p.n_valid) return;
+  if (!STATS && col >= p.n_valid) return;  // (STATS: n_valid is a multiple of the chunk width, checked on the host)
   float4 add[NQ];
 #pragma unroll
   for (int q = 0; q < NQ; ++q) {
@@ -138,6 +142,28 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
       *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out) + (size_t)m * p.out_ld + col) = u;
     } else {
       *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)m * p.out_ld + col) = t[0];
+      if (STATS) {
+        sx[0] += t[0].x; sx[1] += t[0].y; sx[2] += t[0].z; sx[3] += t[0].w;
+        sq[0] = fmaf(t[0].x, t[0].x, sq[0]); sq[1] = fmaf(t[0].y, t[0].y, sq[1]);
+        sq[2] = fmaf(t[0].z, t[0].z, sq[2]); sq[3] = fmaf(t[0].w, t[0].w, sq[3]);
+      }
+    }
+  }
+  if (STATS) {
+    // GroupNorm statistics of the tensor being written (K7 fused): the lanes that share a column quad differ in
+    // lane bits >= log2(LPR); fold them, one float2 {sum, sum of squares} per column per 32-row block
+#pragma unroll
+    for (int o = LPR; o < 32; o <<= 1) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        sx[j] += __shfl_xor_sync(0xffffffffu, sx[j], o);
+        sq[j] += __shfl_xor_sync(0xffffffffu, sq[j], o);
+      }
+    }
+    if (lr == 0) {
+      float4* dst = reinterpret_cast<float4*>(p.colstats + ((size_t)(m0 >> 5) * p.n_valid + col) * 2);
+      dst[0] = make_float4(sx[0], sq[0], sx[1], sq[1]);
+      dst[1] = make_float4(sx[2], sq[2], sx[3], sq[3]);
     }
   }
 }
@@ -159,7 +185,6 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int k_iters = p.taps * (p.c1_chunks + p.c2_chunks);
   const int ntiles = p.tiles_m * p.tiles_n;
 
   if (warp == 0 && lane == 0) {
@@ -187,37 +212,39 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // K loop: taps x channel chunks of BK; the last chunk of each channel range may be partial (multiple of 16):
+  // TMA zero-fills the out-of-range channels of the A box, and only `valid/16` MMAs are issued for it.
+  const int nchunks = p.c1_chunks + p.c2_chunks;
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      uint32_t it = 0;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
-        const int m0 = tm * Cfg::BM;
-        int n_img = 0, h0 = 0;
-        if (p.is_conv) {
-          n_img = m0 / p.hw_out;
-          h0 = (m0 % p.hw_out) / p.w_out;
-        }
-        for (int tap = 0; tap < p.taps; ++tap) {
-          int dh = 0, dw = 0, plane = 0;
-          if (p.ks == 3) {
-            const int kh = tap / 3, kw = tap % 3;
-            if (p.stride == 1) {
-              dh = kh - 1;
-              dw = kw - 1;
-            } else {  // stride 2 on space-to-depth planes: row 2*oh+kh-1 -> (parity, index)
-              const int ph = (kh == 1) ? 0 : 1, pw = (kw == 1) ? 0 : 1;
-              dh = (kh == 0) ? -1 : 0;
-              dw = (kw == 0) ? -1 : 0;
-              plane = ph * 2 + pw;
-            }
+    // ===================== TMA producer (whole warp converged, one elected lane issues) =====================
+    uint32_t it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
+      const int m0 = tm * Cfg::BM;
+      int n_img = 0, h0 = 0;
+      if (p.is_conv) {
+        n_img = m0 / p.hw_out;
+        h0 = (m0 % p.hw_out) / p.w_out;
+      }
+      for (int tap = 0; tap < p.taps; ++tap) {
+        int dh = 0, dw = 0, plane = 0;
+        if (p.ks == 3) {
+          const int kh = tap / 3, kw = tap % 3;
+          if (p.stride == 1) {
+            dh = kh - 1;
+            dw = kw - 1;
+          } else {  // stride 2 on space-to-depth planes: row 2*oh+kh-1 -> (parity, index)
+            const int ph = (kh == 1) ? 0 : 1, pw = (kw == 1) ? 0 : 1;
+            dh = (kh == 0) ? -1 : 0;
+            dw = (kw == 0) ? -1 : 0;
+            plane = ph * 2 + pw;
           }
-          const int nchunks = p.c1_chunks + p.c2_chunks;
-          for (int j = 0; j < nchunks; ++j, ++it) {
-            const int s = it % Cfg::STAGES;
-            const uint32_t ph_ = (it / Cfg::STAGES) & 1;
-            mbar_wait(&empty[s], ph_ ^ 1);
+        }
+        for (int j = 0; j < nchunks; ++j, ++it) {
+          const int s = it % Cfg::STAGES;
+          const uint32_t ph_ = (it / Cfg::STAGES) & 1;
+          mbar_wait(&empty[s], ph_ ^ 1);
+          if (elect_one()) {
             mbar_expect_tx(&full[s], Cfg::TX_BYTES);
             const bool second = j >= p.c1_chunks;
             const CUtensorMap* tm_a = second ? &tmA2 : &tmA1;
@@ -226,37 +253,52 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
               tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, dw, h0 + dh, plane, n_img);
             else
               tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, 0, m0, 0, 0);
-            tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &full[s], tap * p.ctot + j * BK, tn * BN);
+            tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &full[s], tap * p.ctot + (second ? p.c1 : 0) + c0, tn * BN);
           }
+          __syncwarp();
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      const uint32_t idesc = p.idesc;
-      uint32_t it = 0, t_iter = 0;
-      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
-        const uint32_t buf = t_iter & 1;
-        mbar_wait(&tempty[buf], ((t_iter >> 1) & 1) ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + buf * BN;
-        for (int k = 0; k < k_iters; ++k, ++it) {
+    // ===================== MMA issuer (whole warp converged, one elected lane issues) =====================
+    // descriptors: the high word is constant, the low word is (address >> 4) | LBO; K advances by 32 B = +2
+    constexpr uint32_t desc_hi = (uint32_t)((8u * Cfg::SW) >> 4) | (1u << 14) | ((Cfg::SW == 128 ? 2u : 4u) << 29);
+    const uint32_t a_lo0 = ((smem_u32(sA) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t b_lo0 = ((smem_u32(sB) & 0x3FFFFu) >> 4) | (1u << 16);
+    const uint32_t idesc = p.idesc;
+    const int kmax1 = p.c1_tail_k, kmax2 = p.c2_tail_k;
+    uint32_t it = 0, t_iter = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
+      const uint32_t buf = t_iter & 1;
+      mbar_wait(&tempty[buf], ((t_iter >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + buf * BN;
+      uint32_t acc = 0;
+      for (int tap = 0; tap < p.taps; ++tap) {
+        for (int j = 0; j < nchunks; ++j, ++it) {
           const int s = it % Cfg::STAGES;
           const uint32_t ph_ = (it / Cfg::STAGES) & 1;
+          const int kmax = (j == p.c1_chunks - 1) ? kmax1 : (j == nchunks - 1) ? kmax2 : BK / 16;
           mbar_wait(&full[s], ph_);
           tc_fence_after();
-          const uint32_t a_addr = smem_u32(sA + s * Cfg::A_BYTES);
-          const uint32_t b_addr = smem_u32(sB + s * Cfg::B_BYTES);
+          if (elect_one()) {
+            const uint32_t a_lo = a_lo0 + s * (Cfg::A_BYTES >> 4), b_lo = b_lo0 + s * (Cfg::B_BYTES >> 4);
 #pragma unroll
-          for (int kk = 0; kk < BK / 16; ++kk) {
-            umma_bf16_ss(d_tmem, umma_desc_kmajor(a_addr + kk * 32, Cfg::SW), umma_desc_kmajor(b_addr + kk * 32, Cfg::SW),
-                         idesc, (k > 0 || kk > 0) ? 1u : 0u);
+            for (int kk = 0; kk < BK / 16; ++kk) {
+              if (kk < kmax) {
+                umma_bf16_ss(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo + 2 * kk), ((uint64_t)desc_hi << 32) | (b_lo + 2 * kk),
+                             idesc, acc);
+                acc = 1;
+              }
+            }
+            umma_commit(&empty[s]);  // frees the smem stage once these MMAs retire
           }
-          umma_commit(&empty[s]);  // frees the smem stage once these MMAs retire
+          __syncwarp();
+          acc = 1;
         }
-        umma_commit(&tfull[buf]);  // accumulator complete -> epilogue
       }
+      if (elect_one()) umma_commit(&tfull[buf]);  // accumulator complete -> epilogue
+      __syncwarp();
     }
   } else {
     // ===================== epilogue (TC_EPI_WARPS warps) =====================
@@ -328,7 +370,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
               bv[4 * j] = t.x; bv[4 * j + 1] = t.y; bv[4 * j + 2] = t.z; bv[4 * j + 3] = t.w;
             }
 #pragma unroll
-            for (int j = 0; j < 16; ++j) v[j] = (v[j] + bv[j]) * gelu_erf_f(v[16 + j] + bv[16 + j]);
+            for (int j = 0; j < 16; ++j) v[j] = (v[j] + bv[j]) * gelu_erf_fast(v[16 + j] + bv[16 + j]);
 #pragma unroll
             for (int j = 0; j < 4; ++j)
               *reinterpret_cast<float4*>(&st[lane * PITCH + j * 4]) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
@@ -347,6 +389,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
         {
           const int col0 = n0 + cc * Cfg::CH;
           if (out16) epi_store<true, Cfg::CH>(p, st, PITCH, m0, col0, lane, res, has_res, true, tile_sample);
+          else if (p.colstats) epi_store<false, Cfg::CH, true>(p, st, PITCH, m0, col0, lane, res, has_res, true, tile_sample);
           else epi_store<false, Cfg::CH>(p, st, PITCH, m0, col0, lane, res, has_res, true, tile_sample);
         }
         __syncwarp();
@@ -405,7 +448,7 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   LDM_CHECK_ARG(d->ksize == 1 || d->ksize == 3, "igemm_tc: ksize must be 1 or 3");
   LDM_CHECK_ARG(d->stride == 1 || (d->stride == 2 && d->ksize == 3), "igemm_tc: stride 2 only for 3x3");
   const int c1 = d->c1, c2 = d->a2 ? d->c2 : 0;
-  LDM_CHECK_ARG(c1 > 0 && c1 % 32 == 0 && c2 % 32 == 0, "igemm_tc: channel counts must be multiples of 32 (c1=%d c2=%d)", c1, c2);
+  LDM_CHECK_ARG(c1 > 0 && c1 % 16 == 0 && c2 % 16 == 0, "igemm_tc: channel counts must be multiples of 16 (c1=%d c2=%d)", c1, c2);
   LDM_CHECK_ARG(d->n > 0 && d->n % 16 == 0, "igemm_tc: n=%d must be a multiple of 16 (pad the packed weights)", d->n);
   const int h_out = d->stride == 2 ? d->h_in / 2 : d->h_in, w_out = d->stride == 2 ? d->w_in / 2 : d->w_in;
   const int hw_out = h_out * w_out;
@@ -432,6 +475,10 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   p.rowvec_uniform = hw_out % 128 == 0;
   p.out_ld = d->out_ld;
   p.out_nchw = d->out_nchw;
+  p.colstats = d->colstats;
+  LDM_CHECK_ARG(!d->colstats || (d->out_dtype == LDMB200_F32 && !d->geglu && !d->out_nchw && p.M % 32 == 0 &&
+                                 d->n % 32 == 0 && (d->n_valid <= 0 || d->n_valid == d->n)),
+                "igemm_tc: colstats needs an fp32 row-major output with M %% 32 == 0 and n %% 32 == 0, unpadded");
   const int n_cols = d->geglu ? d->n / 2 : d->n;
   p.n_valid = d->n_valid > 0 ? d->n_valid : n_cols;
   LDM_CHECK_ARG(d->out_dtype == LDMB200_F32 || d->out_dtype == LDMB200_BF16 || d->out_dtype == LDMB200_F16,
@@ -445,16 +492,17 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   LDM_CHECK_ARG(!(d->out_nchw && (out16 || d->geglu || d->rowvec || d->residual)), "igemm_tc: out_nchw is a plain fp32 store");
   LDM_CHECK_ARG(!(d->geglu && (!d->bias || d->rowvec || d->residual)), "igemm_tc: geglu epilogue takes the packed bias only");
 
-  int BK = (c1 % 64 == 0 && c2 % 64 == 0) ? 64 : 32;
-  if (const char* e = getenv("LDMB200_TC_BK")) {
-    int v = atoi(e);
-    if (v == 32 || (v == 64 && BK == 64)) BK = v;
-  }
+  // BK = 64 (128-byte swizzled rows) for every shape: a channel range that is not a multiple of 64 ends in a
+  // partial chunk (TMA zero-fills the missing channels, the MMA warp issues only valid/16 instructions for it)
+  constexpr int BK = 64;
   int BN = (d->n % 160 == 0) ? 160 : (d->n % 32 == 0) ? 32 : 16;
   LDM_CHECK_ARG(BN != 16 || d->n == 16, "igemm_tc: n=%d unsupported (need multiple of 32, or exactly 16)", d->n);
   LDM_CHECK_ARG(!(d->geglu && BN == 16), "igemm_tc: geglu needs n %% 32 == 0");
-  p.c1_chunks = c1 / BK;
-  p.c2_chunks = c2 / BK;
+  p.c1 = c1;
+  p.c1_chunks = ceil_div(c1, BK);
+  p.c2_chunks = ceil_div(c2, BK);
+  p.c1_tail_k = (c1 - (p.c1_chunks - 1) * BK) / 16;
+  p.c2_tail_k = c2 ? (c2 - (p.c2_chunks - 1) * BK) / 16 : 0;
   p.tiles_m = ceil_div(p.M, 128);
   p.tiles_n = d->n / BN;
   p.idesc = umma_idesc_f16(128, BN, d->a_dtype == LDMB200_F16 ? 0 : 1);
@@ -491,7 +539,7 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
     if (rc) return rc;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  if (BN == 160) return BK == 64 ? launch_tc<160, 64>(tA1, tA2, tB, p, st) : launch_tc<160, 32>(tA1, tA2, tB, p, st);
-  if (BN == 32) return BK == 64 ? launch_tc<32, 64>(tA1, tA2, tB, p, st) : launch_tc<32, 32>(tA1, tA2, tB, p, st);
-  return BK == 64 ? launch_tc<16, 64>(tA1, tA2, tB, p, st) : launch_tc<16, 32>(tA1, tA2, tB, p, st);
+  if (BN == 160) return launch_tc<160, 64>(tA1, tA2, tB, p, st);
+  if (BN == 32) return launch_tc<32, 64>(tA1, tA2, tB, p, st);
+  return launch_tc<16, 64>(tA1, tA2, tB, p, st);
 }

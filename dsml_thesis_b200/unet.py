@@ -286,10 +286,11 @@ class _Arena:
 
 class _Act:
     """A channels-last activation [rows, c] living in an arena buffer."""
-    __slots__ = ("buf", "rows", "c", "dtype")
+    __slots__ = ("buf", "rows", "c", "dtype", "stats")
 
     def __init__(self, buf: _Buf, rows: int, c: int, dtype: int):
         self.buf, self.rows, self.c, self.dtype = buf, rows, c, dtype
+        self.stats: Optional[_Buf] = None   # GroupNorm column statistics left by the producing GEMM epilogue
 
     @property
     def ptr(self) -> int:
@@ -333,6 +334,9 @@ class _Plan:
         for a in acts:
             if a is not None and id(a) not in self.pinned:
                 self.arena.release(a.buf)
+                if a.stats is not None:
+                    self.arena.release(a.stats)
+                    a.stats = None
 
     def emit(self, name: str, *args, flops: float = 0.0, bytes_: float = 0.0, what: str = ""):
         """Appends one launch.  ``flops`` / ``bytes_`` are the ALGORITHMIC work of the launch (no padding, no
@@ -423,6 +427,16 @@ class _Plan:
         c = x1.c + (x2.c if x2 is not None else 0)
         y = self.new(x1.rows, c, self.act)
         raw = self.new(x1.rows, c, self.act) if want_raw else None
+        s1, s2 = x1.stats, (x2.stats if x2 is not None else None)
+        if s1 is not None and (x2 is None or s2 is not None):
+            # statistics were taken by the GEMM epilogues that wrote x1 / x2: finalize + apply, x is read once
+            self.emit("ldmb200_groupnorm_fused", x1.ptr, x1.c, s1.ptr, x2.ptr if x2 is not None else None,
+                      x2.c if x2 is not None else 0, s2.ptr if s2 is not None else None, gn.weight.data_ptr(),
+                      gn.bias.data_ptr(), y.ptr, raw.ptr if raw is not None else None, self.act, self.B, hw,
+                      gn.num_groups, float(gn.eps), silu, self.gn_ws.data_ptr(),
+                      bytes_=x1.rows * c * (4 + 2 * (2 if want_raw else 1)),
+                      what=f"rows{x1.rows} C{c} fused" + (" cat" if x2 is not None else "") + (" raw" if want_raw else ""))
+            return y, raw
         self.emit("ldmb200_groupnorm", x1.ptr, x1.c, x2.ptr if x2 is not None else None,
                   x2.c if x2 is not None else 0, gn.weight.data_ptr(), gn.bias.data_ptr(), y.ptr,
                   raw.ptr if raw is not None else None, self.act, self.B, hw, gn.num_groups, float(gn.eps), silu,
@@ -441,7 +455,7 @@ class _Plan:
              ksize: int = 1, stride: int = 1, upsample: int = 0, rowvec: Optional[Tuple[int, int]] = None,
              residual: Optional[_Act] = None, geglu: bool = False, out_dtype: int = F32,
              out: Optional[Tuple[int, int]] = None, out_nchw_ptr: Optional[int] = None,
-             force_simt: bool = False, n_true: Optional[int] = None) -> Optional[_Act]:
+             force_simt: bool = False, n_true: Optional[int] = None, want_stats: bool = False) -> Optional[_Act]:
         """Emits one (implicit) GEMM: ``ldmb200_igemm_tc`` in bf16 mode, ``ldmb200_igemm_simt`` otherwise.
         ``key`` names the packed weight; ``out=(ptr, ld)`` writes into an existing matrix (fused QKV in fp32
         mode); ``out_nchw_ptr`` selects the fp32 NCHW store of ``UNetModel.out``."""
@@ -476,6 +490,11 @@ class _Plan:
         else:
             res = self.new(rows, n_cols, out_dtype)
             d.out, d.out_dtype, d.out_ld, d.out_nchw, d.n_valid = res.ptr, out_dtype, n_cols, 0, n_cols
+            if (want_stats and tc and out_dtype == F32 and not geglu and (h_out * w_out) % 32 == 0
+                    and n_true % 32 == 0 and d.n == n_true):
+                # GroupNorm statistics of this tensor, taken in the epilogue (consumed by groupnorm())
+                res.stats = self.arena.alloc((rows // 32) * n_true * 2 * 4)
+                d.colstats = res.stats.ptr
         self.keep.append(d)
         k_true = weight.shape[1] * ksize * ksize if weight.dim() >= 2 and n_true == weight.shape[0] else a.c
         self.emit("ldmb200_igemm_tc" if tc else "ldmb200_igemm_simt", C.byref(d), flops=2.0 * rows * n_true * k_true,
@@ -491,7 +510,8 @@ class _Plan:
             raise NotImplementedError("identity skip over a concatenated input is not reachable from UNetModel")
         y1, raw = self.groupnorm(x1, x2, m.in_layers[0], H * W, 1, has_skip)
         c0 = m.in_layers[2]
-        h1 = self.gemm(y1, name + ".in_layers.2", c0.weight, c0.bias, H, W, ksize=3, rowvec=self.vec[id(m)])
+        h1 = self.gemm(y1, name + ".in_layers.2", c0.weight, c0.bias, H, W, ksize=3, rowvec=self.vec[id(m)],
+                       want_stats=True)
         self.free(y1)
         y2, _ = self.groupnorm(h1, None, m.out_layers[0], H * W, 1, False)
         self.free(h1)
@@ -502,7 +522,7 @@ class _Plan:
         else:
             res = x1
         c1 = m.out_layers[3]
-        h2 = self.gemm(y2, name + ".out_layers.3", c1.weight, c1.bias, H, W, ksize=3, residual=res)
+        h2 = self.gemm(y2, name + ".out_layers.3", c1.weight, c1.bias, H, W, ksize=3, residual=res, want_stats=True)
         self.free(y2)
         if has_skip:
             self.free(res)
@@ -573,7 +593,8 @@ class _Plan:
         nb = len(m.transformer_blocks)
         for i, blk in enumerate(m.transformer_blocks):
             t = self.transformer_block(blk, f"{name}.transformer_blocks.{i}", t, H * W, ctx, i == nb - 1)
-        out = self.gemm(t, name + ".proj_out", m.proj_out.weight, m.proj_out.bias, H * W, 1, residual=x)
+        out = self.gemm(t, name + ".proj_out", m.proj_out.weight, m.proj_out.bias, H * W, 1, residual=x,
+                        want_stats=True)
         self.free(t)
         return out
 
@@ -582,7 +603,7 @@ class _Plan:
         if self.tc:
             s = self.new(x.rows, x.c, self.act)
             self.emit("ldmb200_space_to_depth2", x.ptr, s.ptr, self.act, self.B, H, W, x.c)
-            out = self.gemm(s, name + ".op", m.op.weight, m.op.bias, H, W, ksize=3, stride=2)
+            out = self.gemm(s, name + ".op", m.op.weight, m.op.bias, H, W, ksize=3, stride=2, want_stats=True)
             self.free(s)
             return out
         return self.gemm(x, "", m.op.weight, m.op.bias, H, W, ksize=3, stride=2)
@@ -592,7 +613,7 @@ class _Plan:
         if self.tc:
             u = self.new(4 * x.rows, x.c, self.act)
             self.emit("ldmb200_upsample2x", x.ptr, u.ptr, self.act, self.B, H, W, x.c)
-            out = self.gemm(u, name + ".conv", m.conv.weight, m.conv.bias, 2 * H, 2 * W, ksize=3)
+            out = self.gemm(u, name + ".conv", m.conv.weight, m.conv.bias, 2 * H, 2 * W, ksize=3, want_stats=True)
             self.free(u)
             return out
         return self.gemm(x, "", m.conv.weight, m.conv.bias, H, W, ksize=3, upsample=1)
@@ -620,7 +641,7 @@ class _Plan:
                 self.free(h)
                 H, W = 2 * H, 2 * W
             elif isinstance(layer, nn.Conv2d):
-                new = self.gemm(h, lname, layer.weight, layer.bias, H, W, ksize=3)
+                new = self.gemm(h, lname, layer.weight, layer.bias, H, W, ksize=3, want_stats=True)
                 self.free(h)
             else:
                 raise NotImplementedError(f"{lname}: {type(layer).__name__}")

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define LDMB200_ABI_VERSION 1
+#define LDMB200_ABI_VERSION 2
 
 #define LDMB200_F32 0
 #define LDMB200_BF16 1
@@ -108,6 +108,14 @@ int ldmb200_groupnorm(const float* x1, int c1, const float* x2, int c2, const fl
                       void* y, void* raw_copy, int out_dtype, int batch, int hw, int groups, float eps, int silu,
                       float* stats_ws, void* stream);
 
+/* K7 with the statistics pass fused into the producers: colstats1 / colstats2 are the ldmb200_gemm_desc.colstats
+ * buffers the tensor-core GEMMs that wrote x1 / x2 filled ([B*hw/32][c][2] floats); the statistics never re-read
+ * x.  hw % 32 == 0.  Launches: finalize (float64 fold -> stats_ws[b][g] = {mean, rstd}) + apply. */
+int ldmb200_groupnorm_fused(const float* x1, int c1, const float* colstats1, const float* x2, int c2,
+                            const float* colstats2, const float* gamma, const float* beta, void* y, void* raw_copy,
+                            int out_dtype, int batch, int hw, int groups, float eps, int silu, float* stats_ws,
+                            void* stream);
+
 /* K9  LayerNorm over the last dim — nn.LayerNorm(dim) attention.py:203-205 (eps 1e-5, affine).
  * x fp32 [M, C] -> y [M, C] (out_dtype). */
 int ldmb200_layernorm(const float* x, const float* gamma, const float* beta, void* y, int out_dtype, int64_t rows,
@@ -156,6 +164,9 @@ typedef struct ldmb200_gemm_desc {
   int32_t out_ld;
   int32_t out_nchw;      /* 1: out is fp32 NCHW [B, n_valid, H_out*W_out]  (UNetModel.out conv)       */
   int32_t n_valid;       /* columns actually stored (<= n; TC path pads n to a multiple of 16)        */
+  float* colstats;       /* TC path, optional: [M/32][n][2] per 32-row block {sum, sum of squares} of every stored
+                          * column — the GroupNorm statistics of the tensor being written (util.py:214-216), consumed
+                          * by ldmb200_groupnorm_fused so the normalisation never re-reads its input for statistics */
 } ldmb200_gemm_desc;
 
 /* fp32-exact SIMT path (precision mode "fp32": per-step eps rel-L2 <= 1e-4 vs the fp32 reference). */

@@ -1,17 +1,17 @@
 // Fused flash-style self-attention for d_head = 32 on tcgen05 (K5): softmax(q k^T * scale) v per (sample, head)
 // without materialising the [N, N] score matrix the reference builds (attention.py:180-191).
 //
-// The op is MUFU-bound, not tensor-bound: every score needs one ex2 (16/clk/SM) but only 128 tensor flops, so
-// the design goal is to keep the exponent pipe busy all the time.  One CTA per (256-query block, head, sample),
-// one CTA per SM, two 128-query tiles per CTA that ping-pong: while warpgroup 0 runs the softmax of its tile,
-// the tensor pipe computes the scores / P.V of the other tile, and K/V tiles are shared by both.
-//   warps 0-3 : softmax warpgroup of query tile 0     (thread r <-> query row r <-> TMEM lane r)
-//   warps 4-7 : softmax warpgroup of query tile 1
-//   warp  8   : TMA producer — both Q tiles once, then K/V tiles (128 keys x 32) through a 3-stage ring, all from
-//               the fused QKV matrix [B*N, 3C] through one 2-D tensor map (64B-swizzled K-major rows of 32 x 16 bit)
-//   warp  9   : MMA issuer   — S_q = Q_q K^T (M128 N128 K32) into TMEM cols [128q, 128q+128);
-//               O_q = P_q V (M128 N32 K128, V as MN-major B operand straight from the row-major tile) into
-//               TMEM cols [256+32q, +32).  Issue order per KV tile j:  PV0(j) S0(j+1) | PV1(j) S1(j+1)
+// The op is MUFU / TMEM-read bound, not tensor-bound: every score needs one ex2 (16/clk/SM) and 4 bytes of TMEM
+// read (64 B/clk/SM) but only 128 tensor flops, so the design goal is to keep the exponent pipe busy all the time.
+// One CTA per (384-query block, head, sample), one CTA per SM, three 128-query tiles per CTA (three softmax
+// warpgroups = 3 warps per scheduler to hide the ex2 / TMEM latencies); keys advance in 64-key steps with S and P
+// double-buffered per query tile, so the tensor pipe always works one step ahead of every softmax warpgroup.
+//   warps 0-11 : softmax warpgroup q = warp / 4   (thread r <-> query row r <-> TMEM lane r)
+//   warp  12   : TMA producer — the Q tiles once, then K/V tiles (128 keys x 32) through a 3-stage ring, all from
+//                the fused QKV matrix [B*N, 3C] through one 2-D tensor map (64B-swizzled K-major rows of 32 x 16 bit)
+//   warp  13   : MMA issuer   — S_q(i) = Q_q K(i)^T (M128 N64 K32) into TMEM cols q*128 + (i&1)*64;
+//                O_q += P_q(i) V(i) (M128 N32 K64, V as MN-major B operand straight from the row-major tile) into
+//                TMEM cols 384 + 32q.  Per step i and tile q: wait P_q(i) -> issue P.V_q(i), S_q(i+2), commit.
 // Softmax: ONE pass over S in TMEM per KV tile (TMEM read bandwidth, ~64 B/clk/SM, and the ex2 pipe bound the
 // kernel): p = exp2(s*c - ref) against a per-row reference that is only re-based when a tile's row max outgrows it
 // by more than 2^8 (any finite reference is exact after normalisation); the running output accumulates in TMEM
@@ -23,11 +23,14 @@
 
 namespace ldm {
 
-constexpr int AT_THREADS = 320;
+constexpr int AT_NQ = 3;                      // 128-query tiles per CTA (softmax warpgroups)
+constexpr int AT_THREADS = 32 * (4 * AT_NQ + 2);
+constexpr int AT_TMA_WARP = 4 * AT_NQ, AT_MMA_WARP = 4 * AT_NQ + 1;
+constexpr int AT_O_COL = AT_NQ * 128;          // TMEM: S_q buffers at q*128 + u*64, O_q at AT_O_COL + q*32
 constexpr int AT_STAGES = 3;
 constexpr int AT_TILE_BYTES = 128 * 32 * 2;  // 8 KiB: 128 rows x 32 16-bit values
 constexpr int AT_P_BYTES = 2 * 128 * 128;    // two K-major chunks of [128 x 64] bf16, 128B swizzle
-constexpr int AT_SMEM = 2 * AT_TILE_BYTES + 2 * AT_STAGES * AT_TILE_BYTES + 2 * AT_P_BYTES + 16 * 8 + 16 + 1024;
+constexpr int AT_SMEM = AT_NQ * AT_TILE_BYTES + 2 * AT_STAGES * AT_TILE_BYTES + AT_NQ * AT_P_BYTES + 32 * 8 + 16 + 1024;
 constexpr int AT_TMEM_COLS = 512;
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -108,8 +111,8 @@ __device__ __forceinline__ void reg_fence(float (&v)[32]) {
   asm volatile("" : LDM_R8(v, 0), LDM_R8(v, 8), LDM_R8(v, 16), LDM_R8(v, 24)::"memory");
 }
 
-// One KV tile for query row r, ONE pass over S (128 fp32 columns at tS; TMEM reads are the scarce resource):
-// p = exp2(s*c - mb) against the row's current reference mb (= m_ref*c), the tile's row max and row sum on the
+// One 64-key step for query row r, ONE pass over S (64 fp32 columns at tS; TMEM reads are the scarce resource):
+// p = exp2(s*c - mb) against the row's current reference mb (= m_ref*c), the step's row max and row sum on the
 // side, P (bf16) into the swizzled smem tile.  FIRST: the reference is not known yet — take the max of the
 // first 32 keys (any finite reference is exact after normalisation; the caller re-references on overflow risk).
 template <bool MASK, bool FIRST>
@@ -119,22 +122,14 @@ __device__ __forceinline__ void score_pass(uint32_t tS, int valid, float c_, flo
   float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
   float ls[4] = {0.f, 0.f, 0.f, 0.f};
   tmem_ld_32x32(tS, a);
-  tmem_wait_regs(a);
   tmem_ld_32x32(tS + 32, b);
+  tmem_wait_regs(a);
+  reg_fence(b);
   chunk_max<MASK>(a, mx, 0, valid);
   if (FIRST) mb = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * c_;
   chunk_exp_store<MASK>(a, ls, c_, mb, 0, valid, sP, r);
-  tmem_wait_regs(b);
-  tmem_ld_32x32(tS + 64, a);
   chunk_max<MASK>(b, mx, 32, valid);
   chunk_exp_store<MASK>(b, ls, c_, mb, 1, valid, sP, r);
-  tmem_wait_regs(a);
-  tmem_ld_32x32(tS + 96, b);
-  chunk_max<MASK>(a, mx, 64, valid);
-  chunk_exp_store<MASK>(a, ls, c_, mb, 2, valid, sP, r);
-  tmem_wait_regs(b);
-  chunk_max<MASK>(b, mx, 96, valid);
-  chunk_exp_store<MASK>(b, ls, c_, mb, 3, valid, sP, r);
   tmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
   lsum = (ls[0] + ls[1]) + (ls[2] + ls[3]);
 }
@@ -164,31 +159,32 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sQ = smem;                               // 2 tiles (256 rows), one TMA box
-  uint8_t* sK = sQ + 2 * AT_TILE_BYTES;             // AT_STAGES tiles
+  uint8_t* sK = sQ + AT_NQ * AT_TILE_BYTES;             // AT_STAGES tiles
   uint8_t* sV = sK + AT_STAGES * AT_TILE_BYTES;     // AT_STAGES tiles
   uint8_t* sP = sV + AT_STAGES * AT_TILE_BYTES;     // 2 x 32 KiB, 1024-aligned (8 x 8 KiB offset)
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * AT_P_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + AT_NQ * AT_P_BYTES);
   uint64_t* q_full = bars;
   uint64_t* kv_full = bars + 1;                     // [AT_STAGES]
   uint64_t* kv_empty = kv_full + AT_STAGES;         // [AT_STAGES]
-  uint64_t* s_full = kv_empty + AT_STAGES;          // [2]  S_q(j) ready (and everything issued before it: P.V(j-1))
-  uint64_t* p_full = s_full + 2;                    // [2]  P_q(j) written, S_q(j) and O_q(j-1) consumed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_full + 2);
+  uint64_t* s_full = kv_empty + AT_STAGES;          // [2 q][2 buf]  S_q(i) ready (and every MMA issued before it)
+  uint64_t* p_full = s_full + 2 * AT_NQ;                    // [2 q][2 buf]  P_q(i) written, S_q(i) consumed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_full + 2 * AT_NQ);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qb = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
-  const int n_kv = (n_tok + 127) / 128;
+  const int n_kv = (n_tok + 127) / 128;      // 128-key K/V tiles (TMA stages)
+  const int n_steps = (n_tok + 63) / 64;     // 64-key softmax / MMA steps: S and P are double-buffered per query tile
   const int row_base = b * n_tok;  // first row of this sample in the [B*N, ld] matrix
 
-  if (warp == 8 && lane == 0) prefetch_tmap(&tm);
-  if (warp == 9) {
+  if (warp == AT_TMA_WARP && lane == 0) prefetch_tmap(&tm);
+  if (warp == AT_MMA_WARP) {
     if (lane == 0) {
       mbar_init(q_full, 1);
       for (int s = 0; s < AT_STAGES; ++s) {
         mbar_init(&kv_full[s], 1);
         mbar_init(&kv_empty[s], 1);
       }
-      for (int q = 0; q < 2; ++q) {
+      for (int q = 0; q < 2 * AT_NQ; ++q) {
         mbar_init(&s_full[q], 1);
         mbar_init(&p_full[q], 128);
       }
@@ -202,12 +198,14 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 8) {
+  // query tiles of this CTA that hold real rows (the last CTA of a sample may have fewer than AT_NQ)
+  const int nq = min(AT_NQ, (n_tok - qb * (AT_NQ * 128) + 127) / 128);
+  if (warp == AT_TMA_WARP) {
     // ===================== TMA producer (warp converged, one elected lane issues) =====================
     if (elect_one()) {
-      mbar_expect_tx(q_full, 2 * AT_TILE_BYTES);
-      tma_load_2d(sQ, &tm, q_full, q_off + h * 32, row_base + qb * 256);
-      tma_load_2d(sQ + AT_TILE_BYTES, &tm, q_full, q_off + h * 32, row_base + qb * 256 + 128);
+      mbar_expect_tx(q_full, nq * AT_TILE_BYTES);
+      for (int q = 0; q < nq; ++q)
+        tma_load_2d(sQ + q * AT_TILE_BYTES, &tm, q_full, q_off + h * 32, row_base + qb * (AT_NQ * 128) + q * 128);
     }
     __syncwarp();
     for (int j = 0; j < n_kv; ++j) {
@@ -220,10 +218,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
       }
       __syncwarp();
     }
-  } else if (warp == 9) {
+  } else if (warp == AT_MMA_WARP) {
     // ===================== MMA issuer (warp converged, one elected lane issues) =====================
     // Smem descriptors: constant high word (SBO, version, swizzle mode), low word = (address >> 4) | LBO.
-    constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 128, 0, 0);
+    constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 64, 0, 0);
     constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 32, 0, 1);  // B = V is MN-major
     constexpr uint32_t hi_sw64 = (512u >> 4) | (1u << 14) | (4u << 29);    // Q, K (K-major) and V (MN-major) tiles
     constexpr uint32_t hi_sw128 = (1024u >> 4) | (1u << 14) | (2u << 29);  // P tile
@@ -231,83 +229,98 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
     const uint32_t k_lo = ((smem_u32(sK) & 0x3FFFFu) >> 4) | (1u << 16);
     const uint32_t v_lo = ((smem_u32(sV) & 0x3FFFFu) >> 4) | (1u << 16);
     const uint32_t p_lo = ((smem_u32(sP) & 0x3FFFFu) >> 4) | (1u << 16);
-    auto issue_s = [&](int q, int s) {
+    // S_q(i) = Q_q . K(keys 64 i .. 64 i + 63)^T  -> TMEM columns q*128 + (i&1)*64
+    auto issue_s = [&](int q, int i) {
+      const int st = (i >> 1) % AT_STAGES, hf = i & 1;
 #pragma unroll
       for (int kk = 0; kk < 2; ++kk)
-        umma_bf16_ss(tmem_base + q * 128, ((uint64_t)hi_sw64 << 32) | (q_lo + q * (AT_TILE_BYTES >> 4) + kk * 2),
-                     ((uint64_t)hi_sw64 << 32) | (k_lo + s * (AT_TILE_BYTES >> 4) + kk * 2), idesc_qk, kk > 0);
+        umma_bf16_ss(tmem_base + q * 128 + hf * 64, ((uint64_t)hi_sw64 << 32) | (q_lo + q * (AT_TILE_BYTES >> 4) + kk * 2),
+                     ((uint64_t)hi_sw64 << 32) | (k_lo + st * (AT_TILE_BYTES >> 4) + hf * (4096 >> 4) + kk * 2),
+                     idesc_qk, kk > 0);
     };
-    auto issue_pv = [&](int q, int s, bool acc) {
+    // O_q += P_q(i) . V(keys 64 i ..)   (first step overwrites)
+    auto issue_pv = [&](int q, int i) {
+      const int st = (i >> 1) % AT_STAGES, hf = i & 1;
 #pragma unroll
-      for (int t = 0; t < 8; ++t)
-        umma_bf16_ss(tmem_base + 256 + q * 32,
-                     ((uint64_t)hi_sw128 << 32) | (p_lo + q * (AT_P_BYTES >> 4) + (t >> 2) * ((128 * 128) >> 4) + (t & 3) * 2),
-                     ((uint64_t)hi_sw64 << 32) | (v_lo + s * (AT_TILE_BYTES >> 4) + t * (1024 >> 4)), idesc_pv,
-                     (acc || t > 0) ? 1u : 0u);
+      for (int t = 0; t < 4; ++t)
+        umma_bf16_ss(tmem_base + AT_O_COL + q * 32,
+                     ((uint64_t)hi_sw128 << 32) | (p_lo + q * (AT_P_BYTES >> 4) + hf * ((128 * 128) >> 4) + t * 2),
+                     ((uint64_t)hi_sw64 << 32) | (v_lo + st * (AT_TILE_BYTES >> 4) + (hf * 4 + t) * (1024 >> 4)), idesc_pv,
+                     (i > 0 || t > 0) ? 1u : 0u);
     };
     mbar_wait(q_full, 0);
     mbar_wait(&kv_full[0], 0);
     tc_fence_after();
     if (elect_one()) {
-      issue_s(0, 0);
-      umma_commit(&s_full[0]);
-      issue_s(1, 0);
-      umma_commit(&s_full[1]);
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        if (i < n_steps) {
+          for (int q = 0; q < nq; ++q) {
+            issue_s(q, i);
+            umma_commit(&s_full[q * 2 + i]);
+          }
+        }
+      }
     }
     __syncwarp();
-    for (int j = 0; j < n_kv; ++j) {
-      const int s = j % AT_STAGES, sn = (j + 1) % AT_STAGES;
-      const bool more = j + 1 < n_kv;
-      mbar_wait(&p_full[0], j & 1);
-      tc_fence_after();
-      if (elect_one()) issue_pv(0, s, j > 0);
-      __syncwarp();
-      if (more) {
-        mbar_wait(&kv_full[sn], ((j + 1) / AT_STAGES) & 1);
+    for (int i = 0; i < n_steps; ++i) {
+      const int u = i & 1;
+      const uint32_t par = (i >> 1) & 1;
+      const bool more = i + 2 < n_steps;
+      const bool tile_done = u == 1 || i == n_steps - 1;  // last step that reads K/V tile i >> 1
+      for (int q = 0; q < nq; ++q) {
+        mbar_wait(&p_full[q * 2 + u], par);
         tc_fence_after();
+        if (elect_one()) issue_pv(q, i);
+        __syncwarp();
+        if (q == 0 && more && u == 0) {  // first use of K/V tile (i + 2) >> 1
+          const int jn = (i + 2) >> 1;
+          mbar_wait(&kv_full[jn % AT_STAGES], (jn / AT_STAGES) & 1);
+          tc_fence_after();
+        }
+        if (elect_one()) {
+          if (q == nq - 1 && tile_done) umma_commit(&kv_empty[(i >> 1) % AT_STAGES]);
+          if (more) issue_s(q, i + 2);
+          umma_commit(&s_full[q * 2 + u]);  // always: it also tells the softmax warps that P.V(i) has landed
+        }
+        __syncwarp();
       }
-      if (elect_one()) {
-        if (more) issue_s(0, sn);
-        umma_commit(&s_full[0]);
-      }
-      __syncwarp();
-      mbar_wait(&p_full[1], j & 1);
-      tc_fence_after();
-      if (elect_one()) {
-        issue_pv(1, s, j > 0);
-        umma_commit(&kv_empty[s]);  // K_j / V_j are dead once both P.V of tile j have retired
-        if (more) issue_s(1, sn);
-        umma_commit(&s_full[1]);
-      }
-      __syncwarp();
     }
   } else {
     // ===================== softmax warpgroups: thread r <-> query row r of tile q =====================
     const int q = warp >> 2;
     const int r = threadIdx.x & 127;  // == TMEM lane
     const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
-    const uint32_t tS = tmem_base + lane_sel + q * 128, tO = tmem_base + lane_sel + 256 + q * 32;
+    const uint32_t tS = tmem_base + lane_sel + q * 128, tO = tmem_base + lane_sel + AT_O_COL + q * 32;
     uint8_t* myP = sP + q * AT_P_BYTES;
     float mb = 0.f, l = 0.f;  // mb = (row reference) * c: the running output and l are relative to 2^mb
-    const int last_valid = n_tok - (n_kv - 1) * 128;  // keys in the last tile (1..128)
-    for (int j = 0; j < n_kv; ++j) {
-      const bool masked = (j == n_kv - 1) && last_valid < 128;
-      mbar_wait(&s_full[q], j & 1);  // S_q(j) complete, and with it P_q.V(j-1): O_q in TMEM is quiescent
+    const int last_valid = n_tok - (n_steps - 1) * 64;  // keys in the last step (1..64)
+    const int my_steps = q < nq ? n_steps : 0;  // a query tile past the end of the sample does nothing
+    for (int i = 0; i < my_steps; ++i) {
+      const int u = i & 1;
+      const bool masked = (i == n_steps - 1) && last_valid < 64;
+      const uint32_t tSu = tS + u * 64;
+      uint8_t* Pu = myP + u * (128 * 128);
+      mbar_wait(&s_full[q * 2 + u], (i >> 1) & 1);  // S_q(i) complete (and P_q.V(i-2): the P buffer is free again)
       tc_fence_after();
       float tmax, lsum;
-      if (j == 0) {
-        if (masked) score_pass<true, true>(tS, last_valid, scale_log2e, mb, tmax, lsum, myP, r);
-        else score_pass<false, true>(tS, 128, scale_log2e, mb, tmax, lsum, myP, r);
+      if (i == 0) {
+        if (masked) score_pass<true, true>(tSu, last_valid, scale_log2e, mb, tmax, lsum, Pu, r);
+        else score_pass<false, true>(tSu, 64, scale_log2e, mb, tmax, lsum, Pu, r);
       } else {
-        if (masked) score_pass<true, false>(tS, last_valid, scale_log2e, mb, tmax, lsum, myP, r);
-        else score_pass<false, false>(tS, 128, scale_log2e, mb, tmax, lsum, myP, r);
+        if (masked) score_pass<true, false>(tSu, last_valid, scale_log2e, mb, tmax, lsum, Pu, r);
+        else score_pass<false, false>(tSu, 64, scale_log2e, mb, tmax, lsum, Pu, r);
       }
       // lazy re-referencing: only when some row's scores outgrew its reference by more than 2^AT_REREF
       const bool need = fmaf(tmax, scale_log2e, -mb) > AT_REREF;
       if (__any_sync(0xffffffffu, need)) {
         const float mb_new = need ? tmax * scale_log2e : mb;
         const float f = ex2_approx(mb - mb_new);  // 1 for the rows that keep their reference
-        if (j > 0) {
+        if (i > 0) {
+          // the output is rescaled in place: P.V(i-1) must have landed first (its commit is s_full of step i+1,
+          // issued even when there is no such step); P.V(i) cannot start before this thread arrives on p_full
+          mbar_wait(&s_full[q * 2 + (u ^ 1)], (((i - 1) >> 1) + 1) & 1);
+          tc_fence_after();
           float t[32];
           tmem_ld_32x32(tO, t);
           tmem_wait_regs(t);
@@ -317,22 +330,22 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
         }
         l *= f;
         mb = mb_new;
-        if (masked) score_pass<true, false>(tS, last_valid, scale_log2e, mb, tmax, lsum, myP, r);
-        else score_pass<false, false>(tS, 128, scale_log2e, mb, tmax, lsum, myP, r);
+        if (masked) score_pass<true, false>(tSu, last_valid, scale_log2e, mb, tmax, lsum, Pu, r);
+        else score_pass<false, false>(tSu, 64, scale_log2e, mb, tmax, lsum, Pu, r);
       }
       l += lsum;
       fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the UMMA (async proxy)
       tc_fence_before();
-      mbar_arrive(&p_full[q]);
+      mbar_arrive(&p_full[q * 2 + u]);
     }
-    mbar_wait(&s_full[q], n_kv & 1);  // the commit after the last P.V
-    tc_fence_after();
-    {
+    if (q < nq) {
+      mbar_wait(&s_full[q * 2 + ((n_steps - 1) & 1)], (((n_steps - 1) >> 1) + 1) & 1);  // the commit after the last P.V
+      tc_fence_after();
       float o[32];
       tmem_ld_32x32(tO, o);
       tmem_wait_regs(o);
       const float inv = 1.0f / l;
-      const int qi = qb * 256 + q * 128 + r;
+      const int qi = qb * (AT_NQ * 128) + q * 128 + r;
       if (qi < n_tok) {
         uint16_t* op = out + (size_t)(row_base + qi) * out_ld + h * 32;
 #pragma unroll
@@ -348,7 +361,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) {
+  if (warp == AT_MMA_WARP) {
     tc_fence_after();
     tmem_dealloc(tmem_base, AT_TMEM_COLS);
   }
@@ -381,7 +394,7 @@ extern "C" int ldmb200_attention_tc(const void* qkv, int ld, int q_off, int k_of
   uint32_t box[2] = {32, 128};
   int rc = make_tensor_map_bf16(&tm, qkv, 2, dims, str, box, 64);
   if (rc) return rc;
-  dim3 grid(ceil_div(n_tokens, 256), heads, batch);
+  dim3 grid(ceil_div(n_tokens, AT_NQ * 128), heads, batch);
   const float scale_log2e = scale * 1.4426950408889634f;
   attention_tc_kernel<<<grid, AT_THREADS, AT_SMEM, (cudaStream_t)stream>>>(tm, (uint16_t*)out, out_ld, out_dtype,
                                                                            n_tokens, q_off, k_off, v_off, scale_log2e);

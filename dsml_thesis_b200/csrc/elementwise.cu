@@ -660,11 +660,11 @@ int ldmb200_groupnorm_fused(const float* x1, int c1, const float* colstats1, con
   LDM_CHECK_LAUNCH("groupnorm finalize");
   const int R = gn_rows_per_block(C);
   const int threads = (C / 4) * R;
-  int T = hw / (R * 4);
+  int nblk = hw / (R * 4);
   int want = ceil_div(sm_count() * 4, batch);
-  if (T > want) T = want;
-  if (T < 1) T = 1;
-  LDM_DISPATCH_DTYPE(out_dtype, (gn_apply_kernel<T><<<dim3(T, batch), threads, 0, st>>>(
+  if (nblk > want) nblk = want;
+  if (nblk < 1) nblk = 1;
+  LDM_DISPATCH_DTYPE(out_dtype, (gn_apply_kernel<T><<<dim3(nblk, batch), threads, 0, st>>>(
                                     x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw_copy, hw, groups, R, 0, eps, silu,
                                     stats_ws)));
   LDM_CHECK_LAUNCH("groupnorm apply");

@@ -160,7 +160,7 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
         sq[j] += __shfl_xor_sync(0xffffffffu, sq[j], o);
       }
     }
-    if (lr == 0) {
+    if (lr == 0 && m0 < p.M) {  // (M % 32 == 0: a 32-row block is entirely inside or outside the matrix)
       float4* dst = reinterpret_cast<float4*>(p.colstats + ((size_t)(m0 >> 5) * p.n_valid + col) * 2);
       dst[0] = make_float4(sx[0], sq[0], sx[1], sq[1]);
       dst[1] = make_float4(sx[2], sq[2], sx[3], sq[3]);

@@ -87,7 +87,7 @@ def geglu_perm(n_total, block_n):
 
 
 def igemm(mode, a, B, h_in, w_in, w, bias=None, ksize=1, stride=1, upsample=0, a2=None, rowvec=None,
-          residual=None, geglu=False, out_dtype=F32, out_nchw=False):
+          residual=None, geglu=False, out_dtype=F32, out_nchw=False, colstats=None):
     """mode 'simt' | 'tc'.  a / a2: channels-last matrices [B*h*w, c] (fp32 for simt, bf16 for tc; for tc+stride 2
     ``a`` is the space-to-depth layout).  w: fp32 [n, c1+c2, k, k].  Returns the output tensor."""
     d = GemmDesc()
@@ -122,6 +122,8 @@ def igemm(mode, a, B, h_in, w_in, w, bias=None, ksize=1, stride=1, upsample=0, a
     else:
         out = torch.full((M, n_cols), float("nan"), dtype=tdt, device=DEV)
         d.out, d.out_dtype, d.out_ld, d.out_nchw, d.n_valid = out.data_ptr(), out_dtype, n_cols, 0, n_cols
+    if colstats is not None:
+        d.colstats = colstats.data_ptr()
     _cabi.call("ldmb200_igemm_tc" if mode == "tc" else "ldmb200_igemm_simt", C.byref(d), stream())
     torch.cuda.synchronize()
     return out
@@ -194,6 +196,21 @@ def groupnorm(x1, x2, gamma, beta, B, hw, eps, silu, out_dtype, want_raw=False):
     _cabi.call("ldmb200_groupnorm", x1.data_ptr(), x1.shape[1], ptr(x2), x2.shape[1] if x2 is not None else 0,
                gamma.data_ptr(), beta.data_ptr(), y.data_ptr(), ptr(raw), out_dtype, B, hw, 32, float(eps), int(silu),
                ws.data_ptr(), stream())
+    torch.cuda.synchronize()
+    return y, raw
+
+
+def groupnorm_fused(x1, cs1, x2, cs2, gamma, beta, B, hw, eps, silu, out_dtype, want_raw=False):
+    """Like groupnorm(), statistics from the GEMM epilogues' column sums (ldmb200_gemm_desc.colstats)."""
+    c = x1.shape[1] + (x2.shape[1] if x2 is not None else 0)
+    tdt = TORCH_DT[out_dtype]
+    y = torch.full((B * hw, c), float("nan"), dtype=tdt, device=DEV)
+    raw = torch.full((B * hw, c), float("nan"), dtype=tdt, device=DEV) if want_raw else None
+    lib = _cabi.load()
+    ws = torch.empty(int(lib.ldmb200_groupnorm_ws_floats(B, hw, c)), dtype=torch.float32, device=DEV)
+    _cabi.call("ldmb200_groupnorm_fused", x1.data_ptr(), x1.shape[1], cs1.data_ptr(), ptr(x2),
+               x2.shape[1] if x2 is not None else 0, ptr(cs2), gamma.data_ptr(), beta.data_ptr(), y.data_ptr(),
+               ptr(raw), out_dtype, B, hw, 32, float(eps), int(silu), ws.data_ptr(), stream())
     torch.cuda.synchronize()
     return y, raw
 

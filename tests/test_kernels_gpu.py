@@ -300,6 +300,40 @@ def test_tc_epilogues():
     assert K.rel_l2(out, K.igemm_reference(x, bf(wo), bo)) <= 1e-5
 
 
+@pytest.mark.parametrize("B,H,c1,c2,n1,n2", [(2, 16, 64, 0, 160, 0), (2, 8, 96, 64, 640, 320), (1, 32, 32, 48, 320, 160),
+                                                  (3, 8, 32, 0, 64, 0)])
+def test_tc_colstats_groupnorm_fused(B, H, c1, c2, n1, n2):
+    """GEMM epilogue column statistics (ldmb200_gemm_desc.colstats) -> ldmb200_groupnorm_fused == GroupNorm of the
+    stored fp32 tensors (incl. a virtual concat whose group boundaries straddle the two tensors: 640+320 / 32)."""
+    hw = H * H
+    outs, css = [], []
+    for c, n in ((c1, n1), (c2, n2)):
+        if not n:
+            continue
+        a = bf(rnd(B * hw, c)).to(torch.bfloat16)
+        w, b = rnd(n, c, 3, 3, scale=(9 * c) ** -0.5), rnd(n)
+        res = rnd(B * hw, n) + 0.7
+        guard = torch.full(((B * hw // 32 + 4) * n * 2,), 12345.0, device=a.device)   # M = 192: no write past the end
+        cs = guard[: B * hw // 32 * n * 2].view(B * hw // 32, n, 2)
+        cs.fill_(float("nan"))
+        out = K.igemm("tc", a, B, H, H, w, b, ksize=3, residual=res, colstats=cs)
+        assert bool((guard[B * hw // 32 * n * 2:] == 12345.0).all())
+        blk = out.reshape(B * hw // 32, 32, n).double()
+        assert K.rel_l2(cs[..., 0], blk.sum(1).float()) <= 1e-5
+        assert K.rel_l2(cs[..., 1], (blk * blk).sum(1).float()) <= 1e-5
+        outs.append(out)
+        css.append(cs)
+    x1, x2 = outs[0], (outs[1] if len(outs) > 1 else None)
+    c = n1 + n2
+    g, be = 1 + 0.1 * rnd(c), 0.1 * rnd(c)
+    for dt in (F16, BF16):
+        y, r = K.groupnorm_fused(x1, css[0], x2, css[1] if x2 is not None else None, g, be, B, hw, 1e-5, 1, dt, True)
+        xc = torch.cat([x1, x2], 1) if x2 is not None else x1
+        ref = K.to_cl(F.silu(F.group_norm(K.from_cl(xc, B, H, H).double(), 32, g.double(), be.double(), 1e-5)))
+        assert K.rel_l2(y, ref) <= OUT_TOL[dt]
+        assert torch.equal(r.float(), r16(xc, dt))
+
+
 # ------------------------------------------------------------------------------------------ attention
 @pytest.mark.parametrize("B,N,M,heads", [(2, 64, 64, 2), (1, 256, 256, 5), (2, 100, 7, 3), (1, 130, 1, 1), (2, 16, 77, 4)])
 def test_attn_simt(B, N, M, heads):
@@ -320,3 +354,21 @@ def test_attn_tc(B, N, heads, scale_in, odt):
     ref = K.attention_reference(q, k, v, heads, 32 ** -0.5)
     # P is rounded to bf16 before PV; the output is stored as bf16 / f16
     assert K.rel_l2(out, ref) <= (6e-3 if odt == BF16 else 4e-3)
+
+
+@pytest.mark.parametrize("N", [192, 1024, 1100])
+@pytest.mark.parametrize("growth", [40.0, 400.0])
+def test_attn_tc_rereference(N, growth):
+    """Scores that keep growing along the keys: the row maximum of every later 64-key step exceeds the row's
+    running reference by far more than 2^8, so the kernel must re-reference (rescale the TMEM-resident output in
+    place and recompute the step's P) many times per row — the overflow-safety path of the single-pass softmax."""
+    B, heads, c = 2, 2, 64
+    q = bf(rnd(B, N, c))
+    ramp = torch.linspace(0.0, 1.0, N, device=q.device)[None, :, None]
+    k = bf(rnd(B, N, c) + growth * ramp * torch.sign(rnd(1, 1, c)))
+    q = bf(q.abs() * torch.sign(k[:, -1:, :]))     # every query is aligned with the ramp direction
+    v = bf(rnd(B, N, c))
+    out = K.attention("tc", q, k, v, heads, 32 ** -0.5, out_dtype=F16)
+    ref = K.attention_reference(q, k, v, heads, 32 ** -0.5)
+    assert torch.isfinite(out).all()
+    assert K.rel_l2(out, ref) <= 6e-3

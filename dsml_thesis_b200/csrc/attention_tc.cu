@@ -6,12 +6,14 @@
 // One CTA per (384-query block, head, sample), one CTA per SM, three 128-query tiles per CTA (three softmax
 // warpgroups = 3 warps per scheduler to hide the ex2 / TMEM latencies); keys advance in 64-key steps with S and P
 // double-buffered per query tile, so the tensor pipe always works one step ahead of every softmax warpgroup.
-//   warps 0-11 : softmax warpgroup q = warp / 4   (thread r <-> query row r <-> TMEM lane r)
-//   warp  12   : TMA producer — the Q tiles once, then K/V tiles (128 keys x 32) through a 3-stage ring, all from
-//                the fused QKV matrix [B*N, 3C] through one 2-D tensor map (64B-swizzled K-major rows of 32 x 16 bit)
-//   warp  13   : MMA issuer   — S_q(i) = Q_q K(i)^T (M128 N64 K32) into TMEM cols q*128 + (i&1)*64;
-//                O_q += P_q(i) V(i) (M128 N32 K64, V as MN-major B operand straight from the row-major tile) into
-//                TMEM cols 384 + 32q.  Per step i and tile q: wait P_q(i) -> issue P.V_q(i), S_q(i+2), commit.
+//   warps 0-11  : softmax warpgroup q = warp / 4   (thread r <-> query row r <-> TMEM lane r)
+//   warps 12-14 : MMA issuer of query tile q = warp - 12 (one elected lane) — one per scheduler, so no scheduler
+//                 carries two service warps:  S_q(i) = Q_q K(i)^T (M128 N64 K32) into TMEM cols q*128 + (i&1)*64;
+//                 O_q += P_q(i) V(i) (M128 N32 K64, V as MN-major B operand straight from the row-major tile) into
+//                 TMEM cols 384 + 32q.  Per step i: wait p_full_q(i) -> issue P.V_q(i), S_q(i+2), commit s_full_q.
+//   warp  15    : TMA producer — the Q tiles once, then K/V tiles (128 keys x 32) through a 3-stage ring, all from
+//                 the fused QKV matrix [B*N, 3C] through one 2-D tensor map (64B-swizzled K-major rows of 32 x 16
+//                 bit); also owns barrier initialisation and the TMEM allocation
 // Softmax: ONE pass over S in TMEM per KV tile (TMEM read bandwidth, ~64 B/clk/SM, and the ex2 pipe bound the
 // kernel): p = exp2(s*c - ref) against a per-row reference that is only re-based when a tile's row max outgrows it
 // by more than 2^8 (any finite reference is exact after normalisation); the running output accumulates in TMEM
@@ -24,8 +26,8 @@
 namespace ldm {
 
 constexpr int AT_NQ = 3;                      // 128-query tiles per CTA (softmax warpgroups)
-constexpr int AT_THREADS = 32 * (4 * AT_NQ + 2);
-constexpr int AT_TMA_WARP = 4 * AT_NQ, AT_MMA_WARP = 4 * AT_NQ + 1;
+constexpr int AT_THREADS = 32 * (5 * AT_NQ + 1);  // 12 softmax warps, one MMA warp per query tile, one TMA warp
+constexpr int AT_MMA_WARP0 = 4 * AT_NQ, AT_TMA_WARP = 5 * AT_NQ;
 constexpr int AT_O_COL = AT_NQ * 128;          // TMEM: S_q buffers at q*128 + u*64, O_q at AT_O_COL + q*32
 constexpr int AT_STAGES = 3;
 constexpr int AT_TILE_BYTES = 128 * 32 * 2;  // 8 KiB: 128 rows x 32 16-bit values
@@ -176,13 +178,15 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
   const int n_steps = (n_tok + 63) / 64;     // 64-key softmax / MMA steps: S and P are double-buffered per query tile
   const int row_base = b * n_tok;  // first row of this sample in the [B*N, ld] matrix
 
-  if (warp == AT_TMA_WARP && lane == 0) prefetch_tmap(&tm);
-  if (warp == AT_MMA_WARP) {
+  // query tiles of this CTA that hold real rows (the last CTA of a sample may have fewer than AT_NQ)
+  const int nq = min(AT_NQ, (n_tok - qb * (AT_NQ * 128) + 127) / 128);
+  if (warp == AT_TMA_WARP) {
     if (lane == 0) {
+      prefetch_tmap(&tm);
       mbar_init(q_full, 1);
       for (int s = 0; s < AT_STAGES; ++s) {
         mbar_init(&kv_full[s], 1);
-        mbar_init(&kv_empty[s], 1);
+        mbar_init(&kv_empty[s], nq);  // one tcgen05.commit per active query tile
       }
       for (int q = 0; q < 2 * AT_NQ; ++q) {
         mbar_init(&s_full[q], 1);
@@ -198,8 +202,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  // query tiles of this CTA that hold real rows (the last CTA of a sample may have fewer than AT_NQ)
-  const int nq = min(AT_NQ, (n_tok - qb * (AT_NQ * 128) + 127) / 128);
   if (warp == AT_TMA_WARP) {
     // ===================== TMA producer (warp converged, one elected lane issues) =====================
     if (elect_one()) {
@@ -218,72 +220,74 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
       }
       __syncwarp();
     }
-  } else if (warp == AT_MMA_WARP) {
-    // ===================== MMA issuer (warp converged, one elected lane issues) =====================
-    // Smem descriptors: constant high word (SBO, version, swizzle mode), low word = (address >> 4) | LBO.
-    constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 64, 0, 0);
-    constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 32, 0, 1);  // B = V is MN-major
-    constexpr uint32_t hi_sw64 = (512u >> 4) | (1u << 14) | (4u << 29);    // Q, K (K-major) and V (MN-major) tiles
-    constexpr uint32_t hi_sw128 = (1024u >> 4) | (1u << 14) | (2u << 29);  // P tile
-    const uint32_t q_lo = ((smem_u32(sQ) & 0x3FFFFu) >> 4) | (1u << 16);
-    const uint32_t k_lo = ((smem_u32(sK) & 0x3FFFFu) >> 4) | (1u << 16);
-    const uint32_t v_lo = ((smem_u32(sV) & 0x3FFFFu) >> 4) | (1u << 16);
-    const uint32_t p_lo = ((smem_u32(sP) & 0x3FFFFu) >> 4) | (1u << 16);
-    // S_q(i) = Q_q . K(keys 64 i .. 64 i + 63)^T  -> TMEM columns q*128 + (i&1)*64
-    auto issue_s = [&](int q, int i) {
-      const int st = (i >> 1) % AT_STAGES, hf = i & 1;
+  } else if (warp >= AT_MMA_WARP0) {
+    // ===================== MMA issuers: warp AT_MMA_WARP0 + q drives query tile q (converged, one elected lane) ===
+    // One warp per tile: a single MMA warp serialised the three tiles behind its in-order waits and, sharing its
+    // scheduler with three busy softmax warps, became the bottleneck (profiles/ r01g); with one issuer per
+    // scheduler the load is balanced.  Smem descriptors: constant high word (SBO, version, swizzle mode), low
+    // word = (address >> 4) | LBO.
+    const int q = warp - AT_MMA_WARP0;
+    if (q < nq) {
+      constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 64, 0, 0);
+      constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 32, 0, 1);          // B = V is MN-major
+      constexpr uint32_t hi_sw64 = (512u >> 4) | (1u << 14) | (4u << 29);    // Q, K (K-major) and V (MN-major) tiles
+      constexpr uint32_t hi_sw128 = (1024u >> 4) | (1u << 14) | (2u << 29);  // P tile
+      const uint32_t q_lo = (((smem_u32(sQ) & 0x3FFFFu) >> 4) | (1u << 16)) + q * (AT_TILE_BYTES >> 4);
+      const uint32_t k_lo = ((smem_u32(sK) & 0x3FFFFu) >> 4) | (1u << 16);
+      const uint32_t v_lo = ((smem_u32(sV) & 0x3FFFFu) >> 4) | (1u << 16);
+      const uint32_t p_lo = (((smem_u32(sP) & 0x3FFFFu) >> 4) | (1u << 16)) + q * (AT_P_BYTES >> 4);
+      const uint32_t dS = tmem_base + q * 128, dO = tmem_base + AT_O_COL + q * 32;
+      // S_q(i) = Q_q . K(keys 64 i ..)^T -> TMEM columns q*128 + (i&1)*64;  st = smem stage of K/V tile i >> 1
+      auto issue_s = [&](int i, int st) {
+        const int hf = i & 1;
 #pragma unroll
-      for (int kk = 0; kk < 2; ++kk)
-        umma_bf16_ss(tmem_base + q * 128 + hf * 64, ((uint64_t)hi_sw64 << 32) | (q_lo + q * (AT_TILE_BYTES >> 4) + kk * 2),
-                     ((uint64_t)hi_sw64 << 32) | (k_lo + st * (AT_TILE_BYTES >> 4) + hf * (4096 >> 4) + kk * 2),
-                     idesc_qk, kk > 0);
-    };
-    // O_q += P_q(i) . V(keys 64 i ..)   (first step overwrites)
-    auto issue_pv = [&](int q, int i) {
-      const int st = (i >> 1) % AT_STAGES, hf = i & 1;
+        for (int kk = 0; kk < 2; ++kk)
+          umma_bf16_ss(dS + hf * 64, ((uint64_t)hi_sw64 << 32) | (q_lo + kk * 2),
+                       ((uint64_t)hi_sw64 << 32) | (k_lo + st * (AT_TILE_BYTES >> 4) + hf * (4096 >> 4) + kk * 2),
+                       idesc_qk, kk > 0);
+      };
+      // O_q += P_q(i) . V(keys 64 i ..)   (the first step overwrites)
+      auto issue_pv = [&](int i, int st) {
+        const int hf = i & 1;
 #pragma unroll
-      for (int t = 0; t < 4; ++t)
-        umma_bf16_ss(tmem_base + AT_O_COL + q * 32,
-                     ((uint64_t)hi_sw128 << 32) | (p_lo + q * (AT_P_BYTES >> 4) + hf * ((128 * 128) >> 4) + t * 2),
-                     ((uint64_t)hi_sw64 << 32) | (v_lo + st * (AT_TILE_BYTES >> 4) + (hf * 4 + t) * (1024 >> 4)), idesc_pv,
-                     (i > 0 || t > 0) ? 1u : 0u);
-    };
-    mbar_wait(q_full, 0);
-    mbar_wait(&kv_full[0], 0);
-    tc_fence_after();
-    if (elect_one()) {
-#pragma unroll
-      for (int i = 0; i < 2; ++i) {
-        if (i < n_steps) {
-          for (int q = 0; q < nq; ++q) {
-            issue_s(q, i);
-            umma_commit(&s_full[q * 2 + i]);
-          }
+        for (int t = 0; t < 4; ++t)
+          umma_bf16_ss(dO, ((uint64_t)hi_sw128 << 32) | (p_lo + hf * ((128 * 128) >> 4) + t * 2),
+                       ((uint64_t)hi_sw64 << 32) | (v_lo + st * (AT_TILE_BYTES >> 4) + (hf * 4 + t) * (1024 >> 4)),
+                       idesc_pv, (i > 0 || t > 0) ? 1u : 0u);
+      };
+      mbar_wait(q_full, 0);
+      mbar_wait(&kv_full[0], 0);
+      tc_fence_after();
+      if (elect_one()) {
+        issue_s(0, 0);
+        umma_commit(&s_full[q * 2 + 0]);
+        if (n_steps > 1) {
+          issue_s(1, 0);
+          umma_commit(&s_full[q * 2 + 1]);
         }
       }
-    }
-    __syncwarp();
-    for (int i = 0; i < n_steps; ++i) {
-      const int u = i & 1;
-      const uint32_t par = (i >> 1) & 1;
-      const bool more = i + 2 < n_steps;
-      const bool tile_done = u == 1 || i == n_steps - 1;  // last step that reads K/V tile i >> 1
-      for (int q = 0; q < nq; ++q) {
-        mbar_wait(&p_full[q * 2 + u], par);
+      __syncwarp();
+      int st = 0;  // smem stage of K/V tile i >> 1
+      for (int i = 0; i < n_steps; ++i) {
+        const int u = i & 1;
+        const int st_next = (st + 1 == AT_STAGES) ? 0 : st + 1;
+        const bool more = i + 2 < n_steps;
+        mbar_wait(&p_full[q * 2 + u], (i >> 1) & 1);  // all 128 rows of P_q(i) are in smem, S_q(i) is consumed
         tc_fence_after();
-        if (elect_one()) issue_pv(q, i);
+        if (elect_one()) issue_pv(i, st);
         __syncwarp();
-        if (q == 0 && more && u == 0) {  // first use of K/V tile (i + 2) >> 1
+        if (more && u == 0) {  // S_q(i+2) is the first use of K/V tile (i + 2) >> 1
           const int jn = (i + 2) >> 1;
-          mbar_wait(&kv_full[jn % AT_STAGES], (jn / AT_STAGES) & 1);
+          mbar_wait(&kv_full[st_next], (jn / AT_STAGES) & 1);
           tc_fence_after();
         }
         if (elect_one()) {
-          if (q == nq - 1 && tile_done) umma_commit(&kv_empty[(i >> 1) % AT_STAGES]);
-          if (more) issue_s(q, i + 2);
+          if (u == 1 || i == n_steps - 1) umma_commit(&kv_empty[st]);  // last read of K/V tile i >> 1 by this query tile
+          if (more) issue_s(i + 2, st_next);
           umma_commit(&s_full[q * 2 + u]);  // always: it also tells the softmax warps that P.V(i) has landed
         }
         __syncwarp();
+        if (u == 1) st = st_next;
       }
     }
   } else {
@@ -361,7 +365,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
 
   tc_fence_before();
   __syncthreads();
-  if (warp == AT_MMA_WARP) {
+  if (warp == AT_TMA_WARP) {
     tc_fence_after();
     tmem_dealloc(tmem_base, AT_TMEM_COLS);
   }

@@ -8,6 +8,8 @@ Public surface = the reference's own plugin interface for this path (SURVEY §8b
   * ``install()``       — patches those dotted targets after ``import ldm`` so ``main.py``, the YAML configs and
                           the sampling scripts pick the new classes up with no file edited
   * ``ddim_step``       — the fused x_{t-1} update as a function
+  * ``sample_sharded``  — ``DDIMSampler.sample`` for a global batch split over the GPUs of one box (one process
+                          per GPU, no data-path collective, final all-gather)
 
 All compute goes through ``libldmb200.so`` (C-ABI in ``include/ldmb200.h``); there is no CPU or PyTorch
 fallback — importing works anywhere, running needs the built library and a B200.
@@ -17,6 +19,8 @@ from .unet import UNetModel  # noqa: F401
 from .sampler import DDIMSampler, DDIMSampler2Cond, DDIMSampler2CondFR, ddim_step  # noqa: F401
 from .handle import DiffusionHandle  # noqa: F401
 from .install import install, uninstall  # noqa: F401
+from .sharding import sample_sharded, shard_range, gather_shards, initial_noise  # noqa: F401
 
 __all__ = ["UNetModel", "DDIMSampler", "DDIMSampler2Cond", "DDIMSampler2CondFR", "ddim_step", "install",
-           "uninstall", "DiffusionHandle", "load_library", "Ldmb200Error"]
+           "uninstall", "DiffusionHandle", "load_library", "Ldmb200Error", "sample_sharded", "shard_range",
+           "gather_shards", "initial_noise"]

@@ -214,7 +214,6 @@ def main():
     c_host = torch.randn(B, 1, 512, generator=g).pin_memory()
     out_host = torch.empty(B, 3, HW, HW).pin_memory()
     x_dev, c_dev = x_host.to(dev), c_host.to(dev)
-    gathered = torch.empty(world * B, 3, HW, HW, device=dev) if world > 1 else None
 
     launches = {"n": 0}
     step_fn = S.ddim_step
@@ -227,7 +226,7 @@ def main():
     def sample_resident():
         out, _ = smp.sample(T, batch_size=B, shape=[3, HW, HW], conditioning=c_dev, eta=0.0, x_T=x_dev, verbose=False)
         if world > 1:
-            dist.all_gather_into_tensor(gathered, out.contiguous())   # the one collective: final gather
+            return P.gather_shards(out, world * B)   # the one collective of the path: final all-gather
         return out
 
     def sample_e2e():
@@ -300,6 +299,17 @@ def main():
     peak_src = "MEASURED_PEAKS.json bf16_tflops_sustained (kernel timed inside a long step)" if peaks else \
         "fallback 1.4 PFLOP/s sustained (B200_PROFILING.md)"
     dom = "ldmb200_igemm_tc" if args.precision != "fp32" else "ldmb200_igemm_simt"
+    # DRAM traffic of the family's launches in one eval, from the committed ncu capture of the same workload
+    traffic, traffic_src = None, None
+    if dom == "ldmb200_igemm_tc" and B == 64 and HW == 64 and args.precision == "f16":
+        import glob
+        cand = sorted(glob.glob(os.path.join(ROOT, "profiles", "traffic_gemm_*.json")))
+        if cand:
+            try:
+                tj = json.load(open(cand[-1]))
+                traffic, traffic_src = tj["dram_bytes_total"], os.path.relpath(cand[-1], ROOT)
+            except Exception:
+                pass
     d = fam[dom]
     achieved = d[1] / (d[0] * 1e-3) / 1e12
     total = args.steps * B * world
@@ -323,7 +333,10 @@ def main():
         "gpu_launches": n_launch,
         "clocks": clk,
         "roofline": {"kernel": dom, "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
-                     "frac": achieved / peak_tf, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak_tf, "traffic": traffic, "traffic_source": traffic_src,
+                     "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum summed over the family's launches of "
+                                     "one UNet eval (bytes; achieved is likewise the family aggregate per eval)",
+                     "peak_source": peak_src,
                      "launches_per_eval": d[3], "ms_per_eval": d[0],
                      "how": "sum of algorithmic FLOPs of the family's launches in one UNet eval / sum of their "
                             "CUDA-event durations on the launching stream"},

@@ -423,7 +423,25 @@ __global__ void gn_apply_kernel(const float* __restrict__ x1, int c1, const floa
   const int T_ = gridDim.x;
   const int rows_per = (hw + T_ - 1) / T_;
   const int r0 = blockIdx.x * rows_per, r1 = min(hw, r0 + rows_per);
-  for (int r = r0 + rl; r < r1; r += R) {
+  // four rows per thread in flight: the pass is a pure stream and needs the memory-level parallelism
+  int r = r0 + rl;
+  for (; r + 3 * R < r1; r += 4 * R) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = gn_load(x1, c1, x2, c2, (int64_t)b * hw + r + u * R, cq * 4);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t row = (int64_t)b * hw + r + u * R;
+      float o0 = fmaf(v[u].x, sc[0], sh[0]), o1 = fmaf(v[u].y, sc[1], sh[1]);
+      float o2 = fmaf(v[u].z, sc[2], sh[2]), o3 = fmaf(v[u].w, sc[3], sh[3]);
+      if (silu) {
+        o0 = silu_f(o0); o1 = silu_f(o1); o2 = silu_f(o2); o3 = silu_f(o3);
+      }
+      Store4<T>::st(y + row * C + cq * 4, o0, o1, o2, o3);
+      if (raw) Store4<T>::st(raw + row * C + cq * 4, v[u].x, v[u].y, v[u].z, v[u].w);
+    }
+  }
+  for (; r < r1; r += R) {
     int64_t row = (int64_t)b * hw + r;
     float4 v = gn_load(x1, c1, x2, c2, row, cq * 4);
     float o0 = fmaf(v.x, sc[0], sh[0]), o1 = fmaf(v.y, sc[1], sh[1]);

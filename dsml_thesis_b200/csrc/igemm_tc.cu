@@ -40,20 +40,22 @@ struct TcParams {
   uint32_t idesc;  // tcgen05 instruction descriptor (operand format bf16 or f16, M = 128, N = BN)
 };
 
-constexpr int TC_EPI_WARPS = 8;  // two warps per TMEM lane quarter, alternating 32-column chunks
-constexpr int TC_THREADS = 64 + TC_EPI_WARPS * 32;
+// Epilogue warps: EW / 4 per TMEM lane quarter, round-robin over the tile's 32-column chunks.  8 for the plain
+// epilogues; 16 for GEGLU, whose per-element work (erf GELU) makes the epilogue the bound: 128-wide tiles = 4 chunks
+// = exactly one chunk per warp, 4 warps per scheduler to hide the MUFU / TMEM / smem latencies.
 
-template <int BN, int BK>
+template <int BN, int BK, int EW>
 struct TcCfg {
+  static constexpr int THREADS = 64 + EW * 32;
   static constexpr int BM = 128;
   static constexpr int SW = BK * 2;  // swizzle span in bytes == one K-major row
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = ((BN * BK * 2 + 1023) / 1024) * 1024;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN >= 128) ? (BK == 32 ? 8 : 5) : 8;
+  static constexpr int STAGES = (BN >= 128) ? (EW > 8 ? 4 : 5) : 8;
   static constexpr int TX_BYTES = BM * BK * 2 + BN * BK * 2;
   static constexpr int EPI_PITCH = 36;  // floats; 144 B row pitch: conflict-free 16 B row-owner writes + row reads
-  static constexpr int EPI_BYTES = TC_EPI_WARPS * 32 * EPI_PITCH * 4;
+  static constexpr int EPI_BYTES = EW * 32 * EPI_PITCH * 4;
   static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + (2 * STAGES + 4) * 8 + 16 + 1024;
   static constexpr int CH = BN >= 32 ? 32 : 16;  // epilogue column chunk
@@ -168,11 +170,11 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
   }
 }
 
-template <int BN, int BK>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+template <int BN, int BK, int EW>
+__global__ void __launch_bounds__(64 + EW * 32, 1)
 igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                 const __grid_constant__ CUtensorMap tmB, const TcParams p) {
-  using Cfg = TcCfg<BN, BK>;
+  using Cfg = TcCfg<BN, BK, EW>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;
@@ -200,7 +202,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       }
       for (int b = 0; b < 2; ++b) {
         mbar_init(&tfull[b], 1);
-        mbar_init(&tempty[b], TC_EPI_WARPS);
+        mbar_init(&tempty[b], EW);
       }
       fence_mbar_init();
     }
@@ -301,10 +303,11 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       __syncwarp();
     }
   } else {
-    // ===================== epilogue (TC_EPI_WARPS warps) =====================
+    // ===================== epilogue (EW warps) =====================
     const int ew = warp - 2;
     const int qw = warp & 3;          // TMEM lane quarter accessible to this warp (hardware: warp id % 4)
-    const int par = ew >> 2;          // which of the quarter's two warps: takes chunks cc % 2 == par
+    const int par = ew >> 2;          // which of the quarter's EW/4 warps: takes chunks cc % (EW/4) == par
+    constexpr int CSTEP = EW / 4;
     constexpr int NCH = BN / Cfg::CH;
     constexpr int PITCH = Cfg::EPI_PITCH;
     float* st = epi + ew * 32 * PITCH;
@@ -327,7 +330,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       mbar_wait(&tfull[buf], (t_iter >> 1) & 1);
       tc_fence_after();
 #pragma unroll 1
-      for (int cc = cc_first; cc < NCH; cc += 2) {
+      for (int cc = cc_first; cc < NCH; cc += CSTEP) {
         float v[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16) + buf * BN + cc * Cfg::CH;
         if (Cfg::CH == 32)
@@ -335,10 +338,10 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
         else
           tmem_ld_32x16(taddr, v);
         float4 res_next[8];
-        const bool more = cc + 2 < NCH;
+        const bool more = cc + CSTEP < NCH;
         if (has_res && more) {
-          if (out16) epi_load_residual<true>(p, res_next, m0, n0 + (cc + 2) * Cfg::CH, lane);
-          else epi_load_residual<false>(p, res_next, m0, n0 + (cc + 2) * Cfg::CH, lane);
+          if (out16) epi_load_residual<true>(p, res_next, m0, n0 + (cc + CSTEP) * Cfg::CH, lane);
+          else epi_load_residual<false>(p, res_next, m0, n0 + (cc + CSTEP) * Cfg::CH, lane);
         }
         tmem_ld_wait();
         if (!more) {  // last TMEM read of this warp for this tile: hand the accumulator buffer back early
@@ -414,13 +417,13 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   }
 }
 
-template <int BN, int BK>
+template <int BN, int BK, int EW>
 static int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b, const TcParams& p,
                      cudaStream_t st) {
-  using Cfg = TcCfg<BN, BK>;
+  using Cfg = TcCfg<BN, BK, EW>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::SMEM_BYTES);
     if (e != cudaSuccess) {
       set_error("igemm_tc: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
@@ -429,7 +432,7 @@ static int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtenso
     attr_set = true;
   }
   int grid = std::min(p.tiles_m * p.tiles_n, sm_count());
-  igemm_tc_kernel<BN, BK><<<grid, TC_THREADS, Cfg::SMEM_BYTES, st>>>(a1, a2, b, p);
+  igemm_tc_kernel<BN, BK, EW><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(a1, a2, b, p);
   LDM_CHECK_LAUNCH("igemm_tc");
   return 0;
 }
@@ -495,7 +498,7 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   // BK = 64 (128-byte swizzled rows) for every shape: a channel range that is not a multiple of 64 ends in a
   // partial chunk (TMA zero-fills the missing channels, the MMA warp issues only valid/16 instructions for it)
   constexpr int BK = 64;
-  int BN = (d->n % 160 == 0) ? 160 : (d->n % 32 == 0) ? 32 : 16;
+  int BN = (d->geglu && d->n % 128 == 0) ? 128 : (d->n % 160 == 0) ? 160 : (d->n % 32 == 0) ? 32 : 16;
   LDM_CHECK_ARG(BN != 16 || d->n == 16, "igemm_tc: n=%d unsupported (need multiple of 32, or exactly 16)", d->n);
   LDM_CHECK_ARG(!(d->geglu && BN == 16), "igemm_tc: geglu needs n %% 32 == 0");
   p.c1 = c1;
@@ -539,7 +542,8 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
     if (rc) return rc;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  if (BN == 160) return launch_tc<160, 64>(tA1, tA2, tB, p, st);
-  if (BN == 32) return launch_tc<32, 64>(tA1, tA2, tB, p, st);
-  return launch_tc<16, 64>(tA1, tA2, tB, p, st);
+  if (BN == 128) return launch_tc<128, 64, 16>(tA1, tA2, tB, p, st);
+  if (BN == 160) return launch_tc<160, 64, 8>(tA1, tA2, tB, p, st);
+  if (BN == 32) return launch_tc<32, 64, 8>(tA1, tA2, tB, p, st);
+  return launch_tc<16, 64, 8>(tA1, tA2, tB, p, st);
 }

@@ -168,8 +168,11 @@ def _tc_cpad(c: int) -> int:
     return (c + 31) // 32 * 32
 
 
-def _tc_bn(n: int) -> int:
-    """N tile the C side picks for a packed weight with ``n`` rows (igemm_tc.cu)."""
+def _tc_bn(n: int, geglu: bool = False) -> int:
+    """N tile the C side picks for a packed weight with ``n`` rows (igemm_tc.cu): GEGLU projections run on
+    128-wide tiles with 16 epilogue warps (one 32-column chunk per warp), everything else on 160 / 32 / 16."""
+    if geglu and n % 128 == 0:
+        return 128
     return 160 if n % 160 == 0 else (32 if n % 32 == 0 else 16)
 
 
@@ -197,7 +200,7 @@ class _WeightPack:
             for i, p in enumerate(parts):
                 last = i == len(parts) - 1
                 rows = (n_pad - row) if last else p.shape[0]
-                jobs.append((p, base, kind, p.shape[0], c, ksize, rows, c_pad, row, _tc_bn(n_pad)))
+                jobs.append((p, base, kind, p.shape[0], c, ksize, rows, c_pad, row, _tc_bn(n_pad, kind == 1)))
                 row += p.shape[0]
             self.entries[key] = (base, n_pad, c_pad)
             off += n_pad * ksize * ksize * c_pad * 2
@@ -215,7 +218,7 @@ class _WeightPack:
                 add(name + ".ff.net.0.proj", [g.weight], 1, kind=1)
                 self.f32_entries[name + ".ff.net.0.proj.bias"] = foff
                 jobs.append((g.bias, ("f32", foff), 2, g.bias.shape[0], 1, 1, g.bias.shape[0], 1, 0,
-                             _tc_bn(g.weight.shape[0])))
+                             _tc_bn(g.weight.shape[0], True)))
                 foff += g.bias.shape[0]
                 add(name + ".ff.net.2", [m.ff.net[2].weight], 1)
         self.bf16 = torch.empty(max(off, 256), dtype=torch.uint8, device=dev)

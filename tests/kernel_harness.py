@@ -61,10 +61,10 @@ def pack_weight(w, kind=0, bias=None, parts=None, dtype=BF16):
     row = 0
     for i, p in enumerate(ws):
         rows = (n_pad - row) if i == len(ws) - 1 else p.shape[0]
-        jobs.append((p.data_ptr(), dst.data_ptr(), kind, p.shape[0], c, ks, rows, c_pad, row, _tc_bn(n_pad)))
+        jobs.append((p.data_ptr(), dst.data_ptr(), kind, p.shape[0], c, ks, rows, c_pad, row, _tc_bn(n_pad, kind == 1)))
         row += p.shape[0]
     if fb is not None:
-        jobs.append((bias.data_ptr(), fb.data_ptr(), 2, n_tot, 1, 1, n_tot, 1, 0, _tc_bn(n_pad)))
+        jobs.append((bias.data_ptr(), fb.data_ptr(), 2, n_tot, 1, 1, n_tot, 1, 0, _tc_bn(n_pad, True)))
     arr = (PackJob * len(jobs))()
     for j, v in zip(arr, jobs):
         (j.src, j.dst, j.kind, j.n, j.c, j.ksize, j.n_pad, j.c_pad, j.row_offset, j.block_n) = v

@@ -16,4 +16,10 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:igem
     -f -o gpurun_out/prof_gemm_$tag $CMD > gpurun_out/ncu_gemm_$tag.log 2>&1
 echo "ncu gemm exit $?"
 fi
+if [ "$what" = traffic ]; then
+# DRAM bytes of every implicit-GEMM launch of ONE UNet eval (147 launches; the first eval's 148 are skipped)
+timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none \
+    -k regex:igemm_tc -s 148 -c 147 --csv --log-file gpurun_out/traffic_gemm_$tag.csv $CMD > gpurun_out/ncu_traffic_$tag.log 2>&1
+echo "ncu traffic exit $?"
+fi
 ls -la gpurun_out | tail -8

@@ -4,6 +4,8 @@ Public surface = the reference's own plugin interface for this path (SURVEY §8b
 
   * ``UNetModel``       — drop-in for ``ldm.modules.diffusionmodules.openaimodel.UNetModel``
   * ``DDIMSampler``     — drop-in for ``ldm.models.diffusion.ddim.DDIMSampler``
+  * ``DDIMSampler2``    — drop-in for ``ldm.models.diffusion.ddim2.DDIMSampler2`` (strength-scaled grid) plus the DDIM
+                          inversion ``q_sample_ddim`` / ``latent_manipulation`` of FR/latent_manipulation.py
   * ``DDIMSampler2Cond`` / ``DDIMSampler2CondFR`` — drop-ins for the two ``ddim2cond.DDIMSampler`` flavours
   * ``install()``       — patches those dotted targets after ``import ldm`` so ``main.py``, the YAML configs and
                           the sampling scripts pick the new classes up with no file edited
@@ -16,11 +18,11 @@ fallback — importing works anywhere, running needs the built library and a B20
 """
 from ._cabi import Ldmb200Error, load as load_library  # noqa: F401
 from .unet import UNetModel  # noqa: F401
-from .sampler import DDIMSampler, DDIMSampler2Cond, DDIMSampler2CondFR, ddim_step  # noqa: F401
+from .sampler import DDIMSampler, DDIMSampler2, DDIMSampler2Cond, DDIMSampler2CondFR, ddim_step  # noqa: F401
 from .handle import DiffusionHandle  # noqa: F401
 from .install import install, uninstall  # noqa: F401
 from .sharding import sample_sharded, shard_range, gather_shards, initial_noise  # noqa: F401
 
-__all__ = ["UNetModel", "DDIMSampler", "DDIMSampler2Cond", "DDIMSampler2CondFR", "ddim_step", "install",
+__all__ = ["UNetModel", "DDIMSampler", "DDIMSampler2", "DDIMSampler2Cond", "DDIMSampler2CondFR", "ddim_step", "install",
            "uninstall", "DiffusionHandle", "load_library", "Ldmb200Error", "sample_sharded", "shard_range",
            "gather_shards", "initial_noise"]

@@ -543,6 +543,10 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   }
   cudaStream_t st = (cudaStream_t)stream;
   if (BN == 128) return launch_tc<128, 64, 16>(tA1, tA2, tB, p, st);
+  // experiment switch (measured r01n: 16 epilogue warps on the plain 1x1 GEMMs are SLOWER, 32.1 vs 30.0 ms per UNet
+  // eval — 5 chunks over 4 warps per quarter is unbalanced and the ring loses a stage — so the default stays 8)
+  static const bool ew16 = getenv("LDMB200_TC_EW16") ? atoi(getenv("LDMB200_TC_EW16")) != 0 : false;
+  if (BN == 160 && d->ksize == 1 && ew16) return launch_tc<160, 64, 16>(tA1, tA2, tB, p, st);
   if (BN == 160) return launch_tc<160, 64, 8>(tA1, tA2, tB, p, st);
   if (BN == 32) return launch_tc<32, 64, 8>(tA1, tA2, tB, p, st);
   return launch_tc<16, 64, 8>(tA1, tA2, tB, p, st);

@@ -37,7 +37,7 @@ def install(verbose: bool = False):
     """Patches the reference's dotted targets.  Needs the reference's ``ldm`` package importable (it is when a
     reference script runs from its own directory).  Returns the list of patched ``module.attr`` names."""
     from .unet import UNetModel
-    from .sampler import DDIMSampler, DDIMSampler2Cond, DDIMSampler2CondFR
+    from .sampler import DDIMSampler, DDIMSampler2, DDIMSampler2Cond, DDIMSampler2CondFR
     done = []
 
     def p(mod, attr, val):
@@ -46,6 +46,7 @@ def install(verbose: bool = False):
 
     p("ldm.modules.diffusionmodules.openaimodel", "UNetModel", UNetModel)
     p("ldm.models.diffusion.ddim", "DDIMSampler", DDIMSampler)
+    p("ldm.models.diffusion.ddim2", "DDIMSampler2", DDIMSampler2)   # strength-scaled grid + DDIM inversion (FR only)
     # the two ddim2cond flavours differ by their dict keys: talking_face uses 'class_label_&_audio'
     try:
         src = open(importlib.import_module("ldm.models.diffusion.ddim2cond").__file__).read()

@@ -117,6 +117,10 @@ class DDIMSampler(object):
         self.ddim_timesteps = make_ddim_timesteps(ddim_discr_method=ddim_discretize,
                                                   num_ddim_timesteps=ddim_num_steps,
                                                   num_ddpm_timesteps=self.ddpm_num_timesteps, verbose=verbose)
+        self._set_schedule(ddim_eta, verbose)
+
+    def _set_schedule(self, ddim_eta, verbose):
+        """Everything of make_schedule after the timestep subset is chosen (ddim.py:27-53)."""
         alphas_cumprod = self.model.alphas_cumprod
         assert alphas_cumprod.shape[0] == self.ddpm_num_timesteps, 'alphas have to be defined for each timestep'
         to_torch = lambda x: x.clone().detach().to(torch.float32).to(self.model.betas.device)
@@ -134,10 +138,13 @@ class DDIMSampler(object):
         sqrt_1ma = np.sqrt(1. - ddim_alphas)
         # host-side per-step scalars, rounded to fp32 like torch.full does: no device->host read in the loop
         n = len(self.ddim_timesteps)
+        sqrt_1ma_prev = np.sqrt(1. - ddim_alphas_prev)   # ddim2.py:96 (float64 numpy, like ddim_alphas_prev)
         self._coef = dict(a_t=[_f32(ddim_alphas[i]) for i in range(n)],
                           a_prev=[_f32(ddim_alphas_prev[i]) for i in range(n)],
                           sigma=[_f32(ddim_sigmas[i]) for i in range(n)],
-                          s1=[_f32(sqrt_1ma[i]) for i in range(n)])
+                          s1=[_f32(sqrt_1ma[i]) for i in range(n)],
+                          s1_prev=[_f32(sqrt_1ma_prev[i]) for i in range(n)])
+        self.register_buffer('ddim_sqrt_one_minus_alphas_prev', sqrt_1ma_prev)
         self._coef_orig = None
         self.register_buffer('ddim_sigmas', ddim_sigmas)
         self.register_buffer('ddim_alphas', ddim_alphas)
@@ -326,6 +333,108 @@ class DDIMSampler2CondFR(DDIMSampler2Cond):
 
     def ddim_sampling(self, *a, log_every_t=100, **k):
         return DDIMSampler.ddim_sampling(self, *a, log_every_t=log_every_t, **k)
+
+
+def make_ddim_timesteps_strength(ddim_discr_method, num_ddim_timesteps, num_ddpm_timesteps, strength=1.0, verbose=True):
+    """ddim2.py:9-29 / latent_manipulation.py:52-72: S timesteps spread over [0, T*strength], first one forced to 1
+    (no +1 shift) — the grid of the DDIM inversion / re-generation used for emotion manipulation."""
+    if ddim_discr_method == 'uniform':
+        ddim_timesteps = np.linspace(0, 1, num_ddim_timesteps) * int(num_ddpm_timesteps * strength)
+        ddim_timesteps = [int(s) for s in list(ddim_timesteps)]
+    elif ddim_discr_method == 'quad':
+        ddim_timesteps = ((np.linspace(0, np.sqrt(num_ddpm_timesteps * .8), num_ddim_timesteps)) ** 2).astype(int)
+        ddim_timesteps = [int(s) for s in list(ddim_timesteps)]
+    else:
+        raise NotImplementedError(f'There is no ddim discretization method called "{ddim_discr_method}"')
+    steps_out = np.asarray([1] + ddim_timesteps[1:])
+    if verbose:
+        print(f'Selected timesteps for ddim sampler: {steps_out}')
+    return steps_out
+
+
+class DDIMSampler2(DDIMSampler):
+    """``ldm.models.diffusion.ddim2.DDIMSampler2`` (FR ddim2.py:53-284) plus the DDIM inversion that the thesis'
+    manipulation scripts carry as private sampler copies (``q_sample_ddim`` / ``latent_manipulation``,
+    FR/latent_manipulation.py:377-489; ``compute_latents.py:257``): SURVEY §8f row n1.  The inversion step is the
+    SAME fused update kernel with the roles of (a_t, a_prev) swapped and sigma = 0, so it is bit-identical to the
+    reference's chain of torch ops like the sampling step."""
+
+    def make_schedule(self, ddim_num_steps, ddim_discretize="uniform", ddim_eta=0., strength=1.0, verbose=True):
+        """ddim2.py:66-97."""
+        self.ddim_timesteps = make_ddim_timesteps_strength(ddim_discretize, ddim_num_steps, self.ddpm_num_timesteps,
+                                                           strength=strength, verbose=verbose)
+        self._set_schedule(ddim_eta, verbose)
+
+    @torch.no_grad()
+    def q_sample_ddim(self, x, c, t, index, repeat_noise=False, use_original_steps=False, quantize_denoised=False,
+                      temperature=1., noise_dropout=0., score_corrector=None, corrector_kwargs=None,
+                      unconditional_guidance_scale=1., unconditional_conditioning=None):
+        """latent_manipulation.py:377-419: one deterministic step x_t -> x_{t+1} (towards noise)."""
+        if not x.is_cuda:
+            raise _cabi.Ldmb200Error("dsml_thesis_b200.DDIMSampler2 runs on a CUDA device only (no CPU fallback)")
+        if use_original_steps:
+            raise NotImplementedError("q_sample_ddim(use_original_steps=True) reads model.sqrt_one_minus_alphas_cumprod_prev, "
+                                      "which the reference model does not define either")
+        e_c, e_u = self._eps(x, c, t, unconditional_guidance_scale, unconditional_conditioning)
+        if score_corrector is not None:
+            assert self.model.parameterization == "eps"
+            e_mix = e_c if e_u is None else e_u + unconditional_guidance_scale * (e_c - e_u)
+            e_c, e_u = score_corrector.modify_score(self.model, e_mix, x, t, c, **(corrector_kwargs or {})), None
+        k = self._coef
+        at, at_next, s1 = k["a_prev"][index], k["a_t"][index], k["s1_prev"][index]
+        if quantize_denoised:
+            e_t = e_c if e_u is None else e_u + unconditional_guidance_scale * (e_c - e_u)
+            f = lambda v: torch.full((x.shape[0], 1, 1, 1), v, device=x.device)
+            pred_x0 = (x - f(s1) * e_t) / f(at).sqrt()
+            pred_x0, _, *_ = self.model.first_stage_model.quantize(pred_x0)
+            return f(at_next).sqrt() * pred_x0 + (1. - f(at_next)).sqrt() * e_t, pred_x0
+        # x_next = sqrt(a_next) * pred_x0 + sqrt(1 - a_next) * e   ==  the sampling update with sigma = 0
+        return ddim_step(x, e_c, e_u, None, at, at_next, 0.0, s1, float(unconditional_guidance_scale), 1.0)
+
+    @torch.no_grad()
+    def encode(self, x0, c, S, strength=1.0, unconditional_guidance_scale=1., unconditional_conditioning=None,
+               verbose=False):
+        """DDIM inversion x0 -> x_T' over the strength-scaled grid (compute_latents.py / latent_manipulation.py:470-477)."""
+        self.make_schedule(ddim_num_steps=S, ddim_eta=0., verbose=verbose, strength=strength)
+        b, device = x0.shape[0], x0.device
+        x = x0.clone().detach()
+        with contextlib.ExitStack() as stack:
+            for u in _find_unets(self.model):
+                stack.enter_context(u.frozen_weights())
+            for i, step in enumerate(self.ddim_timesteps):
+                ts = torch.full((b,), int(step), device=device, dtype=torch.long)
+                x, _ = self.q_sample_ddim(x, c, ts, index=i, unconditional_guidance_scale=unconditional_guidance_scale,
+                                          unconditional_conditioning=unconditional_conditioning)
+        return x
+
+    @torch.no_grad()
+    def latent_manipulation(self, c_src, c_trg, S, batch_size, shape, callback=None, normals_sequence=None,
+                            img_callback=None, quantize_x0=False, eta=0., mask=None, x0=None, temperature=1.,
+                            noise_dropout=0., score_corrector=None, corrector_kwargs=None, verbose=True, x_T=None,
+                            log_every_t=100, unconditional_guidance_scale=1., unconditional_conditioning=None,
+                            strength=1.0, **kwargs):
+        """latent_manipulation.py:421-489: invert x0 under the source condition, regenerate under the target one.
+        Returns ``(img, x_T', x0)``."""
+        assert c_src is not None and c_trg is not None
+        assert x0 is not None
+        assert x_T is None
+        assert eta == 0
+        x = self.encode(x0, c_src, S, strength=strength, unconditional_guidance_scale=unconditional_guidance_scale,
+                        unconditional_conditioning=unconditional_conditioning, verbose=verbose)
+        b, device = x0.shape[0], x0.device
+        timesteps = self.ddim_timesteps
+        total_steps = timesteps.shape[0]
+        img = x.clone().detach()
+        with contextlib.ExitStack() as stack:
+            for u in _find_unets(self.model):
+                stack.enter_context(u.frozen_weights())
+            for i, step in enumerate(np.flip(timesteps)):
+                index = total_steps - i - 1
+                ts = torch.full((b,), int(step), device=device, dtype=torch.long)
+                img, _ = self.p_sample_ddim(img, c_trg, ts, index=index,
+                                            unconditional_guidance_scale=unconditional_guidance_scale,
+                                            unconditional_conditioning=unconditional_conditioning)
+        return img, x, x0
 
 
 # ----------------------------------------------------------------------------------------------

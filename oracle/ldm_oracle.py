@@ -426,6 +426,75 @@ def ddim_sample(apply_model, alphas_cumprod_f32: Tensor, S: int, x_T: Tensor, co
     return img, inter, eps_trace
 
 
+def make_ddim_timesteps_strength(num_ddim: int, num_ddpm: int = NUM_TIMESTEPS, strength: float = 1.0) -> np.ndarray:
+    """ddim2.py:9-29 / latent_manipulation.py:52-72 ('uniform'): linspace over [0, int(T*strength)], truncated
+    to int, first entry forced to 1, no +1 shift."""
+    ts = np.linspace(0, 1, num_ddim) * int(num_ddpm * strength)
+    ts = [int(v) for v in list(ts)]
+    return np.asarray([1] + ts[1:])
+
+
+def ddim_schedule_strength(alphas_cumprod_f32: Tensor, num_ddim: int, strength: float, eta: float = 0.0) -> dict:
+    """ddim2.py:66-97 (DDIMSampler2.make_schedule with ``strength``): the coefficient arrays of ddim_schedule on the
+    strength-scaled grid plus ``sqrt_one_minus_a_prev`` = np.sqrt(1. - ddim_alphas_prev) (float64 numpy, ddim2.py:96),
+    every value rounded to fp32 the way ``torch.full`` rounds it."""
+    ts = make_ddim_timesteps_strength(num_ddim, alphas_cumprod_f32.shape[0], strength)
+    ac = alphas_cumprod_f32.cpu()
+    alphas = ac[ts]
+    alphas_prev = np.asarray([ac[0]] + ac[ts[:-1]].tolist())
+    ap64 = torch.from_numpy(alphas_prev)
+    sig = eta * torch.sqrt((1 - alphas).reciprocal() * (1 - ap64) * (1 - alphas / ap64))
+    sqrt_1ma = np.sqrt((1.0 - alphas).numpy())
+    return dict(timesteps=ts,
+                a_t=alphas.numpy().astype(np.float32),
+                a_prev=alphas_prev.astype(np.float32),
+                sigma_t=sig.numpy().astype(np.float32),
+                sqrt_one_minus_at=np.asarray(sqrt_1ma, dtype=np.float32),
+                sqrt_one_minus_a_prev=np.sqrt(1. - alphas_prev).astype(np.float32))
+
+
+def ddim_invert_update(x: Tensor, e_t: Tensor, a_t, a_next, sqrt_one_minus_at) -> Tuple[Tensor, Tensor]:
+    """latent_manipulation.py:404-419 (``q_sample_ddim``): x_t -> x_{t+1}.  ``a_t`` = ddim_alphas_prev[index],
+    ``a_next`` = ddim_alphas[index], ``sqrt_one_minus_at`` = ddim_sqrt_one_minus_alphas_prev[index]."""
+    b = x.shape[0]
+    full = lambda v: torch.full((b, 1, 1, 1), float(v), dtype=torch.float32)
+    at, at_next, s1 = full(a_t), full(a_next), full(sqrt_one_minus_at)
+    pred_x0 = (x - s1 * e_t) / at.sqrt()
+    dir_xt = (1. - at_next).sqrt() * e_t
+    return at_next.sqrt() * pred_x0 + dir_xt, pred_x0
+
+
+@torch.no_grad()
+def ddim_latent_manipulation(apply_model, alphas_cumprod_f32: Tensor, S: int, x0: Tensor, c_src, c_trg,
+                             strength: float = 1.0, unconditional_guidance_scale: float = 1.0,
+                             unconditional_conditioning=None):
+    """latent_manipulation.py:421-489: DDIM inversion of ``x0`` under ``c_src`` over the strength-scaled grid, then
+    deterministic (eta = 0) re-generation under ``c_trg``.  Returns ``(img, x_inverted, x0)``."""
+    sch = ddim_schedule_strength(alphas_cumprod_f32, S, strength, 0.0)
+    ts = sch["timesteps"]
+    total = ts.shape[0]
+    b = x0.shape[0]
+
+    def eps(img, t, cond):
+        if unconditional_conditioning is None or unconditional_guidance_scale == 1.0:
+            return apply_model(img, t, cond)
+        e_u, e_c = apply_model(torch.cat([img] * 2), torch.cat([t] * 2),
+                               torch.cat([unconditional_conditioning, cond])).chunk(2)
+        return e_u + unconditional_guidance_scale * (e_c - e_u)
+
+    x = x0.clone()
+    for i, step in enumerate(ts):
+        t = torch.full((b,), int(step), dtype=torch.long)
+        x, _ = ddim_invert_update(x, eps(x, t, c_src), sch["a_prev"][i], sch["a_t"][i], sch["sqrt_one_minus_a_prev"][i])
+    img = x.clone()
+    for i, step in enumerate(np.flip(ts)):
+        index = total - i - 1
+        t = torch.full((b,), int(step), dtype=torch.long)
+        img, _ = ddim_update(img, eps(img, t, c_trg), sch["a_t"][index], sch["a_prev"][index], sch["sigma_t"][index],
+                             sch["sqrt_one_minus_at"][index])
+    return img, x, x0
+
+
 def rel_l2(a: Tensor, b: Tensor) -> float:
     """‖a−b‖₂ / ‖b‖₂ in float64 — the parity metric of BASELINE.json's north_star."""
     a, b = a.detach().double().cpu(), b.detach().double().cpu()

@@ -127,3 +127,37 @@ def cpu_ddim_sampler(model, flavour: str = "face_reenactment"):
             setattr(self, name, attr)
 
     return CpuDDIMSampler(model)
+
+
+def cpu_manipulation_sampler(model):
+    """The reference's DDIM-inversion sampler runnable here: ``ddim2.DDIMSampler2`` (FR ddim2.py:53) provides the
+    strength-scaled schedule and ``p_sample_ddim``; ``q_sample_ddim`` and ``latent_manipulation`` exist only inside
+    the private sampler class of FR/latent_manipulation.py (whose module-level imports — omegaconf, the AffectNet
+    dataset — are absent here), so their UNMODIFIED source text is cut out of that file and bound to a subclass."""
+    import re
+    import textwrap
+    import numpy as np
+    from tqdm import tqdm
+    import_reference("face_reenactment")
+    from ldm.models.diffusion.ddim2 import DDIMSampler2
+    src = open(os.path.join(REFERENCE_ROOT, "face_reenactment", "latent_manipulation.py")).read()
+
+    def cut(name):
+        m = re.search(r"^(    (?:@torch\.no_grad\(\)\n    )?def %s\(.*?)(?=^    (?:@|def )|^if __name__|\Z)" % name, src, re.S | re.M)
+        assert m, name
+        return textwrap.dedent(m.group(1))
+
+    ns = {"torch": torch, "np": np, "tqdm": lambda it, **k: it}
+    exec(cut("q_sample_ddim"), ns)
+    exec(cut("latent_manipulation"), ns)
+
+    class CpuManipulationSampler(DDIMSampler2):
+        q_sample_ddim = ns["q_sample_ddim"]
+        latent_manipulation = ns["latent_manipulation"]
+
+        def register_buffer(self, name, attr):  # ddim2.py:60-64 without the hard-coded cuda move
+            if type(attr) == torch.Tensor and attr.device != model.device:
+                attr = attr.to(model.device)
+            setattr(self, name, attr)
+
+    return CpuManipulationSampler(model)

@@ -34,6 +34,11 @@ def golden_unet64():
     return np.load(os.path.join(GOLDEN, "unet64.npz"))
 
 
+@pytest.fixture(scope="session")
+def golden_manip():
+    return np.load(os.path.join(GOLDEN, "manipulation.npz"))
+
+
 def record_parity(key, value):
     """Appends one measured parity figure to gpurun_out/parity_report.jsonl (kept as evidence under profiles/)."""
     import json

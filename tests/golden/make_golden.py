@@ -163,11 +163,50 @@ def trajectory_goldens():
     return out
 
 
+def manipulation_goldens():
+    """DDIM inversion + re-generation from the reference's own ``DDIMSampler2`` schedule and the
+    ``q_sample_ddim`` / ``latent_manipulation`` source of FR/latent_manipulation.py, tiny UNet on CPU."""
+    out = {}
+    cfg = O.TINY_UNET
+    sd = O.init_state_dict(cfg, seed=0)
+    B, hw = 2, 8
+    ref = R.reference_unet(cfg, "face_reenactment").eval()
+    ref.load_state_dict(sd, strict=True)
+    model = R.LatentDiffusionStandIn(ref)
+    x0, c_src = synth_inputs(cfg, B, hw, seed=5)
+    g = torch.Generator().manual_seed(6)
+    c_trg = torch.randn(B, 1, cfg["context_dim"], generator=g)
+    uc = torch.randn(B, 1, cfg["context_dim"], generator=g)
+    out["manip/x0"], out["manip/c_src"], out["manip/c_trg"], out["manip/uc"] = (t.numpy() for t in (x0, c_src, c_trg, uc))
+    for S, strength in ((10, 0.8), (12, 0.6), (50, 0.35)):
+        smp = R.cpu_manipulation_sampler(model)
+        smp.make_schedule(S, ddim_eta=0.0, strength=strength, verbose=False)
+        n = smp.ddim_timesteps.shape[0]
+        f = lambda arr: np.asarray([torch.full((1,), arr[i]).item() for i in range(n)], dtype=np.float32)
+        k = f"manip/S{S}_s{int(strength * 100)}"
+        out[k + "/timesteps"] = np.asarray(smp.ddim_timesteps, dtype=np.int64)
+        out[k + "/a_t"] = f(smp.ddim_alphas)
+        out[k + "/a_prev"] = f(smp.ddim_alphas_prev)
+        out[k + "/sqrt_one_minus_at"] = f(smp.ddim_sqrt_one_minus_alphas)
+        out[k + "/sqrt_one_minus_a_prev"] = f(smp.ddim_sqrt_one_minus_alphas_prev)
+    for tag, S, strength, scale in (("S10_s80", 10, 0.8, 1.0), ("S12_s60", 12, 0.6, 1.0), ("S8_s50_cfg2", 8, 0.5, 2.0)):
+        smp = R.cpu_manipulation_sampler(model)
+        import contextlib, io
+        with contextlib.redirect_stdout(io.StringIO()):
+            img, x_inv, _ = smp.latent_manipulation(c_src, c_trg, S, B, [3, hw, hw], x0=x0, eta=0., verbose=False,
+                                                    strength=strength, unconditional_guidance_scale=scale,
+                                                    unconditional_conditioning=uc if scale != 1.0 else None)
+        out[f"manip/{tag}/img"] = img.numpy()
+        out[f"manip/{tag}/x_inv"] = x_inv.numpy()
+    return out
+
+
 def main():
     torch.set_num_threads(max(1, os.cpu_count() or 1))
     only = sys.argv[1:]
     for fn, gen in (("unet.npz", unet_goldens), ("schedule.npz", schedule_goldens),
-                    ("trajectory.npz", trajectory_goldens), ("unet64.npz", unet64_goldens)):
+                    ("trajectory.npz", trajectory_goldens), ("unet64.npz", unet64_goldens),
+                    ("manipulation.npz", manipulation_goldens)):
         if only and fn not in only:
             continue
         data = gen()

@@ -136,3 +136,35 @@ def test_oracle_bit_exact_vs_live_reference():
     t = torch.tensor([3, 777])
     with torch.no_grad():
         assert torch.equal(ref(x, t, context=ctx), O.unet_forward(sd, cfg, x, t, ctx))
+
+
+# ------------------------------------------------------------------ DDIM inversion / manipulation
+@pytest.mark.parametrize("S,strength", [(10, 0.8), (12, 0.6), (50, 0.35)])
+def test_strength_schedule_bit_exact(S, strength, golden_manip):
+    """ddim2.py make_schedule(strength=) coefficient arrays, incl. sqrt(1 - a_prev) of the inversion step."""
+    sch = O.ddim_schedule_strength(O.ddpm_buffers()["alphas_cumprod"], S, strength, 0.0)
+    k = f"manip/S{S}_s{int(strength * 100)}"
+    assert np.array_equal(sch["timesteps"], golden_manip[k + "/timesteps"])
+    for name in ("a_t", "a_prev", "sqrt_one_minus_at", "sqrt_one_minus_a_prev"):
+        assert np.array_equal(sch[name], golden_manip[f"{k}/{name}"]), name
+
+
+def test_strength_one_is_out_of_range_like_the_reference():
+    # int(1000 * 1.0) = 1000 indexes past alphas_cumprod in the reference too (ddim2.py:34)
+    with pytest.raises(IndexError):
+        O.ddim_schedule_strength(O.ddpm_buffers()["alphas_cumprod"], 10, 1.0, 0.0)
+
+
+@pytest.mark.parametrize("tag,S,strength,scale", [("S10_s80", 10, 0.8, 1.0), ("S12_s60", 12, 0.6, 1.0),
+                                                  ("S8_s50_cfg2", 8, 0.5, 2.0)])
+def test_latent_manipulation_matches_reference_golden(tag, S, strength, scale, golden_manip):
+    """Inversion under c_src + regeneration under c_trg vs the reference's own q_sample_ddim / latent_manipulation."""
+    cfg = O.TINY_UNET
+    sd = O.init_state_dict(cfg, 0)
+    t = lambda k: torch.from_numpy(golden_manip["manip/" + k])
+    apply_model = lambda x, tt, c: O.unet_forward(sd, cfg, x, tt, c)
+    img, x_inv, _ = O.ddim_latent_manipulation(apply_model, O.ddpm_buffers()["alphas_cumprod"], S, t("x0"), t("c_src"),
+                                               t("c_trg"), strength=strength, unconditional_guidance_scale=scale,
+                                               unconditional_conditioning=t("uc") if scale != 1.0 else None)
+    assert O.rel_l2(x_inv, t(f"{tag}/x_inv")) <= 2e-6
+    assert O.rel_l2(img, t(f"{tag}/img")) <= 2e-6

@@ -226,3 +226,45 @@ def test_batch_sharding_is_result_invariant():
         full = m(x.cuda(), t, context=ctx.cuda())
         halves = torch.cat([m(x[:2].cuda(), t[:2], context=ctx[:2].cuda()), m(x[2:].cuda(), t[2:], context=ctx[2:].cuda())])
     assert torch.equal(full, halves)
+
+
+# ------------------------------------------------------------------ DDIM inversion / manipulation
+@pytest.mark.parametrize("precision", PRECISIONS)
+@pytest.mark.parametrize("tag,S,strength,scale", [("S10_s80", 10, 0.8, 1.0), ("S12_s60", 12, 0.6, 1.0),
+                                                  ("S8_s50_cfg2", 8, 0.5, 2.0)])
+def test_latent_manipulation_vs_reference_golden(tag, S, strength, scale, precision, golden_manip):
+    """DDIMSampler2.latent_manipulation (inversion under c_src, regeneration under c_trg) vs the reference."""
+    model = handle_for(O.TINY_UNET, precision)
+    t = lambda k: torch.from_numpy(golden_manip["manip/" + k]).cuda()
+    smp = P.DDIMSampler2(model)
+    img, x_inv, x0 = smp.latent_manipulation(t("c_src"), t("c_trg"), S, 2, [3, 8, 8], x0=t("x0"), eta=0., verbose=False,
+                                             strength=strength, unconditional_guidance_scale=scale,
+                                             unconditional_conditioning=t("uc") if scale != 1.0 else None)
+    k = f"manip/S{S}_s{int(strength * 100)}" if f"manip/S{S}_s{int(strength * 100)}/timesteps" in golden_manip else None
+    if k:
+        assert np.array_equal(smp.ddim_timesteps, golden_manip[k + "/timesteps"])
+    tol = TRAJ_TOL[precision]
+    e1, e2 = O.rel_l2(x_inv, t(f"{tag}/x_inv").cpu()), O.rel_l2(img, t(f"{tag}/img").cpu())
+    record_parity(f"manip/{tag}/{precision}", [e1, e2])
+    assert e1 <= tol and e2 <= tol, (e1, e2)
+    assert torch.equal(x0, t("x0"))
+
+
+def test_inversion_step_is_bit_exact():
+    """q_sample_ddim's update (the fused kernel with swapped coefficients and sigma = 0) is bit-identical to the
+    reference's chain of separately rounded IEEE fp32 ops (latent_manipulation.py:404-419) — restated in numpy
+    float32, because torch's CPU ``sqrt`` is not correctly rounded for every input (0.57086742 -> 1 ulp low) while
+    CUDA's, which the reference runs on, is — and within that 1-ulp coefficient difference of the torch-CPU oracle."""
+    g = torch.Generator().manual_seed(9)
+    x, e = torch.randn(4, 3, 16, 16, generator=g), torch.randn(4, 3, 16, 16, generator=g)
+    sch = O.ddim_schedule_strength(O.ddpm_buffers()["alphas_cumprod"], 12, 0.6, 0.0)
+    f = np.float32
+    for i in (0, 5, 11):
+        a_t, a_next, s1 = float(sch["a_prev"][i]), float(sch["a_t"][i]), float(sch["sqrt_one_minus_a_prev"][i])
+        got_x, got_p = P.ddim_step(x.cuda(), e.cuda(), None, None, a_t, a_next, 0.0, s1)
+        xn, en = x.numpy(), e.numpy()
+        p0 = (xn - f(s1) * en) / np.sqrt(f(a_t))
+        xp = np.sqrt(f(a_next)) * p0 + np.sqrt(f(1) - f(a_next)) * en
+        assert np.array_equal(got_p.cpu().numpy(), p0) and np.array_equal(got_x.cpu().numpy(), xp)
+        ref_x, ref_p = O.ddim_invert_update(x, e, a_t, a_next, s1)
+        assert O.rel_l2(got_x.cpu(), ref_x) <= 2e-7 and O.rel_l2(got_p.cpu(), ref_p) <= 2e-7

@@ -11,7 +11,7 @@ import ctypes as C
 import os
 
 F32, BF16, F16 = 0, 1, 2
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("LDMB200_LIB", os.path.join(_HERE, "libldmb200.so"))
@@ -63,6 +63,18 @@ class LinearJob(C.Structure):
     ]
 
 
+class WgradDesc(C.Structure):
+    """``ldmb200_wgrad_desc`` (include/ldmb200.h)."""
+    _fields_ = [
+        ("dy", C.c_void_p), ("x", C.c_void_p), ("dw", C.c_void_p),
+        ("n_stride", C.c_int64), ("c_stride", C.c_int64), ("tap_stride", C.c_int64),
+        ("dy_ld", C.c_int32), ("n", C.c_int32),
+        ("c_ld", C.c_int32), ("c", C.c_int32),
+        ("batch", C.c_int32), ("h", C.c_int32), ("w", C.c_int32),
+        ("ksize", C.c_int32), ("stride", C.c_int32), ("pad_", C.c_int32),
+    ]
+
+
 #: every symbol include/ldmb200.h declares: name -> (restype, argtypes)
 _i, _i64, _f, _p = C.c_int, C.c_int64, C.c_float, C.c_void_p
 SIGNATURES = {
@@ -87,6 +99,22 @@ SIGNATURES = {
     "ldmb200_pack_weights": (_i, [_p, _i, _p]),
     "ldmb200_attention_simt": (_i, [_p, _i, _i, _p, _i, _p, _i, _i, _p, _i, _i, _i, _i, _i, _f, _p]),
     "ldmb200_attention_tc": (_i, [_p, _i, _i, _i, _i, _p, _i, _i, _i, _i, _i, _f, _p]),
+    # ---- training step
+    "ldmb200_attention_tc_lse": (_i, [_p, _i, _i, _i, _i, _p, _i, _i, _p, _i, _i, _i, _f, _p]),
+    "ldmb200_q_sample": (_i, [_p, _p, _p, _p, _p, _p, _i, _i64, _p]),
+    "ldmb200_mse_loss_grad": (_i, [_p, _p, _p, _p, _i, _i64, _p]),
+    "ldmb200_grad_cast": (_i, [_p, _i, _p, _i64, _i, _i, _p, _i, _p, _p, _i, _p]),
+    "ldmb200_wgrad": (_i, [C.POINTER(WgradDesc), _p]),
+    "ldmb200_groupnorm_bwd": (_i, [_p, _i, _p, _i, _p, _p, _p, _p, _i, _p, _i, _p, _i, _p, _p, _i, _i, _i, _f, _i, _p,
+                                   _i, _p, _p]),
+    "ldmb200_layernorm_bwd": (_i, [_p, _p, _p, _p, _p, _p, _p, _i64, _i, _f, _p]),
+    "ldmb200_geglu_fwd": (_i, [_p, _p, _i64, _i, _p]),
+    "ldmb200_geglu_bwd": (_i, [_p, _p, _p, _i64, _i, _p]),
+    "ldmb200_attention_bwd": (_i, [_p, _i, _i, _i, _i, _p, _p, _i, _p, _p, _i, _i, _i, _f, _p]),
+    "ldmb200_zero_insert2x": (_i, [_p, _p, _i, _i, _i, _i, _p]),
+    "ldmb200_downsum2x": (_i, [_p, _p, _i, _i, _i, _i, _p]),
+    "ldmb200_small_linear_bwd": (_i, [_p, _i, _p, _p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "ldmb200_adamw_ema": (_i, [_p, _p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _f, _f, _f, _p]),
 }
 
 _lib = None

@@ -157,7 +157,7 @@ constexpr float AT_REREF = 8.0f;
 
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict__ out, int out_ld, int out_dtype,
-                    int n_tok, int q_off, int k_off, int v_off, float scale_log2e) {
+                    int n_tok, int q_off, int k_off, int v_off, float scale_log2e, float* __restrict__ lse2) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sQ = smem;                               // 2 tiles (256 rows), one TMA box
@@ -351,6 +351,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
       const float inv = 1.0f / l;
       const int qi = qb * (AT_NQ * 128) + q * 128 + r;
       if (qi < n_tok) {
+        // training: log2 of the softmax denominator in the exp2 domain (scores scaled by scale*log2 e)
+        if (lse2) lse2[((size_t)b * gridDim.y + h) * n_tok + qi] = mb + log2f(l);
         uint16_t* op = out + (size_t)(row_base + qi) * out_ld + h * 32;
 #pragma unroll
         for (int d = 0; d < 32; d += 8) {
@@ -375,8 +377,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
 
 using namespace ldm;
 
-extern "C" int ldmb200_attention_tc(const void* qkv, int ld, int q_off, int k_off, int v_off, void* out, int out_ld,
-                                    int out_dtype, int batch, int heads, int n_tokens, float scale, void* stream) {
+static int attention_tc_launch(const void* qkv, int ld, int q_off, int k_off, int v_off, void* out, int out_ld,
+                               int out_dtype, float* lse2, int batch, int heads, int n_tokens, float scale, void* stream) {
   LDM_CHECK_ARG(qkv && out && batch > 0 && heads > 0 && n_tokens > 0, "attention_tc: bad arguments");
   LDM_CHECK_ARG(ld % 8 == 0 && out_ld % 8 == 0 && q_off % 8 == 0 && k_off % 8 == 0 && v_off % 8 == 0,
                 "attention_tc: leading dims / offsets must be multiples of 8 elements (16 bytes)");
@@ -401,7 +403,21 @@ extern "C" int ldmb200_attention_tc(const void* qkv, int ld, int q_off, int k_of
   dim3 grid(ceil_div(n_tokens, AT_NQ * 128), heads, batch);
   const float scale_log2e = scale * 1.4426950408889634f;
   attention_tc_kernel<<<grid, AT_THREADS, AT_SMEM, (cudaStream_t)stream>>>(tm, (uint16_t*)out, out_ld, out_dtype,
-                                                                           n_tokens, q_off, k_off, v_off, scale_log2e);
+                                                                           n_tokens, q_off, k_off, v_off, scale_log2e, lse2);
   LDM_CHECK_LAUNCH("attention_tc");
   return 0;
+}
+
+extern "C" int ldmb200_attention_tc(const void* qkv, int ld, int q_off, int k_off, int v_off, void* out, int out_ld,
+                                    int out_dtype, int batch, int heads, int n_tokens, float scale, void* stream) {
+  return attention_tc_launch(qkv, ld, q_off, k_off, v_off, out, out_ld, out_dtype, nullptr, batch, heads, n_tokens, scale,
+                             stream);
+}
+
+extern "C" int ldmb200_attention_tc_lse(const void* qkv, int ld, int q_off, int k_off, int v_off, void* out, int out_ld,
+                                        int out_dtype, float* lse2, int batch, int heads, int n_tokens, float scale,
+                                        void* stream) {
+  LDM_CHECK_ARG(lse2, "attention_tc_lse: lse2 is NULL");
+  return attention_tc_launch(qkv, ld, q_off, k_off, v_off, out, out_ld, out_dtype, lse2, batch, heads, n_tokens, scale,
+                             stream);
 }

@@ -523,8 +523,25 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const ldmb200_pack_jo
   }
   const int taps = j.ksize * j.ksize;
   const int64_t kp = (int64_t)taps * j.c_pad;
-  const int64_t total = (int64_t)j.n_pad * kp;
   uint16_t* dst = reinterpret_cast<uint16_t*>(j.dst);
+  if (j.kind == 3) {
+    // data-gradient operand: rows = source input channels (padded to n_pad), row = [tap'][c_pad columns], this job
+    // fills columns [row_offset, row_offset + block_n) from source output channels [0, n); taps flipped
+    const int ncols = j.block_n;
+    const int64_t total3 = (int64_t)j.n_pad * taps * ncols;
+    for (int64_t i = i0; i < total3; i += stride) {
+      const int nn = (int)(i % ncols);
+      const int64_t t = i / ncols;
+      const int tapd = (int)(t % taps), cc = (int)(t / taps);
+      float v = 0.f;
+      if (nn < j.n && cc < j.c) v = j.src[((size_t)nn * j.c + cc) * taps + (taps - 1 - tapd)];
+      dst[(size_t)cc * kp + (size_t)tapd * j.c_pad + j.row_offset + nn] =
+          j.dst_dtype == LDMB200_F16 ? __half_as_ushort(__float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f)))
+                                     : __bfloat16_as_ushort(__float2bfloat16_rn(v));
+    }
+    return;
+  }
+  const int64_t total = (int64_t)j.n_pad * kp;
   for (int64_t i = i0; i < total; i += stride) {
     int rp = (int)(i / kp);
     int rem = (int)(i % kp);

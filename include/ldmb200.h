@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define LDMB200_ABI_VERSION 2
+#define LDMB200_ABI_VERSION 3
 
 #define LDMB200_F32 0
 #define LDMB200_BF16 1
@@ -181,6 +181,11 @@ int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream);
  *   kind 0  conv/linear weight [n, c, k, k] -> [n_pad, k, k, c_pad]   (zero padded)
  *   kind 1  same, rows permuted for the GEGLU epilogue (value/gate interleaved in groups of 16)
  *   kind 2  fp32 vector copy with the GEGLU permutation (bias of ff.net.0.proj)
+ *   kind 3  data-gradient operand (training): the transposed, tap-flipped matrix
+ *           [c_pad_as_rows, k, k, n_pad_as_cols]:  dst[cc, (2-kh, 2-kw), nn] = src[nn, cc, kh, kw], so that
+ *           dX = conv(dY, dst) through the same ldmb200_igemm_tc (autograd's conv2d / linear input gradient).
+ *           n_pad = padded row count (from c), c_pad = padded column count (from n); row_offset here offsets the
+ *           destination COLUMN (fused QKV: the q, k, v blocks sit side by side along K)
  * jobs is a DEVICE array of n_jobs ldmb200_pack_job.
  */
 typedef struct ldmb200_pack_job {
@@ -211,6 +216,103 @@ int ldmb200_attention_simt(const float* q, int q_ld, int q_off, const float* k, 
                            void* stream);
 int ldmb200_attention_tc(const void* qkv, int ld, int q_off, int k_off, int v_off, void* out, int out_ld,
                          int out_dtype, int batch, int heads, int n_tokens, float scale, void* stream);
+
+/* Self-attention forward for training: as ldmb200_attention_tc, plus lse2[b, h, i] = log2 sum_j exp2(s_ij) with
+ * s = scale * log2(e) * q.k (fp32 [B, heads, N]) which the backward kernels use to recompute P. */
+int ldmb200_attention_tc_lse(const void* qkv, int ld, int q_off, int k_off, int v_off, void* out, int out_ld,
+                             int out_dtype, float* lse2, int batch, int heads, int n_tokens, float scale, void* stream);
+
+/* ===================================================================================================
+ * Training step (BASELINE config 4): the backward kernels of LatentDiffusion.p_losses
+ * (ldm/models/diffusion/ddpm.py:1014-1047; talking_face ddpm2cond.py:965-998) through the UNet.  In the reference
+ * these are autograd's derivative formulas of the ATen ops cited per function; operands are bf16, accumulation
+ * and the residual-stream gradient are fp32.  Parameter gradients are ACCUMULATED (+=) into fp32 buffers in the
+ * nn.Parameter layouts, which the caller zeroes at the start of a step.
+ * =================================================================================================== */
+
+/* q_sample — ddpm.py:273-276:  out[b] = sqrt_ac[t_b] * x0[b] + sqrt_1mac[t_b] * noise[b]  (fp32, separately
+ * rounded products like the reference's extract_into_tensor arithmetic).  per_sample = C*H*W. */
+int ldmb200_q_sample(const float* x0, const float* noise, const int64_t* t, const float* sqrt_ac,
+                     const float* sqrt_1mac, float* out, int batch, int64_t per_sample, void* stream);
+
+/* get_loss(pred, target, mean=False).mean([1,2,3]) then .mean() with l_simple_weight = 1, logvar = 0
+ * (ddpm.py:1029-1044, loss_type l2):  loss_per_sample[b] = mean_j (pred - target)^2 ;
+ * dpred = 2 (pred - target) / (batch * per_sample)  — the gradient of the batch-mean loss. */
+int ldmb200_mse_loss_grad(const float* pred, const float* target, float* loss_per_sample, float* dpred, int batch,
+                          int64_t per_sample, void* stream);
+
+/* Gradient cast + column sums.  g [rows, n] (in_dtype fp32 | bf16) -> g16 [rows, n] bf16 (nullable);
+ * per_sample_sum[b, j] += sum of sample b's rows (nullable; [batch, ps_ld]; autograd of the `h + emb_out[..., None,
+ * None]` broadcast openaimodel.py:270 and of the length-1 cross-attention row vector), total_sum[j] += sum over all
+ * rows for j < n_valid (nullable; bias gradients); total_sum2 likewise (second bias fed by the same gradient). */
+int ldmb200_grad_cast(const void* g, int in_dtype, void* g16, int64_t rows, int n, int rows_per_sample,
+                      float* per_sample_sum, int ps_ld, float* total_sum, float* total_sum2, int n_valid, void* stream);
+
+/* Weight gradient of a convolution / linear on the tensor cores (autograd of F.conv2d / F.linear w.r.t. weight):
+ *   dw[nn, cc, tap] += sum_m dy[m, nn] * X(m, tap, cc)
+ * dy bf16 [M, dy_ld] (M = batch*h*w output pixels, columns [0, n) used); x bf16 channels-last with row pitch c_ld,
+ * channels [0, c) used: stride 1 -> [batch, h, w, c_ld]; stride 2 -> the space_to_depth2 planes [batch, 4, h, w, c_ld]
+ * of the 2h x 2w input.  dw is addressed dw[nn*n_stride + cc*c_stride + tap*tap_stride] (fp32, atomically
+ * accumulated; nn.Conv2d layout: n_stride = c*k*k, c_stride = k*k, tap_stride = 1). */
+typedef struct ldmb200_wgrad_desc {
+  const void* dy;
+  const void* x;
+  float* dw;
+  int64_t n_stride, c_stride, tap_stride;
+  int32_t dy_ld, n;
+  int32_t c_ld, c;
+  int32_t batch, h, w;
+  int32_t ksize, stride;
+  int32_t pad_;
+} ldmb200_wgrad_desc;
+int ldmb200_wgrad(const ldmb200_wgrad_desc* d, void* stream);
+
+/* GroupNorm (+SiLU) backward — autograd of GroupNorm32 util.py:214-216 followed by nn.SiLU.
+ * x1/x2, gamma, beta, groups, eps, silu, stats_ws: exactly what the forward call took (stats_ws still holds what it
+ * left there; fused = 1 if that call was ldmb200_groupnorm_fused).  dy bf16 [B*hw, C].  addend (nullable; dtype
+ * add_dtype fp32 | bf16, [B*hw, C]) is added to the input gradient (the identity skip / the raw-copy branch).
+ * dx1 [B*hw, c1], dx2 [B*hw, c2] fp32: written (acc = 0) or accumulated (acc = 1).  dgamma/dbeta [C] accumulated.
+ * ws2: workspace of ldmb200_groupnorm_ws_floats floats. */
+int ldmb200_groupnorm_bwd(const float* x1, int c1, const float* x2, int c2, const float* gamma, const float* beta,
+                          const void* dy, const void* addend, int add_dtype, float* dx1, int acc1, float* dx2,
+                          int acc2, float* dgamma, float* dbeta, int batch, int hw, int groups, float eps, int silu,
+                          const float* stats_ws, int fused, float* ws2, void* stream);
+
+/* LayerNorm backward (nn.LayerNorm attention.py:203-205): dx = ln'(x)^T dy + addend (fp32, nullable); dx may alias
+ * addend.  dy bf16 [rows, c].  dgamma/dbeta accumulated. */
+int ldmb200_layernorm_bwd(const float* x, const float* gamma, const void* dy, const float* addend, float* dx,
+                          float* dgamma, float* dbeta, int64_t rows, int c, float eps, void* stream);
+
+/* GEGLU (attention.py:37-44) unfused for training: u bf16 [rows, 2*inner] = proj(x) (value | gate halves);
+ * fwd: out = value * gelu_erf(gate) (bf16 [rows, inner]); bwd: du from dout. */
+int ldmb200_geglu_fwd(const void* u, void* out, int64_t rows, int inner, void* stream);
+int ldmb200_geglu_bwd(const void* u, const void* dout, void* du, int64_t rows, int inner, void* stream);
+
+/* Self-attention backward (autograd of attention.py:178-192 with d_head = 32), recomputing P from lse2:
+ * qkv bf16 [B*N, ld] (offsets as the forward), dout bf16 [B*N, o_ld], out bf16 [B*N, o_ld] (forward output, for
+ * D = rowsum(dout * out)), lse2 from ldmb200_attention_tc_lse -> dqkv bf16 [B*N, ld] at the same offsets. */
+int ldmb200_attention_bwd(const void* qkv, int ld, int q_off, int k_off, int v_off, const void* out, const void* dout,
+                          int o_ld, const float* lse2, void* dqkv, int batch, int heads, int n_tokens, float scale,
+                          void* stream);
+
+/* Resampling backward: zero_insert2x — dy bf16 [B, h, w, C] -> z bf16 [B, 2h, 2w, C], z[2i, 2j] = dy[i, j], else 0
+ * (input gradient of the stride-2 Downsample.op conv = 3x3 conv of z with the kind-3 weights);
+ * downsum2x — du fp32 [B, 2h, 2w, C] -> dx fp32 [B, h, w, C] = sum of each 2x2 block (autograd of F.interpolate
+ * nearest 2x, openaimodel.py:116). */
+int ldmb200_zero_insert2x(const void* dy, void* z, int batch, int h, int w, int c, void* stream);
+int ldmb200_downsum2x(const float* du, float* dx, int batch, int h, int w, int c, void* stream);
+
+/* Backward of ldmb200_small_linear (out = bias + act(in) W^T): dw [n, k] += dout^T act(in); dbias [n] += colsum(dout);
+ * din [rows, k] (nullable) = or += (acc_din) (dout W) * act'(in).  Any of dw/dbias/din may be NULL. */
+int ldmb200_small_linear_bwd(const float* in, int in_ld, const float* w, const float* dout, int dout_ld, float* dw,
+                             float* dbias, float* din, int din_ld, int acc_din, int rows, int k, int n, int silu_in,
+                             void* stream);
+
+/* Fused AdamW step + LitEma update over flat fp32 arrays (torch.optim.AdamW semantics ddpm.py:1363-1372;
+ * LitEma.forward ema.py:25-44: shadow -= (1 - decay) * (shadow - param)).  ema may be NULL. */
+int ldmb200_adamw_ema(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, float* ema, int64_t n,
+                      float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1,
+                      float bias_corr2, float ema_one_minus_decay, void* stream);
 
 #ifdef __cplusplus
 }

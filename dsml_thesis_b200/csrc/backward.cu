@@ -150,13 +150,12 @@ __global__ void gn_bwd_reduce_kernel(const float* __restrict__ x1, int c1, const
                                      const uint16_t* __restrict__ dy, float* __restrict__ dgamma,
                                      float* __restrict__ dbeta, int hw, int groups, int R, int S_fwd, float eps, int silu,
                                      const float* __restrict__ ws, float* __restrict__ ws2) {
-  extern __shared__ float sm[];  // [2][C] group-partial staging, then s_mean/s_rstd
+  extern __shared__ float sm[];  // [2][C] channel sums, then [2][R][C] per-row-lane partials (fixed-order fold)
   __shared__ float s_mean[64], s_rstd[64];
   const int C = c1 + c2, q = C >> 2, cpg = C / groups;
   const int cq = threadIdx.x % q, rl = threadIdx.x / q;
   const int S = gridDim.x, s = blockIdx.x, b = blockIdx.y;
   for (int g = threadIdx.x; g < groups; g += blockDim.x) gn_group_stats(ws, b, g, groups, S_fwd, cpg, hw, eps, s_mean[g], s_rstd[g]);
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sm[i] = 0.f;
   __syncthreads();
   float mu[4], rs[4], ga[4], be[4];
 #pragma unroll
@@ -164,6 +163,7 @@ __global__ void gn_bwd_reduce_kernel(const float* __restrict__ x1, int c1, const
     const int c = cq * 4 + j, g = c / cpg;
     mu[j] = s_mean[g]; rs[j] = s_rstd[g]; ga[j] = gamma[c]; be[j] = beta[c];
   }
+  float* part = sm + 2 * C;  // [2][R][C]
   const int rows_per = (hw + S - 1) / S;
   const int r0 = s * rows_per, r1 = min(hw, r0 + rows_per);
   float s1[4] = {0, 0, 0, 0}, s2[4] = {0, 0, 0, 0};
@@ -183,14 +183,23 @@ __global__ void gn_bwd_reduce_kernel(const float* __restrict__ x1, int c1, const
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    atomicAdd(&sm[cq * 4 + j], s1[j]);
-    atomicAdd(&sm[C + cq * 4 + j], s2[j]);
+    part[rl * C + cq * 4 + j] = s1[j];
+    part[(R + rl) * C + cq * 4 + j] = s2[j];
   }
   __syncthreads();
+  // fixed-order fold over the row lanes: the group sums that enter the data gradient are run-to-run deterministic
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    atomicAdd(dbeta + c, sm[c]);
-    atomicAdd(dgamma + c, sm[C + c]);
+    float a = 0.f, b2 = 0.f;
+    for (int r = 0; r < R; ++r) {
+      a += part[r * C + c];
+      b2 += part[(R + r) * C + c];
+    }
+    sm[c] = a;
+    sm[C + c] = b2;
+    atomicAdd(dbeta + c, a);
+    atomicAdd(dgamma + c, b2);
   }
+  __syncthreads();
   for (int g = threadIdx.x; g < groups; g += blockDim.x) {
     float a = 0.f, c = 0.f;
     for (int j = 0; j < cpg; ++j) {
@@ -571,7 +580,7 @@ int ldmb200_groupnorm_bwd(const float* x1, int c1, const float* x2, int c2, cons
   if (S2 > GNB_MAX_SPLITS) S2 = GNB_MAX_SPLITS;
   const int threads = q * R;
   cudaStream_t st = (cudaStream_t)stream;
-  gn_bwd_reduce_kernel<<<dim3(S2, batch), threads, 2 * C * sizeof(float), st>>>(
+  gn_bwd_reduce_kernel<<<dim3(S2, batch), threads, (size_t)(2 + 2 * R) * C * sizeof(float), st>>>(
       x1, c1, x2, c2, gamma, beta, (const uint16_t*)dy, dgamma, dbeta, hw, groups, R, S_fwd, eps, silu, stats_ws, ws2);
   LDM_CHECK_LAUNCH("groupnorm_bwd reduce");
   int T = hw / (R * 4);

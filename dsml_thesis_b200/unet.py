@@ -317,7 +317,7 @@ class _Plan:
         self.py_ops: Dict[int, object] = {}  # op index -> python callable run before that op
         self.keep: List[object] = []     # ctypes structs referenced by pointer from ops
         self.arena = _Arena(dev)
-        self.pack = model._weight_pack(self.act) if self.tc else None
+        self.pack = self._make_pack()
         f32 = dict(dtype=torch.float32, device=dev)
         self.x_in = torch.empty(B, model.in_channels, H, W, **f32)
         self.t_in = torch.empty(B, dtype=torch.int64, device=dev)
@@ -330,6 +330,9 @@ class _Plan:
         self._build()
 
     # ---- small helpers -------------------------------------------------------------------
+    def _make_pack(self):
+        return self.model._weight_pack(self.act) if self.tc else None
+
     def new(self, rows: int, c: int, dtype: int) -> _Act:
         return _Act(self.arena.alloc(rows * c * (4 if dtype == F32 else 2)), rows, c, dtype)
 
@@ -841,6 +844,7 @@ class UNetModel(nn.Module):
         self._frozen = 0
         self._pack_valid: set = set()              # dtypes whose pack matches the current parameters
         self.launches = 0   # kernels launched by forward() so far (bench.py's gpu_launches)
+        self._train_state = None  # dsml_thesis_b200.train._TrainState (gradient arena, training plans)
 
     # ---- reference API stubs (openaimodel.py:694-708): the fp16 conversion is a no-op there too -------
     def convert_to_fp16(self):
@@ -855,6 +859,7 @@ class UNetModel(nn.Module):
 
     def _apply(self, fn, *a, **k):
         # .to()/.cuda()/.float() may move parameter storage: drop everything that holds raw pointers
+        self._train_state = None
         self._plans = {}
         self._packs = {}
         self._pack_valid = set()
@@ -902,9 +907,13 @@ class UNetModel(nn.Module):
     def _forward(self, x, timesteps, context, y=None, clone=True):
         if not x.is_cuda:
             raise _cabi.Ldmb200Error("dsml_thesis_b200.UNetModel runs on a CUDA device only (no CPU fallback)")
-        if torch.is_grad_enabled() and (self.training or x.requires_grad):
-            raise NotImplementedError("the autograd/training path of the B200 UNet is not built yet; "
-                                      "call under torch.no_grad() with model.eval()")
+        if torch.is_grad_enabled() and self.training:
+            # DDPM training step (ddpm.py:1014-1047): forward that keeps what the backward kernels need + autograd node
+            from .train import unet_train_forward
+            return unet_train_forward(self, x, timesteps, context, y)
+        if torch.is_grad_enabled() and x.requires_grad:
+            raise NotImplementedError("gradients w.r.t. the latent in eval mode (guidance by gradient) are not built; "
+                                      "call under torch.no_grad(), or model.train() for the training step")
         if context is None:
             raise ValueError("context is required (use_spatial_transformer=True, attention.py:170-176)")
         if timesteps is None or timesteps.dtype.is_floating_point:

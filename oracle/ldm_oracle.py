@@ -297,10 +297,10 @@ def run_layers(sd, layers, h: Tensor, emb: Tensor, context) -> Tensor:
     return h
 
 
-@torch.no_grad()
-def unet_forward(sd: Dict[str, Tensor], cfg: dict, x: Tensor, timesteps: Tensor,
-                 context: Optional[Tensor] = None, taps: Optional[dict] = None) -> Tensor:
-    """openaimodel.py:710-742.  ``taps`` (optional dict) receives each block's output for block-level parity."""
+def unet_forward_autograd(sd: Dict[str, Tensor], cfg: dict, x: Tensor, timesteps: Tensor,
+                          context: Optional[Tensor] = None, taps: Optional[dict] = None) -> Tensor:
+    """openaimodel.py:710-742 with autograd left on (the training oracle differentiates through it).
+    ``taps`` (optional dict) receives each block's output for block-level parity."""
     st = unet_structure(cfg)
     t_emb = timestep_embedding(timesteps, cfg["model_channels"])
     emb = F.linear(F.silu(F.linear(t_emb, sd["time_embed.0.weight"], sd["time_embed.0.bias"])),
@@ -323,6 +323,44 @@ def unet_forward(sd: Dict[str, Tensor], cfg: dict, x: Tensor, timesteps: Tensor,
     h = h.type(x.dtype)
     h = F.silu(group_norm32(h, sd["out.0.weight"], sd["out.0.bias"], 1e-5))
     return F.conv2d(h, sd["out.2.weight"], sd["out.2.bias"], padding=1)
+
+
+@torch.no_grad()
+def unet_forward(sd: Dict[str, Tensor], cfg: dict, x: Tensor, timesteps: Tensor,
+                 context: Optional[Tensor] = None, taps: Optional[dict] = None) -> Tensor:
+    """openaimodel.py:710-742 (inference: no autograd graph)."""
+    return unet_forward_autograd(sd, cfg, x, timesteps, context, taps)
+
+
+# ----------------------------------------------------------------------------------------
+# training step: LatentDiffusion.p_losses (ddpm.py:1014-1047; talking_face ddpm2cond.py:965-998)
+# ----------------------------------------------------------------------------------------
+
+def q_sample(x_start: Tensor, t: Tensor, noise: Tensor, bufs: Optional[dict] = None) -> Tensor:
+    """ddpm.py:273-276: extract_into_tensor(sqrt_alphas_cumprod, t) * x_start + extract(sqrt_one_minus, t) * noise."""
+    bufs = ddpm_buffers() if bufs is None else bufs
+    e = lambda a: a.gather(-1, t).reshape(-1, 1, 1, 1)
+    return e(bufs["sqrt_alphas_cumprod"]) * x_start + e(bufs["sqrt_one_minus_alphas_cumprod"]) * noise
+
+
+def p_losses(sd: Dict[str, Tensor], cfg: dict, x_start: Tensor, t: Tensor, noise: Tensor, context: Tensor,
+             c_concat: Optional[Tensor] = None):
+    """ddpm.py:1014-1047 for parameterization "eps", loss_type "l2", logvar == 0 (not learned), l_simple_weight 1,
+    original_elbo_weight 0:  x_noisy = q_sample; eps = apply_model (TF: cat([x_noisy, c34], 1), ddpm2cond.py:1307-1311);
+    loss_simple = mse(eps, noise).mean([1,2,3]); loss = loss_simple.mean().
+    Returns ``(loss, grads)`` with ``grads`` = d loss / d sd[name] for every parameter, plus ``"context"``."""
+    leaves = {k: v.detach().clone().requires_grad_(True) for k, v in sd.items()}
+    ctx = context.detach().clone().requires_grad_(True)
+    x_noisy = q_sample(x_start, t, noise)
+    x_in = torch.cat([x_noisy, c_concat], dim=1) if c_concat is not None else x_noisy
+    eps = unet_forward_autograd(leaves, cfg, x_in, t, ctx)
+    loss_simple = ((eps - noise) ** 2).mean([1, 2, 3])
+    loss = loss_simple.mean()
+    names = list(leaves)
+    gs = torch.autograd.grad(loss, [leaves[k] for k in names] + [ctx], allow_unused=True)
+    grads = {k: (g if g is not None else torch.zeros_like(leaves[k])) for k, g in zip(names, gs[:-1])}
+    grads["context"] = gs[-1] if gs[-1] is not None else torch.zeros_like(ctx)
+    return loss.detach(), grads
 
 
 # ----------------------------------------------------------------------------------------

@@ -201,12 +201,47 @@ def manipulation_goldens():
     return out
 
 
+def train_goldens():
+    """p_losses through the REAL reference UNetModel + torch autograd (ddpm.py:1014-1047 arithmetic spelled out with the
+    reference's own q_sample / schedule; LatentDiffusion itself needs pytorch_lightning): loss and the gradient of
+    a fingerprint (L2 norm + 64 / 8 evenly spaced entries) of the gradient of every parameter of the tiny / FR / TF UNets
+    at 16x16 latents."""
+    out = {}
+    for tag, cfg, flavour, B, hw in (("tiny", O.TINY_UNET, "face_reenactment", 2, 16),
+                                     ("fr16", O.FR_UNET, "face_reenactment", 2, 16),
+                                     ("tf16", O.TF_UNET, "talking_face", 2, 16)):
+        unet = R.reference_unet(cfg, flavour)
+        sd = O.init_state_dict(cfg, 0)
+        unet.load_state_dict(sd, strict=True)
+        unet.train()
+        model = R.LatentDiffusionStandIn(unet, two_cond=(flavour == "talking_face"))
+        g = torch.Generator().manual_seed(77)
+        x0 = torch.randn(B, 3, hw, hw, generator=g)
+        noise = torch.randn(B, 3, hw, hw, generator=g)
+        ctx = torch.randn(B, 1, cfg["context_dim"], generator=g).requires_grad_(True)
+        c34 = torch.randn(B, 6, hw, hw, generator=g) if flavour == "talking_face" else None
+        t = torch.tensor([731, 12][:B])
+        x_noisy = model.q_sample(x0, t, noise)
+        eps = model.apply_model(x_noisy, t, ctx, c34) if c34 is not None else model.apply_model(x_noisy, t, ctx)
+        loss = torch.nn.functional.mse_loss(eps, noise, reduction="none").mean([1, 2, 3]).mean()
+        loss.backward()
+        out[f"train/{tag}/loss"] = loss.detach().numpy()
+        out[f"train/{tag}/x_noisy"] = x_noisy.detach().numpy()
+        out[f"train/{tag}/dctx"] = ctx.grad.numpy()
+        for name, p in unet.named_parameters():
+            gr = p.grad if p.grad is not None else torch.zeros_like(p)
+            flat = gr.reshape(-1)
+            idx = torch.linspace(0, flat.numel() - 1, 64 if tag == "tiny" else 8).long()
+            out[f"train/{tag}/gradfp/{name}"] = torch.cat([gr.double().norm().reshape(1), flat[idx].double()]).numpy()
+    return out
+
+
 def main():
     torch.set_num_threads(max(1, os.cpu_count() or 1))
     only = sys.argv[1:]
     for fn, gen in (("unet.npz", unet_goldens), ("schedule.npz", schedule_goldens),
                     ("trajectory.npz", trajectory_goldens), ("unet64.npz", unet64_goldens),
-                    ("manipulation.npz", manipulation_goldens)):
+                    ("manipulation.npz", manipulation_goldens), ("train.npz", train_goldens)):
         if only and fn not in only:
             continue
         data = gen()

@@ -1,5 +1,7 @@
 """Pins the oracle restatement (oracle/ldm_oracle.py) to the committed golden vectors, which are
 outputs of the REAL reference (tests/golden/make_golden.py).  CPU only."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -168,3 +170,40 @@ def test_latent_manipulation_matches_reference_golden(tag, S, strength, scale, g
                                                unconditional_conditioning=t("uc") if scale != 1.0 else None)
     assert O.rel_l2(x_inv, t(f"{tag}/x_inv")) <= 2e-6
     assert O.rel_l2(img, t(f"{tag}/img")) <= 2e-6
+
+
+# ---- training step: oracle p_losses + autograd vs the REAL reference UNet's gradients ----
+@pytest.fixture(scope="module")
+def golden_train():
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "train.npz"))
+
+
+def _train_inputs(cfg, two_cond, B=2, hw=16):
+    g = torch.Generator().manual_seed(77)
+    x0 = torch.randn(B, 3, hw, hw, generator=g)
+    noise = torch.randn(B, 3, hw, hw, generator=g)
+    ctx = torch.randn(B, 1, cfg["context_dim"], generator=g)
+    c34 = torch.randn(B, 6, hw, hw, generator=g) if two_cond else None
+    t = torch.tensor([731, 12][:B])
+    return x0, noise, ctx, c34, t
+
+
+@pytest.mark.parametrize("tag,cfg,two_cond", [("tiny", O.TINY_UNET, False), ("fr16", O.FR_UNET, False),
+                                              ("tf16", O.TF_UNET, True)])
+def test_p_losses_gradients_match_reference_golden(tag, cfg, two_cond, golden_train):
+    x0, noise, ctx, c34, t = _train_inputs(cfg, two_cond)
+    assert np.array_equal(O.q_sample(x0, t, noise).numpy(), golden_train[f"train/{tag}/x_noisy"])
+    sd = O.init_state_dict(cfg, 0)
+    loss, grads = O.p_losses(sd, cfg, x0, t, noise, ctx, c34)
+    assert abs(float(loss) - float(golden_train[f"train/{tag}/loss"])) <= 1e-6 * abs(float(loss))
+    assert O.rel_l2(grads["context"], torch.from_numpy(golden_train[f"train/{tag}/dctx"])) <= 1e-5
+    worst = 0.0
+    for name in sd:
+        fp = golden_train[f"train/{tag}/gradfp/{name}"]
+        gr = grads[name]
+        flat = gr.reshape(-1)
+        idx = torch.linspace(0, flat.numel() - 1, len(fp) - 1).long()
+        mine = torch.cat([gr.double().norm().reshape(1), flat[idx].double()]).numpy()
+        scale = max(float(fp[0]), 1e-12)
+        worst = max(worst, float(np.abs(mine - fp).max()) / scale)
+    assert worst <= 1e-5, worst

@@ -1,0 +1,132 @@
+"""GPU parity of the DDPM training step (BASELINE config 4) through the drop-in ``UNetModel`` in
+``.train()`` mode: loss and the gradient of every parameter against the CPU oracle's ``p_losses`` + autograd (fp32),
+which ``tests/test_oracle_golden.py`` pins to the real reference UNet's gradients.
+
+Tolerances (bf16 operands, fp32 accumulation; the reference's own bf16 autocast is ~1e-2 on eps):
+loss within 2 % ; the gradient of all parameters taken together within 6e-2 rel-L2; every sizeable tensor within 0.15."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import dsml_thesis_b200 as P  # noqa: E402
+from dsml_thesis_b200 import train as T  # noqa: E402
+from oracle import ldm_oracle as O  # noqa: E402
+from conftest import record_parity  # noqa: E402
+
+
+def _inputs(cfg, two_cond, B, hw, seed=77):
+    g = torch.Generator().manual_seed(seed)
+    x0 = torch.randn(B, 3, hw, hw, generator=g)
+    noise = torch.randn(B, 3, hw, hw, generator=g)
+    ctx = torch.randn(B, 1, cfg["context_dim"], generator=g)
+    c34 = torch.randn(B, 6, hw, hw, generator=g) if two_cond else None
+    t = torch.tensor([731, 12, 400, 999, 0, 250, 600, 3][:B])
+    return x0, noise, ctx, c34, t
+
+
+def _build(cfg, two_cond):
+    sd = O.init_state_dict(cfg, 0)
+    unet = P.UNetModel(**cfg)
+    unet.load_state_dict(sd, strict=True)
+    unet = unet.cuda().train()
+    return sd, unet, P.DiffusionHandle(unet, two_cond=two_cond).cuda().train()
+
+
+def _compare(tag, sd, unet, grads, dctx, ctx_grad):
+    num = den = 0.0
+    worst, worst_name = 0.0, ""
+    named = dict(unet.named_parameters())
+    for name in sd:
+        mine = named[name].grad
+        assert mine is not None, name
+        ref = grads[name].double()
+        d = (mine.detach().cpu().double() - ref)
+        num += float((d * d).sum())
+        den += float((ref * ref).sum())
+        if float(ref.norm()) > 1e-6 * np.sqrt(ref.numel()):
+            e = float(d.norm() / ref.norm())
+            if e > worst:
+                worst, worst_name = e, name
+        else:   # exactly-zero gradients (attn2.to_q / to_k / norm2 on a length-1 context) must stay tiny
+            assert float(d.norm()) <= 1e-5 * max(1.0, np.sqrt(den)), name
+    total = float(np.sqrt(num / den))
+    cerr = O.rel_l2(ctx_grad.cpu(), dctx)
+    record_parity(f"train/{tag}/grad_rel_l2_all", total)
+    record_parity(f"train/{tag}/grad_rel_l2_worst", [worst, worst_name])
+    record_parity(f"train/{tag}/dctx_rel_l2", cerr)
+    print(f"{tag}: all-parameter gradient rel-L2 {total:.3e}; worst tensor {worst_name} {worst:.3e}; dctx {cerr:.3e}")
+    return total, worst, worst_name, cerr
+
+
+@pytest.mark.parametrize("tag,cfg,two_cond,B,hw", [("tiny16", O.TINY_UNET, False, 2, 16), ("tiny32", O.TINY_UNET, False, 3, 32),
+                                                   ("fr16", O.FR_UNET, False, 2, 16), ("tf16", O.TF_UNET, True, 2, 16)])
+def test_training_step_gradients_vs_oracle(tag, cfg, two_cond, B, hw):
+    sd, unet, handle = _build(cfg, two_cond)
+    x0, noise, ctx, c34, t = _inputs(cfg, two_cond, B, hw)
+    ref_loss, grads = O.p_losses(sd, cfg, x0, t, noise, ctx, c34)
+    ctx_d = ctx.cuda().requires_grad_(True)
+    loss, loss_dict = T.p_losses(handle, x0.cuda(), ctx_d, t.cuda(), noise.cuda(),
+                                 c34.cuda() if c34 is not None else None)
+    loss.backward()
+    torch.cuda.synchronize()
+    lerr = abs(float(loss) - float(ref_loss)) / abs(float(ref_loss))
+    record_parity(f"train/{tag}/loss_rel_err", lerr)
+    assert lerr <= 2e-2, (float(loss), float(ref_loss))
+    assert set(loss_dict) == {"train/loss_simple", "train/loss_gamma", "train/loss"}
+    total, worst, worst_name, cerr = _compare(tag, sd, unet, grads, grads["context"], ctx_d.grad)
+    assert total <= 6e-2, total
+    assert worst <= 0.15, (worst_name, worst)
+    assert cerr <= 6e-2, cerr
+
+
+def test_training_step_accumulates_and_rezeroes():
+    sd, unet, handle = _build(O.TINY_UNET, False)
+    x0, noise, ctx, _, t = _inputs(O.TINY_UNET, False, 2, 16)
+    args = (x0.cuda(), ctx.cuda(), t.cuda(), noise.cuda())
+    T.p_losses(handle, *args)[0].backward()
+    g1 = {n: p.grad.clone() for n, p in unet.named_parameters()}
+    T.p_losses(handle, *args)[0].backward()          # grads not zeroed: accumulate like autograd
+    # run-to-run tolerance: weight gradients are summed with fp32 atomics in arbitrary order, and every bf16 cast of the
+    # gradient signal amplifies that last-bit noise up to the bf16 epsilon (0.4 %), so two runs agree to ~1e-2, not 1e-6
+    big = lambda t: float(t.norm()) > 1e-5 * t.numel() ** 0.5
+    for n, p in unet.named_parameters():
+        assert O.rel_l2(p.grad, 2 * g1[n]) <= 3e-2 or not big(g1[n]), n
+    unet.zero_grad(set_to_none=True)
+    T.p_losses(handle, *args)[0].backward()
+    for n, p in unet.named_parameters():
+        assert O.rel_l2(p.grad, g1[n]) <= 3e-2 or not big(g1[n]), n
+
+
+def test_fused_adamw_ema_step_matches_torch_adamw():
+    sd, unet, handle = _build(O.TINY_UNET, False)
+    x0, noise, ctx, _, t = _inputs(O.TINY_UNET, False, 2, 16)
+    args = (x0.cuda(), ctx.cuda(), t.cuda(), noise.cuda())
+    T.p_losses(handle, *args)[0].backward()
+    ref = {n: torch.nn.Parameter(p.detach().clone()) for n, p in unet.named_parameters()}
+    for n, p in unet.named_parameters():
+        ref[n].grad = p.grad.clone()
+    topt = torch.optim.AdamW(list(ref.values()), lr=1e-4)
+    opt = T.FusedAdamWEMA(unet, lr=1e-4)
+    opt.step()
+    topt.step()
+    for n, p in unet.named_parameters():
+        assert O.rel_l2(p.detach(), ref[n].detach()) <= 1e-6, n
+    # the next step runs on the re-pointed parameters and still trains
+    opt.zero_grad()
+    l2 = T.p_losses(handle, *args)[0]
+    l2.backward()
+    assert torch.isfinite(l2) and all(p.grad is not None for p in unet.parameters())
+
+
+def test_eval_mode_sampling_unaffected_by_training_state():
+    sd, unet, handle = _build(O.TINY_UNET, False)
+    x0, noise, ctx, _, t = _inputs(O.TINY_UNET, False, 2, 16)
+    T.p_losses(handle, x0.cuda(), ctx.cuda(), t.cuda(), noise.cuda())[0].backward()
+    unet.eval()
+    unet.precision = "bf16"
+    with torch.no_grad():
+        eps = unet(x0.cuda(), t.cuda(), context=ctx.cuda())
+    ref = O.unet_forward(sd, O.TINY_UNET, x0, t, ctx)
+    assert O.rel_l2(eps, ref) <= 1.5e-2

@@ -75,6 +75,17 @@ class WgradDesc(C.Structure):
     ]
 
 
+class LinearBwdJob(C.Structure):
+    """``ldmb200_linear_bwd_job`` (include/ldmb200.h)."""
+    _fields_ = [
+        ("in_", C.c_void_p), ("w", C.c_void_p), ("dout", C.c_void_p), ("dw", C.c_void_p), ("dbias", C.c_void_p),
+        ("din", C.c_void_p),
+        ("in_ld", C.c_int32), ("dout_ld", C.c_int32), ("din_ld", C.c_int32),
+        ("rows", C.c_int32), ("k", C.c_int32), ("n", C.c_int32),
+        ("silu_in", C.c_int32), ("pad_", C.c_int32),
+    ]
+
+
 #: every symbol include/ldmb200.h declares: name -> (restype, argtypes)
 _i, _i64, _f, _p = C.c_int, C.c_int64, C.c_float, C.c_void_p
 SIGNATURES = {
@@ -114,6 +125,7 @@ SIGNATURES = {
     "ldmb200_zero_insert2x": (_i, [_p, _p, _i, _i, _i, _i, _p]),
     "ldmb200_downsum2x": (_i, [_p, _p, _i, _i, _i, _i, _p]),
     "ldmb200_small_linear_bwd": (_i, [_p, _i, _p, _p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "ldmb200_small_linear_bwd_batched": (_i, [_p, _i, _p]),
     "ldmb200_adamw_ema": (_i, [_p, _p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _f, _f, _f, _p]),
 }
 

@@ -78,34 +78,40 @@ __global__ void __launch_bounds__(256) grad_cast_kernel(const void* __restrict__
                                                         int n, int rows_per_sample, int rows_per_block,
                                                         float* __restrict__ ps, int ps_ld, float* __restrict__ tot,
                                                         float* __restrict__ tot2, int n_valid) {
+  extern __shared__ float colsum[];    // [n] block-level column sums: ONE global atomic per column per block
   const int Q = n >> 2;
   const int qt = min(Q, 256);          // column-quad lanes
   const int R = 256 / qt;              // row lanes
   const int cq0 = threadIdx.x % qt, rl = threadIdx.x / qt;
-  if (rl >= R) return;
   const int b = blockIdx.y;
   const int r0 = blockIdx.x * rows_per_block, r1 = min(rows_per_sample, r0 + rows_per_block);
   const bool sums = ps || tot || tot2;
-  for (int cq = cq0; cq < Q; cq += qt) {
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int r = r0 + rl; r < r1; r += R) {
-      const int64_t off = ((int64_t)b * rows_per_sample + r) * n + cq * 4;
-      const float4 v = load4(g, in_dt, off);
-      if (g16) store4_bf16(g16, off, v);
-      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-    }
-    if (sums) {
-      const float a[4] = {acc.x, acc.y, acc.z, acc.w};
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int col = cq * 4 + j;
-        if (col < n_valid) {
-          if (ps) atomicAdd(ps + (size_t)b * ps_ld + col, a[j]);
-          if (tot) atomicAdd(tot + col, a[j]);
-          if (tot2) atomicAdd(tot2 + col, a[j]);
-        }
+  if (sums) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) colsum[i] = 0.f;
+    __syncthreads();
+  }
+  if (rl < R) {
+    for (int cq = cq0; cq < Q; cq += qt) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int r = r0 + rl; r < r1; r += R) {
+        const int64_t off = ((int64_t)b * rows_per_sample + r) * n + cq * 4;
+        const float4 v = load4(g, in_dt, off);
+        if (g16) store4_bf16(g16, off, v);
+        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      }
+      if (sums) {
+        atomicAdd(&colsum[cq * 4 + 0], acc.x); atomicAdd(&colsum[cq * 4 + 1], acc.y);
+        atomicAdd(&colsum[cq * 4 + 2], acc.z); atomicAdd(&colsum[cq * 4 + 3], acc.w);
       }
     }
+  }
+  if (!sums) return;
+  __syncthreads();
+  for (int col = threadIdx.x; col < n_valid; col += blockDim.x) {
+    const float a = colsum[col];
+    if (ps) atomicAdd(ps + (size_t)b * ps_ld + col, a);
+    if (tot) atomicAdd(tot + col, a);
+    if (tot2) atomicAdd(tot2 + col, a);
   }
 }
 
@@ -486,6 +492,46 @@ __global__ void __launch_bounds__(256) slb_din_kernel(const float* __restrict__ 
   }
 }
 
+// the same for a whole table of independent layers in ONE launch (grid.y = job); din is accumulated with atomics
+// because several jobs may feed the same input gradient (all 17 ResBlock emb projections read emb)
+__global__ void __launch_bounds__(256) slb_batched_kernel(const ldmb200_linear_bwd_job* __restrict__ jobs) {
+  const ldmb200_linear_bwd_job j = jobs[blockIdx.y];
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j.dw || j.dbias) {
+    const int64_t total = (int64_t)j.n * j.k;
+    for (int64_t i = i0; i < total; i += stride) {
+      const int nn = (int)(i / j.k), kk = (int)(i % j.k);
+      float acc = 0.f, bsum = 0.f;
+      for (int r = 0; r < j.rows; ++r) {
+        float a = j.in[(size_t)r * j.in_ld + kk];
+        if (j.silu_in) a = silu_f(a);
+        const float d = j.dout[(size_t)r * j.dout_ld + nn];
+        acc = fmaf(d, a, acc);
+        bsum += d;
+      }
+      if (j.dw) j.dw[i] += acc;
+      if (j.dbias && kk == 0) j.dbias[nn] += bsum;
+    }
+  }
+  if (j.din) {
+    const int64_t total = (int64_t)j.rows * j.k;
+    for (int64_t i = i0; i < total; i += stride) {
+      const int r = (int)(i / j.k), kk = (int)(i % j.k);
+      float acc0 = 0.f, acc1 = 0.f;
+      int nn = 0;
+      for (; nn + 1 < j.n; nn += 2) {
+        acc0 = fmaf(j.dout[(size_t)r * j.dout_ld + nn], j.w[(size_t)nn * j.k + kk], acc0);
+        acc1 = fmaf(j.dout[(size_t)r * j.dout_ld + nn + 1], j.w[(size_t)(nn + 1) * j.k + kk], acc1);
+      }
+      if (nn < j.n) acc0 = fmaf(j.dout[(size_t)r * j.dout_ld + nn], j.w[(size_t)nn * j.k + kk], acc0);
+      float acc = acc0 + acc1;
+      if (j.silu_in) acc *= dsilu_f(j.in[(size_t)r * j.in_ld + kk]);
+      atomicAdd(j.din + (size_t)r * j.din_ld + kk, acc);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // fused AdamW + EMA over a flat parameter arena
 // ---------------------------------------------------------------------------------------------
@@ -546,10 +592,11 @@ int ldmb200_grad_cast(const void* g, int in_dtype, void* g16, int64_t rows, int 
   const int batch = (int)(rows / rows_per_sample);
   LDM_CHECK_ARG(batch <= 65535, "grad_cast: batch exceeds grid limits");
   if (n_valid <= 0 || n_valid > n) n_valid = n;
-  int chunks = ceil_div(sm_count() * 8, batch);
-  int rpb = std::max(8, ceil_div(rows_per_sample, chunks));
+  int chunks = ceil_div(sm_count() * 4, batch);
+  int rpb = std::max(16, ceil_div(rows_per_sample, chunks));
   chunks = ceil_div(rows_per_sample, rpb);
-  grad_cast_kernel<<<dim3(chunks, batch), 256, 0, (cudaStream_t)stream>>>(g, in_dtype, g16, n, rows_per_sample, rpb,
+  LDM_CHECK_ARG(n <= 12288, "grad_cast: n=%d too wide for the shared-memory column sums", n);
+  grad_cast_kernel<<<dim3(chunks, batch), 256, (size_t)n * sizeof(float), (cudaStream_t)stream>>>(g, in_dtype, g16, n, rows_per_sample, rpb,
                                                                            per_sample_sum, ps_ld, total_sum, total_sum2,
                                                                            n_valid);
   LDM_CHECK_LAUNCH("grad_cast");
@@ -657,6 +704,13 @@ int ldmb200_small_linear_bwd(const float* in, int in_ld, const float* w, const f
     slb_din_kernel<<<grid_for((int64_t)rows * k), 256, 0, st>>>(in, in_ld, w, dout, dout_ld, din, din_ld, acc_din, rows, k, n, silu_in);
     LDM_CHECK_LAUNCH("small_linear_bwd din");
   }
+  return 0;
+}
+
+int ldmb200_small_linear_bwd_batched(const ldmb200_linear_bwd_job* jobs, int n_jobs, void* stream) {
+  LDM_CHECK_ARG(jobs && n_jobs > 0 && n_jobs <= 65535, "small_linear_bwd_batched: bad job table");
+  slb_batched_kernel<<<dim3(64, n_jobs), 256, 0, (cudaStream_t)stream>>>(jobs);
+  LDM_CHECK_LAUNCH("small_linear_bwd_batched");
   return 0;
 }
 

@@ -6,6 +6,7 @@
 // through a 3-stage cp.async ring (zero-filled halo = the conv padding) and adds its partial tile into dw with
 // fp32 atomics.  The tcgen05 version (MN-major UMMA operands straight from the TMA boxes) is the next step.
 #include <algorithm>
+#include <stdlib.h>
 
 #include <mma.h>
 
@@ -157,6 +158,9 @@ __global__ void __launch_bounds__(WG_THREADS) wgrad_mma_kernel(const WgParams p)
 
 }  // namespace ldm
 
+namespace ldm {
+int wgrad_tc_launch(const ldmb200_wgrad_desc* d, cudaStream_t st);  // wgrad_tc.cu
+}
 using namespace ldm;
 
 extern "C" int ldmb200_wgrad(const ldmb200_wgrad_desc* d, void* stream) {
@@ -167,6 +171,12 @@ extern "C" int ldmb200_wgrad(const ldmb200_wgrad_desc* d, void* stream) {
   LDM_CHECK_ARG(d->n > 0 && d->n <= d->dy_ld && d->c > 0 && d->c <= d->c_ld, "wgrad: n / c out of range");
   const int64_t M = (int64_t)d->batch * d->h * d->w;
   LDM_CHECK_ARG(M > 0 && M < (1ll << 31), "wgrad: M out of range");
+  // tcgen05 kernel first (power-of-two maps); LDMB200_WGRAD_MMA=1 forces the warp-level kernel (A/B comparisons)
+  static const bool force_mma = getenv("LDMB200_WGRAD_MMA") && atoi(getenv("LDMB200_WGRAD_MMA")) != 0;
+  if (!force_mma) {
+    const int rc = wgrad_tc_launch(d, (cudaStream_t)stream);
+    if (rc <= 0) return rc;
+  }
   WgParams p;
   p.dy = (const uint16_t*)d->dy;
   p.x = (const uint16_t*)d->x;

@@ -23,13 +23,14 @@ NCCL call per bucket and the fused AdamW+EMA kernel sweeps it in one launch.  Th
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, List, Optional, Tuple
 
 import torch
 import torch.nn as nn
 
 from . import _cabi
-from ._cabi import BF16, F32, GemmDesc, PackJob, WgradDesc
+from ._cabi import BF16, F32, GemmDesc, LinearBwdJob, PackJob, WgradDesc
 from .unet import (BasicTransformerBlock, Downsample, ResBlock, SpatialTransformer, Upsample, _Act, _Buf, _Plan,
                    _tc_cpad, _tc_npad)
 
@@ -156,6 +157,9 @@ class _TrainPlan(_Plan):
         self.bwd_meta: List[tuple] = []
         self.building_bwd = False
         self.grad_marks: Dict[int, Tuple[int, int]] = {}   # backward op index -> gradient arena range complete BEFORE it
+        self.fwd_graph, self.bwd_graphs, self.steps = None, {}, 0
+        self.side_stream = torch.cuda.Stream(device=model._device())
+        self.overlap_wgrad = os.environ.get("LDMB200_WGRAD_OVERLAP", "1") == "1"
         super().__init__(model, B, H, W, L, "bf16")
         dev = model._device()
         self.dout_in = torch.empty(B, model.out_channels, H, W, dtype=torch.float32, device=dev)
@@ -173,7 +177,9 @@ class _TrainPlan(_Plan):
     def emit(self, name: str, *args, flops: float = 0.0, bytes_: float = 0.0, what: str = ""):
         if not self.building_bwd:
             return super().emit(name, *args, flops=flops, bytes_=bytes_, what=what)
-        self.bwd_ops.append((getattr(self.lib, name), args, name))
+        # weight gradients are leaves of the dependency graph (nothing downstream reads them before the step ends):
+        # they run on a side stream and fill the SMs the latency-bound main chain leaves idle
+        self.bwd_ops.append((getattr(self.lib, name), args, name, name == "ldmb200_wgrad"))
         self.bwd_meta.append((name, float(flops), float(bytes_), what))
 
     def g(self, p) -> int:
@@ -352,6 +358,7 @@ class _TrainPlan(_Plan):
         d.dy_ld, d.n, d.c_ld, d.c = dy16.c, n, x16.c, c
         d.batch, d.h, d.w, d.ksize, d.stride = self.B, h, w, ksize, stride
         self.keep.append(d)
+        self.pinned.add(id(dy16))     # read asynchronously on the side stream: never recycled by the arena
         self.emit("ldmb200_wgrad", C.byref(d), flops=2.0 * self.B * h * w * n * c * taps,
                   what=f"M{self.B * h * w} N{n} C{c} ks{ksize} s{stride}")
 
@@ -395,6 +402,26 @@ class _TrainPlan(_Plan):
                   what=f"rows{x.rows} C{x.c}")
         return dx
 
+    def queue_small_bwd(self, queue: list, in_ptr, in_ld, weight, bias, dout_ptr, dout_ld, din_ptr, din_ld, rows,
+                        silu_in):
+        """Defers one small dense layer's backward into a batched launch (``flush_small``); din accumulates."""
+        n, k = weight.shape
+        queue.append((in_ptr, weight.data_ptr(), dout_ptr, self.g(weight), self.g(bias) if bias is not None else None,
+                      din_ptr, in_ld, dout_ld, din_ld, rows, k, n, silu_in))
+
+    def flush_small(self):
+        """Two launches: (emb projections + attn2.to_out) then (attn2.to_v, which consumes to_out's input gradient)."""
+        for queue, what in ((self.pending_a, "emb_layers + attn2.to_out"), (self.pending_b, "attn2.to_v")):
+            if not queue:
+                continue
+            arr = (LinearBwdJob * len(queue))()
+            for j, q in zip(arr, queue):
+                (j.in_, j.w, j.dout, j.dw, j.dbias, j.din, j.in_ld, j.dout_ld, j.din_ld, j.rows, j.k, j.n, j.silu_in) = q
+            table = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(self.model._device())
+            self.keep.append(table)
+            self.emit("ldmb200_small_linear_bwd_batched", table.data_ptr(), len(queue), what=f"{what} x{len(queue)}")
+            queue.clear()
+
     def small_bwd(self, in_ptr, in_ld, lin, dout_ptr, dout_ld, din_ptr, din_ld, acc_din, rows, silu_in):
         n, k = lin.weight.shape
         self.emit("ldmb200_small_linear_bwd", in_ptr, in_ld, lin.weight.data_ptr(), dout_ptr, dout_ld,
@@ -416,7 +443,9 @@ class _TrainPlan(_Plan):
         d1 = self.cast(dh1, hw, ps=(evp, evld), tot=self.g(c0.bias))
         self.free(dh1)
         # emb_layers = SiLU -> Linear(emb) (openaimodel.py:218-224,264): its output gradient is the per-sample sum
-        self.small_bwd(self.emb.ptr, self.emb.c, m.emb_layers[1], evp, evld, self.demb.ptr, self.demb.c, 1, self.B, 1)
+        el = m.emb_layers[1]
+        self.queue_small_bwd(self.pending_a, self.emb.ptr, self.emb.c, el.weight, el.bias, evp, evld, self.demb.ptr,
+                             self.demb.c, self.B, 1)
         self.wgrad(d1, r["y1"], c0.weight, H, W, 3)
         dy1 = self.dgrad(d1, name + ".in_layers.2", H, W, 3)
         self.free(d1)
@@ -456,10 +485,9 @@ class _TrainPlan(_Plan):
         lo2, a2 = m.attn2.to_out[0], m.attn2
         vp, vld = self.vec[("v", id(m))]
         dvp, dvld = self.dvec[("v", id(m))]
-        self.small_bwd(vp, vld, lo2, cvp, cvld, dvp, dvld, 0, self.B, 0)
-        self.emit("ldmb200_small_linear_bwd", self.ctx_act.ptr, self.ctx_act.c, a2.to_v.weight.data_ptr(), dvp, dvld,
-                  self.g(a2.to_v.weight), None, self.dctx.data_ptr(), self.ctx_act.c, 1, self.B,
-                  a2.to_v.weight.shape[1], a2.to_v.weight.shape[0], 0, what="attn2.to_v")
+        self.queue_small_bwd(self.pending_a, vp, vld, lo2.weight, lo2.bias, cvp, cvld, dvp, dvld, self.B, 0)
+        self.queue_small_bwd(self.pending_b, self.ctx_act.ptr, self.ctx_act.c, a2.to_v.weight, None, dvp, dvld,
+                             self.dctx.data_ptr(), self.ctx_act.c, self.B, 0)
         self.wgrad(d2, r["o"], lo.weight, hw, 1)
         do = self.dgrad(d2, name + ".attn1.to_out.0", hw, 1)
         self.free(d2)
@@ -549,6 +577,7 @@ class _TrainPlan(_Plan):
     def _build_backward(self):
         m, B, H, W = self.model, self.B, self.H, self.W
         self.building_bwd = True
+        self.pending_a, self.pending_b = [], []
         dev = m._device()
         self.gn_ws2 = torch.empty(int(self.lib.ldmb200_groupnorm_ws_floats(B, H * W, 0)), dtype=torch.float32, device=dev)
         # per-sample gradient vectors (zeroed at the start of every backward): d emb_out of every ResBlock, d of the
@@ -591,9 +620,9 @@ class _TrainPlan(_Plan):
         dskips: List[_Act] = []
         for rec in reversed(blocks[n_in + 1:]):
             dh, dskip = self.bwd_block(rec, dh, None)
-            dskips.append(dskip)          # gradient of hs[k], k descending from 0 (input_blocks.0) ... wait: order below
+            dskips.append(dskip)          # dskips[j] = gradient of hs[j], the skip popped by output_blocks[n_out-1-j]
+        self.flush_small()
         self.grad_marks[len(self.bwd_ops)] = self.state.bucket_bounds(m)
-        # dskips[j] belongs to the skip popped by output_blocks[n_out-1-j] = hs[j]
         # middle block: its input is hs[-1], whose gradient buffer already holds the skip contribution
         dh, _ = self.bwd_block(blocks[n_in], dh, dskips[n_in - 1])
         for k in range(n_in - 1, -1, -1):
@@ -601,22 +630,76 @@ class _TrainPlan(_Plan):
             into = dskips[k - 1] if k > 0 else None
             dh, _ = self.bwd_block(blocks[k], dh, into)
         # ---- time_embed: Linear -> SiLU -> Linear (openaimodel.py:506-511)
+        self.flush_small()
         te0, te2 = m.time_embed[0], m.time_embed[2]
         self.small_bwd(self.e1.ptr, self.e1.c, te2, self.demb.ptr, ted, self.de1.ptr, ted, 0, B, 1)
         self.small_bwd(self.temb.ptr, self.temb.c, te0, self.de1.ptr, ted, None, 0, 0, B, 0)
         self.building_bwd = False
 
     # ---- execution -----------------------------------------------------------------------------
-    def run_backward(self, stream: int, on_mark=None):
-        self.scratch.zero_()
-        self.dctx.zero_()
-        marks = self.grad_marks
-        for i, (fn, args, name) in enumerate(self.bwd_ops):
-            if on_mark is not None and i in marks:
-                on_mark(*marks[i])
-            rc = fn(*args, stream)
+    def _run_bwd_range(self, lo: int, hi: int, stream: int):
+        cur = torch.cuda.current_stream()
+        side = self.side_stream if self.overlap_wgrad else None
+        forked = False
+        for fn, args, name, on_side in self.bwd_ops[lo:hi]:
+            if on_side and side is not None:
+                side.wait_stream(cur)            # everything launched so far (the gradient operand) is ordered first
+                rc = fn(*args, side.cuda_stream)
+                forked = True
+            else:
+                rc = fn(*args, stream)
             if rc:
                 _cabi.check(rc, name)
+        if forked:
+            cur.wait_stream(side)                # join: parameter gradients complete before the range ends
+
+    def run_forward(self, use_graph: bool):
+        """Weight pack + forward launch list; replayed from a CUDA graph after the first eager run (every pointer and
+        tensor map of the step is static, so the ~1000 launches cost no host time)."""
+        if not use_graph:
+            stream = torch.cuda.current_stream().cuda_stream
+            self.state.pack.run(stream)
+            self.run(stream)
+            return
+        if self.fwd_graph is None:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                stream = torch.cuda.current_stream().cuda_stream
+                self.state.pack.run(stream)
+                self.run(stream)
+            self.fwd_graph = g
+        self.fwd_graph.replay()
+
+    def run_backward(self, stream: int, on_mark=None, use_graph: bool = False):
+        """The backward launch list.  With ``on_mark`` (gradient all-reduce buckets) it is cut at the marks so the
+        collective of a finished bucket is issued between the two halves."""
+        cuts = sorted(self.grad_marks) if on_mark is not None else []
+        bounds = [0] + cuts + [len(self.bwd_ops)]
+        if not use_graph:
+            self.scratch.zero_()
+            self.dctx.zero_()
+            for k in range(len(bounds) - 1):
+                if k > 0:
+                    on_mark(*self.grad_marks[bounds[k]])
+                self._run_bwd_range(bounds[k], bounds[k + 1], stream)
+            return
+        key = tuple(bounds)
+        graphs = self.bwd_graphs.get(key)
+        if graphs is None:
+            graphs = []
+            for k in range(len(bounds) - 1):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    if k == 0:
+                        self.scratch.zero_()
+                        self.dctx.zero_()
+                    self._run_bwd_range(bounds[k], bounds[k + 1], torch.cuda.current_stream().cuda_stream)
+                graphs.append(g)
+            self.bwd_graphs[key] = graphs
+        for k, g in enumerate(graphs):
+            if k > 0:
+                on_mark(*self.grad_marks[bounds[k]])
+            g.replay()
 
     def run_timed(self, stream_obj, backward: bool = False):
         if not backward:
@@ -624,7 +707,7 @@ class _TrainPlan(_Plan):
         self.scratch.zero_()
         self.dctx.zero_()
         evs = []
-        for fn, args, name in self.bwd_ops:
+        for fn, args, name, _side in self.bwd_ops:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(stream_obj)
             rc = fn(*args, stream_obj.cuda_stream)
@@ -659,7 +742,8 @@ class _UNetTrainFn(torch.autograd.Function):
             if fresh:
                 st.flat.zero_()
             plan.dout_in.copy_(dout)
-            plan.run_backward(stream, getattr(model, "_grad_bucket_hook", None))
+            plan.run_backward(stream, getattr(model, "_grad_bucket_hook", None),
+                              use_graph=model.use_cuda_graph and plan.steps > 1)
             st.launches += len(plan.bwd_ops)
             for p, gr in foreign:
                 st.views[id(p)].add_(gr)
@@ -694,9 +778,8 @@ def unet_train_forward(model, x, timesteps, context, y=None):
         plan.x_in.copy_(x.detach())
         plan.t_in.copy_(timesteps)
         plan.ctx_in.copy_(context.detach())
-        stream = torch.cuda.current_stream().cuda_stream
-        st.pack.run(stream)       # weights change every optimizer step
-        plan.run(stream)
+        plan.steps += 1           # step 1 runs eagerly (lazy per-kernel setup), later steps replay CUDA graphs
+        plan.run_forward(model.use_cuda_graph and plan.steps > 1)   # incl. the weight pack: weights change every step
         st.launches += len(plan.ops) + 1
         out = _UNetTrainFn.apply(x, context, st.anchor, model, plan)
     return out if out.dtype == x.dtype else out.to(x.dtype)

@@ -308,6 +308,22 @@ int ldmb200_small_linear_bwd(const float* in, int in_ld, const float* w, const f
                              float* dbias, float* din, int din_ld, int acc_din, int rows, int k, int n, int silu_in,
                              void* stream);
 
+/* The same for a table of independent layers in ONE launch (DEVICE array of jobs).  din is ACCUMULATED atomically
+ * (several jobs may share one input gradient: every ResBlock's emb projection reads emb, openaimodel.py:264). */
+typedef struct ldmb200_linear_bwd_job {
+  const float* in;
+  const float* w;
+  const float* dout;
+  float* dw;
+  float* dbias;
+  float* din;
+  int32_t in_ld, dout_ld, din_ld;
+  int32_t rows, k, n;
+  int32_t silu_in;
+  int32_t pad_;
+} ldmb200_linear_bwd_job;
+int ldmb200_small_linear_bwd_batched(const ldmb200_linear_bwd_job* jobs, int n_jobs, void* stream);
+
 /* Fused AdamW step + LitEma update over flat fp32 arrays (torch.optim.AdamW semantics ddpm.py:1363-1372;
  * LitEma.forward ema.py:25-44: shadow -= (1 - decay) * (shadow - param)).  ema may be NULL. */
 int ldmb200_adamw_ema(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, float* ema, int64_t n,

@@ -32,7 +32,8 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layouts_match_the_header():
     # field order / count of the ctypes mirrors vs the C structs (names are identical by construction)
     hdr = open(os.path.join(ROOT, "include", "ldmb200.h")).read()
-    for cname, cls in (("ldmb200_gemm_desc", _cabi.GemmDesc), ("ldmb200_pack_job", _cabi.PackJob)):
+    for cname, cls in (("ldmb200_gemm_desc", _cabi.GemmDesc), ("ldmb200_pack_job", _cabi.PackJob),
+                       ("ldmb200_wgrad_desc", _cabi.WgradDesc), ("ldmb200_linear_bwd_job", _cabi.LinearBwdJob)):
         body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (cname, cname), hdr, re.S).group(1)
         body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
         names = []
@@ -44,7 +45,7 @@ def test_struct_layouts_match_the_header():
             first = parts[0].split()[-1].lstrip("*")
             names.append(first)
             names += [p.strip().lstrip("*") for p in parts[1:]]
-        assert names == [f[0] for f in cls._fields_], (cname, names)
+        assert names == [f[0].rstrip("_") if f[0] == "in_" else f[0] for f in cls._fields_], (cname, names)
 
 
 @pytest.mark.parametrize("cfg", [O.TINY_UNET, O.FR_UNET, O.TF_UNET])

@@ -130,3 +130,23 @@ def test_eval_mode_sampling_unaffected_by_training_state():
         eps = unet(x0.cuda(), t.cuda(), context=ctx.cuda())
     ref = O.unet_forward(sd, O.TINY_UNET, x0, t, ctx)
     assert O.rel_l2(eps, ref) <= 1.5e-2
+
+
+def test_cuda_graph_replay_matches_eager_training_step():
+    sd, unet, handle = _build(O.TINY_UNET, False)
+    x0, noise, ctx, _, t = _inputs(O.TINY_UNET, False, 2, 16)
+    args = (x0.cuda(), ctx.cuda(), t.cuda(), noise.cuda())
+    unet.zero_grad(set_to_none=True)
+    l0 = T.p_losses(handle, *args)[0]
+    l0.backward()
+    g0 = {n: p.grad.clone() for n, p in unet.named_parameters()}
+    unet.use_cuda_graph = True
+    for _ in range(3):      # step 2 captures, step 3+ replays
+        unet.zero_grad(set_to_none=True)
+        l1 = T.p_losses(handle, *args)[0]
+        l1.backward()
+    torch.cuda.synchronize()
+    assert abs(float(l1) - float(l0)) <= 1e-6 * abs(float(l0))
+    big = lambda t_: float(t_.norm()) > 1e-5 * t_.numel() ** 0.5
+    for n, p in unet.named_parameters():
+        assert O.rel_l2(p.grad, g0[n]) <= 3e-2 or not big(g0[n]), n

@@ -314,6 +314,30 @@ def test_small_linear_backward(rows, k, n, silu):
     assert rel_l2(din - din0, x64.grad) < 1e-5
 
 
+def test_small_linear_backward_batched_accumulates_shared_input_gradient():
+    from dsml_thesis_b200._cabi import LinearBwdJob
+    rows, k = 4, 128
+    x = randn(rows, k, seed=121)
+    probs = [(randn(n, k, seed=122 + i, scale=0.1), randn(rows, n, seed=130 + i)) for i, n in enumerate((64, 160, 32))]
+    din = torch.zeros(rows, k, device=DEV)
+    dws = [torch.zeros_like(w) for w, _ in probs]
+    dbs = [torch.zeros(w.shape[0], device=DEV) for w, _ in probs]
+    arr = (LinearBwdJob * len(probs))()
+    for j, (w, dout), dw, db in zip(arr, probs, dws, dbs):
+        j.in_, j.w, j.dout, j.dw, j.dbias, j.din = (x.data_ptr(), w.data_ptr(), dout.data_ptr(), dw.data_ptr(),
+                                                    db.data_ptr(), din.data_ptr())
+        j.in_ld, j.dout_ld, j.din_ld, j.rows, j.k, j.n, j.silu_in = k, w.shape[0], k, rows, k, w.shape[0], 1
+    table = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(DEV)
+    _cabi.call("ldmb200_small_linear_bwd_batched", table.data_ptr(), len(probs), stream())
+    x64 = x.double().requires_grad_()
+    ws = [w.double().requires_grad_() for w, _ in probs]
+    bs = [torch.zeros(w.shape[0], device=DEV, dtype=torch.float64, requires_grad=True) for w, _ in probs]
+    sum((F.linear(F.silu(x64), w, b) * dout.double()).sum() for w, b, (_, dout) in zip(ws, bs, probs)).backward()
+    assert rel_l2(din, x64.grad) < 1e-5
+    for dw, db, w, b in zip(dws, dbs, ws, bs):
+        assert rel_l2(dw, w.grad) < 1e-5 and rel_l2(db, b.grad) < 1e-5
+
+
 def test_adamw_ema_matches_torch():
     n = 10007
     p0, grad = randn(n, seed=111), randn(n, seed=112)

@@ -121,7 +121,8 @@ SIGNATURES = {
     "ldmb200_layernorm_bwd": (_i, [_p, _p, _p, _p, _p, _p, _p, _i64, _i, _f, _p]),
     "ldmb200_geglu_fwd": (_i, [_p, _p, _i64, _i, _p]),
     "ldmb200_geglu_bwd": (_i, [_p, _p, _p, _i64, _i, _p]),
-    "ldmb200_attention_bwd": (_i, [_p, _i, _i, _i, _i, _p, _p, _i, _p, _p, _i, _i, _i, _f, _p]),
+    "ldmb200_attention_bwd_ws_floats": (_i64, [_i, _i, _i]),
+    "ldmb200_attention_bwd": (_i, [_p, _i, _i, _i, _i, _p, _p, _i, _p, _p, _p, _i, _i, _i, _f, _p]),
     "ldmb200_zero_insert2x": (_i, [_p, _p, _i, _i, _i, _i, _p]),
     "ldmb200_downsum2x": (_i, [_p, _p, _i, _i, _i, _i, _p]),
     "ldmb200_small_linear_bwd": (_i, [_p, _i, _p, _p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),

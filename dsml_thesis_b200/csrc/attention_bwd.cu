@@ -5,6 +5,8 @@
 // Round-1 implementation on the warp-level tensor-core path (nvcuda::wmma, fp32 accumulate): two kernels without
 // atomics — one CTA per 64-key block accumulates dK/dV over all query blocks, one CTA per 64-query block accumulates
 // dQ over all key blocks (S and dP are recomputed in both; 7 instead of 5 small GEMMs per tile pair).
+#include <stdlib.h>
+
 #include <mma.h>
 
 #include "common.cuh"
@@ -262,17 +264,30 @@ __global__ void __launch_bounds__(AB_THREADS) attention_bwd_q_kernel(const AbPar
   ab_store_tile(m.sS, p.dqkv + row_base * p.ld + h * 32 + p.q_off, p.ld, q0, p.n_tok);
 }
 
+int attention_bwd_tc_launch(const void* qkv, int ld, int q_off, int k_off, int v_off, const void* out, const void* dout,
+                            int o_ld, const float* lse2, void* dqkv, float* ws, int batch, int heads, int n_tokens,
+                            float scale, cudaStream_t st);  // attention_bwd_tc.cu
+
 }  // namespace ldm
 
 using namespace ldm;
 
+extern "C" int64_t ldmb200_attention_bwd_ws_floats(int batch, int heads, int n_tokens) {
+  return (int64_t)batch * heads * ((n_tokens + 63) / 64 * 64) * 2;
+}
+
 extern "C" int ldmb200_attention_bwd(const void* qkv, int ld, int q_off, int k_off, int v_off, const void* out,
-                                     const void* dout, int o_ld, const float* lse2, void* dqkv, int batch, int heads,
-                                     int n_tokens, float scale, void* stream) {
+                                     const void* dout, int o_ld, const float* lse2, void* dqkv, float* ws, int batch,
+                                     int heads, int n_tokens, float scale, void* stream) {
   LDM_CHECK_ARG(qkv && out && dout && lse2 && dqkv && batch > 0 && heads > 0 && n_tokens > 0, "attention_bwd: bad arguments");
   LDM_CHECK_ARG(ld % 8 == 0 && o_ld % 8 == 0 && q_off % 8 == 0 && k_off % 8 == 0 && v_off % 8 == 0,
                 "attention_bwd: leading dims / offsets must be multiples of 8 elements (16 bytes)");
   LDM_CHECK_ARG(batch <= 65535 && heads <= 65535, "attention_bwd: batch/heads exceed grid limits");
+  // tcgen05 kernels when the caller provides the {lse2, D} workspace; LDMB200_ATTN_BWD_MMA=1 forces the warp-level kernels
+  static const bool force_mma = getenv("LDMB200_ATTN_BWD_MMA") && atoi(getenv("LDMB200_ATTN_BWD_MMA")) != 0;
+  if (ws && !force_mma)
+    return attention_bwd_tc_launch(qkv, ld, q_off, k_off, v_off, out, dout, o_ld, lse2, dqkv, ws, batch, heads, n_tokens, scale,
+                                   (cudaStream_t)stream);
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e1 = cudaFuncSetAttribute(attention_bwd_kv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AB_SMEM);

@@ -492,10 +492,12 @@ class _TrainPlan(_Plan):
         do = self.dgrad(d2, name + ".attn1.to_out.0", hw, 1)
         self.free(d2)
         dqkv = self.new(do.rows, 3 * Cc, BF16)
+        ws = self.arena.alloc(4 * int(self.lib.ldmb200_attention_bwd_ws_floats(self.B, r["heads"], hw)))
         self.emit("ldmb200_attention_bwd", r["qkv"].ptr, 3 * Cc, 0, Cc, 2 * Cc, r["o"].ptr, do.ptr, Cc, r["lse"].ptr,
-                  dqkv.ptr, self.B, r["heads"], hw, r["scale"], flops=10.0 * self.B * r["heads"] * hw * hw * 32,
+                  dqkv.ptr, ws.ptr, self.B, r["heads"], hw, r["scale"], flops=10.0 * self.B * r["heads"] * hw * hw * 32,
                   what=f"B{self.B} h{r['heads']} N{hw}")
         self.free(do)
+        self.arena.release(ws)
         a1 = m.attn1
         for i, lin in enumerate((a1.to_q, a1.to_k, a1.to_v)):
             self.wgrad(dqkv, r["a"], lin.weight, hw, 1, col_off=i * Cc)

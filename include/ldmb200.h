@@ -290,10 +290,13 @@ int ldmb200_geglu_bwd(const void* u, const void* dout, void* du, int64_t rows, i
 
 /* Self-attention backward (autograd of attention.py:178-192 with d_head = 32), recomputing P from lse2:
  * qkv bf16 [B*N, ld] (offsets as the forward), dout bf16 [B*N, o_ld], out bf16 [B*N, o_ld] (forward output, for
- * D = rowsum(dout * out)), lse2 from ldmb200_attention_tc_lse -> dqkv bf16 [B*N, ld] at the same offsets. */
+ * D = rowsum(dout * out)), lse2 from ldmb200_attention_tc_lse -> dqkv bf16 [B*N, ld] at the same offsets.
+ * ws: workspace of ldmb200_attention_bwd_ws_floats floats ({lse2, D} pairs) — with it the tcgen05 kernels run;
+ * NULL selects the warp-level (mma.sync) kernels. */
+int64_t ldmb200_attention_bwd_ws_floats(int batch, int heads, int n_tokens);
 int ldmb200_attention_bwd(const void* qkv, int ld, int q_off, int k_off, int v_off, const void* out, const void* dout,
-                          int o_ld, const float* lse2, void* dqkv, int batch, int heads, int n_tokens, float scale,
-                          void* stream);
+                          int o_ld, const float* lse2, void* dqkv, float* ws, int batch, int heads, int n_tokens,
+                          float scale, void* stream);
 
 /* Resampling backward: zero_insert2x — dy bf16 [B, h, w, C] -> z bf16 [B, 2h, 2w, C], z[2i, 2j] = dy[i, j], else 0
  * (input gradient of the stride-2 Downsample.op conv = 3x3 conv of z with the kind-3 weights);

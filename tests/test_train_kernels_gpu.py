@@ -271,8 +271,10 @@ def test_geglu_forward_backward(rows, inner):
     assert rel_l2(du, u64.grad) < 4e-3
 
 
-@pytest.mark.parametrize("B,N,heads", [(1, 64, 1), (2, 256, 2), (1, 1024, 5), (2, 16, 3), (1, 100, 2), (1, 200, 1)])
-def test_attention_backward(B, N, heads):
+@pytest.mark.parametrize("impl", ["tc", "mma"])
+@pytest.mark.parametrize("B,N,heads", [(1, 64, 1), (2, 256, 2), (1, 1024, 5), (2, 16, 3), (1, 100, 2), (1, 200, 1),
+                                       (3, 4096, 2), (2, 130, 1)])
+def test_attention_backward(B, N, heads, impl):
     Cc = heads * 32
     scale = 32 ** -0.5
     qkv = bf(randn(B * N, 3 * Cc, seed=91))
@@ -282,8 +284,11 @@ def test_attention_backward(B, N, heads):
     _cabi.call("ldmb200_attention_tc_lse", qkv.data_ptr(), 3 * Cc, 0, Cc, 2 * Cc, out.data_ptr(), Cc, BF16,
                lse.data_ptr(), B, heads, N, scale, stream())
     dqkv = torch.full((B * N, 3 * Cc), float("nan"), dtype=torch.bfloat16, device=DEV)
+    ws = None
+    if impl == "tc":
+        ws = torch.empty(int(_cabi.load().ldmb200_attention_bwd_ws_floats(B, heads, N)), device=DEV)
     _cabi.call("ldmb200_attention_bwd", qkv.data_ptr(), 3 * Cc, 0, Cc, 2 * Cc, out.data_ptr(), dout.data_ptr(), Cc,
-               lse.data_ptr(), dqkv.data_ptr(), B, heads, N, scale, stream())
+               lse.data_ptr(), dqkv.data_ptr(), ptr(ws), B, heads, N, scale, stream())
     x = qkv.double().reshape(B, N, 3, heads, 32).requires_grad_()
     q, k, v = (x[:, :, i].permute(0, 2, 1, 3) for i in range(3))
     s = torch.einsum("bhid,bhjd->bhij", q, k) * scale

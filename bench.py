@@ -242,7 +242,7 @@ def train_main(args):
     def step_e2e():
         d = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
         loss = step(d, t_host.to(dev, non_blocking=True))
-        return float(loss)          # device -> host read of the step's result
+        return float(loss.detach())   # device -> host read of the step's result
 
     def barrier():
         if world > 1:

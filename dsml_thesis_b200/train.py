@@ -878,29 +878,37 @@ class FusedAdamWEMA:
 
 
 class GradAllReduce:
-    """Data-parallel gradient averaging over NCCL / NVLink: the flat arena is reduced in two buckets — the output half
-    of the UNet as soon as its backward is done (overlapping the rest of the backward on a side stream), the rest at
-    the end.  ``install(model)`` hooks it into the backward; ``finish()`` must be called before the optimizer step."""
+    """Data-parallel gradient averaging over NCCL / NVLink (the one collective of the training path): the
+    flat arena is reduced in two buckets — the output half of the UNet as soon as its backward is done (overlapping
+    the rest of the backward on a side stream), the rest at the end.  Constructing it hooks the bucket into the
+    model's backward; ``finish()`` must be called before the optimizer step.  ``flat`` may be given directly (CPU /
+    gloo tests of the bucket logic)."""
 
-    def __init__(self, model, group=None):
+    def __init__(self, model=None, group=None, flat: Optional[torch.Tensor] = None):
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.world = dist.get_world_size(group)
-        self.model, self.st = model, train_state(model)
-        self.side = torch.cuda.Stream()
+        self.flat = flat if flat is not None else train_state(model).flat
+        self.side = torch.cuda.Stream(device=self.flat.device) if self.flat.is_cuda else None
         self.split = None
-        model._grad_bucket_hook = self._bucket_ready
+        if model is not None:
+            model._grad_bucket_hook = self.bucket_ready
 
-    def _bucket_ready(self, lo, hi):
+    def bucket_ready(self, lo: int, hi: int):
+        """Elements [lo, hi) of the arena are final: start their all-reduce while the backward continues."""
         self.split = lo
+        if self.side is None:
+            self.dist.all_reduce(self.flat[lo:hi], group=self.group)
+            return
         self.side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self.side):
-            self.dist.all_reduce(self.st.flat[lo:hi], group=self.group)
+            self.dist.all_reduce(self.flat[lo:hi], group=self.group)
 
     def finish(self):
-        lo = self.split if self.split is not None else self.st.numel
+        lo = self.split if self.split is not None else self.flat.numel()
         if lo > 0:
-            self.dist.all_reduce(self.st.flat[:lo], group=self.group)
-        torch.cuda.current_stream().wait_stream(self.side)
-        self.st.flat.mul_(1.0 / self.world)
+            self.dist.all_reduce(self.flat[:lo], group=self.group)
+        if self.side is not None:
+            torch.cuda.current_stream().wait_stream(self.side)
+        self.flat.mul_(1.0 / self.world)
         self.split = None

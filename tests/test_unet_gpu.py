@@ -145,12 +145,16 @@ def test_unet_rejects_what_it_cannot_run():
     x, ctx = synth_inputs(cfg, 2, 8, 5)
     with pytest.raises(P.Ldmb200Error):
         m(x, torch.tensor([1, 2]), context=ctx)            # CPU tensors: no fallback
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(NotImplementedError):               # gradient w.r.t. the latent in eval mode (guidance) is not built
+        m(x.cuda().requires_grad_(True), torch.tensor([1, 2]).cuda(), context=ctx.cuda())
+    m.precision = "fp32"
+    with pytest.raises(NotImplementedError):               # the training step exists in bf16 tensor-core mode only
         m.train()
         try:
             m(x.cuda(), torch.tensor([1, 2]).cuda(), context=ctx.cuda())
         finally:
             m.eval()
+            m.precision = "f16"
     with pytest.raises(AssertionError):
         with torch.no_grad():
             m(x.cuda(), torch.tensor([1, 2]).cuda(), context=ctx.cuda(), y=torch.tensor([0, 1]).cuda())

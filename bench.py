@@ -348,35 +348,46 @@ def train_main(args):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--workload", default="sample", choices=["sample", "train"],
-                    help="sample = BASELINE config 2 (the headline metric); train = config 4 (DDPM training step)")
+    ap.add_argument("--workload", default="sample", choices=["sample", "train", "c3"],
+                    help="sample = BASELINE config 2 (the headline metric); train = config 4 (DDPM training step); "
+                         "c3 = config 3 (talking_face UNet, 200-step progressive DDIM, autoregressive frames)")
+    ap.add_argument("--frames", type=int, default=2, help="c3: autoregressive frames per step")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=None, help="samples per GPU (weak scaling); default 64 (sample) / 32 (train)")
     ap.add_argument("--hw", type=int, default=64)
-    ap.add_argument("--ddim", type=int, default=50)
+    ap.add_argument("--ddim", type=int, default=None, help="DDIM steps: default 50 (sample) / 200 (c3)")
     ap.add_argument("--precision", default="f16", choices=["f16", "bf16", "fp32"])
     ap.add_argument("--graph", type=int, default=int(os.environ.get("LDMB200_CUDA_GRAPH", "1")))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.batch is None:
-        args.batch = 32 if args.workload == "train" else 64
+        args.batch = 64 if args.workload == "sample" else 32
+    if args.ddim is None:
+        args.ddim = 200 if args.workload == "c3" else 50
     if args.workload == "train":
         return train_main(args)
+    c3 = args.workload == "c3"
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     workload = (f"C2: face_reenactment UNet (in 3, ctx 512, 156.8M params), {args.hw}x{args.hw}x3 latents, "
                 f"batch {args.batch}/GPU, {args.ddim}-step DDIM eta=0")
+    metric = METRIC
+    if c3:
+        workload = (f"C3: talking_face UNet (in 9 = latent + masked-frame + reference-frame latents, audio ctx 1024), "
+                    f"{args.hw}x{args.hw} latents, {args.batch} streams/GPU, {args.frames} autoregressive frames x "
+                    f"{args.ddim}-step DDIM eta=0 (previous output -> reference channels)")
+        metric = f"DDIM frames/s (talking_face, {args.hw}x{args.hw}x3 latent, {args.ddim} steps, progressive)"
 
     if args.impl == "reference":
         if rank != 0:
             return
         value, cores, sample, per, n = cpu_reference_leg(args.hw, args.ddim, max(1, args.steps), max(0, args.warmup))
-        line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": args.gpus,
+        line = {"impl": "reference", "metric": metric, "value": value, "unit": "samples/s", "n_gpus": args.gpus,
                 "steps": n, "warmup": args.warmup, "ms_per_step": per * 1e3, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": workload, "arm": "reference algorithm on host CPU (oracle port)"},
@@ -398,20 +409,33 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     B, HW, T = args.batch, args.hw, args.ddim
 
-    unet = P.UNetModel(**FR_UNET)
+    unet = P.UNetModel(**(TF_UNET if c3 else FR_UNET))
     init_weights(unet, 0)
     unet = unet.to(dev).eval()
     unet.precision = args.precision
     unet.use_cuda_graph = bool(args.graph)
-    model = P.DiffusionHandle(unet).to(dev)
-    smp = P.DDIMSampler(model)
+    model = P.DiffusionHandle(unet, two_cond=c3).to(dev)
+    smp = P.DDIMSampler2Cond(model) if c3 else P.DDIMSampler(model)
+    ctx_dim = 1024 if c3 else 512
 
     # per-rank synthetic inputs: seeds derive from the GLOBAL sample index, so results do not depend on N
     g = torch.Generator().manual_seed(1000 + rank)
     x_host = torch.randn(B, 3, HW, HW, generator=g).pin_memory()
-    c_host = torch.randn(B, 1, 512, generator=g).pin_memory()
+    c_host = torch.randn(B, 1, ctx_dim, generator=g).pin_memory()
+    c34_host = torch.randn(B, 6, HW, HW, generator=g).pin_memory() if c3 else None
     out_host = torch.empty(B, 3, HW, HW).pin_memory()
     x_dev, c_dev = x_host.to(dev), c_host.to(dev)
+    c34_dev = c34_host.to(dev) if c3 else None
+
+    def progressive(x, c12, c34):
+        """progressive_sampling_difftalk.py:286-317: frame f's output becomes the reference-frame latent of f+1."""
+        c34 = c34.clone()
+        out = None
+        for _f in range(args.frames):
+            cond = {P.DDIMSampler2Cond.CROSS_KEY: c12, P.DDIMSampler2Cond.CONCAT_KEY: c34}
+            out, _ = smp.sample(T, batch_size=B, shape=[3, HW, HW], conditioning=cond, eta=0.0, x_T=x, verbose=False)
+            c34[:, 3:] = out
+        return out
 
     launches = {"n": 0}
     step_fn = S.ddim_step
@@ -422,6 +446,9 @@ def main():
     S.ddim_step = counted_step
 
     def sample_resident():
+        if c3:
+            out = progressive(x_dev, c_dev, c34_dev)   # streams stay on their rank: no collective
+            return out
         out, _ = smp.sample(T, batch_size=B, shape=[3, HW, HW], conditioning=c_dev, eta=0.0, x_T=x_dev, verbose=False)
         if world > 1:
             return P.gather_shards(out, world * B)   # the one collective of the path: final all-gather
@@ -430,7 +457,10 @@ def main():
     def sample_e2e():
         x = x_host.to(dev, non_blocking=True)
         c = c_host.to(dev, non_blocking=True)
-        out, _ = smp.sample(T, batch_size=B, shape=[3, HW, HW], conditioning=c, eta=0.0, x_T=x, verbose=False)
+        if c3:
+            out = progressive(x, c, c34_host.to(dev, non_blocking=True))
+        else:
+            out, _ = smp.sample(T, batch_size=B, shape=[3, HW, HW], conditioning=c, eta=0.0, x_T=x, verbose=False)
         out_host.copy_(out, non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return out_host
@@ -454,7 +484,7 @@ def main():
         return float(ms.item())
 
     with torch.no_grad():
-        for _ in range(max(3, args.warmup)):
+        for _ in range(max(3, args.warmup) if not c3 else max(1, args.warmup)):
             sample_resident()
         clocks = ClockSampler(local_rank)
         if rank == 0:
@@ -510,12 +540,13 @@ def main():
                 pass
     d = fam[dom]
     achieved = d[1] / (d[0] * 1e-3) / 1e12
-    total = args.steps * B * world
+    frames = args.frames if c3 else 1
+    total = args.steps * B * world * frames
     value = total / (ms * 1e-3)
     e2e_value = total / (ms_e2e * 1e-3)
     ref_gflop = REF_GFLOP_PER_EVAL.get(HW)
     line = {
-        "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+        "metric": metric, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": {"f16": "f16 operands (bf16 attention internals), f32 accumulate", "bf16": "bf16",
                                       "fp32": "f32"}[args.precision], "data": "synthetic",
@@ -527,7 +558,8 @@ def main():
         "unet_tflops_algorithmic": (value * T * ref_gflop / 1e3) if ref_gflop else None,
         "tensor_frac_of_measured_peak": (value / world * T * ref_gflop / 1e3 / peak_tf) if ref_gflop else None,
         "e2e": {"value": e2e_value, "unit": "samples/s", "ms_per_step": ms_e2e / args.steps,
-                "h2d_bytes_per_step": x_host.numel() * 4 + c_host.numel() * 4, "d2h_bytes_per_step": out_host.numel() * 4},
+                "h2d_bytes_per_step": x_host.numel() * 4 + c_host.numel() * 4 + (c34_host.numel() * 4 if c3 else 0),
+                "d2h_bytes_per_step": out_host.numel() * 4},
         "gpu_launches": n_launch,
         "clocks": clk,
         "roofline": {"kernel": dom, "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
@@ -541,7 +573,7 @@ def main():
         "kernel_breakdown_ms_per_eval": {k: round(v[0], 4) for k, v in sorted(fam.items(), key=lambda kv: -kv[1][0])},
         "eval_ms_sum_of_kernels": eval_ms,
     }
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and not c3:
         v, cores, sample, per, n = cpu_reference_leg(HW, T, 3, 1)
         line["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample}
     print(json.dumps(line))

@@ -89,6 +89,20 @@ def unet64_goldens():
     return out
 
 
+def unet128_goldens():
+    """BASELINE config 5 (roofline stress): the shipped FR architecture at 128x128 latents — attention over
+    16384 / 4096 / 1024 tokens (SURVEY 8d reading C5a) — one eval of the real reference UNet, B=1."""
+    out = {}
+    cfg = O.FR_UNET
+    sd = O.init_state_dict(cfg, seed=0)
+    ref = R.reference_unet(cfg, "face_reenactment").eval()
+    ref.load_state_dict(sd, strict=True)
+    x, ctx = synth_inputs(cfg, 1, 128, seed=1, ctx_len=1)
+    with torch.no_grad():
+        out["fr_128/eps_t501"] = ref(x, torch.tensor([501], dtype=torch.long), context=ctx).numpy()
+    return out
+
+
 def schedule_goldens():
     out = {}
     R.import_reference("face_reenactment")
@@ -241,7 +255,8 @@ def main():
     only = sys.argv[1:]
     for fn, gen in (("unet.npz", unet_goldens), ("schedule.npz", schedule_goldens),
                     ("trajectory.npz", trajectory_goldens), ("unet64.npz", unet64_goldens),
-                    ("manipulation.npz", manipulation_goldens), ("train.npz", train_goldens)):
+                    ("manipulation.npz", manipulation_goldens), ("train.npz", train_goldens),
+                    ("unet128.npz", unet128_goldens)):
         if only and fn not in only:
             continue
         data = gen()

@@ -207,3 +207,14 @@ def test_p_losses_gradients_match_reference_golden(tag, cfg, two_cond, golden_tr
         scale = max(float(fp[0]), 1e-12)
         worst = max(worst, float(np.abs(mine - fp).max()) / scale)
     assert worst <= 1e-5, worst
+
+
+def test_unet_eps_128_matches_reference_golden():
+    """BASELINE config 5's latent size (128x128: 16384-token self-attention) — one oracle eval vs the real reference."""
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "unet128.npz"))
+    sd = O.init_state_dict(O.FR_UNET, 0)
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(1, 3, 128, 128, generator=g)
+    ctx = torch.randn(1, 1, 512, generator=g)
+    eps = O.unet_forward(sd, O.FR_UNET, x, torch.tensor([501]), ctx)
+    assert O.rel_l2(eps, torch.from_numpy(gold["fr_128/eps_t501"])) <= 2e-6

@@ -95,6 +95,21 @@ def test_unet_eps_64_vs_reference_golden(name, cfg, tsteps, precision, golden_un
             assert err <= TOL[precision], (name, t, err)
 
 
+@pytest.mark.parametrize("precision", ["f16", "bf16"])
+def test_unet_eps_128_vs_reference_golden(precision):
+    """BASELINE config 5 (roofline stress): the shipped architecture at 128x128 latents — self-attention over 16384 /
+    4096 / 1024 tokens — vs the real reference's eps (tensor-core modes; the fp32 SIMT attention is O(N^2) slow here)."""
+    import os
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "unet128.npz"))
+    m = build(O.FR_UNET, precision)
+    x, ctx = synth_inputs(O.FR_UNET, 1, 128, 1, 1)
+    with torch.no_grad():
+        eps = m(x.cuda(), torch.tensor([501]).cuda(), context=ctx.cuda())
+    err = O.rel_l2(eps, torch.from_numpy(gold["fr_128/eps_t501"]))
+    record_parity(f"eps/fr_128/t501/{precision}", err)
+    assert err <= TOL[precision], err
+
+
 @pytest.mark.parametrize("precision", PRECISIONS)
 def test_unet_cuda_graph_replay_matches_eager(precision):
     cfg = O.TINY_UNET

@@ -34,11 +34,30 @@ constexpr int AT_TILE_BYTES = 128 * 32 * 2;  // 8 KiB: 128 rows x 32 16-bit valu
 constexpr int AT_P_BYTES = 2 * 128 * 128;    // two K-major chunks of [128 x 64] bf16, 128B swizzle
 constexpr int AT_SMEM = AT_NQ * AT_TILE_BYTES + 2 * AT_STAGES * AT_TILE_BYTES + AT_NQ * AT_P_BYTES + 32 * 8 + 16 + 1024;
 constexpr int AT_TMEM_COLS = 512;
+#ifndef LDM_AT_POLY_PAIRS
+#define LDM_AT_POLY_PAIRS 0
+#endif
+// 0..4: share (x 25 %) of the exponentials emulated on the FMA pipe.  Measured r01s (tools/attn_sweep.py, B=64 N=4096):
+// 0 -> 1.766 ms, 1 -> 1.831 ms, 2 -> 2.048 ms: the softmax warps are latency-bound (ex2 unit 70 % busy, issue slots
+// 36 %), the extra ~8 FMA-pipe instructions per emulated exponential only lengthen the critical path, so the default is 0.
+constexpr int AT_POLY_PAIRS = LDM_AT_POLY_PAIRS;
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+// exp2 on the FMA pipe (FlashAttention-4 style): the ex2 unit (16/clk/SM) is the co-bound of this kernel with the TMEM
+// read port, so a fraction of the exponentials is emulated — round-to-nearest split x = n + f, |f| <= 0.5 (magic-number
+// add), degree-3 minimax 2^f (max rel. error 7.5e-5, far below the bf16 rounding of P), exponent add of n.
+__device__ __forceinline__ float ex2_poly(float x) {
+  x = fmaxf(x, -125.0f);
+  const float t = x + 12582912.0f;                 // 1.5 * 2^23: the integer part lands in the low mantissa bits
+  const float f = x - (t - 12582912.0f);
+  float p = fmaf(0.05517146f, f, 0.24261086f);
+  p = fmaf(p, f, 0.69326099f);
+  p = fmaf(p, f, 0.99992809f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
 }
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
   float y;
@@ -89,8 +108,15 @@ __device__ __forceinline__ void chunk_exp_store(const float (&v)[32], float (&ls
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
       const int i = u * 8 + e * 2;
-      float p0 = ex2_approx(fmaf(v[i], c_, -mb));
-      float p1 = ex2_approx(fmaf(v[i + 1], c_, -mb));
+      // AT_POLY_PAIRS of every 4 column pairs go to the FMA pipe, the rest to the ex2 unit
+      float p0, p1;
+      if (e >= 4 - AT_POLY_PAIRS) {
+        p0 = ex2_poly(fmaf(v[i], c_, -mb));
+        p1 = ex2_poly(fmaf(v[i + 1], c_, -mb));
+      } else {
+        p0 = ex2_approx(fmaf(v[i], c_, -mb));
+        p1 = ex2_approx(fmaf(v[i + 1], c_, -mb));
+      }
       if (MASK) {
         if (c * 32 + i >= valid) p0 = 0.f;
         if (c * 32 + i + 1 >= valid) p1 = 0.f;

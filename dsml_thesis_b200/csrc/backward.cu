@@ -459,78 +459,71 @@ __global__ void __launch_bounds__(256) downsum2x_kernel(const float* __restrict_
 // ---------------------------------------------------------------------------------------------
 // small dense layers backward (rows = batch: per-sample vectors)
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) slb_dw_kernel(const float* __restrict__ in, int in_ld, const float* __restrict__ dout,
-                                                     int dout_ld, float* __restrict__ dw, float* __restrict__ dbias,
-                                                     int rows, int k, int n, int silu_in) {
-  const int64_t total = (int64_t)n * k;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int nn = (int)(i / k), kk = (int)(i % k);
-    float acc = 0.f, bsum = 0.f;
-    for (int r = 0; r < rows; ++r) {
-      float a = in[(size_t)r * in_ld + kk];
-      if (silu_in) a = silu_f(a);
-      const float d = dout[(size_t)r * dout_ld + nn];
-      acc = fmaf(d, a, acc);
-      bsum += d;
+// The same for a whole table of independent layers in ONE launch (grid.y = job).  Thread <-> input column kk of a
+// 256-wide k tile; the block walks its share of the output columns n in 64-wide tiles of dout staged in smem, so every
+// weight element is read once and feeds 32 row FMAs (din) while act(in) sits in registers (dw).  din is accumulated with
+// atomics: several jobs / n-parts feed the same input gradient (all 17 ResBlock emb projections read emb).
+constexpr int SLB_ROWS = 32, SLB_NT = 64, SLB_PARTS = 4;
+
+__device__ __forceinline__ void slb_body(const ldmb200_linear_bwd_job& j) {
+  __shared__ float sd[SLB_ROWS][SLB_NT + 1];
+  const int ktiles = (j.k + 255) / 256;
+  const int kt = blockIdx.x % ktiles, part = blockIdx.x / ktiles;
+  if (blockIdx.x >= ktiles * SLB_PARTS) return;
+  const int kk = kt * 256 + threadIdx.x;
+  const bool kok = kk < j.k;
+  const int n_per = (j.n + SLB_PARTS - 1) / SLB_PARTS;
+  const int n_lo = part * n_per, n_hi = min(j.n, n_lo + n_per);
+  for (int r0 = 0; r0 < j.rows; r0 += SLB_ROWS) {
+    const int nr = min(SLB_ROWS, j.rows - r0);
+    float a[SLB_ROWS], acc[SLB_ROWS], raw[SLB_ROWS];
+#pragma unroll
+    for (int r = 0; r < SLB_ROWS; ++r) {
+      raw[r] = (kok && r < nr) ? j.in[(size_t)(r0 + r) * j.in_ld + kk] : 0.f;
+      a[r] = j.silu_in ? silu_f(raw[r]) : raw[r];
+      acc[r] = 0.f;
     }
-    if (dw) dw[i] += acc;
-    if (dbias && kk == 0) dbias[nn] += bsum;
+    for (int nt = n_lo; nt < n_hi; nt += SLB_NT) {
+      const int nn_max = min(SLB_NT, n_hi - nt);
+      __syncthreads();
+      for (int i = threadIdx.x; i < SLB_ROWS * SLB_NT; i += 256) {
+        const int r = i / SLB_NT, c = i % SLB_NT;
+        sd[r][c] = (r < nr && c < nn_max) ? j.dout[(size_t)(r0 + r) * j.dout_ld + nt + c] : 0.f;
+      }
+      __syncthreads();
+      if (j.dbias && kt == 0 && threadIdx.x < nn_max) {
+        float bsum = 0.f;
+#pragma unroll
+        for (int r = 0; r < SLB_ROWS; ++r) bsum += sd[r][threadIdx.x];
+        j.dbias[nt + threadIdx.x] += bsum;       // one block owns (k tile 0, this n range): no race; row chunks add up
+      }
+      if (kok) {
+        for (int c = 0; c < nn_max; ++c) {
+          const float w = j.din ? j.w[(size_t)(nt + c) * j.k + kk] : 0.f;
+          float s_ = 0.f;
+#pragma unroll
+          for (int r = 0; r < SLB_ROWS; ++r) {
+            const float d = sd[r][c];
+            s_ = fmaf(d, a[r], s_);
+            acc[r] = fmaf(d, w, acc[r]);
+          }
+          if (j.dw) j.dw[(size_t)(nt + c) * j.k + kk] += s_;
+        }
+      }
+    }
+    if (j.din && kok) {
+#pragma unroll
+      for (int r = 0; r < SLB_ROWS; ++r)
+        if (r < nr) atomicAdd(j.din + (size_t)(r0 + r) * j.din_ld + kk, j.silu_in ? acc[r] * dsilu_f(raw[r]) : acc[r]);
+    }
   }
 }
 
-__global__ void __launch_bounds__(256) slb_din_kernel(const float* __restrict__ in, int in_ld, const float* __restrict__ w,
-                                                      const float* __restrict__ dout, int dout_ld, float* __restrict__ din,
-                                                      int din_ld, int acc_din, int rows, int k, int n, int silu_in) {
-  const int64_t total = (int64_t)rows * k;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int r = (int)(i / k), kk = (int)(i % k);
-    float acc = 0.f;
-    for (int nn = 0; nn < n; ++nn) acc = fmaf(dout[(size_t)r * dout_ld + nn], w[(size_t)nn * k + kk], acc);
-    if (silu_in) acc *= dsilu_f(in[(size_t)r * in_ld + kk]);
-    float* o = din + (size_t)r * din_ld + kk;
-    *o = acc_din ? *o + acc : acc;
-  }
-}
-
-// the same for a whole table of independent layers in ONE launch (grid.y = job); din is accumulated with atomics
-// because several jobs may feed the same input gradient (all 17 ResBlock emb projections read emb)
 __global__ void __launch_bounds__(256) slb_batched_kernel(const ldmb200_linear_bwd_job* __restrict__ jobs) {
   const ldmb200_linear_bwd_job j = jobs[blockIdx.y];
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (j.dw || j.dbias) {
-    const int64_t total = (int64_t)j.n * j.k;
-    for (int64_t i = i0; i < total; i += stride) {
-      const int nn = (int)(i / j.k), kk = (int)(i % j.k);
-      float acc = 0.f, bsum = 0.f;
-      for (int r = 0; r < j.rows; ++r) {
-        float a = j.in[(size_t)r * j.in_ld + kk];
-        if (j.silu_in) a = silu_f(a);
-        const float d = j.dout[(size_t)r * j.dout_ld + nn];
-        acc = fmaf(d, a, acc);
-        bsum += d;
-      }
-      if (j.dw) j.dw[i] += acc;
-      if (j.dbias && kk == 0) j.dbias[nn] += bsum;
-    }
-  }
-  if (j.din) {
-    const int64_t total = (int64_t)j.rows * j.k;
-    for (int64_t i = i0; i < total; i += stride) {
-      const int r = (int)(i / j.k), kk = (int)(i % j.k);
-      float acc0 = 0.f, acc1 = 0.f;
-      int nn = 0;
-      for (; nn + 1 < j.n; nn += 2) {
-        acc0 = fmaf(j.dout[(size_t)r * j.dout_ld + nn], j.w[(size_t)nn * j.k + kk], acc0);
-        acc1 = fmaf(j.dout[(size_t)r * j.dout_ld + nn + 1], j.w[(size_t)(nn + 1) * j.k + kk], acc1);
-      }
-      if (nn < j.n) acc0 = fmaf(j.dout[(size_t)r * j.dout_ld + nn], j.w[(size_t)nn * j.k + kk], acc0);
-      float acc = acc0 + acc1;
-      if (j.silu_in) acc *= dsilu_f(j.in[(size_t)r * j.in_ld + kk]);
-      atomicAdd(j.din + (size_t)r * j.din_ld + kk, acc);
-    }
-  }
+  slb_body(j);
 }
+__global__ void __launch_bounds__(256) slb_single_kernel(const __grid_constant__ ldmb200_linear_bwd_job j) { slb_body(j); }
 
 // ---------------------------------------------------------------------------------------------
 // fused AdamW + EMA over a flat parameter arena
@@ -695,21 +688,27 @@ int ldmb200_small_linear_bwd(const float* in, int in_ld, const float* w, const f
                              void* stream) {
   LDM_CHECK_ARG(in && dout && rows > 0 && k > 0 && n > 0, "small_linear_bwd: bad arguments");
   LDM_CHECK_ARG(!din || w, "small_linear_bwd: din needs w");
+  LDM_CHECK_ARG(k <= 4096, "small_linear_bwd: k=%d exceeds the 16 k tiles of the launch grid", k);
   cudaStream_t st = (cudaStream_t)stream;
-  if (dw || dbias) {
-    slb_dw_kernel<<<grid_for((int64_t)n * k), 256, 0, st>>>(in, in_ld, dout, dout_ld, dw, dbias, rows, k, n, silu_in);
-    LDM_CHECK_LAUNCH("small_linear_bwd dw");
+  if (din && !acc_din) {   // the kernel accumulates (its n parts add up): "write" = zero first
+    cudaError_t e = cudaMemset2DAsync(din, (size_t)din_ld * 4, 0, (size_t)k * 4, rows, st);
+    if (e != cudaSuccess) {
+      set_error("small_linear_bwd: memset failed: %s", cudaGetErrorString(e));
+      return LDMB200_ERR_CUDA;
+    }
   }
-  if (din) {
-    slb_din_kernel<<<grid_for((int64_t)rows * k), 256, 0, st>>>(in, in_ld, w, dout, dout_ld, din, din_ld, acc_din, rows, k, n, silu_in);
-    LDM_CHECK_LAUNCH("small_linear_bwd din");
-  }
+  ldmb200_linear_bwd_job j;
+  j.in = in; j.w = w; j.dout = dout; j.dw = dw; j.dbias = dbias; j.din = din;
+  j.in_ld = in_ld; j.dout_ld = dout_ld; j.din_ld = din_ld; j.rows = rows; j.k = k; j.n = n; j.silu_in = silu_in; j.pad_ = 0;
+  slb_single_kernel<<<dim3(ceil_div(k, 256) * SLB_PARTS, 1), 256, 0, st>>>(j);
+  LDM_CHECK_LAUNCH("small_linear_bwd");
   return 0;
 }
 
 int ldmb200_small_linear_bwd_batched(const ldmb200_linear_bwd_job* jobs, int n_jobs, void* stream) {
   LDM_CHECK_ARG(jobs && n_jobs > 0 && n_jobs <= 65535, "small_linear_bwd_batched: bad job table");
-  slb_batched_kernel<<<dim3(64, n_jobs), 256, 0, (cudaStream_t)stream>>>(jobs);
+  // grid.x covers the widest job (k <= 4096: 16 k tiles x 4 n parts); narrower jobs leave their extra blocks idle
+  slb_batched_kernel<<<dim3(16 * SLB_PARTS, n_jobs), 256, 0, (cudaStream_t)stream>>>(jobs);
   LDM_CHECK_LAUNCH("small_linear_bwd_batched");
   return 0;
 }

@@ -93,7 +93,18 @@ __global__ void __launch_bounds__(256) grad_cast_kernel(const void* __restrict__
   if (rl < R) {
     for (int cq = cq0; cq < Q; cq += qt) {
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int r = r0 + rl; r < r1; r += R) {
+      int r = r0 + rl;
+      for (; r + 3 * R < r1; r += 4 * R) {   // four rows in flight: the pass is a pure stream
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = load4(g, in_dt, ((int64_t)b * rows_per_sample + r + u * R) * n + cq * 4);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (g16) store4_bf16(g16, ((int64_t)b * rows_per_sample + r + u * R) * n + cq * 4, v[u]);
+          acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w;
+        }
+      }
+      for (; r < r1; r += R) {
         const int64_t off = ((int64_t)b * rows_per_sample + r) * n + cq * 4;
         const float4 v = load4(g, in_dt, off);
         if (g16) store4_bf16(g16, off, v);
@@ -173,10 +184,7 @@ __global__ void gn_bwd_reduce_kernel(const float* __restrict__ x1, int c1, const
   const int rows_per = (hw + S - 1) / S;
   const int r0 = s * rows_per, r1 = min(hw, r0 + rows_per);
   float s1[4] = {0, 0, 0, 0}, s2[4] = {0, 0, 0, 0};
-  for (int r = r0 + rl; r < r1; r += R) {
-    const int64_t row = (int64_t)b * hw + r;
-    const float4 xv = gnb_load_x(x1, c1, x2, c2, row, cq * 4);
-    const float4 dv = load4(dy, LDMB200_BF16, row * C + cq * 4);
+  auto accum = [&](const float4& xv, const float4& dv) {
     const float xs[4] = {xv.x, xv.y, xv.z, xv.w}, ds[4] = {dv.x, dv.y, dv.z, dv.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -186,6 +194,22 @@ __global__ void gn_bwd_reduce_kernel(const float* __restrict__ x1, int c1, const
       s1[j] += dz;
       s2[j] = fmaf(dz, xh, s2[j]);
     }
+  };
+  int r = r0 + rl;
+  for (; r + 3 * R < r1; r += 4 * R) {   // four rows in flight
+    float4 xv[4], dv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t row = (int64_t)b * hw + r + u * R;
+      xv[u] = gnb_load_x(x1, c1, x2, c2, row, cq * 4);
+      dv[u] = load4(dy, LDMB200_BF16, row * C + cq * 4);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) accum(xv[u], dv[u]);
+  }
+  for (; r < r1; r += R) {
+    const int64_t row = (int64_t)b * hw + r;
+    accum(gnb_load_x(x1, c1, x2, c2, row, cq * 4), load4(dy, LDMB200_BF16, row * C + cq * 4));
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
@@ -251,12 +275,7 @@ __global__ void gn_bwd_apply_kernel(const float* __restrict__ x1, int c1, const 
   const int rows_per = (hw + T_ - 1) / T_;
   const int r0 = blockIdx.x * rows_per, r1 = min(hw, r0 + rows_per);
   const int c0 = cq * 4;
-  for (int r = r0 + rl; r < r1; r += R) {
-    const int64_t row = (int64_t)b * hw + r;
-    const float4 xv = gnb_load_x(x1, c1, x2, c2, row, c0);
-    const float4 dv = load4(dy, LDMB200_BF16, row * C + c0);
-    float4 av = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (addend) av = load4(addend, add_dt, row * C + c0);
+  auto finish = [&](int64_t row, const float4& xv, const float4& dv, const float4& av) {
     const float xs[4] = {xv.x, xv.y, xv.z, xv.w}, ds[4] = {dv.x, dv.y, dv.z, dv.w}, as[4] = {av.x, av.y, av.z, av.w};
     float o[4];
 #pragma unroll
@@ -280,6 +299,25 @@ __global__ void gn_bwd_apply_kernel(const float* __restrict__ x1, int c1, const 
       o[0] += old.x; o[1] += old.y; o[2] += old.z; o[3] += old.w;
     }
     *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+  };
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  int r = r0 + rl;
+  for (; r + 3 * R < r1; r += 4 * R) {   // four rows in flight: the pass is a pure stream
+    float4 xv[4], dv[4], av[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t row = (int64_t)b * hw + r + u * R;
+      xv[u] = gnb_load_x(x1, c1, x2, c2, row, c0);
+      dv[u] = load4(dy, LDMB200_BF16, row * C + c0);
+      av[u] = addend ? load4(addend, add_dt, row * C + c0) : zero4;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) finish((int64_t)b * hw + r + u * R, xv[u], dv[u], av[u]);
+  }
+  for (; r < r1; r += R) {
+    const int64_t row = (int64_t)b * hw + r;
+    finish(row, gnb_load_x(x1, c1, x2, c2, row, c0), load4(dy, LDMB200_BF16, row * C + c0),
+           addend ? load4(addend, add_dt, row * C + c0) : zero4);
   }
 }
 

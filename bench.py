@@ -346,9 +346,172 @@ def train_main(args):
         dist.destroy_process_group()
 
 
+DECODE_METRIC = "first-stage decode images/s (VQ-f4: 64x64x3 latent -> 256x256x3 image)"
+VQ_F4 = dict(embed_dim=3, n_embed=16384,
+             ddconfig=dict(double_z=False, z_channels=3, resolution=128, in_channels=3, out_ch=3, ch=128,
+                           ch_mult=[1, 2, 4], num_res_blocks=2, attn_resolutions=[32], dropout=0.0))
+
+
+def decode_main(args):
+    """--workload decode: VQModelInterface.decode of a batch of latents (nearest-code lookup,
+    post_quant_conv, Decoder) - per-frame work of the sampling scripts after the DDIM loop."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    B, HW = args.batch, args.hw
+    workload = (f"n2: VQ-f4 first stage (embed 3, 16384 codes, Decoder ch 128 x [1,2,4], attention at the lowest level, "
+                f"36.2M params), {HW}x{HW}x3 latents -> {4 * HW}x{4 * HW} images, batch {B}/GPU")
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        import torch
+        from oracle import vq_oracle as V
+        torch.set_num_threads(os.cpu_count() or 1)
+        sd = V.init_vq_state_dict(V.VQ_F4, 0)
+        hw = min(HW, 32)
+        z = torch.randn(1, 3, hw, hw)
+        for _ in range(min(1, args.warmup)):
+            V.vq_decode(sd, V.VQ_F4, z)
+        t0 = time.perf_counter()
+        n = max(1, min(args.steps, 3))
+        for _ in range(n):
+            V.vq_decode(sd, V.VQ_F4, z)
+        per = (time.perf_counter() - t0) / n * (HW / hw) ** 2
+        value = 1.0 / per
+        sample = f"oracle port, B=1, {hw}x{hw} latent, {n} decodes timed, scaled by pixel count to {HW}x{HW}"
+        print(json.dumps({"impl": "reference", "metric": DECODE_METRIC, "value": value, "unit": "images/s",
+                          "n_gpus": args.gpus, "steps": n, "warmup": args.warmup, "ms_per_step": per * 1e3,
+                          "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                          "data": "synthetic", "config": {"workload": workload, "arm": "reference algorithm on host CPU (oracle port)"},
+                          "cpu_baseline": {"value": value, "unit": "images/s", "cores": os.cpu_count(), "kind": "port", "sample": sample},
+                          "e2e": {"value": value, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                          "gpu_launches": 0}))
+        return
+    import torch
+    import torch.distributed as dist
+    import dsml_thesis_b200 as P
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    m = P.VQDecoder(**VQ_F4)
+    g = torch.Generator().manual_seed(0)
+    with torch.no_grad():
+        for name, prm in sorted(m.named_parameters()):
+            if name == "quantize.embedding.weight":
+                prm.copy_(torch.randn(prm.shape, generator=g))
+            elif prm.dim() >= 2:
+                prm.copy_((torch.rand(prm.shape, generator=g) * 2 - 1) * (3.0 / prm[0].numel()) ** 0.5)
+            elif "norm" in name and name.endswith("weight"):
+                prm.copy_(1.0 + 0.1 * torch.randn(prm.shape, generator=g))
+            else:
+                prm.copy_(0.05 * torch.randn(prm.shape, generator=g))
+    m = m.to(dev).eval()
+    m.precision = args.precision
+    m.use_cuda_graph = bool(args.graph)
+    g = torch.Generator().manual_seed(3000 + rank)
+    z_host = torch.randn(B, 3, HW, HW, generator=g).pin_memory()
+    z_dev = z_host.to(dev)
+    out_host = torch.empty(B, 3, 4 * HW, 4 * HW).pin_memory()
+
+    def step_resident():
+        return m.decode(z_dev)
+
+    def step_e2e():
+        img = m.decode(z_host.to(dev, non_blocking=True))
+        out_host.copy_(img, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, k):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(k):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(max(3, args.warmup)):
+        step_resident()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    ms = timed(step_resident, args.steps)
+    clk = clocks.stop() if rank == 0 else None
+    step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+    plan = next(iter(m._plans.values()))
+    cur = torch.cuda.current_stream()
+    plan.run_timed(cur)
+    ops = plan.run_timed(cur)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    if os.environ.get("LDMB200_OP_TABLE"):
+        with open(os.environ["LDMB200_OP_TABLE"], "w") as f:
+            f.write(f"# one first-stage decode, B={B}, {HW}x{HW} latents, {args.precision}: per-launch CUDA-event times\n")
+            for i, (name, t_ms, fl, by, what) in enumerate(ops):
+                tf = fl / (t_ms * 1e-3) / 1e12 if t_ms > 0 else 0.0
+                gb = by / (t_ms * 1e-3) / 1e9 if t_ms > 0 else 0.0
+                f.write(f"{i:4d} {name[8:]:24s} {what:44s} {t_ms:8.4f} ms {tf:8.1f} TF/s {gb:8.0f} GB/s\n")
+    fam = {}
+    for name, t_ms, fl, by, what in ops:
+        f = fam.setdefault(name, [0.0, 0.0, 0.0, 0])
+        f[0] += t_ms
+        f[1] += fl
+        f[2] += by
+        f[3] += 1
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_tf = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    dom = max(fam.items(), key=lambda kv: kv[1][0])
+    achieved = dom[1][1] / (dom[1][0] * 1e-3) / 1e12 if dom[1][1] else None
+    flops = sum(v[1] for v in fam.values())
+    total = args.steps * B * world
+    value = total / (ms * 1e-3)
+    line = {
+        "metric": DECODE_METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": f"{args.precision} operands, f32 accumulate / residual stream / softmax / code distances",
+        "data": "synthetic",
+        "config": {"workload": workload, "cuda_graph": bool(args.graph),
+                   "l2": "per-decode working set (GBs of activations) far exceeds the 126 MB L2",
+                   "init": "synthetic non-zero weights, N(0,1) codebook, seed 0", "parallelism": f"batch-sharded x{world}"},
+        "decode_gflop_per_image": flops / B / 1e9,
+        "decode_tflops_algorithmic": value / world * flops / B / 1e12,
+        "tensor_frac_of_measured_peak": value / world * flops / B / 1e12 / peak_tf,
+        "e2e": {"value": total / (ms_e2e * 1e-3), "unit": "images/s", "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": z_host.numel() * 4, "d2h_bytes_per_step": out_host.numel() * 4},
+        "gpu_launches": args.steps * (len(ops) + (1 if plan.pack is not None else 0)), "clocks": clk,
+        "roofline": {"kernel": dom[0], "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
+                     "frac": (achieved / peak_tf) if achieved else None, "traffic": None,
+                     "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s",
+                     "launches_per_step": dom[1][3], "ms_per_step": dom[1][0],
+                     "how": "the family with the largest share of the decode: sum of algorithmic FLOPs / sum of CUDA-event durations"},
+        "kernel_breakdown_ms_per_step": {k: round(v[0], 3) for k, v in sorted(fam.items(), key=lambda kv: -kv[1][0])},
+        "step_ms_sum_of_kernels": sum(v[0] for v in fam.values()),
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--workload", default="sample", choices=["sample", "train", "c3"],
+    ap.add_argument("--workload", default="sample", choices=["sample", "train", "c3", "decode"],
                     help="sample = BASELINE config 2 (the headline metric); train = config 4 (DDPM training step); "
                          "c3 = config 3 (talking_face UNet, 200-step progressive DDIM, autoregressive frames)")
     ap.add_argument("--frames", type=int, default=2, help="c3: autoregressive frames per step")
@@ -364,11 +527,13 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.batch is None:
-        args.batch = 64 if args.workload == "sample" else 32
+        args.batch = 64 if args.workload == "sample" else 16 if args.workload == "decode" else 32
     if args.ddim is None:
         args.ddim = 200 if args.workload == "c3" else 50
     if args.workload == "train":
         return train_main(args)
+    if args.workload == "decode":
+        return decode_main(args)
     c3 = args.workload == "c3"
 
     rank = int(os.environ.get("RANK", "0"))

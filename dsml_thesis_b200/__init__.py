@@ -10,6 +10,8 @@ Public surface = the reference's own plugin interface for this path (SURVEY §8b
   * ``install()``       — patches those dotted targets after ``import ldm`` so ``main.py``, the YAML configs and
                           the sampling scripts pick the new classes up with no file edited
   * ``ddim_step``       — the fused x_{t-1} update as a function
+  * ``VQDecoder`` / ``accelerate_first_stage`` — the decode half of ``ldm.models.autoencoder.VQModelInterface``
+                          (nearest-code lookup, post_quant_conv, Decoder) on the same kernels
   * ``sample_sharded``  — ``DDIMSampler.sample`` for a global batch split over the GPUs of one box (one process
                           per GPU, no data-path collective, final all-gather)
 
@@ -21,8 +23,9 @@ from .unet import UNetModel  # noqa: F401
 from .sampler import DDIMSampler, DDIMSampler2, DDIMSampler2Cond, DDIMSampler2CondFR, ddim_step  # noqa: F401
 from .handle import DiffusionHandle  # noqa: F401
 from .install import install, uninstall  # noqa: F401
+from .vqdecode import VQDecoder, accelerate_first_stage  # noqa: F401
 from .sharding import sample_sharded, shard_range, gather_shards, initial_noise  # noqa: F401
 
 __all__ = ["UNetModel", "DDIMSampler", "DDIMSampler2", "DDIMSampler2Cond", "DDIMSampler2CondFR", "ddim_step", "install",
            "uninstall", "DiffusionHandle", "load_library", "Ldmb200Error", "sample_sharded", "shard_range",
-           "gather_shards", "initial_noise"]
+           "gather_shards", "initial_noise", "VQDecoder", "accelerate_first_stage"]

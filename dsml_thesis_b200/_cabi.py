@@ -11,7 +11,7 @@ import ctypes as C
 import os
 
 F32, BF16, F16 = 0, 1, 2
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("LDMB200_LIB", os.path.join(_HERE, "libldmb200.so"))
@@ -128,6 +128,8 @@ SIGNATURES = {
     "ldmb200_small_linear_bwd": (_i, [_p, _i, _p, _p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "ldmb200_small_linear_bwd_batched": (_i, [_p, _i, _p]),
     "ldmb200_adamw_ema": (_i, [_p, _p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _f, _f, _f, _p]),
+    "ldmb200_vq_lookup_postconv": (_i, [_p, _p, _i, _i, _p, _p, _i, _p, _i, _i, _p, _p, _i, _i, _p]),
+    "ldmb200_softmax_rows": (_i, [_p, _i64, _p, _i, _i64, _i, _i, _f, _p]),
 }
 
 _lib = None

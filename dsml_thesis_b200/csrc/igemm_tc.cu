@@ -223,10 +223,11 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
       const int m0 = tm * Cfg::BM;
-      int n_img = 0, h0 = 0;
+      int n_img = 0, h0 = 0, w0 = 0;
       if (p.is_conv) {
         n_img = m0 / p.hw_out;
         h0 = (m0 % p.hw_out) / p.w_out;
+        w0 = m0 % p.w_out;  // non-zero only for maps wider than one 128-pixel tile (first-stage decoder at 256x256)
       }
       for (int tap = 0; tap < p.taps; ++tap) {
         int dh = 0, dw = 0, plane = 0;
@@ -252,7 +253,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
             const CUtensorMap* tm_a = second ? &tmA2 : &tmA1;
             const int c0 = (second ? j - p.c1_chunks : j) * BK;
             if (p.is_conv)
-              tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, dw, h0 + dh, plane, n_img);
+              tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, w0 + dw, h0 + dh, plane, n_img);
             else
               tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, 0, m0, 0, 0);
             tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &full[s], tap * p.ctot + (second ? p.c1 : 0) + c0, tn * BN);
@@ -498,7 +499,9 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   // BK = 64 (128-byte swizzled rows) for every shape: a channel range that is not a multiple of 64 ends in a
   // partial chunk (TMA zero-fills the missing channels, the MMA warp issues only valid/16 instructions for it)
   constexpr int BK = 64;
-  int BN = (d->geglu && d->n % 128 == 0) ? 128 : (d->n % 160 == 0) ? 160 : (d->n % 32 == 0) ? 32 : 16;
+  // 128-wide tiles also serve the plain GEMMs whose n is a multiple of 128 but not of 160 (the first-stage decoder's
+  // 128/256/512-channel convolutions and its n x n attention scores); no UNet shape falls in that class
+  int BN = (d->geglu && d->n % 128 == 0) ? 128 : (d->n % 160 == 0) ? 160 : (d->n % 128 == 0) ? 128 : (d->n % 32 == 0) ? 32 : 16;
   LDM_CHECK_ARG(BN != 16 || d->n == 16, "igemm_tc: n=%d unsupported (need multiple of 32, or exactly 16)", d->n);
   LDM_CHECK_ARG(!(d->geglu && BN == 16), "igemm_tc: geglu needs n %% 32 == 0");
   p.c1 = c1;
@@ -519,9 +522,9 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
     uint64_t dims[5], str[4];
     uint32_t box[5];
     if (p.is_conv) {
-      LDM_CHECK_ARG(is_pow2(w_out) && is_pow2(h_out) && w_out <= 128,
-                    "igemm_tc: 3x3 conv needs power-of-two output H,W with W <= 128 (got %dx%d)", h_out, w_out);
-      const int bw = w_out, bh = std::min(h_out, 128 / bw), bn = 128 / (bw * bh);
+      LDM_CHECK_ARG(is_pow2(w_out) && is_pow2(h_out) && (w_out <= 128 || d->stride == 1),
+                    "igemm_tc: 3x3 conv needs power-of-two output H,W (W <= 128 for stride 2) (got %dx%d)", h_out, w_out);
+      const int bw = std::min(w_out, 128), bh = std::min(h_out, 128 / bw), bn = 128 / (bw * bh);
       dims[0] = C; dims[1] = w_out; dims[2] = h_out; dims[3] = planes; dims[4] = d->batch;
       str[0] = C * 2; str[1] = (uint64_t)w_out * C * 2; str[2] = (uint64_t)hw_out * C * 2; str[3] = (uint64_t)planes * hw_out * C * 2;
       box[0] = BK; box[1] = bw; box[2] = bh; box[3] = 1; box[4] = bn;

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define LDMB200_ABI_VERSION 3
+#define LDMB200_ABI_VERSION 4
 
 #define LDMB200_F32 0
 #define LDMB200_BF16 1
@@ -333,6 +333,24 @@ int ldmb200_small_linear_bwd_batched(const ldmb200_linear_bwd_job* jobs, int n_j
 int ldmb200_adamw_ema(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, float* ema, int64_t n,
                       float lr, float beta1, float beta2, float eps, float weight_decay, float bias_corr1,
                       float bias_corr2, float ema_one_minus_decay, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * First-stage decode - VQModelInterface.decode, ldm/models/autoencoder.py:274-283.
+ *
+ * vq_lookup_postconv: VectorQuantizer2.forward (taming/modules/vqvae/quantize.py:285-309) + post_quant_conv
+ *   (autoencoder.py:43,280) + the channels-last staging of Decoder.conv_in's input, one thread per latent pixel.
+ *   z fp32 NCHW [B, e_dim, HW]; codebook fp32 [n_e, e_dim] or NULL (force_not_quantize=True: z passes through);
+ *   d = (sum z^2 + sum e^2) - 2 z.e in fp32, first index of the minimum; z_q = z + (e - z);
+ *   y[pixel, c] = bias[c] + sum_e w[c, e] z_q[e] for c < z_channels, 0 for z_channels <= c < c_pad (out_dtype);
+ *   indices int64 [B*HW] and zq fp32 NCHW are optional outputs (NULL to skip).
+ * softmax_rows: p[r, :] = softmax(scale * s[r, :]) - AttnBlock.forward model.py:186-187 (single head, d = C, so
+ *   the two contractions are plain GEMMs run through ldmb200_igemm_* with the per-sample K / V^T as "weight").
+ *   s fp32, p out_dtype, n <= 16384. */
+int ldmb200_vq_lookup_postconv(const float* z, const float* codebook, int n_e, int e_dim, const float* w,
+                               const float* bias, int z_channels, void* y, int out_dtype, int c_pad, int64_t* indices,
+                               float* zq, int batch, int hw, void* stream);
+int ldmb200_softmax_rows(const float* s, int64_t s_ld, void* p, int out_dtype, int64_t p_ld, int rows, int n, float scale,
+                         void* stream);
 
 #ifdef __cplusplus
 }

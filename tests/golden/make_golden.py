@@ -250,13 +250,63 @@ def train_goldens():
     return out
 
 
+def vq_goldens():
+    """First-stage decode through the REAL reference modules: ``VectorQuantizer2`` (taming, vendored in the
+    reference tree), ``post_quant_conv`` and ``Decoder`` assembled exactly as ``VQModel.__init__`` does
+    (autoencoder.py:36-43; ``VQModelInterface`` itself needs pytorch_lightning), synthetic weights of
+    ``oracle.vq_oracle.init_vq_state_dict`` loaded with strict=True (which proves the parameter names / shapes)."""
+    import contextlib
+    import io
+    from oracle import vq_oracle as V
+    R.import_reference("face_reenactment")
+    from ldm.modules.diffusionmodules.model import Decoder
+    from taming.modules.vqvae.quantize import VectorQuantizer2
+
+    class FirstStage(torch.nn.Module):
+        def __init__(self, cfg):
+            super().__init__()
+            dd = cfg["ddconfig"]
+            with contextlib.redirect_stdout(io.StringIO()):
+                self.decoder = Decoder(**dd)
+            self.quantize = VectorQuantizer2(cfg["n_embed"], cfg["embed_dim"], beta=0.25)
+            self.post_quant_conv = torch.nn.Conv2d(cfg["embed_dim"], dd["z_channels"], 1)
+
+        def decode(self, h, force_not_quantize=False):      # autoencoder.py:274-283 verbatim semantics
+            info = None
+            if not force_not_quantize:
+                quant, _, info = self.quantize(h)
+            else:
+                quant = h
+            return self.decoder(self.post_quant_conv(quant)), info
+
+    out = {}
+    for name, cfg, B, hw, seed in [("tiny_8", V.VQ_TINY, 2, 8, 5), ("tiny_16", V.VQ_TINY, 1, 16, 6),
+                                   ("f4_16", V.VQ_F4, 1, 16, 7)]:
+        sd = V.init_vq_state_dict(cfg, 0)
+        m = FirstStage(cfg)
+        m.load_state_dict(sd, strict=True)
+        m.eval()
+        g = torch.Generator().manual_seed(seed)
+        z = torch.randn(B, cfg["embed_dim"], hw, hw, generator=g)
+        with torch.no_grad():
+            img_q, info = m.decode(z)
+            img_n, _ = m.decode(z, force_not_quantize=True)
+        out[f"{name}/z"] = z.numpy()
+        out[f"{name}/image_quantized"] = img_q.numpy()
+        out[f"{name}/image_not_quantized"] = img_n.numpy()
+        out[f"{name}/indices"] = info[2].numpy().astype(np.int64)
+        a, b = O.state_dict_checksum(sd)
+        out[f"{name}/sd_checksum"] = np.array([a, b])
+    return out
+
+
 def main():
     torch.set_num_threads(max(1, os.cpu_count() or 1))
     only = sys.argv[1:]
     for fn, gen in (("unet.npz", unet_goldens), ("schedule.npz", schedule_goldens),
                     ("trajectory.npz", trajectory_goldens), ("unet64.npz", unet64_goldens),
                     ("manipulation.npz", manipulation_goldens), ("train.npz", train_goldens),
-                    ("unet128.npz", unet128_goldens)):
+                    ("unet128.npz", unet128_goldens), ("vqdecode.npz", vq_goldens)):
         if only and fn not in only:
             continue
         data = gen()

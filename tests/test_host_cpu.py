@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     lib = P.load_library()
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.ldmb200_abi_version() == 3
+    assert lib.ldmb200_abi_version() == 4
 
 
 def test_struct_layouts_match_the_header():
@@ -138,3 +138,33 @@ def test_install_patches_the_reference_targets():
     finally:
         P.uninstall()
     assert oam.UNetModel is ref_unet and ddim_mod.DDIMSampler is ref_smp
+
+
+# ------------------------------------------------------------------------------------------ first-stage decode (8f n2)
+def test_vq_decoder_parameter_inventory_matches_the_reference_names():
+    """VQDecoder's state dict = the decode-side keys of the reference VQModel (oracle.vq_oracle.vq_param_shapes, proven
+    against the real modules by load_state_dict(strict=True) in tests/golden/make_golden.py)."""
+    import dsml_thesis_b200 as P
+    from oracle import vq_oracle as V
+    for cfg in (V.VQ_TINY, V.VQ_F4):
+        m = P.VQDecoder(**cfg, lossconfig={"target": "torch.nn.Identity"}, ckpt_path=None)
+        mine = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+        assert mine == V.vq_param_shapes(cfg)
+        assert not any(p.requires_grad for p in m.parameters())
+    # a full first-stage checkpoint (encoder / quant_conv / loss keys too) loads with strict=False and nothing missing
+    sd = dict(V.init_vq_state_dict(V.VQ_TINY, 0))
+    sd["encoder.conv_in.weight"] = torch.zeros(32, 3, 3, 3)
+    sd["quant_conv.weight"] = torch.zeros(3, 3, 1, 1)
+    missing, unexpected = P.VQDecoder(**V.VQ_TINY).load_state_dict(sd, strict=False)
+    assert not missing and sorted(unexpected) == ["encoder.conv_in.weight", "quant_conv.weight"]
+
+
+def test_vq_decoder_has_no_cpu_fallback_and_rejects_other_variants():
+    import dsml_thesis_b200 as P
+    from oracle import vq_oracle as V
+    m = P.VQDecoder(**V.VQ_TINY)
+    with pytest.raises(P.Ldmb200Error):
+        m.decode(torch.zeros(1, 3, 8, 8))
+    dd = dict(V.VQ_TINY["ddconfig"], attn_type="linear")
+    with pytest.raises(NotImplementedError):
+        P.VQDecoder(dd, 3, 512)

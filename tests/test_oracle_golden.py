@@ -218,3 +218,25 @@ def test_unet_eps_128_matches_reference_golden():
     ctx = torch.randn(1, 1, 512, generator=g)
     eps = O.unet_forward(sd, O.FR_UNET, x, torch.tensor([501]), ctx)
     assert O.rel_l2(eps, torch.from_numpy(gold["fr_128/eps_t501"])) <= 2e-6
+
+
+# ------------------------------------------------------------------------------------------ first-stage decode (8f n2)
+@pytest.mark.parametrize("name,cfg_name", [("tiny_8", "VQ_TINY"), ("tiny_16", "VQ_TINY"), ("f4_16", "VQ_F4")])
+def test_vq_decode_matches_reference_golden(name, cfg_name):
+    """oracle/vq_oracle.py vs outputs of the real reference VectorQuantizer2 + post_quant_conv + Decoder
+    (tests/golden/make_golden.py: vq_goldens): code indices and images bit-exact on CPU."""
+    import os
+    from conftest import GOLDEN
+    from oracle import vq_oracle as V
+    g = np.load(os.path.join(GOLDEN, "vqdecode.npz"))
+    cfg = getattr(V, cfg_name)
+    sd = V.init_vq_state_dict(cfg, 0)
+    a, b = O.state_dict_checksum(sd)
+    np.testing.assert_allclose([a, b], g[f"{name}/sd_checksum"], rtol=1e-9)
+    z = torch.from_numpy(g[f"{name}/z"])
+    img, idx = V.vq_decode(sd, cfg, z)
+    np.testing.assert_array_equal(idx.numpy(), g[f"{name}/indices"])
+    assert O.rel_l2(img, torch.from_numpy(g[f"{name}/image_quantized"])) <= 1e-6
+    img, none = V.vq_decode(sd, cfg, z, force_not_quantize=True)
+    assert none is None
+    assert O.rel_l2(img, torch.from_numpy(g[f"{name}/image_not_quantized"])) <= 1e-6

@@ -1,0 +1,185 @@
+"""GPU parity of the first-stage decode through ``dsml_thesis_b200.VQDecoder`` and the C-ABI:
+``VQModelInterface.decode`` = VectorQuantizer2 nearest-code lookup → post_quant_conv → Decoder.
+
+Checked against (i) the committed outputs of the REAL reference modules (``tests/golden/vqdecode.npz``) and (ii) the CPU
+oracle (``oracle/vq_oracle.py``, itself bit-exact on those goldens) at the sizes the goldens do not reach.
+
+Tolerances: code indices bit-exact (the goldens have no fp32 near-ties); image rel-L2 ≤ 1e-4 in fp32 mode and ≤ 2e-2 in
+the 16-bit tensor-core modes (≈20 GroupNorm/conv layers; the reference's own bf16 autocast is ~1e-2 on the UNet)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import dsml_thesis_b200 as P  # noqa: E402
+from dsml_thesis_b200 import _cabi  # noqa: E402
+from dsml_thesis_b200._cabi import BF16, F16, F32  # noqa: E402
+from oracle import ldm_oracle as O  # noqa: E402
+from oracle import vq_oracle as V  # noqa: E402
+from conftest import GOLDEN, record_parity  # noqa: E402
+
+TOL = {"fp32": 1e-4, "f16": 2e-2, "bf16": 3e-2}
+
+
+@pytest.fixture(scope="module")
+def golden_vq():
+    return np.load(os.path.join(GOLDEN, "vqdecode.npz"))
+
+
+def _model(cfg):
+    sd = V.init_vq_state_dict(cfg, 0)
+    m = P.VQDecoder(**cfg)
+    m.load_state_dict(sd, strict=True)
+    return sd, m.cuda().eval()
+
+
+def _real_index_mismatches(sd, z, mine, ref):
+    """Indices must agree except at fp32 near-ties: where they differ, the two chosen codes must be equidistant from z to
+    within 2 ulp of the distance (the reference's einsum may sum z.e in another order than the kernel's FMA chain)."""
+    bad = (mine != ref).nonzero().flatten()
+    if bad.numel() == 0:
+        return 0
+    e = sd["quantize.embedding.weight"].double()
+    zf = z.permute(0, 2, 3, 1).reshape(-1, e.shape[1]).double()[bad]
+    da = ((zf - e[mine[bad]]) ** 2).sum(1)
+    db = ((zf - e[ref[bad]]) ** 2).sum(1)
+    scale = (zf ** 2).sum(1) + 1.0
+    return int(((da - db).abs() > 2.4e-7 * scale).sum())
+
+
+# ------------------------------------------------------------------------------------------ kernels
+@pytest.mark.parametrize("B,hw,n_e", [(1, 64, 512), (2, 256, 16384), (3, 100, 1000)])
+def test_vq_lookup_postconv_vs_oracle(B, hw, n_e):
+    g = torch.Generator().manual_seed(3)
+    e, zc, cpad = 3, 3, 32
+    z = torch.randn(B, e, hw, 1, generator=g)
+    sd = {"quantize.embedding.weight": torch.randn(n_e, e, generator=g)}
+    w, bias = torch.randn(zc, e, generator=g), torch.randn(zc, generator=g)
+    zq_ref, idx_ref = V.vector_quantize(sd, z)
+    y_ref = torch.einsum("ce,behw->bhwc", w, zq_ref).reshape(B * hw, zc) + bias
+    zd, cb, wd, bd = z.cuda(), sd["quantize.embedding.weight"].cuda(), w.cuda(), bias.cuda()
+    for dt, tdt, tol in ((F32, torch.float32, 1e-6), (BF16, torch.bfloat16, 4e-3), (F16, torch.float16, 5e-4)):
+        y = torch.full((B * hw, cpad), float("nan"), device="cuda", dtype=tdt)
+        idx = torch.full((B * hw,), -1, device="cuda", dtype=torch.int64)
+        zq = torch.empty_like(zd)
+        _cabi.call("ldmb200_vq_lookup_postconv", zd.data_ptr(), cb.data_ptr(), n_e, e, wd.data_ptr(), bd.data_ptr(), zc,
+                   y.data_ptr(), dt, cpad, idx.data_ptr(), zq.data_ptr(), B, hw, 0)
+        torch.cuda.synchronize()
+        assert _real_index_mismatches(sd, z, idx.cpu(), idx_ref) == 0
+        same = (idx.cpu() == idx_ref).view(B, hw, 1, 1).permute(0, 3, 1, 2).expand_as(zq_ref)
+        assert torch.equal(zq.cpu()[same], zq_ref[same])                      # z + (e - z), bit-exact
+        if not torch.equal(idx.cpu(), idx_ref):
+            continue
+        assert float(y[:, zc:].float().abs().max()) == 0.0                    # padding channels are zero
+        assert O.rel_l2(y[:, :zc].float().cpu(), y_ref) <= tol
+    # force_not_quantize: z passes through
+    y = torch.empty(B * hw, cpad, device="cuda")
+    _cabi.call("ldmb200_vq_lookup_postconv", zd.data_ptr(), None, 0, e, wd.data_ptr(), bd.data_ptr(), zc, y.data_ptr(), F32,
+               cpad, None, None, B, hw, 0)
+    y_ref = torch.einsum("ce,behw->bhwc", w, z).reshape(B * hw, zc) + bias
+    assert O.rel_l2(y[:, :zc].cpu(), y_ref) <= 1e-6
+
+
+def test_vq_lookup_rejects_bad_arguments():
+    z = torch.zeros(1, 9, 4, device="cuda")
+    with pytest.raises(_cabi.Ldmb200Error):
+        _cabi.call("ldmb200_vq_lookup_postconv", z.data_ptr(), None, 0, 9, z.data_ptr(), None, 3, z.data_ptr(), F32, 32,
+                   None, None, 1, 4, 0)
+
+
+@pytest.mark.parametrize("rows,n", [(5, 64), (128, 1024), (17, 4096), (3, 16384), (4, 1000)])
+def test_softmax_rows_vs_torch(rows, n):
+    s = torch.randn(rows, n, device="cuda") * 30
+    scale = 512 ** -0.5
+    ref = torch.softmax(s.double() * scale, dim=1)
+    for dt, tdt, tol in ((F32, torch.float32, 2e-6), (BF16, torch.bfloat16, 4e-3), (F16, torch.float16, 6e-4)):
+        p = torch.empty(rows, n, device="cuda", dtype=tdt)
+        _cabi.call("ldmb200_softmax_rows", s.data_ptr(), n, p.data_ptr(), dt, n, rows, n, scale, 0)
+        torch.cuda.synchronize()
+        assert O.rel_l2(p.double().cpu(), ref.cpu()) <= tol, (dt, O.rel_l2(p.double().cpu(), ref.cpu()))
+    with pytest.raises(_cabi.Ldmb200Error):
+        _cabi.call("ldmb200_softmax_rows", s.data_ptr(), n, s.data_ptr(), F32, n, rows, 20000, scale, 0)
+
+
+# ------------------------------------------------------------------------------------------ whole decode vs goldens
+@pytest.mark.parametrize("name,cfg", [("tiny_8", V.VQ_TINY), ("tiny_16", V.VQ_TINY), ("f4_16", V.VQ_F4)])
+@pytest.mark.parametrize("precision", ["fp32", "f16", "bf16"])
+def test_decode_vs_reference_golden(golden_vq, name, cfg, precision):
+    sd, m = _model(cfg)
+    a, b = O.state_dict_checksum(sd)
+    np.testing.assert_allclose([a, b], golden_vq[f"{name}/sd_checksum"], rtol=1e-9)
+    m.precision = precision
+    z = torch.from_numpy(golden_vq[f"{name}/z"]).cuda()
+    for rep in range(3):   # eager, then the captured graph, then its replay
+        img = m.decode(z)
+        assert torch.equal(m.last_indices.cpu(), torch.from_numpy(golden_vq[f"{name}/indices"]))
+        err = O.rel_l2(img.cpu(), torch.from_numpy(golden_vq[f"{name}/image_quantized"]))
+        assert err <= TOL[precision], (name, precision, rep, err)
+    record_parity(f"vqdecode/{name}/{precision}/image_quantized_rel_l2", err)
+    img = m.decode(z, force_not_quantize=True)
+    err = O.rel_l2(img.cpu(), torch.from_numpy(golden_vq[f"{name}/image_not_quantized"]))
+    record_parity(f"vqdecode/{name}/{precision}/image_not_quantized_rel_l2", err)
+    assert err <= TOL[precision], (name, precision, err)
+    assert img.dtype == torch.float32 and img.shape == golden_vq[f"{name}/image_quantized"].shape
+
+
+# ------------------------------------------------------------------------------------------ full size vs the oracle
+@pytest.mark.parametrize("hw", [32, 64])
+def test_decode_full_size_vs_oracle(hw):
+    """The shipped first stage at the shipped latent size (32x32 -> 128x128 image) and at BASELINE's 64x64 latents
+    (256x256 image: convolution maps wider than one 128-pixel tile, attention over 4096 positions)."""
+    sd, m = _model(V.VQ_F4)
+    g = torch.Generator().manual_seed(100 + hw)
+    z = torch.randn(1, 3, hw, hw, generator=g)
+    ref, idx = V.vq_decode(sd, V.VQ_F4, z)
+    ref_nq, _ = V.vq_decode(sd, V.VQ_F4, z, force_not_quantize=True)
+    for precision in ("fp32", "f16"):
+        m.precision = precision
+        img = m.decode(z.cuda(), force_not_quantize=True)
+        err = O.rel_l2(img.cpu(), ref_nq)
+        record_parity(f"vqdecode/f4_{hw}/{precision}/image_not_quantized_rel_l2", err)
+        assert err <= TOL[precision], (hw, precision, err)
+        img = m.decode(z.cuda())
+        mine = m.last_indices.cpu()
+        assert _real_index_mismatches(sd, z, mine, idx) == 0
+        if torch.equal(mine, idx):      # (an fp32 near-tie picks another, equidistant code: a different but equally valid image)
+            err = O.rel_l2(img.cpu(), ref)
+            record_parity(f"vqdecode/f4_{hw}/{precision}/image_quantized_rel_l2", err)
+            assert err <= TOL[precision], (hw, precision, err)
+
+
+def test_decode_is_batch_invariant_and_deterministic():
+    sd, m = _model(V.VQ_TINY)
+    g = torch.Generator().manual_seed(9)
+    z = torch.randn(4, 3, 16, 16, generator=g).cuda()
+    full = m.decode(z)
+    again = m.decode(z)
+    assert torch.equal(full, again)
+    for b in range(4):
+        one = m.decode(z[b:b + 1])
+        assert O.rel_l2(one.cpu(), full[b:b + 1].cpu()) <= 1e-6
+
+
+def test_accelerate_first_stage_rebinds_decode():
+    """A stand-in with the reference VQModel's attribute layout (decoder / quantize / post_quant_conv) gets its decode
+    rebound; the result equals the oracle on the stand-in's own weights."""
+    sd, donor = _model(V.VQ_TINY)
+
+    class FirstStage(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.decoder, self.quantize, self.post_quant_conv = donor.decoder, donor.quantize, donor.post_quant_conv
+            self.decoder.resolution, self.decoder.in_channels = 32, 3
+
+        def decode(self, h, force_not_quantize=False):
+            raise AssertionError("reference decode must have been replaced")
+
+    fs = FirstStage().cuda()
+    fast = P.accelerate_first_stage(fs, precision="fp32")
+    z = torch.randn(1, 3, 8, 8, generator=torch.Generator().manual_seed(4))
+    ref, _ = V.vq_decode(sd, V.VQ_TINY, z)
+    assert O.rel_l2(fs.decode(z.cuda()).cpu(), ref) <= 1e-4
+    assert fast.precision == "fp32"

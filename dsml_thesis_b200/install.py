@@ -10,6 +10,9 @@ Usage (no reference file edited):  put this repo on ``PYTHONPATH`` and either ru
 ``python -c "import dsml_thesis_b200; dsml_thesis_b200.install()" ...`` / add the two lines to a
 ``sitecustomize.py``, or set ``LDMB200_AUTOINSTALL=1`` with the ``sitecustomize`` shipped in INTEGRATION.md.
 
+``ldm.models.autoencoder.VQModelInterface.decode`` is wrapped so that CUDA latents decode through ``VQDecoder``
+(built lazily per instance from the live module's own weights).
+
 It also wraps ``ldm.modules.ema.LitEma.copy_to`` / ``restore`` (ema.py:46-76): they overwrite ``param.data`` in
 place, which bumps neither ``_version`` nor ``data_ptr`` — the UNet's packed bf16 weights must be told.
 """
@@ -87,6 +90,18 @@ def install(verbose: bool = False):
             lit.restore = wrap(lit.restore)
             lit._ldmb200_wrapped = True
             done.append("ldm.modules.ema.LitEma.copy_to/restore")
+    except Exception:
+        pass
+    # first-stage decode: VQModelInterface.decode -> VQDecoder, built lazily per instance
+    try:
+        ae = importlib.import_module("ldm.models.autoencoder")
+        vqi = ae.VQModelInterface
+        if not getattr(vqi, "_ldmb200_wrapped", False):
+            from .vqdecode import accelerated_decode
+            _saved[("ldm.models.autoencoder", "VQModelInterface.decode")] = vqi.decode
+            vqi.decode = accelerated_decode(vqi.decode)
+            vqi._ldmb200_wrapped = True
+            done.append("ldm.models.autoencoder.VQModelInterface.decode")
     except Exception:
         pass
     if verbose:

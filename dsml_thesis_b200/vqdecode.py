@@ -331,9 +331,8 @@ class VQDecoder(nn.Module):
         return self.decode(h, force_not_quantize)
 
 
-def accelerate_first_stage(first_stage_model, precision: Optional[str] = None):
-    """Builds a ``VQDecoder`` from a live reference ``VQModelInterface`` (shapes are read from its own modules, weights
-    copied once) and rebinds ``first_stage_model.decode`` to it.  Encoding stays on the reference path."""
+def _build_from(first_stage_model) -> VQDecoder:
+    """A ``VQDecoder`` with the shapes and weights of a live reference ``VQModelInterface`` (read from its own modules)."""
     dec = first_stage_model.decoder
     n_e, e_dim = first_stage_model.quantize.embedding.weight.shape
     nres = dec.num_resolutions
@@ -343,15 +342,37 @@ def accelerate_first_stage(first_stage_model, precision: Optional[str] = None):
     resolution = getattr(dec, "resolution", 2 ** (nres - 1))
     attn_res = [resolution // 2 ** i for i in attn_levels]
     dd = dict(ch=ch, out_ch=dec.conv_out.out_channels, ch_mult=ch_mult, num_res_blocks=dec.num_res_blocks,
-              attn_resolutions=attn_res, in_channels=dec.in_channels, resolution=resolution,
+              attn_resolutions=attn_res, in_channels=getattr(dec, "in_channels", 3), resolution=resolution,
               z_channels=dec.conv_in.in_channels)
     fast = VQDecoder(dd, e_dim, n_e)
     missing, _ = fast.load_state_dict(first_stage_model.state_dict(), strict=False)
     if missing:
         raise _cabi.Ldmb200Error(f"first stage state dict lacks {missing[:4]}...")
-    fast = fast.to(first_stage_model.post_quant_conv.weight.device)
+    return fast.to(first_stage_model.post_quant_conv.weight.device)
+
+
+def accelerate_first_stage(first_stage_model, precision: Optional[str] = None) -> VQDecoder:
+    """Builds a ``VQDecoder`` from a live reference ``VQModelInterface`` (weights copied once — the first stage is frozen
+    in every LDM config) and rebinds ``first_stage_model.decode`` to it.  Encoding stays on the reference path."""
+    fast = _build_from(first_stage_model)
     if precision is not None:
         fast.precision = precision
     first_stage_model.decode = fast.decode
-    first_stage_model._ldmb200_decoder = fast
+    first_stage_model.__dict__["_ldmb200_decoder"] = fast
     return fast
+
+
+def accelerated_decode(reference_decode):
+    """Class-level wrapper for ``VQModelInterface.decode`` used by ``install()``: CUDA latents under ``no_grad`` go
+    through a ``VQDecoder`` built lazily per instance; anything else (CPU tensors, gradients through the decoder) is not
+    this path and stays on the reference's own method."""
+    def decode(self, h, force_not_quantize=False):
+        if not h.is_cuda or (torch.is_grad_enabled() and h.requires_grad):
+            return reference_decode(self, h, force_not_quantize)
+        fast = self.__dict__.get("_ldmb200_decoder")
+        if fast is None or fast._device() != h.device:
+            fast = _build_from(self)
+            self.__dict__["_ldmb200_decoder"] = fast
+        return fast.decode(h, force_not_quantize)
+    decode._ldmb200_reference = reference_decode
+    return decode

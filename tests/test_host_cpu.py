@@ -168,3 +168,32 @@ def test_vq_decoder_has_no_cpu_fallback_and_rejects_other_variants():
     dd = dict(V.VQ_TINY["ddconfig"], attn_type="linear")
     with pytest.raises(NotImplementedError):
         P.VQDecoder(dd, 3, 512)
+
+
+def test_install_wraps_first_stage_decode(monkeypatch):
+    """``ldm.models.autoencoder`` needs pytorch_lightning (absent here), so a stand-in module with the reference's class
+    name is registered: install() must wrap ``VQModelInterface.decode`` at class level, keep CPU calls on the reference
+    method, and uninstall() must restore it."""
+    import types
+    import dsml_thesis_b200 as P
+    R.import_reference("face_reenactment")
+    calls = []
+
+    class VQModelInterface(torch.nn.Module):
+        def decode(self, h, force_not_quantize=False):
+            calls.append(force_not_quantize)
+            return h
+
+    mod = types.ModuleType("ldm.models.autoencoder")
+    mod.VQModelInterface = VQModelInterface
+    monkeypatch.setitem(sys.modules, "ldm.models.autoencoder", mod)
+    ref_decode = VQModelInterface.decode
+    try:
+        done = P.install()
+        assert "ldm.models.autoencoder.VQModelInterface.decode" in done
+        assert VQModelInterface.decode is not ref_decode
+        x = torch.zeros(1, 3, 4, 4)
+        assert VQModelInterface().decode(x, True) is x and calls == [True]     # CPU tensor: the reference's own method
+    finally:
+        P.uninstall()
+    assert VQModelInterface.decode is ref_decode

@@ -4,8 +4,8 @@
 Checked against (i) the committed outputs of the REAL reference modules (``tests/golden/vqdecode.npz``) and (ii) the CPU
 oracle (``oracle/vq_oracle.py``, itself bit-exact on those goldens) at the sizes the goldens do not reach.
 
-Tolerances: code indices bit-exact (the goldens have no fp32 near-ties); image rel-L2 ≤ 1e-4 in fp32 mode and ≤ 2e-2 in
-the 16-bit tensor-core modes (≈20 GroupNorm/conv layers; the reference's own bf16 autocast is ~1e-2 on the UNet)."""
+Tolerances: code indices bit-exact (the goldens have no fp32 near-ties); image rel-L2 ≤ 1e-4 in fp32 mode (measured 4e-6), ≤ 5e-3 in
+f16 mode (measured 1.3e-3) and ≤ 2e-2 in bf16 mode (measured 9e-3; the reference's own bf16 autocast is ~1e-2 on the UNet)."""
 import os
 
 import numpy as np
@@ -21,7 +21,7 @@ from oracle import ldm_oracle as O  # noqa: E402
 from oracle import vq_oracle as V  # noqa: E402
 from conftest import GOLDEN, record_parity  # noqa: E402
 
-TOL = {"fp32": 1e-4, "f16": 2e-2, "bf16": 3e-2}
+TOL = {"fp32": 1e-4, "f16": 5e-3, "bf16": 2e-2}
 
 
 @pytest.fixture(scope="module")
@@ -163,23 +163,39 @@ def test_decode_is_batch_invariant_and_deterministic():
         assert O.rel_l2(one.cpu(), full[b:b + 1].cpu()) <= 1e-6
 
 
-def test_accelerate_first_stage_rebinds_decode():
-    """A stand-in with the reference VQModel's attribute layout (decoder / quantize / post_quant_conv) gets its decode
-    rebound; the result equals the oracle on the stand-in's own weights."""
-    sd, donor = _model(V.VQ_TINY)
-
-    class FirstStage(torch.nn.Module):
+def _first_stage_stand_in(donor):
+    class VQModelInterface(torch.nn.Module):          # attribute layout of the reference VQModel (autoencoder.py:36-43)
         def __init__(self):
             super().__init__()
             self.decoder, self.quantize, self.post_quant_conv = donor.decoder, donor.quantize, donor.post_quant_conv
             self.decoder.resolution, self.decoder.in_channels = 32, 3
 
         def decode(self, h, force_not_quantize=False):
-            raise AssertionError("reference decode must have been replaced")
+            raise AssertionError("the reference decode must have been replaced for CUDA latents")
 
-    fs = FirstStage().cuda()
+    return VQModelInterface
+
+
+def test_accelerate_first_stage_rebinds_decode():
+    """A stand-in with the reference VQModel's attribute layout gets its decode rebound; the result equals the oracle on
+    the stand-in's own weights."""
+    sd, donor = _model(V.VQ_TINY)
+    fs = _first_stage_stand_in(donor)().cuda()
     fast = P.accelerate_first_stage(fs, precision="fp32")
     z = torch.randn(1, 3, 8, 8, generator=torch.Generator().manual_seed(4))
     ref, _ = V.vq_decode(sd, V.VQ_TINY, z)
     assert O.rel_l2(fs.decode(z.cuda()).cpu(), ref) <= 1e-4
     assert fast.precision == "fp32"
+
+
+def test_install_wrapper_decodes_cuda_latents_through_the_kernels():
+    from dsml_thesis_b200.vqdecode import accelerated_decode
+    sd, donor = _model(V.VQ_TINY)
+    cls = _first_stage_stand_in(donor)
+    cls.decode = accelerated_decode(cls.decode)
+    fs = cls().cuda()
+    z = torch.randn(2, 3, 8, 8, generator=torch.Generator().manual_seed(5))
+    ref, _ = V.vq_decode(sd, V.VQ_TINY, z, force_not_quantize=True)
+    out = fs.decode(z.cuda(), force_not_quantize=True)
+    assert O.rel_l2(out.cpu(), ref) <= TOL[fs._ldmb200_decoder.precision]
+    assert fs.decode(z.cuda()).shape == ref.shape and len(fs._ldmb200_decoder._plans) == 2

@@ -14,6 +14,7 @@ Public surface = the reference's own plugin interface for this path (SURVEY §8b
                           (nearest-code lookup, post_quant_conv, Decoder) on the same kernels
   * ``sample_sharded``  — ``DDIMSampler.sample`` for a global batch split over the GPUs of one box (one process
                           per GPU, no data-path collective, final all-gather)
+  * ``Conv1DTemporalAttention`` — the talking-face audio conditioning encoder as one fused launch
 
 All compute goes through ``libldmb200.so`` (C-ABI in ``include/ldmb200.h``); there is no CPU or PyTorch
 fallback — importing works anywhere, running needs the built library and a B200.
@@ -24,8 +25,10 @@ from .sampler import DDIMSampler, DDIMSampler2, DDIMSampler2Cond, DDIMSampler2Co
 from .handle import DiffusionHandle  # noqa: F401
 from .install import install, uninstall  # noqa: F401
 from .vqdecode import VQDecoder, accelerate_first_stage  # noqa: F401
+from .cond import Conv1DTemporalAttention  # noqa: F401
 from .sharding import sample_sharded, shard_range, gather_shards, initial_noise  # noqa: F401
 
 __all__ = ["UNetModel", "DDIMSampler", "DDIMSampler2", "DDIMSampler2Cond", "DDIMSampler2CondFR", "ddim_step", "install",
            "uninstall", "DiffusionHandle", "load_library", "Ldmb200Error", "sample_sharded", "shard_range",
-           "gather_shards", "initial_noise", "VQDecoder", "accelerate_first_stage"]
+           "gather_shards", "initial_noise", "VQDecoder", "accelerate_first_stage",
+           "Conv1DTemporalAttention"]

@@ -130,6 +130,7 @@ SIGNATURES = {
     "ldmb200_adamw_ema": (_i, [_p, _p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _f, _f, _f, _p]),
     "ldmb200_vq_lookup_postconv": (_i, [_p, _p, _i, _i, _p, _p, _i, _p, _i, _i, _p, _p, _i, _i, _p]),
     "ldmb200_softmax_rows": (_i, [_p, _i64, _p, _i, _i64, _i, _i, _f, _p]),
+    "ldmb200_conv1d_temporal_attention": (_i, [_p, _p, _p, _p, _p, _i, _p, _p, _i, _i, _f, _p]),
 }
 
 _lib = None

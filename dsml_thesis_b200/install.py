@@ -104,6 +104,18 @@ def install(verbose: bool = False):
             done.append("ldm.models.autoencoder.VQModelInterface.decode")
     except Exception:
         pass
+    # audio conditioning encoder (talking_face only): one fused launch per frame when no gradient is needed
+    try:
+        enc = importlib.import_module("ldm.modules.encoders.modules")
+        cta = getattr(enc, "Conv1DTemporalAttention", None)
+        if cta is not None and not getattr(cta, "_ldmb200_wrapped", False):
+            from .cond import accelerated_forward
+            _saved[("ldm.modules.encoders.modules", "Conv1DTemporalAttention.forward")] = cta.forward
+            cta.forward = accelerated_forward(cta.forward)
+            cta._ldmb200_wrapped = True
+            done.append("ldm.modules.encoders.modules.Conv1DTemporalAttention.forward")
+    except Exception:
+        pass
     if verbose:
         print("dsml_thesis_b200.install():", ", ".join(done) or "nothing patched (is `ldm` importable?)")
     return done

@@ -352,6 +352,17 @@ int ldmb200_vq_lookup_postconv(const float* z, const float* codebook, int n_e, i
 int ldmb200_softmax_rows(const float* s, int64_t s_ld, void* p, int out_dtype, int64_t p_ld, int rows, int n, float scale,
                          void* stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Audio conditioning encoder - Conv1DTemporalAttention.forward,
+ * talking_face/ldm/modules/encoders/modules.py:76-113 (cond_stage_config_2 of mead-128-ldm-f4.yaml:75-80):
+ *   s = attentionConvNet(x^T): n_layers x [Conv1d(k=3, pad=1) + LeakyReLU(slope)], channels[0] = D -> ... -> 1;
+ *   a = softmax(Linear(L, L)(s));  out[b, :] = sum_l a[l] * x[b, l, :]        (torch.bmm(x^T, attention))
+ * x fp32 [B, L, D], conv_w[i] fp32 [channels[i+1], channels[i], 3], lin_w fp32 [L, L]; out fp32 [B, D].
+ * conv_w / conv_b / channels are HOST arrays (of device pointers / ints); L <= 32; one CTA per sample. */
+int ldmb200_conv1d_temporal_attention(const float* x, float* out, const float* const* conv_w, const float* const* conv_b,
+                                      const int* channels, int n_layers, const float* lin_w, const float* lin_b,
+                                      int batch, int seq_len, float leaky_slope, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -300,13 +300,40 @@ def vq_goldens():
     return out
 
 
+def cond_goldens():
+    """Audio conditioning encoder: the REAL ``Conv1DTemporalAttention`` of
+    talking_face/ldm/modules/encoders/modules.py (its module-level imports of ``clip`` and ``kornia``, absent here and
+    unused by this class, are stubbed) with the synthetic weights of ``oracle.cond_oracle.init_cond_state_dict``."""
+    import types
+    from oracle import cond_oracle as CO
+    R.import_reference("talking_face")
+    for name in ("clip", "kornia"):
+        if name not in sys.modules:
+            sys.modules[name] = types.ModuleType(name)
+    from ldm.modules.encoders.modules import Conv1DTemporalAttention
+    out = {}
+    for name, cfg, B, seed in [("tf_audio", CO.TF_AUDIO, 3, 21),
+                               ("hidden", dict(seq_len=9, subspace_dim=64, subspace2hidden=True, hidden_dim=48), 2, 22)]:
+        sd = CO.init_cond_state_dict(cfg, 0)
+        m = Conv1DTemporalAttention(**cfg)
+        m.load_state_dict(sd, strict=True)
+        m.eval()
+        g = torch.Generator().manual_seed(seed)
+        x = torch.randn(B, cfg["seq_len"], cfg["subspace_dim"], generator=g)
+        with torch.no_grad():
+            y = m(x)
+        out[f"{name}/x"] = x.numpy()
+        out[f"{name}/y"] = y.numpy()
+    return out
+
+
 def main():
     torch.set_num_threads(max(1, os.cpu_count() or 1))
     only = sys.argv[1:]
     for fn, gen in (("unet.npz", unet_goldens), ("schedule.npz", schedule_goldens),
                     ("trajectory.npz", trajectory_goldens), ("unet64.npz", unet64_goldens),
                     ("manipulation.npz", manipulation_goldens), ("train.npz", train_goldens),
-                    ("unet128.npz", unet128_goldens), ("vqdecode.npz", vq_goldens)):
+                    ("unet128.npz", unet128_goldens), ("vqdecode.npz", vq_goldens), ("cond.npz", cond_goldens)):
         if only and fn not in only:
             continue
         data = gen()

@@ -240,3 +240,19 @@ def test_vq_decode_matches_reference_golden(name, cfg_name):
     img, none = V.vq_decode(sd, cfg, z, force_not_quantize=True)
     assert none is None
     assert O.rel_l2(img, torch.from_numpy(g[f"{name}/image_not_quantized"])) <= 1e-6
+
+
+# ------------------------------------------------------------------------------------------ audio conditioning (8f n4)
+@pytest.mark.parametrize("name,cfg", [("tf_audio", None), ("hidden", dict(seq_len=9, subspace_dim=64, subspace2hidden=True,
+                                                                          hidden_dim=48))])
+def test_conv1d_temporal_attention_matches_reference_golden(name, cfg):
+    """oracle/cond_oracle.py vs the output of the real reference Conv1DTemporalAttention (make_golden.py: cond_goldens)."""
+    import os
+    from conftest import GOLDEN
+    from oracle import cond_oracle as CO
+    g = np.load(os.path.join(GOLDEN, "cond.npz"))
+    cfg = cfg or CO.TF_AUDIO
+    sd = CO.init_cond_state_dict(cfg, 0)
+    y = CO.conv1d_temporal_attention(sd, cfg, torch.from_numpy(g[f"{name}/x"]))
+    assert y.shape == g[f"{name}/y"].shape
+    assert O.rel_l2(y, torch.from_numpy(g[f"{name}/y"])) <= 1e-6

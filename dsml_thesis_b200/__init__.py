@@ -24,11 +24,11 @@ from .unet import UNetModel  # noqa: F401
 from .sampler import DDIMSampler, DDIMSampler2, DDIMSampler2Cond, DDIMSampler2CondFR, ddim_step  # noqa: F401
 from .handle import DiffusionHandle  # noqa: F401
 from .install import install, uninstall  # noqa: F401
-from .vqdecode import VQDecoder, accelerate_first_stage  # noqa: F401
+from .vqdecode import VQDecoder, VQEncoder, accelerate_first_stage  # noqa: F401
 from .cond import Conv1DTemporalAttention  # noqa: F401
 from .sharding import sample_sharded, shard_range, gather_shards, initial_noise  # noqa: F401
 
 __all__ = ["UNetModel", "DDIMSampler", "DDIMSampler2", "DDIMSampler2Cond", "DDIMSampler2CondFR", "ddim_step", "install",
            "uninstall", "DiffusionHandle", "load_library", "Ldmb200Error", "sample_sharded", "shard_range",
-           "gather_shards", "initial_noise", "VQDecoder", "accelerate_first_stage",
+           "gather_shards", "initial_noise", "VQDecoder", "VQEncoder", "accelerate_first_stage",
            "Conv1DTemporalAttention"]

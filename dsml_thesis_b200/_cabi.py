@@ -38,6 +38,7 @@ class GemmDesc(C.Structure):
         ("out", C.c_void_p),
         ("out_dtype", C.c_int32), ("out_ld", C.c_int32), ("out_nchw", C.c_int32), ("n_valid", C.c_int32),
         ("colstats", C.c_void_p),
+        ("pad_mode", C.c_int32), ("pad_", C.c_int32),
     ]
 
 

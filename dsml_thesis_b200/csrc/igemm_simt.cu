@@ -9,7 +9,7 @@ namespace ldm {
 constexpr int SG_BM = 64, SG_BN = 64, SG_BK = 16, SG_THREADS = 256;
 
 struct SimtGeom {
-  int c1, c2, ctot, taps, ks, stride, upsample;
+  int c1, c2, ctot, taps, ks, stride, upsample, pad_asym;
   int h_in, w_in, h_eff, w_eff, h_out, w_out;
   int64_t M;
   int K;
@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(SG_THREADS) igemm_simt_kernel(const TA* __rest
     loh[i] = p / g.w_out;
     low[i] = p % g.w_out;
   }
-  const int pad = g.ks == 3 ? 1 : 0;
+  const int pad = (g.ks == 3 && !g.pad_asym) ? 1 : 0;
 
   float acc[4][4], accg[GEGLU ? 4 : 1][4];
 #pragma unroll
@@ -160,6 +160,8 @@ extern "C" int ldmb200_igemm_simt(const ldmb200_gemm_desc* d, void* stream) {
   LDM_CHECK_ARG(d && d->a && d->w && d->out, "igemm_simt: null pointer");
   LDM_CHECK_ARG(d->ksize == 1 || d->ksize == 3, "igemm_simt: ksize must be 1 or 3");
   LDM_CHECK_ARG(d->stride == 1 || d->stride == 2, "igemm_simt: stride must be 1 or 2");
+  LDM_CHECK_ARG(d->pad_mode == 0 || (d->pad_mode == 1 && d->ksize == 3 && d->stride == 2 && !d->upsample),
+                "igemm_simt: pad_mode 1 is the (0,1,0,1)-padded 3x3 stride-2 convolution");
   LDM_CHECK_ARG(d->batch > 0 && d->h_in > 0 && d->w_in > 0 && d->c1 > 0 && d->n > 0, "igemm_simt: empty problem");
   LDM_CHECK_ARG(!(d->geglu && (d->n % 2)), "igemm_simt: geglu needs even n");
   SimtGeom g;
@@ -170,6 +172,7 @@ extern "C" int ldmb200_igemm_simt(const ldmb200_gemm_desc* d, void* stream) {
   g.taps = g.ks * g.ks;
   g.stride = d->stride;
   g.upsample = d->upsample;
+  g.pad_asym = d->pad_mode == 1;
   g.h_in = d->h_in;
   g.w_in = d->w_in;
   g.h_eff = d->upsample ? 2 * d->h_in : d->h_in;

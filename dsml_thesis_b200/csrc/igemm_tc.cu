@@ -24,6 +24,7 @@ struct TcParams {
   int M;
   int tiles_m, tiles_n;
   int taps, ks, stride, is_conv;
+  int pad_asym;  // stride 2 over an input padded (0,1,0,1): input row = 2*oh + kh instead of 2*oh + kh - 1
   int c1_chunks, c2_chunks, ctot, c1;
   int c1_tail_k, c2_tail_k;  // MMAs (K = 16 each) of the last chunk of each channel range
   int hw_out, w_out, rows_per_sample;
@@ -237,9 +238,18 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
             dh = kh - 1;
             dw = kw - 1;
           } else {  // stride 2 on space-to-depth planes: row 2*oh+kh-1 -> (parity, index)
-            const int ph = (kh == 1) ? 0 : 1, pw = (kw == 1) ? 0 : 1;
-            dh = (kh == 0) ? -1 : 0;
-            dw = (kw == 0) ? -1 : 0;
+            int ph, pw;
+            if (p.pad_asym) {  // row 2*oh+kh: kh 0 / 2 are even rows (oh, oh + 1), kh 1 the odd row oh
+              ph = (kh == 1) ? 1 : 0;
+              pw = (kw == 1) ? 1 : 0;
+              dh = (kh == 2) ? 1 : 0;
+              dw = (kw == 2) ? 1 : 0;
+            } else {
+              ph = (kh == 1) ? 0 : 1;
+              pw = (kw == 1) ? 0 : 1;
+              dh = (kh == 0) ? -1 : 0;
+              dw = (kw == 0) ? -1 : 0;
+            }
             plane = ph * 2 + pw;
           }
         }
@@ -464,6 +474,9 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   p.taps = d->ksize * d->ksize;
   p.stride = d->stride;
   p.is_conv = d->ksize == 3;
+  LDM_CHECK_ARG(d->pad_mode == 0 || (d->pad_mode == 1 && d->ksize == 3 && d->stride == 2),
+                "igemm_tc: pad_mode 1 is the (0,1,0,1)-padded 3x3 stride-2 convolution");
+  p.pad_asym = d->pad_mode == 1;
   p.ctot = c1 + c2;
   p.hw_out = hw_out;
   p.w_out = w_out;

@@ -97,11 +97,14 @@ def install(verbose: bool = False):
         ae = importlib.import_module("ldm.models.autoencoder")
         vqi = ae.VQModelInterface
         if not getattr(vqi, "_ldmb200_wrapped", False):
-            from .vqdecode import accelerated_decode
+            from .vqdecode import accelerated_decode, accelerated_encode
             _saved[("ldm.models.autoencoder", "VQModelInterface.decode")] = vqi.decode
+            _saved[("ldm.models.autoencoder", "VQModelInterface.encode")] = vqi.encode
             vqi.decode = accelerated_decode(vqi.decode)
+            vqi.encode = accelerated_encode(vqi.encode)
             vqi._ldmb200_wrapped = True
             done.append("ldm.models.autoencoder.VQModelInterface.decode")
+            done.append("ldm.models.autoencoder.VQModelInterface.encode")
     except Exception:
         pass
     # audio conditioning encoder (talking_face only): one fused launch per frame when no gradient is needed

@@ -112,6 +112,56 @@ class Decoder(nn.Module):
         self.conv_out = nn.Conv2d(block_in, out_ch, 3, padding=1)
 
 
+class DownsampleConv(nn.Module):
+    """model.py:60-79 (with_conv=True): pad (0,1,0,1) then conv 3x3 stride 2 padding 0."""
+
+    def __init__(self, c: int):
+        super().__init__()
+        self.conv = nn.Conv2d(c, c, 3, stride=2, padding=0)
+
+
+class Encoder(nn.Module):
+    """Parameter layout of model.py:368-431."""
+
+    def __init__(self, *, ch, out_ch, ch_mult=(1, 2, 4, 8), num_res_blocks, attn_resolutions, dropout=0.0,
+                 resamp_with_conv=True, in_channels, resolution, z_channels, double_z=True, use_linear_attn=False,
+                 attn_type="vanilla", **ignore_kwargs):
+        super().__init__()
+        if use_linear_attn or attn_type != "vanilla" or not resamp_with_conv:
+            raise NotImplementedError("only the shipped Encoder variant (vanilla attention, conv downsampling) is built")
+        ch_mult = [int(v) for v in ch_mult]
+        attn_resolutions = [int(v) for v in attn_resolutions]
+        self.num_resolutions = len(ch_mult)
+        self.num_res_blocks = int(num_res_blocks)
+        self.in_channels = in_channels
+        self.out_channels = 2 * z_channels if double_z else z_channels
+        self.conv_in = nn.Conv2d(in_channels, ch, 3, padding=1)
+        curr_res = resolution
+        in_ch_mult = [1] + ch_mult
+        self.down = nn.ModuleList()
+        block_in = ch
+        for i_level in range(self.num_resolutions):
+            block, attn = nn.ModuleList(), nn.ModuleList()
+            block_in, block_out = ch * in_ch_mult[i_level], ch * ch_mult[i_level]
+            for _ in range(self.num_res_blocks):
+                block.append(ResnetBlock(block_in, block_out))
+                block_in = block_out
+                if curr_res in attn_resolutions:
+                    attn.append(AttnBlock(block_in))
+            down = nn.Module()
+            down.block, down.attn = block, attn
+            if i_level != self.num_resolutions - 1:
+                down.downsample = DownsampleConv(block_in)
+                curr_res //= 2
+            self.down.append(down)
+        self.mid = nn.Module()
+        self.mid.block_1 = ResnetBlock(block_in, block_in)
+        self.mid.attn_1 = AttnBlock(block_in)
+        self.mid.block_2 = ResnetBlock(block_in, block_in)
+        self.norm_out = _norm(block_in)
+        self.conv_out = nn.Conv2d(block_in, self.out_channels, 3, padding=1)
+
+
 class _Quantize(nn.Module):
     def __init__(self, n_e: int, e_dim: int):
         super().__init__()
@@ -256,8 +306,92 @@ class _VQPlan(_Plan):
         self.free(y)
 
 
+class _VQEncPlan(_VQPlan):
+    """Static launch list of one ``encode`` (Encoder + quant_conv) for a fixed (B, H, W, precision)."""
+
+    def __init__(self, model: "VQEncoder", B: int, H: int, W: int, mode: str):
+        self.model, self.B, self.H, self.W, self.L, self.mode = model, B, H, W, 0, mode
+        self.quantize = False
+        self.tc = mode in ("bf16", "f16")
+        self.act = {"bf16": _cabi.BF16, "f16": _cabi.F16, "fp32": F32}[mode]
+        dev = model._device()
+        self.lib = _cabi.load()
+        self.ops, self.meta, self.py_ops, self.keep = [], [], {}, []
+        self.arena = _Arena(dev)
+        self.pack = model._weight_pack(self.act) if self.tc else None
+        f32 = dict(dtype=torch.float32, device=dev)
+        enc = model.encoder
+        f = 2 ** (enc.num_resolutions - 1)
+        assert H % f == 0 and W % f == 0, (H, W, f)
+        self.x_in = torch.empty(B, enc.in_channels, H, W, **f32)
+        self.h_nchw = torch.empty(B, enc.out_channels, H // f, W // f, **f32)      # Encoder output (before quant_conv)
+        self.h_nhwc = torch.empty(B * (H // f) * (W // f), model.embed_dim, **f32)
+        self.out = torch.empty(B, model.embed_dim, H // f, W // f, **f32)
+        self.gn_ws = torch.empty(int(self.lib.ldmb200_groupnorm_ws_floats(B, H * W, 0)), **f32)
+        self.graph = None
+        self.runs = 0
+        self.pinned = set()
+        self._build()
+
+    def down2x(self, m: DownsampleConv, name: str, x: _Act, H: int, W: int) -> _Act:
+        """model.py:72-76: zero row below / zero column right, conv 3x3 stride 2 (no other padding)."""
+        if self.tc:
+            sp = self.new(x.rows, x.c, self.act)
+            self.emit("ldmb200_space_to_depth2", x.ptr, sp.ptr, self.act, self.B, H, W, x.c,
+                      bytes_=x.rows * x.c * (4 + 2), what=f"rows{x.rows} C{x.c}")
+            out = self.gemm(sp, name + ".conv", m.conv.weight, m.conv.bias, H, W, ksize=3, stride=2, want_stats=True)
+            self.keep[-1].pad_mode = 1
+            self.free(sp)
+            return out
+        out = self.gemm(x, "", m.conv.weight, m.conv.bias, H, W, ksize=3, stride=2)
+        self.keep[-1].pad_mode = 1
+        return out
+
+    def _build(self):
+        m, B, H, W = self.model, self.B, self.H, self.W
+        enc = m.encoder
+        cin = enc.in_channels
+        cpad = _tc_cpad(cin) if self.tc else cin
+        h = self.new(B * H * W, cpad, self.act)
+        self.emit("ldmb200_nchw_to_nhwc", self.x_in.data_ptr(), h.ptr, B, cin, H * W, cpad, self.act,
+                  bytes_=B * H * W * cin * 6, what=f"pixels{B * H * W}")
+        x = self.gemm(h, "encoder.conv_in", enc.conv_in.weight, enc.conv_in.bias, H, W, ksize=3, want_stats=True)
+        self.free(h)
+
+        def step(fn):
+            nonlocal x
+            new = fn()
+            self.free(x)
+            x = new
+
+        for i_level in range(enc.num_resolutions):
+            lv = enc.down[i_level]
+            for j in range(enc.num_res_blocks):
+                step(lambda: self.resnet(lv.block[j], f"encoder.down.{i_level}.block.{j}", x, H, W))
+                if len(lv.attn) > 0:
+                    step(lambda: self.attn(lv.attn[j], f"encoder.down.{i_level}.attn.{j}", x, H, W))
+            if i_level != enc.num_resolutions - 1:
+                step(lambda: self.down2x(lv.downsample, f"encoder.down.{i_level}.downsample", x, H, W))
+                H, W = H // 2, W // 2
+        step(lambda: self.resnet(enc.mid.block_1, "encoder.mid.block_1", x, H, W))
+        step(lambda: self.attn(enc.mid.attn_1, "encoder.mid.attn_1", x, H, W))
+        step(lambda: self.resnet(enc.mid.block_2, "encoder.mid.block_2", x, H, W))
+        y, _ = self.groupnorm(x, None, enc.norm_out, H * W, 1, False)
+        self.free(x)
+        self.gemm(y, "encoder.conv_out", enc.conv_out.weight, enc.conv_out.bias, H, W, ksize=3,
+                  out_nchw_ptr=self.h_nchw.data_ptr())
+        self.free(y)
+        # quant_conv (autoencoder.py:42,271): 1x1 over z_channels -> embed_dim, fp32, then back to NCHW
+        qc = m.quant_conv
+        self.emit("ldmb200_vq_lookup_postconv", self.h_nchw.data_ptr(), None, 0, enc.out_channels, qc.weight.data_ptr(),
+                  qc.bias.data_ptr(), m.embed_dim, self.h_nhwc.data_ptr(), F32, m.embed_dim, None, None, B, H * W,
+                  what=f"quant_conv pixels{B * H * W}")
+        self.emit("ldmb200_nhwc_to_nchw", self.h_nhwc.data_ptr(), m.embed_dim, self.out.data_ptr(), B, m.embed_dim, H * W,
+                  what=f"pixels{B * H * W}")
+
+
 # ----------------------------------------------------------------------------------------------
-# the drop-in module
+# the drop-in modules
 # ----------------------------------------------------------------------------------------------
 
 class VQDecoder(nn.Module):
@@ -329,6 +463,103 @@ class VQDecoder(nn.Module):
 
     def forward(self, h, force_not_quantize: bool = False):
         return self.decode(h, force_not_quantize)
+
+
+class VQEncoder(nn.Module):
+    """Encode half of ``VQModelInterface`` (autoencoder.py:269-272): ``quant_conv(encoder(x))`` — no quantisation, exactly
+    like the reference's ``encode``.  Same ctor as ``VQDecoder``; parameters ``encoder.*`` and ``quant_conv.*``."""
+
+    def __init__(self, ddconfig, embed_dim, n_embed=None, lossconfig=None, **ignored):
+        super().__init__()
+        dd = dict(ddconfig)
+        self.embed_dim = int(embed_dim)
+        self.encoder = Encoder(**dd)
+        self.quant_conv = nn.Conv2d(self.encoder.out_channels, self.embed_dim, 1)
+        self.precision = os.environ.get("LDMB200_PRECISION", "f16")
+        self.use_cuda_graph = os.environ.get("LDMB200_CUDA_GRAPH", "1") != "0"
+        self._plans: Dict[tuple, _VQEncPlan] = {}
+        self._packs: Dict[int, _WeightPack] = {}
+        for p in self.parameters():
+            p.requires_grad_(False)
+
+    def _device(self):
+        return self.quant_conv.weight.device
+
+    def _apply(self, fn, *a, **k):
+        out = super()._apply(fn, *a, **k)
+        self._plans, self._packs = {}, {}
+        return out
+
+    def _weight_pack(self, dtype: int) -> _WeightPack:
+        if dtype not in self._packs:
+            self._packs[dtype] = _WeightPack(self, dtype)
+        return self._packs[dtype]
+
+    @torch.no_grad()
+    def encode(self, x: torch.Tensor) -> torch.Tensor:
+        """x [B, in_channels, H, W] image in [-1, 1] -> latent [B, embed_dim, H/f, W/f] (fp32, same device)."""
+        if not x.is_cuda:
+            raise _cabi.Ldmb200Error("dsml_thesis_b200.VQEncoder runs on a CUDA device only (no CPU fallback)")
+        mode = self.precision
+        if mode not in ("f16", "bf16", "fp32"):
+            raise ValueError(f"precision must be 'f16', 'bf16' or 'fp32', got {mode!r}")
+        B, Cin, H, W = x.shape
+        assert Cin == self.encoder.in_channels, (Cin, self.encoder.in_channels)
+        with torch.cuda.device(x.device):
+            key = (B, H, W, mode)
+            plan = self._plans.get(key)
+            if plan is None:
+                if len(self._plans) >= 4:
+                    self._plans.pop(next(iter(self._plans)))
+                plan = self._plans[key] = _VQEncPlan(self, B, H, W, mode)
+            plan.x_in.copy_(x)
+            stream = torch.cuda.current_stream()
+            if plan.pack is not None:
+                plan.pack.run(stream.cuda_stream)
+            if self.use_cuda_graph and plan.runs >= 1:
+                if plan.graph is None:
+                    gr = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(gr):
+                        plan.run(torch.cuda.current_stream().cuda_stream)
+                    plan.graph = gr
+                plan.graph.replay()
+            else:
+                plan.run(stream.cuda_stream)
+            return plan.out.clone()
+
+    def forward(self, x):
+        return self.encode(x)
+
+
+def _build_encoder_from(first_stage_model) -> VQEncoder:
+    enc = first_stage_model.encoder
+    nres = enc.num_resolutions
+    ch = enc.conv_in.out_channels
+    ch_mult = [enc.down[i].block[0].conv1.out_channels // ch for i in range(nres)]
+    resolution = getattr(enc, "resolution", 2 ** (nres - 1))
+    attn_res = [resolution // 2 ** i for i in range(nres) if len(enc.down[i].attn) > 0]
+    zc = enc.conv_out.out_channels
+    dd = dict(ch=ch, out_ch=3, ch_mult=ch_mult, num_res_blocks=enc.num_res_blocks, attn_resolutions=attn_res,
+              in_channels=enc.conv_in.in_channels, resolution=resolution, z_channels=zc, double_z=False)
+    fast = VQEncoder(dd, first_stage_model.quant_conv.out_channels)
+    missing, _ = fast.load_state_dict(first_stage_model.state_dict(), strict=False)
+    if missing:
+        raise _cabi.Ldmb200Error(f"first stage state dict lacks {missing[:4]}...")
+    return fast.to(first_stage_model.quant_conv.weight.device)
+
+
+def accelerated_encode(reference_encode):
+    """Class-level wrapper for ``VQModelInterface.encode`` used by ``install()`` (same rules as ``accelerated_decode``)."""
+    def encode(self, x):
+        if not x.is_cuda or (torch.is_grad_enabled() and x.requires_grad):
+            return reference_encode(self, x)
+        fast = self.__dict__.get("_ldmb200_encoder")
+        if fast is None or fast._device() != x.device:
+            fast = _build_encoder_from(self)
+            self.__dict__["_ldmb200_encoder"] = fast
+        return fast.encode(x)
+    encode._ldmb200_reference = reference_encode
+    return encode
 
 
 def _build_from(first_stage_model) -> VQDecoder:

@@ -167,6 +167,10 @@ typedef struct ldmb200_gemm_desc {
   float* colstats;       /* TC path, optional: [M/32][n][2] per 32-row block {sum, sum of squares} of every stored
                           * column — the GroupNorm statistics of the tensor being written (util.py:214-216), consumed
                           * by ldmb200_groupnorm_fused so the normalisation never re-reads its input for statistics */
+  int32_t pad_mode;      /* 0: symmetric padding ksize/2.  1: 3x3 stride 2 over an input padded (0,1,0,1) - one zero
+                          * row below and one zero column right, none above / left - the Downsample of the first-stage
+                          * Encoder (ldm/modules/diffusionmodules/model.py:72-76)                                    */
+  int32_t pad_;
 } ldmb200_gemm_desc;
 
 /* fp32-exact SIMT path (precision mode "fp32": per-step eps rel-L2 <= 1e-4 vs the fp32 reference). */

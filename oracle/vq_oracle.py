@@ -198,3 +198,118 @@ def vq_decode(sd, cfg: dict, h: Tensor, force_not_quantize: bool = False):
         quant, idx = vector_quantize(sd, h)
     quant = F.conv2d(quant, sd["post_quant_conv.weight"], sd["post_quant_conv.bias"])
     return decoder_forward(sd, cfg, quant), idx
+
+
+# ----------------------------------------------------------------------------------------
+# encode half (encode_first_stage per frame) — VQModelInterface.encode, autoencoder.py:269-272
+# ----------------------------------------------------------------------------------------
+
+def encoder_structure(dd: dict):
+    """Walks ``Encoder.__init__`` (model.py:383-412): per-level list of (in_ch, out_ch, has_attn), which levels
+    downsample, and the channel count at the lowest level."""
+    ch, ch_mult, nrb = dd["ch"], list(dd["ch_mult"]), dd["num_res_blocks"]
+    in_ch_mult = [1] + ch_mult
+    curr_res = dd["resolution"]
+    levels = []
+    block_in = ch
+    for i_level in range(len(ch_mult)):
+        block_in, block_out = ch * in_ch_mult[i_level], ch * ch_mult[i_level]
+        blocks = []
+        for _ in range(nrb):
+            blocks.append((block_in, block_out, curr_res in dd["attn_resolutions"]))
+            block_in = block_out
+        down = i_level != len(ch_mult) - 1
+        levels.append(dict(blocks=blocks, downsample=down, ch=block_in))
+        if down:
+            curr_res //= 2
+    return levels, block_in
+
+
+def vq_encoder_param_shapes(cfg: dict) -> Dict[str, Tuple[int, ...]]:
+    """Names and shapes of the ``VQModelInterface`` state-dict entries the encode path reads."""
+    dd = cfg["ddconfig"]
+    sh: Dict[str, Tuple[int, ...]] = {}
+
+    def conv(p, cin, cout, k):
+        sh[p + ".weight"] = (cout, cin, k, k)
+        sh[p + ".bias"] = (cout,)
+
+    def norm(p, c):
+        sh[p + ".weight"] = (c,)
+        sh[p + ".bias"] = (c,)
+
+    def resnet(p, cin, cout):
+        norm(p + ".norm1", cin)
+        conv(p + ".conv1", cin, cout, 3)
+        norm(p + ".norm2", cout)
+        conv(p + ".conv2", cout, cout, 3)
+        if cin != cout:
+            conv(p + ".nin_shortcut", cin, cout, 1)
+
+    def attn(p, c):
+        norm(p + ".norm", c)
+        for n in ("q", "k", "v", "proj_out"):
+            conv(f"{p}.{n}", c, c, 1)
+
+    levels, last = encoder_structure(dd)
+    conv("encoder.conv_in", dd["in_channels"], dd["ch"], 3)
+    for i_level, lv in enumerate(levels):
+        for j, (cin, cout, has_attn) in enumerate(lv["blocks"]):
+            resnet(f"encoder.down.{i_level}.block.{j}", cin, cout)
+            if has_attn:
+                attn(f"encoder.down.{i_level}.attn.{j}", cout)
+        if lv["downsample"]:
+            conv(f"encoder.down.{i_level}.downsample.conv", lv["ch"], lv["ch"], 3)
+    resnet("encoder.mid.block_1", last, last)
+    attn("encoder.mid.attn_1", last)
+    resnet("encoder.mid.block_2", last, last)
+    norm("encoder.norm_out", last)
+    zc = 2 * dd["z_channels"] if dd.get("double_z", True) else dd["z_channels"]
+    conv("encoder.conv_out", last, zc, 3)
+    conv("quant_conv", zc, cfg["embed_dim"], 1)
+    return sh
+
+
+def init_vq_encoder_state_dict(cfg: dict, seed: int = 0) -> Dict[str, Tensor]:
+    g = torch.Generator().manual_seed(seed + 1000)
+    sd: Dict[str, Tensor] = {}
+    for name, shape in sorted(vq_encoder_param_shapes(cfg).items()):
+        if len(shape) >= 2:
+            fan_in = int(np.prod(shape[1:]))
+            sd[name] = ((torch.rand(shape, generator=g) * 2 - 1) * math.sqrt(3.0 / fan_in)).contiguous()
+        elif "norm" in name:
+            sd[name] = (1.0 + 0.1 * torch.randn(shape, generator=g)) if name.endswith("weight") \
+                else 0.1 * torch.randn(shape, generator=g)
+        else:
+            sd[name] = 0.05 * torch.randn(shape, generator=g)
+    return sd
+
+
+def downsample(sd, p: str, x: Tensor) -> Tensor:
+    """model.py:72-76: pad (0,1,0,1) with zeros, conv 3x3 stride 2 padding 0."""
+    x = F.pad(x, (0, 1, 0, 1), mode="constant", value=0)
+    return F.conv2d(x, sd[p + ".conv.weight"], sd[p + ".conv.bias"], stride=2, padding=0)
+
+
+def encoder_forward(sd, cfg: dict, x: Tensor) -> Tensor:
+    """model.py:433-459."""
+    levels, _ = encoder_structure(cfg["ddconfig"])
+    h = F.conv2d(x, sd["encoder.conv_in.weight"], sd["encoder.conv_in.bias"], padding=1)
+    for i_level, lv in enumerate(levels):
+        for j, (_, _, has_attn) in enumerate(lv["blocks"]):
+            h = resnet_block(sd, f"encoder.down.{i_level}.block.{j}", h)
+            if has_attn:
+                h = attn_block(sd, f"encoder.down.{i_level}.attn.{j}", h)
+        if lv["downsample"]:
+            h = downsample(sd, f"encoder.down.{i_level}.downsample", h)
+    h = resnet_block(sd, "encoder.mid.block_1", h)
+    h = attn_block(sd, "encoder.mid.attn_1", h)
+    h = resnet_block(sd, "encoder.mid.block_2", h)
+    h = swish(normalize(sd, "encoder.norm_out", h))
+    return F.conv2d(h, sd["encoder.conv_out.weight"], sd["encoder.conv_out.bias"], padding=1)
+
+
+@torch.no_grad()
+def vq_encode(sd, cfg: dict, x: Tensor) -> Tensor:
+    """autoencoder.py:269-272: quant_conv(encoder(x)), no quantisation."""
+    return F.conv2d(encoder_forward(sd, cfg, x), sd["quant_conv.weight"], sd["quant_conv.bias"])

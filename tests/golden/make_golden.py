@@ -327,13 +327,50 @@ def cond_goldens():
     return out
 
 
+def vq_encode_goldens():
+    """First-stage encode (encode_first_stage of the masked frame) through the REAL reference ``Encoder`` +
+    ``quant_conv`` assembled as ``VQModel.__init__`` does (autoencoder.py:36,42), synthetic weights loaded strict=True."""
+    import contextlib
+    import io
+    from oracle import vq_oracle as V
+    R.import_reference("face_reenactment")
+    from ldm.modules.diffusionmodules.model import Encoder
+
+    class FirstStage(torch.nn.Module):
+        def __init__(self, cfg):
+            super().__init__()
+            dd = cfg["ddconfig"]
+            with contextlib.redirect_stdout(io.StringIO()):
+                self.encoder = Encoder(**dd)
+            self.quant_conv = torch.nn.Conv2d(dd["z_channels"], cfg["embed_dim"], 1)
+
+        def encode(self, x):                                # autoencoder.py:269-272
+            return self.quant_conv(self.encoder(x))
+
+    out = {}
+    for name, cfg, B, hw, seed in [("tiny_32", V.VQ_TINY, 2, 32, 15), ("tiny_64", V.VQ_TINY, 1, 64, 16),
+                                   ("f4_64", V.VQ_F4, 1, 64, 17)]:
+        sd = V.init_vq_encoder_state_dict(cfg, 0)
+        m = FirstStage(cfg)
+        m.load_state_dict(sd, strict=True)
+        m.eval()
+        g = torch.Generator().manual_seed(seed)
+        x = torch.randn(B, 3, hw, hw, generator=g).clamp_(-1, 1)
+        with torch.no_grad():
+            z = m.encode(x)
+        out[f"{name}/x"] = x.numpy()
+        out[f"{name}/z"] = z.numpy()
+    return out
+
+
 def main():
     torch.set_num_threads(max(1, os.cpu_count() or 1))
     only = sys.argv[1:]
     for fn, gen in (("unet.npz", unet_goldens), ("schedule.npz", schedule_goldens),
                     ("trajectory.npz", trajectory_goldens), ("unet64.npz", unet64_goldens),
                     ("manipulation.npz", manipulation_goldens), ("train.npz", train_goldens),
-                    ("unet128.npz", unet128_goldens), ("vqdecode.npz", vq_goldens), ("cond.npz", cond_goldens)):
+                    ("unet128.npz", unet128_goldens), ("vqdecode.npz", vq_goldens), ("cond.npz", cond_goldens),
+                    ("vqencode.npz", vq_encode_goldens)):
         if only and fn not in only:
             continue
         data = gen()

@@ -151,6 +151,8 @@ def test_vq_decoder_parameter_inventory_matches_the_reference_names():
         mine = {k: tuple(v.shape) for k, v in m.state_dict().items()}
         assert mine == V.vq_param_shapes(cfg)
         assert not any(p.requires_grad for p in m.parameters())
+        enc = P.VQEncoder(**cfg)
+        assert {k: tuple(v.shape) for k, v in enc.state_dict().items()} == V.vq_encoder_param_shapes(cfg)
     # a full first-stage checkpoint (encoder / quant_conv / loss keys too) loads with strict=False and nothing missing
     sd = dict(V.init_vq_state_dict(V.VQ_TINY, 0))
     sd["encoder.conv_in.weight"] = torch.zeros(32, 3, 3, 3)
@@ -184,16 +186,22 @@ def test_install_wraps_first_stage_decode(monkeypatch):
             calls.append(force_not_quantize)
             return h
 
+        def encode(self, x):
+            calls.append("encode")
+            return x
+
     mod = types.ModuleType("ldm.models.autoencoder")
     mod.VQModelInterface = VQModelInterface
     monkeypatch.setitem(sys.modules, "ldm.models.autoencoder", mod)
-    ref_decode = VQModelInterface.decode
+    ref_decode, ref_encode = VQModelInterface.decode, VQModelInterface.encode
     try:
         done = P.install()
         assert "ldm.models.autoencoder.VQModelInterface.decode" in done
         assert VQModelInterface.decode is not ref_decode
         x = torch.zeros(1, 3, 4, 4)
         assert VQModelInterface().decode(x, True) is x and calls == [True]     # CPU tensor: the reference's own method
+        assert "ldm.models.autoencoder.VQModelInterface.encode" in done
+        assert VQModelInterface().encode(x) is x and calls == [True, "encode"]
     finally:
         P.uninstall()
-    assert VQModelInterface.decode is ref_decode
+    assert VQModelInterface.decode is ref_decode and VQModelInterface.encode is ref_encode

@@ -256,3 +256,15 @@ def test_conv1d_temporal_attention_matches_reference_golden(name, cfg):
     y = CO.conv1d_temporal_attention(sd, cfg, torch.from_numpy(g[f"{name}/x"]))
     assert y.shape == g[f"{name}/y"].shape
     assert O.rel_l2(y, torch.from_numpy(g[f"{name}/y"])) <= 1e-6
+
+
+@pytest.mark.parametrize("name,cfg_name", [("tiny_32", "VQ_TINY"), ("tiny_64", "VQ_TINY"), ("f4_64", "VQ_F4")])
+def test_vq_encode_matches_reference_golden(name, cfg_name):
+    """oracle/vq_oracle.py: vq_encode vs the real reference Encoder + quant_conv (make_golden.py: vq_encode_goldens)."""
+    import os
+    from conftest import GOLDEN
+    from oracle import vq_oracle as V
+    g = np.load(os.path.join(GOLDEN, "vqencode.npz"))
+    cfg = getattr(V, cfg_name)
+    z = V.vq_encode(V.init_vq_encoder_state_dict(cfg, 0), cfg, torch.from_numpy(g[f"{name}/x"]))
+    assert O.rel_l2(z, torch.from_numpy(g[f"{name}/z"])) <= 1e-6

@@ -199,3 +199,65 @@ def test_install_wrapper_decodes_cuda_latents_through_the_kernels():
     out = fs.decode(z.cuda(), force_not_quantize=True)
     assert O.rel_l2(out.cpu(), ref) <= TOL[fs._ldmb200_decoder.precision]
     assert fs.decode(z.cuda()).shape == ref.shape and len(fs._ldmb200_decoder._plans) == 2
+
+
+# ------------------------------------------------------------------------------------------ encode half (8f n4)
+@pytest.fixture(scope="module")
+def golden_vqenc():
+    return np.load(os.path.join(GOLDEN, "vqencode.npz"))
+
+
+def _encoder(cfg):
+    sd = V.init_vq_encoder_state_dict(cfg, 0)
+    m = P.VQEncoder(**cfg)
+    m.load_state_dict(sd, strict=True)
+    return sd, m.cuda().eval()
+
+
+@pytest.mark.parametrize("name,cfg", [("tiny_32", V.VQ_TINY), ("tiny_64", V.VQ_TINY), ("f4_64", V.VQ_F4)])
+@pytest.mark.parametrize("precision", ["fp32", "f16", "bf16"])
+def test_encode_vs_reference_golden(golden_vqenc, name, cfg, precision):
+    """VQModelInterface.encode = quant_conv(Encoder(x)) (autoencoder.py:269-272) incl. the (0,1,0,1)-padded stride-2
+    Downsample (model.py:72-76), against outputs of the real reference modules."""
+    _, m = _encoder(cfg)
+    m.precision = precision
+    x = torch.from_numpy(golden_vqenc[f"{name}/x"]).cuda()
+    for rep in range(3):    # eager, graph capture, replay
+        z = m.encode(x)
+        err = O.rel_l2(z.cpu(), torch.from_numpy(golden_vqenc[f"{name}/z"]))
+        assert err <= TOL[precision], (name, precision, rep, err)
+    record_parity(f"vqencode/{name}/{precision}/latent_rel_l2", err)
+    assert z.dtype == torch.float32 and z.shape == golden_vqenc[f"{name}/z"].shape
+
+
+@pytest.mark.parametrize("hw", [128, 256])
+def test_encode_full_size_vs_oracle(hw):
+    """The shipped first stage on 128x128 (shipped) and 256x256 (BASELINE's 64x64 latents) images."""
+    sd, m = _encoder(V.VQ_F4)
+    x = torch.randn(1, 3, hw, hw, generator=torch.Generator().manual_seed(hw)).clamp_(-1, 1)
+    ref = V.vq_encode(sd, V.VQ_F4, x)
+    for precision in ("fp32", "f16"):
+        m.precision = precision
+        err = O.rel_l2(m.encode(x.cuda()).cpu(), ref)
+        record_parity(f"vqencode/f4_{hw}/{precision}/latent_rel_l2", err)
+        assert err <= TOL[precision], (hw, precision, err)
+
+
+def test_install_wrapper_encodes_cuda_images_through_the_kernels():
+    from dsml_thesis_b200.vqdecode import accelerated_encode
+    sd, donor = _encoder(V.VQ_TINY)
+
+    class VQModelInterface(torch.nn.Module):          # attribute layout of the reference VQModel (autoencoder.py:36-42)
+        def __init__(self):
+            super().__init__()
+            self.encoder, self.quant_conv = donor.encoder, donor.quant_conv
+            self.encoder.resolution = 32
+
+        def encode(self, x):
+            raise AssertionError("the reference encode must have been replaced for CUDA images")
+
+    VQModelInterface.encode = accelerated_encode(VQModelInterface.encode)
+    fs = VQModelInterface().cuda()
+    x = torch.randn(2, 3, 32, 32, generator=torch.Generator().manual_seed(8)).clamp_(-1, 1)
+    z = fs.encode(x.cuda())
+    assert O.rel_l2(z.cpu(), V.vq_encode(sd, V.VQ_TINY, x)) <= TOL[fs._ldmb200_encoder.precision]

@@ -352,6 +352,24 @@ VQ_F4 = dict(embed_dim=3, n_embed=16384,
                            ch_mult=[1, 2, 4], num_res_blocks=2, attn_resolutions=[32], dropout=0.0))
 
 
+def init_synthetic(module, seed=0, gain=1.0):
+    """Non-zero synthetic weights for the first-stage / conditioning modules (sorted-name order, one generator):
+    matrices gain*sqrt(3)*U(-1,1)/sqrt(fan_in), N(0,1) codebook, norm gains 1+0.1N, biases 0.05N."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, prm in sorted(module.named_parameters()):
+            if name == "quantize.embedding.weight":
+                prm.copy_(torch.randn(prm.shape, generator=g))
+            elif prm.dim() >= 2:
+                prm.copy_((torch.rand(prm.shape, generator=g) * 2 - 1) * gain * (3.0 / prm[0].numel()) ** 0.5)
+            elif "norm" in name and name.endswith("weight"):
+                prm.copy_(1.0 + 0.1 * torch.randn(prm.shape, generator=g))
+            else:
+                prm.copy_(0.05 * torch.randn(prm.shape, generator=g))
+    return module
+
+
 def decode_main(args):
     """--workload decode: VQModelInterface.decode of a batch of latents (nearest-code lookup,
     post_quant_conv, Decoder) - per-frame work of the sampling scripts after the DDIM loop."""
@@ -394,19 +412,7 @@ def decode_main(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    m = P.VQDecoder(**VQ_F4)
-    g = torch.Generator().manual_seed(0)
-    with torch.no_grad():
-        for name, prm in sorted(m.named_parameters()):
-            if name == "quantize.embedding.weight":
-                prm.copy_(torch.randn(prm.shape, generator=g))
-            elif prm.dim() >= 2:
-                prm.copy_((torch.rand(prm.shape, generator=g) * 2 - 1) * (3.0 / prm[0].numel()) ** 0.5)
-            elif "norm" in name and name.endswith("weight"):
-                prm.copy_(1.0 + 0.1 * torch.randn(prm.shape, generator=g))
-            else:
-                prm.copy_(0.05 * torch.randn(prm.shape, generator=g))
-    m = m.to(dev).eval()
+    m = init_synthetic(P.VQDecoder(**VQ_F4), 0).to(dev).eval()
     m.precision = args.precision
     m.use_cuda_graph = bool(args.graph)
     g = torch.Generator().manual_seed(3000 + rank)
@@ -515,6 +521,9 @@ def main():
                     help="sample = BASELINE config 2 (the headline metric); train = config 4 (DDPM training step); "
                          "c3 = config 3 (talking_face UNet, 200-step progressive DDIM, autoregressive frames)")
     ap.add_argument("--frames", type=int, default=2, help="c3: autoregressive frames per step")
+    ap.add_argument("--first-stage", type=int, default=0,
+                    help="c3: 1 = also run the per-frame work around the DDIM loop on the GPU path (audio conditioning "
+                         "encoder, first-stage encode of the masked frame, first-stage decode of the result)")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
@@ -547,6 +556,11 @@ def main():
                     f"{args.hw}x{args.hw} latents, {args.batch} streams/GPU, {args.frames} autoregressive frames x "
                     f"{args.ddim}-step DDIM eta=0 (previous output -> reference channels)")
         metric = f"DDIM frames/s (talking_face, {args.hw}x{args.hw}x3 latent, {args.ddim} steps, progressive)"
+        if args.first_stage:
+            workload += ("; per frame also Conv1DTemporalAttention over a 17x768 audio window, VQ-f4 encode of the "
+                         f"{4 * args.hw}x{4 * args.hw} masked frame and VQ-f4 decode of the generated latent")
+            metric = (f"talking-face frames/s ({4 * args.hw}x{4 * args.hw} image in -> image out, {args.ddim}-step DDIM, "
+                      "audio conditioning + first-stage encode/decode per frame)")
 
     if args.impl == "reference":
         if rank != 0:
@@ -592,15 +606,35 @@ def main():
     x_dev, c_dev = x_host.to(dev), c_host.to(dev)
     c34_dev = c34_host.to(dev) if c3 else None
 
-    def progressive(x, c12, c34):
-        """progressive_sampling_difftalk.py:286-317: frame f's output becomes the reference-frame latent of f+1."""
+    fs = None
+    if c3 and args.first_stage:
+        aud = init_synthetic(P.Conv1DTemporalAttention(seq_len=17, subspace_dim=768), 1, gain=1.6).to(dev).eval()
+        enc = init_synthetic(P.VQEncoder(**VQ_F4), 2).to(dev).eval()
+        dec = init_synthetic(P.VQDecoder(**VQ_F4), 0).to(dev).eval()
+        enc.precision = dec.precision = args.precision
+        fs_host = dict(audio=torch.randn(args.frames, B, 17, 768, generator=g).pin_memory(),
+                       masked=torch.randn(args.frames, B, 3, 4 * HW, 4 * HW, generator=g).clamp_(-1, 1).pin_memory())
+        fs = {k: v.to(dev) for k, v in fs_host.items()}
+        out_host = torch.empty(B, 3, 4 * HW, 4 * HW).pin_memory()
+
+    def progressive(x, c12, c34, fsd=None):
+        """progressive_sampling_difftalk.py:286-317: frame f's output becomes the reference-frame latent of f+1.
+        With --first-stage: c2 = cond_stage_model_2(audio window), c3 = encode_first_stage(masked frame) per frame
+        (286-296) and decode_first_stage of the result."""
         c34 = c34.clone()
         out = None
-        for _f in range(args.frames):
-            cond = {P.DDIMSampler2Cond.CROSS_KEY: c12, P.DDIMSampler2Cond.CONCAT_KEY: c34}
+        for f in range(args.frames):
+            c12f = c12
+            if fsd is not None:
+                c2 = aud(fsd["audio"][f])                                    # (B, 1, 768)
+                c12f = torch.cat([c12[:, :, :256], c2], dim=2)               # class embedding || audio -> (B, 1, 1024)
+                c34[:, :3] = enc.encode(fsd["masked"][f])
+            cond = {P.DDIMSampler2Cond.CROSS_KEY: c12f, P.DDIMSampler2Cond.CONCAT_KEY: c34}
             out, _ = smp.sample(T, batch_size=B, shape=[3, HW, HW], conditioning=cond, eta=0.0, x_T=x, verbose=False)
             c34[:, 3:] = out
-        return out
+            if fsd is not None:
+                img = dec.decode(out)
+        return img if fsd is not None else out
 
     launches = {"n": 0}
     step_fn = S.ddim_step
@@ -612,7 +646,7 @@ def main():
 
     def sample_resident():
         if c3:
-            out = progressive(x_dev, c_dev, c34_dev)   # streams stay on their rank: no collective
+            out = progressive(x_dev, c_dev, c34_dev, fs)   # streams stay on their rank: no collective
             return out
         out, _ = smp.sample(T, batch_size=B, shape=[3, HW, HW], conditioning=c_dev, eta=0.0, x_T=x_dev, verbose=False)
         if world > 1:
@@ -623,7 +657,8 @@ def main():
         x = x_host.to(dev, non_blocking=True)
         c = c_host.to(dev, non_blocking=True)
         if c3:
-            out = progressive(x, c, c34_host.to(dev, non_blocking=True))
+            out = progressive(x, c, c34_host.to(dev, non_blocking=True),
+                              {k: v.to(dev, non_blocking=True) for k, v in fs_host.items()} if fs is not None else None)
         else:
             out, _ = smp.sample(T, batch_size=B, shape=[3, HW, HW], conditioning=c, eta=0.0, x_T=x, verbose=False)
         out_host.copy_(out, non_blocking=True)
@@ -723,9 +758,12 @@ def main():
         "unet_tflops_algorithmic": (value * T * ref_gflop / 1e3) if ref_gflop else None,
         "tensor_frac_of_measured_peak": (value / world * T * ref_gflop / 1e3 / peak_tf) if ref_gflop else None,
         "e2e": {"value": e2e_value, "unit": "samples/s", "ms_per_step": ms_e2e / args.steps,
-                "h2d_bytes_per_step": x_host.numel() * 4 + c_host.numel() * 4 + (c34_host.numel() * 4 if c3 else 0),
+                "h2d_bytes_per_step": x_host.numel() * 4 + c_host.numel() * 4 + (c34_host.numel() * 4 if c3 else 0)
+                + (sum(v.numel() * 4 for v in fs_host.values()) if fs is not None else 0),
                 "d2h_bytes_per_step": out_host.numel() * 4},
-        "gpu_launches": n_launch,
+        "gpu_launches": n_launch + (args.steps * args.frames * (len(next(iter(enc._plans.values())).ops)
+                                                                + len(next(iter(dec._plans.values())).ops) + 3)
+                                    if fs is not None else 0),
         "clocks": clk,
         "roofline": {"kernel": dom, "bound": "tensor", "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
                      "frac": achieved / peak_tf, "traffic": traffic, "traffic_source": traffic_src,

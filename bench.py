@@ -510,6 +510,18 @@ def decode_main(args):
         "kernel_breakdown_ms_per_step": {k: round(v[0], 3) for k, v in sorted(fam.items(), key=lambda kv: -kv[1][0])},
         "step_ms_sum_of_kernels": sum(v[0] for v in fam.values()),
     }
+    if not args.no_cpu_baseline:
+        from oracle import vq_oracle as V
+        torch.set_num_threads(os.cpu_count() or 1)
+        sd = V.init_vq_state_dict(V.VQ_F4, 0)
+        zc = torch.randn(1, 3, 32, 32)
+        V.vq_decode(sd, V.VQ_F4, zc)
+        t0 = time.perf_counter()
+        V.vq_decode(sd, V.VQ_F4, zc)
+        per = (time.perf_counter() - t0) * (HW / 32) ** 2
+        line["cpu_baseline"] = {"value": 1.0 / per, "unit": "images/s", "cores": os.cpu_count(), "kind": "port",
+                                "sample": f"oracle port, B=1, 32x32 latent, 1 decode timed after 1 warm-up, scaled by pixel "
+                                          f"count to {HW}x{HW} (attention scales faster: this favours the CPU)"}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -37,17 +37,25 @@ constexpr int VQ_MAX_E = 8;       // embed_dim / z_channels bound (3 in every sh
 constexpr int VQ_CHUNK = 1024;    // codes staged in shared memory per pass
 constexpr int VQ_THREADS = 256;
 
-// One thread per latent pixel.  Distances follow quantize.py:292-294 term by term in fp32:
-//   d = (sum z^2 + sum e^2) - 2 * (z . e), argmin = first index of the minimum (torch.argmin),
+// 32 latent pixels per CTA (one per lane); the CTA's 8 warps each scan one eighth of every codebook chunk staged in
+// shared memory and the per-warp winners are merged (smaller distance, then smaller index = torch.argmin's first
+// minimum).  Distances follow quantize.py:292-294 term by term in fp32:
+//   d = (sum z^2 + sum e^2) - 2 * (z . e)
 // z_q = z + (e - z) (the straight-through form of quantize.py:309, kept because it is not exactly e in fp32).
-template <typename T>
+// EC = 3 is the shipped embed_dim: codes are staged as {e0, e1, e2, |e|^2} quads (one 16-byte shared-memory load and
+// seven fp32 instructions per pixel-code pair); EC = 0 is the generic embed_dim <= 8 path.
+template <typename T, int EC>
 __global__ void __launch_bounds__(VQ_THREADS)
 vq_lookup_postconv_kernel(const float* __restrict__ z, const float* __restrict__ codebook, int n_e, int E,
                           const float* __restrict__ w, const float* __restrict__ bias, int zc, T* __restrict__ y,
                           int c_pad, int64_t* __restrict__ indices, float* __restrict__ zq_out, int batch, int hw) {
-  __shared__ float s_code[VQ_CHUNK * VQ_MAX_E];
+  __shared__ __align__(16) float s_code[VQ_CHUNK * VQ_MAX_E];
   __shared__ float s_ee[VQ_CHUNK];
-  const int64_t pix = (int64_t)blockIdx.x * VQ_THREADS + threadIdx.x;
+  __shared__ float s_best[VQ_THREADS];
+  __shared__ int s_besti[VQ_THREADS];
+  constexpr int NW = VQ_THREADS / 32;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t pix = (int64_t)blockIdx.x * 32 + lane;
   const int64_t total = (int64_t)batch * hw;
   const bool live = pix < total;
   const int b = live ? (int)(pix / hw) : 0, p = live ? (int)(pix % hw) : 0;
@@ -67,35 +75,73 @@ vq_lookup_postconv_kernel(const float* __restrict__ z, const float* __restrict__
     for (int c0 = 0; c0 < n_e; c0 += VQ_CHUNK) {
       const int nc = min(VQ_CHUNK, n_e - c0);
       __syncthreads();
-      for (int i = threadIdx.x; i < nc * E; i += VQ_THREADS) s_code[i] = codebook[(int64_t)c0 * E + i];
-      __syncthreads();
-      for (int i = threadIdx.x; i < nc; i += VQ_THREADS) {
-        float ee = __fmul_rn(s_code[i * E], s_code[i * E]);
-        for (int e = 1; e < E; ++e) ee = __fadd_rn(ee, __fmul_rn(s_code[i * E + e], s_code[i * E + e]));
-        s_ee[i] = ee;
+      if constexpr (EC == 3) {
+        float4* c4 = reinterpret_cast<float4*>(s_code);
+        for (int i = threadIdx.x; i < nc; i += VQ_THREADS) {
+          const float* src = codebook + (int64_t)(c0 + i) * 3;
+          const float e0 = src[0], e1 = src[1], e2 = src[2];
+          c4[i] = make_float4(e0, e1, e2, __fadd_rn(__fadd_rn(__fmul_rn(e0, e0), __fmul_rn(e1, e1)), __fmul_rn(e2, e2)));
+        }
+      } else {
+        for (int i = threadIdx.x; i < nc * E; i += VQ_THREADS) s_code[i] = codebook[(int64_t)c0 * E + i];
+        __syncthreads();
+        for (int i = threadIdx.x; i < nc; i += VQ_THREADS) {
+          float ee = __fmul_rn(s_code[i * E], s_code[i * E]);
+          for (int e = 1; e < E; ++e) ee = __fadd_rn(ee, __fmul_rn(s_code[i * E + e], s_code[i * E + e]));
+          s_ee[i] = ee;
+        }
       }
       __syncthreads();
-      for (int i = 0; i < nc; ++i) {
-        const float* ce = s_code + i * E;
-        float dot = __fmul_rn(zv[0], ce[0]);
+      const int per = (nc + NW - 1) / NW, i0 = warp * per, i1 = min(nc, i0 + per);
+      if constexpr (EC == 3) {
+        const float4* c4 = reinterpret_cast<const float4*>(s_code);
+#pragma unroll 4
+        for (int i = i0; i < i1; ++i) {
+          const float4 c = c4[i];
+          const float dot = fmaf(zv[2], c.z, fmaf(zv[1], c.y, __fmul_rn(zv[0], c.x)));
+          const float d = fmaf(-2.0f, dot, __fadd_rn(zz, c.w));   // == (zz + ee) - 2*dot: the product by 2 is exact
+          if (d < best) {
+            best = d;
+            best_i = c0 + i;
+          }
+        }
+      } else {
+        for (int i = i0; i < i1; ++i) {
+          const float* ce = s_code + i * E;
+          float dot = __fmul_rn(zv[0], ce[0]);
 #pragma unroll
-        for (int e = 1; e < VQ_MAX_E; ++e)
-          if (e < E) dot = fmaf(zv[e], ce[e], dot);
-        const float d = __fsub_rn(__fadd_rn(zz, s_ee[i]), 2.0f * dot);
-        if (d < best) {
-          best = d;
-          best_i = c0 + i;
+          for (int e = 1; e < VQ_MAX_E; ++e)
+            if (e < E) dot = fmaf(zv[e], ce[e], dot);
+          const float d = __fsub_rn(__fadd_rn(zz, s_ee[i]), 2.0f * dot);
+          if (d < best) {   // ascending scan inside the warp's slice: the first minimum of the slice
+            best = d;
+            best_i = c0 + i;
+          }
         }
       }
     }
-    if (live) {
+    s_best[threadIdx.x] = best;
+    s_besti[threadIdx.x] = best_i;
+    __syncthreads();
+    if (warp == 0) {
 #pragma unroll
-      for (int e = 0; e < VQ_MAX_E; ++e)
-        if (e < E) q[e] = __fadd_rn(zv[e], __fsub_rn(codebook[(int64_t)best_i * E + e], zv[e]));
-      if (indices) indices[pix] = best_i;
+      for (int ww = 1; ww < NW; ++ww) {
+        const float d = s_best[ww * 32 + lane];
+        const int di = s_besti[ww * 32 + lane];
+        if (d < best || (d == best && di < best_i)) {
+          best = d;
+          best_i = di;
+        }
+      }
+      if (live) {
+#pragma unroll
+        for (int e = 0; e < VQ_MAX_E; ++e)
+          if (e < E) q[e] = __fadd_rn(zv[e], __fsub_rn(codebook[(int64_t)best_i * E + e], zv[e]));
+        if (indices) indices[pix] = best_i;
+      }
     }
   }
-  if (!live) return;
+  if (!live || warp != 0) return;
   if (zq_out) {
 #pragma unroll
     for (int e = 0; e < VQ_MAX_E; ++e)
@@ -166,9 +212,14 @@ int ldmb200_vq_lookup_postconv(const float* z, const float* codebook, int n_e, i
                 "vq_lookup_postconv: embed_dim %d (max %d) / z_channels %d / c_pad %d", e_dim, VQ_MAX_E, z_channels, c_pad);
   LDM_CHECK_ARG(!codebook || n_e > 0, "vq_lookup_postconv: empty codebook");
   const int64_t total = (int64_t)batch * hw;
-  const int blocks = (int)ceil_div64(total, VQ_THREADS);
-  VQ_DISPATCH_DTYPE(out_dtype, (vq_lookup_postconv_kernel<T><<<blocks, VQ_THREADS, 0, (cudaStream_t)stream>>>(
-                                   z, codebook, n_e, e_dim, w, bias, z_channels, (T*)y, c_pad, indices, zq, batch, hw)));
+  const int blocks = (int)ceil_div64(total, 32);
+  if (e_dim == 3) {
+    VQ_DISPATCH_DTYPE(out_dtype, (vq_lookup_postconv_kernel<T, 3><<<blocks, VQ_THREADS, 0, (cudaStream_t)stream>>>(
+                                     z, codebook, n_e, e_dim, w, bias, z_channels, (T*)y, c_pad, indices, zq, batch, hw)));
+  } else {
+    VQ_DISPATCH_DTYPE(out_dtype, (vq_lookup_postconv_kernel<T, 0><<<blocks, VQ_THREADS, 0, (cudaStream_t)stream>>>(
+                                     z, codebook, n_e, e_dim, w, bias, z_channels, (T*)y, c_pad, indices, zq, batch, hw)));
+  }
   LDM_CHECK_LAUNCH("vq_lookup_postconv");
   return 0;
 }

@@ -46,7 +46,7 @@ def to_base(v, unit, kind):
     """ncu prints per-column units; normalise times to us and byte counts to MB."""
     if v is None:
         return None
-    u = (unit or "").strip().lower()
+    u = (unit or "").strip().lower().split("/")[0]
     if kind == "time":
         return v * {"ns": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3, "msecond": 1e3, "s": 1e6, "second": 1e6,
                     "nsecond": 1e-3}.get(u, 1e-3)

@@ -2,6 +2,7 @@
 // (K12), GroupNorm+SiLU over (virtually concatenated) channels-last maps (K7/K11), LayerNorm (K9), layout
 // changes, and the one-launch weight packer for the tensor-core path.
 #include <algorithm>
+#include <stdlib.h>
 
 #include <cuda_fp16.h>
 
@@ -696,7 +697,8 @@ int ldmb200_groupnorm_fused(const float* x1, int c1, const float* colstats1, con
   const int R = gn_rows_per_block(C);
   const int threads = (C / 4) * R;
   int nblk = hw / (R * 4);
-  int want = ceil_div(sm_count() * 4, batch);
+  static const int per_sm = getenv("LDMB200_GN_BLOCKS_PER_SM") ? atoi(getenv("LDMB200_GN_BLOCKS_PER_SM")) : 8;  // measured r01t: 4 -> 2.68, 8 -> 2.47, 16 -> 2.47, 32 -> 2.56 ms of GroupNorm per UNet eval
+  int want = ceil_div(sm_count() * per_sm, batch);
   if (nblk > want) nblk = want;
   if (nblk < 1) nblk = 1;
   LDM_DISPATCH_DTYPE(out_dtype, (gn_apply_kernel<T><<<dim3(nblk, batch), threads, 0, st>>>(

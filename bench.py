@@ -527,6 +527,49 @@ def decode_main(args):
         dist.destroy_process_group()
 
 
+def torch_eager_gpu_leg(args):
+    """--impl torch-eager: the second baseline BASELINE.md names - the reference algorithm as eager PyTorch ops ON THE SAME
+    B200 (the oracle's functional restatement, which is bit-identical to the reference modules on CPU; the reference tree
+    itself does not travel to the GPU box): fp32 with TF32 off, fp32 with torch's defaults (cuDNN TF32 convolutions), and
+    torch.autocast(bfloat16).  Times UNet evals only (the DDIM update is <0.1 % of a step) on config C2."""
+    import torch
+    from oracle import ldm_oracle as O
+    torch.cuda.set_device(0)
+    B, HW, T = args.batch, args.hw, args.ddim
+    sd = {k: v.cuda() for k, v in O.init_state_dict(O.FR_UNET, 0).items()}
+    g = torch.Generator().manual_seed(1000)
+    x = torch.randn(B, 3, HW, HW, generator=g).cuda()
+    ctx = torch.randn(B, 1, 512, generator=g).cuda()
+    t = torch.full((B,), 501, dtype=torch.long, device="cuda")
+    out = {}
+    ref = None
+    for mode in ("fp32_no_tf32", "fp32_default", "bf16_autocast"):
+        torch.backends.cuda.matmul.allow_tf32 = False
+        torch.backends.cudnn.allow_tf32 = mode != "fp32_no_tf32"
+        ac = torch.autocast("cuda", dtype=torch.bfloat16, enabled=(mode == "bf16_autocast"))
+        with torch.no_grad(), ac:
+            for _ in range(max(1, args.warmup)):
+                y = O.unet_forward(sd, O.FR_UNET, x, t, ctx)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(max(1, args.steps)):
+                y = O.unet_forward(sd, O.FR_UNET, x, t, ctx)
+            e1.record()
+            torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / max(1, args.steps)
+        if ref is None:
+            ref = y.float()
+        out[mode] = {"unet_eval_ms": ms, "samples_per_s": B / (T * ms * 1e-3),
+                     "eps_rel_l2_vs_fp32": float((y.float() - ref).norm() / ref.norm())}
+    best = max(v["samples_per_s"] for v in out.values())
+    print(json.dumps({"impl": "torch-eager-gpu", "metric": METRIC, "value": best, "unit": "samples/s", "n_gpus": 1,
+                      "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "data": "synthetic",
+                      "config": {"workload": f"C2: FR UNet, {HW}x{HW}x3 latents, batch {B}, {T} UNet evals per sample "
+                                             "(eager PyTorch ops of the reference algorithm on the same GPU)"},
+                      "modes": out}))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", default="sample", choices=["sample", "train", "c3", "decode"],
@@ -539,7 +582,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch-eager"])
     ap.add_argument("--batch", type=int, default=None, help="samples per GPU (weak scaling); default 64 (sample) / 32 (train)")
     ap.add_argument("--hw", type=int, default=64)
     ap.add_argument("--ddim", type=int, default=None, help="DDIM steps: default 50 (sample) / 200 (c3)")
@@ -551,6 +594,8 @@ def main():
         args.batch = 64 if args.workload == "sample" else 16 if args.workload == "decode" else 32
     if args.ddim is None:
         args.ddim = 200 if args.workload == "c3" else 50
+    if args.impl == "torch-eager":
+        return torch_eager_gpu_leg(args)
     if args.workload == "train":
         return train_main(args)
     if args.workload == "decode":

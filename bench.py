@@ -536,6 +536,55 @@ def torch_eager_gpu_leg(args):
     from oracle import ldm_oracle as O
     torch.cuda.set_device(0)
     B, HW, T = args.batch, args.hw, args.ddim
+    if args.workload == "train":
+        # C4: p_losses forward + autograd backward + torch.optim.AdamW(fused) + a foreach EMA sweep, TF UNet.  No
+        # activation checkpointing (the reference always checkpoints its transformer blocks): this favours the baseline.
+        g = torch.Generator().manual_seed(2000)
+        x0, nz = torch.randn(B, 3, HW, HW, generator=g), torch.randn(B, 3, HW, HW, generator=g)
+        ctx, c34 = torch.randn(B, 1, 1024, generator=g).cuda(), torch.randn(B, 6, HW, HW, generator=g).cuda()
+        t = torch.randint(0, 1000, (B,), generator=g)
+        x_in = torch.cat([O.q_sample(x0, t, nz).cuda(), c34], dim=1)
+        nz, t = nz.cuda(), t.cuda()
+        out = {}
+        for mode in ("fp32_default", "bf16_autocast"):
+            torch.backends.cuda.matmul.allow_tf32 = False
+            torch.backends.cudnn.allow_tf32 = True
+            leaves = {k: v.cuda().requires_grad_(True) for k, v in O.init_state_dict(O.TF_UNET, 0).items()}
+            params = list(leaves.values())
+            ema = [p.detach().clone() for p in params]
+            opt = torch.optim.AdamW(params, lr=2e-6, fused=True)
+
+            def step():
+                opt.zero_grad(set_to_none=True)
+                with torch.autocast("cuda", dtype=torch.bfloat16, enabled=(mode == "bf16_autocast")):
+                    eps = O.unet_forward_autograd(leaves, O.TF_UNET, x_in, t, ctx)
+                loss = ((eps.float() - nz) ** 2).mean([1, 2, 3]).mean()
+                loss.backward()
+                opt.step()
+                with torch.no_grad():
+                    torch._foreach_lerp_(ema, [p.detach() for p in params], 1.0 - 0.9999)
+                return loss
+            for _ in range(max(1, args.warmup)):
+                step()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(max(1, args.steps)):
+                step()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / max(1, args.steps)
+            out[mode] = {"step_ms": ms, "samples_per_s": B / (ms * 1e-3)}
+            del leaves, params, ema, opt
+            torch.cuda.empty_cache()
+        best = max(v["samples_per_s"] for v in out.values())
+        print(json.dumps({"impl": "torch-eager-gpu", "metric": TRAIN_METRIC, "value": best, "unit": "samples/s", "n_gpus": 1,
+                          "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "data": "synthetic",
+                          "config": {"workload": f"C4: TF UNet p_losses + autograd + fused AdamW + EMA, {HW}x{HW} latents, "
+                                                 f"batch {B} (eager PyTorch ops of the reference algorithm on the same GPU, "
+                                                 "no activation checkpointing)"},
+                          "modes": out}))
+        return
     sd = {k: v.cuda() for k, v in O.init_state_dict(O.FR_UNET, 0).items()}
     g = torch.Generator().manual_seed(1000)
     x = torch.randn(B, 3, HW, HW, generator=g).cuda()

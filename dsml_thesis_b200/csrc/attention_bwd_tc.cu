@@ -12,8 +12,12 @@
 // write the bf16 operand tiles (P^T and dS^T, or dS) K-major with the 128-byte swizzle; the MMA warp then accumulates
 // the outputs in TMEM with the streamed slab as the MN-major B operand (like V in the forward kernel), always one slab
 // ahead on T1 / T2.
-//   warps 0-7: softmax   warp 8: MMA issuer   warp 9: TMA producer (+ barrier init, TMEM allocation)
+//   warps 0-15: softmax, two sets of eight — set u owns the TMEM / operand buffer pair u, i.e. every other slab, so two
+//   slabs are in the softmax stage at any time (the stage is latency-bound: ex2, two packs and two swizzled 16-byte
+//   stores per column pair on one thread per row);   warp 16: MMA issuer   warp 17: TMA producer (+ barrier init,
+//   TMEM allocation)
 #include <algorithm>
+#include <type_traits>
 
 #include "common.cuh"
 
@@ -26,7 +30,12 @@ constexpr int AX_LD = 64 * 8;                  // {lse2, D} of the slab's 64 que
 constexpr int AX_STAGE = 2 * AX_SLAB + AX_LD;  // 8.5 KiB, keeps 512-byte alignment of the slabs
 constexpr int AX_OP = 128 * 128;               // operand tile: 128 rows x 64 bf16 (16 KiB, 128B-swizzled K-major)
 constexpr int AX_SMEM = 2 * AX_RES + AX_ST * AX_STAGE + 4 * AX_OP + (1 + 2 * AX_ST + 6) * 8 + 16 + 1024;
-constexpr int AX_THREADS = 320;
+#ifndef LDM_AX_SETS
+#define LDM_AX_SETS 1   // measured r01t at 64x64, B=32: one set 21.8 ms, two sets 22.1 ms (the stage is TMEM-read / issue bound, not latency bound)
+#endif
+constexpr int AX_SETS = LDM_AX_SETS;           // softmax warp sets of 8 (set u owns buffer pair u when there are two)
+constexpr int AX_MMA_WARP = 8 * AX_SETS, AX_TMA_WARP = 8 * AX_SETS + 1;
+constexpr int AX_THREADS = 32 * (8 * AX_SETS + 2);
 constexpr int AX_ACC = 256;                    // TMEM: T1_u at u*128, T2_u at u*128 + 64, accA at 256, accB at 288
 
 struct AxParams {
@@ -84,7 +93,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv128, const __g
   const int row0 = rb * 128;
   const int n_slabs = (p.n_tok + 63) / 64;
 
-  if (warp == 9) {
+  if (warp == AX_TMA_WARP) {
     if (lane == 0) {
       prefetch_tmap(&tm_qkv128);
       prefetch_tmap(&tm_qkv64);
@@ -109,7 +118,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv128, const __g
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (warp == 9) {
+  if (warp == AX_TMA_WARP) {
     // ===================== TMA producer =====================
     if (elect_one()) {
       mbar_expect_tx(r_full, 2 * AX_RES);
@@ -140,7 +149,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv128, const __g
       }
       __syncwarp();
     }
-  } else if (warp == 8) {
+  } else if (warp == AX_MMA_WARP) {
     // ===================== MMA issuer =====================
     constexpr uint32_t idesc_t = umma_idesc_bf16(128, 64, 0, 0);          // T = R . S^T, both K-major
     constexpr uint32_t idesc_acc = umma_idesc_bf16(128, 32, 0, 1);        // acc += Op . S, S as MN-major B
@@ -206,7 +215,8 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv128, const __g
     }
   } else {
     // ===================== softmax warps: thread <-> row (TMEM lane), warpgroup <-> 32-column half ===============
-    const int wg = warp >> 2;                       // 0 | 1
+    const int set = warp >> 3;                      // owns buffer pair u == set (slabs i with i & 1 == set) if AX_SETS == 2
+    const int wg = (warp >> 2) & 1;                 // 0 | 1: 32-column half of the slab
     const int r = (warp & 3) * 32 + lane;           // row of the 128-row block == TMEM lane
     const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
     const int grow = row0 + r;                      // row index inside the sample
@@ -217,7 +227,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv128, const __g
       d_r = v.y;
     }
     const float c_ = p.scale_log2e, sc = p.scale;
-    for (int i = 0; i < n_slabs; ++i) {
+    for (int i = set; i < n_slabs; i += AX_SETS) {
       const int u = i & 1, s = i % AX_ST;
       if (KV) mbar_wait(&st_full[s], (i / AX_ST) & 1);     // the slab's {lse2, D}
       mbar_wait(&t_full[u], (i >> 1) & 1);
@@ -231,34 +241,43 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv128, const __g
       uint8_t* ds_row = sOp + u * (2 * AX_OP) + r * 128;
       uint8_t* pw_row = ds_row + AX_OP;
       const int col0 = i * 64 + wg * 32;            // first streamed index of this thread's 32 columns
+      // {lse2, D * scale} per streamed index (KV role) or per row (Q role): dS = P (dP scale - D scale)
+      auto columns = [&](auto check_tag) {
+        constexpr bool CHECK = decltype(check_tag)::value;   // only the sample's last, partial slab needs column masks
 #pragma unroll
-      for (int q4 = 0; q4 < 4; ++q4) {              // 8 columns -> one 16-byte unit of each operand row
-        uint32_t pk[4], dk[4];
+        for (int q4 = 0; q4 < 4; ++q4) {            // 8 columns -> one 16-byte unit of each operand row
+          uint32_t pk[4], dk[4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int j = q4 * 8 + e * 2;
-          float l0 = lse_r, l1 = lse_r, dd0 = d_r, dd1 = d_r;
-          if (KV) {
-            const float4 v = *reinterpret_cast<const float4*>(ldp + j);   // {lse, D} of columns j, j+1 (broadcast read)
-            l0 = v.x; dd0 = v.y; l1 = v.z; dd1 = v.w;
+          for (int e = 0; e < 4; ++e) {
+            const int j = q4 * 8 + e * 2;
+            float l0 = lse_r, l1 = lse_r, dd0 = d_r, dd1 = d_r;
+            if (KV) {
+              const float4 v = *reinterpret_cast<const float4*>(ldp + j);   // {lse, D} of columns j, j+1 (broadcast read)
+              l0 = v.x; dd0 = v.y; l1 = v.z; dd1 = v.w;
+            }
+            float p0 = ax_ex2(fmaf(t1[j], c_, -l0)), p1 = ax_ex2(fmaf(t1[j + 1], c_, -l1));
+            if (CHECK) {
+              if (col0 + j >= p.n_tok) p0 = 0.f;
+              if (col0 + j + 1 >= p.n_tok) p1 = 0.f;
+            }
+            dk[e] = ax_pack(p0 * fmaf(t2[j], sc, -dd0), p1 * fmaf(t2[j + 1], sc, -dd1));
+            if (KV) pk[e] = ax_pack(p0, p1);
           }
-          float p0 = ax_ex2(fmaf(t1[j], c_, -l0)), p1 = ax_ex2(fmaf(t1[j + 1], c_, -l1));
-          if (col0 + j >= p.n_tok) p0 = 0.f;
-          if (col0 + j + 1 >= p.n_tok) p1 = 0.f;
-          const float s0 = p0 * (t2[j] - dd0) * sc, s1 = p1 * (t2[j + 1] - dd1) * sc;
-          dk[e] = ax_pack(col0 + j < p.n_tok ? s0 : 0.f, col0 + j + 1 < p.n_tok ? s1 : 0.f);
-          if (KV) pk[e] = ax_pack(p0, p1);
+          const int unit = wg * 4 + q4;
+          *reinterpret_cast<uint4*>(ds_row + ((unit ^ (r & 7)) << 4)) = make_uint4(dk[0], dk[1], dk[2], dk[3]);
+          if (KV) *reinterpret_cast<uint4*>(pw_row + ((unit ^ (r & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
         }
-        const int unit = wg * 4 + q4;
-        *reinterpret_cast<uint4*>(ds_row + ((unit ^ (r & 7)) << 4)) = make_uint4(dk[0], dk[1], dk[2], dk[3]);
-        if (KV) *reinterpret_cast<uint4*>(pw_row + ((unit ^ (r & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-      }
+      };
+      if (col0 + 32 <= p.n_tok) columns(std::false_type{});
+      else columns(std::true_type{});
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(&op_full[u]);
     }
     // ---- epilogue: accumulators -> bf16 rows of dqkv
+    // (by the set that owns the last slab's buffers: only its threads have followed every phase of that op_free barrier)
     const int last = n_slabs - 1;
+    if (AX_SETS == 1 || set == (last & 1)) {
     mbar_wait(&op_free[last & 1], (last >> 1) & 1);
     tc_fence_after();
     if (wg == 0 || KV) {                            // Q role: one accumulator, warpgroup 0 stores it
@@ -275,20 +294,21 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv128, const __g
                                                          ax_pack(o[d + 4], o[d + 5]), ax_pack(o[d + 6], o[d + 7]));
       }
     }
+    }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) {
+  if (warp == AX_TMA_WARP) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
 }
 
-// D_i = sum_d dO_id O_id and the forward's lse2 -> ld[b, h, i] = {lse2, D}   (thread per (row, head))
+// D_i = sum_d dO_id O_id and the forward's lse2 -> ld[b, h, i] = {lse2, D * scale}   (thread per (row, head))
 __global__ void __launch_bounds__(256) attention_bwd_prep_kernel(const uint16_t* __restrict__ o, const uint16_t* __restrict__ dout,
                                                                  int o_ld, const float* __restrict__ lse2,
                                                                  float2* __restrict__ ld, int batch, int heads, int n_tok,
-                                                                 int n_pad) {
+                                                                 int n_pad, float scale) {
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t total = (int64_t)batch * n_pad * heads;
   if (idx >= total) return;
@@ -311,7 +331,7 @@ __global__ void __launch_bounds__(256) attention_bwd_prep_kernel(const uint16_t*
         acc = fmaf(__uint_as_float(xs[e] & 0xffff0000u), __uint_as_float(ys[e] & 0xffff0000u), acc);
       }
     }
-    out = make_float2(lse2[((size_t)b * heads + h) * n_tok + i], acc);
+    out = make_float2(lse2[((size_t)b * heads + h) * n_tok + i], acc * scale);
   }
   ld[((size_t)b * heads + h) * n_pad + i] = out;
 }
@@ -333,7 +353,7 @@ int attention_bwd_tc_launch(const void* qkv, int ld, int q_off, int k_off, int v
   float2* ldbuf = reinterpret_cast<float2*>(ws);
   const int64_t total = (int64_t)batch * n_pad * heads;
   attention_bwd_prep_kernel<<<(unsigned)ceil_div64(total, 256), 256, 0, st>>>((const uint16_t*)out, (const uint16_t*)dout, o_ld,
-                                                                             lse2, ldbuf, batch, heads, n_tokens, n_pad);
+                                                                             lse2, ldbuf, batch, heads, n_tokens, n_pad, scale);
   CUtensorMap t128, t64, d128, d64;
   {
     uint64_t dims[2] = {(uint64_t)ld, (uint64_t)batch * n_tokens};

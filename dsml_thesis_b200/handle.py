@@ -16,7 +16,8 @@ import torch.nn as nn
 
 class DiffusionHandle(nn.Module):
     def __init__(self, unet: nn.Module, timesteps: int = 1000, linear_start: float = 0.0015,
-                 linear_end: float = 0.0205, two_cond: bool = False):
+                 linear_end: float = 0.0205, two_cond: bool = False, first_stage_decoder: nn.Module = None,
+                 first_stage_encoder: nn.Module = None, scale_factor: float = 1.0):
         super().__init__()
         betas = (torch.linspace(linear_start ** 0.5, linear_end ** 0.5, timesteps, dtype=torch.float64) ** 2).numpy()
         alphas_cumprod = np.cumprod(1.0 - betas, axis=0)
@@ -31,6 +32,11 @@ class DiffusionHandle(nn.Module):
         self.register_buffer("sqrt_one_minus_alphas_cumprod", f32(np.sqrt(1.0 - alphas_cumprod)))
         self.diffusion_model = unet
         self.two_cond = two_cond
+        # optional first stage (``VQDecoder`` / ``VQEncoder``): latent <-> image like LatentDiffusion (ddpm.py:541-548,
+        # 707-771, 827-866; no shipped config sets split_input_params, so the patch-wise branches are not built)
+        self.first_stage_decoder = first_stage_decoder
+        self.first_stage_encoder = first_stage_encoder
+        self.scale_factor = float(scale_factor)
 
     @property
     def device(self):
@@ -47,3 +53,25 @@ class DiffusionHandle(nn.Module):
         noise = torch.randn_like(x_start) if noise is None else noise
         e = lambda a: a.gather(-1, t).reshape(-1, 1, 1, 1)
         return e(self.sqrt_alphas_cumprod) * x_start + e(self.sqrt_one_minus_alphas_cumprod) * noise
+
+    @torch.no_grad()
+    def decode_first_stage(self, z, predict_cids=False, force_not_quantize=False):
+        """ddpm.py:707-771 (tensor latents): ``first_stage_model.decode(z / scale_factor)``."""
+        if self.first_stage_decoder is None:
+            raise RuntimeError("DiffusionHandle was built without a first_stage_decoder")
+        if predict_cids:
+            raise NotImplementedError("predict_cids (logits over code ids) is not used by any shipped config")
+        return self.first_stage_decoder.decode(1.0 / self.scale_factor * z, force_not_quantize=force_not_quantize)
+
+    @torch.no_grad()
+    def encode_first_stage(self, x):
+        """ddpm.py:827-866: ``first_stage_model.encode(x)`` (VQModelInterface: no quantisation)."""
+        if self.first_stage_encoder is None:
+            raise RuntimeError("DiffusionHandle was built without a first_stage_encoder")
+        return self.first_stage_encoder.encode(x)
+
+    def get_first_stage_encoding(self, encoder_posterior):
+        """ddpm.py:541-548 for tensor posteriors (VQ first stage)."""
+        if not isinstance(encoder_posterior, torch.Tensor):
+            raise NotImplementedError(f"encoder_posterior of type '{type(encoder_posterior)}' not yet implemented")
+        return self.scale_factor * encoder_posterior

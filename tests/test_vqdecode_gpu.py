@@ -261,3 +261,21 @@ def test_install_wrapper_encodes_cuda_images_through_the_kernels():
     x = torch.randn(2, 3, 32, 32, generator=torch.Generator().manual_seed(8)).clamp_(-1, 1)
     z = fs.encode(x.cuda())
     assert O.rel_l2(z.cpu(), V.vq_encode(sd, V.VQ_TINY, x)) <= TOL[fs._ldmb200_encoder.precision]
+
+
+def test_handle_round_trips_latents_through_the_first_stage():
+    """DiffusionHandle.decode_first_stage / encode_first_stage / get_first_stage_encoding (ddpm.py:541-548,707-771,827-866)."""
+    sd_d, dec = _model(V.VQ_TINY)
+    sd_e, enc = _encoder(V.VQ_TINY)
+    dec.precision = enc.precision = "fp32"
+    unet = P.UNetModel(**O.TINY_UNET).cuda().eval()
+    h = P.DiffusionHandle(unet, first_stage_decoder=dec, first_stage_encoder=enc, scale_factor=0.5).cuda()
+    z = torch.randn(2, 3, 8, 8, generator=torch.Generator().manual_seed(12))
+    img = h.decode_first_stage(z.cuda())
+    ref, _ = V.vq_decode(sd_d, V.VQ_TINY, z / 0.5)
+    assert O.rel_l2(img.cpu(), ref) <= 1e-4
+    lat = h.get_first_stage_encoding(h.encode_first_stage(img))
+    ref_lat = 0.5 * V.vq_encode(sd_e, V.VQ_TINY, ref)
+    assert O.rel_l2(lat.cpu(), ref_lat) <= 1e-4
+    with pytest.raises(RuntimeError):
+        P.DiffusionHandle(unet).cuda().decode_first_stage(z.cuda())

@@ -851,6 +851,20 @@ def main():
     value = total / (ms * 1e-3)
     e2e_value = total / (ms_e2e * 1e-3)
     ref_gflop = REF_GFLOP_PER_EVAL.get(HW)
+    # second kernel of the step: attention at d_head 32 is bound by the ex2 unit (one exponential per 128 MMA flops,
+    # 16 ex2/clk/SM) and the TMEM read port, not by the tensor pipe - report it against THAT roofline
+    attn_roof = None
+    af = fam.get("ldmb200_attention_tc")
+    if af and af[0] > 0:
+        mhz = (clk or {}).get("sm_mhz") or (clk or {}).get("sm_max_mhz") or 1965.0
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        peak_ex2 = 16.0 * sms * mhz * 1e6
+        ach_ex2 = (af[1] / 128.0) / (af[0] * 1e-3)
+        attn_roof = {"kernel": "ldmb200_attention_tc", "bound": "mufu (ex2) / tmem-read", "achieved": ach_ex2 / 1e12,
+                     "peak": peak_ex2 / 1e12, "unit": "Texp2/s", "frac": ach_ex2 / peak_ex2,
+                     "tensor_tflops": af[1] / (af[0] * 1e-3) / 1e12, "ms_per_eval": af[0],
+                     "how": "exponentials = attention flops / 128 (4*N^2*32 flops and N^2 exponentials per head); peak = "
+                            "16 ex2/clk/SM x SM count x the median SM clock sampled under load"}
     line = {
         "metric": metric, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -879,6 +893,7 @@ def main():
                      "launches_per_eval": d[3], "ms_per_eval": d[0],
                      "how": "sum of algorithmic FLOPs of the family's launches in one UNet eval / sum of their "
                             "CUDA-event durations on the launching stream"},
+        "roofline_attention": attn_roof,
         "kernel_breakdown_ms_per_eval": {k: round(v[0], 4) for k, v in sorted(fam.items(), key=lambda kv: -kv[1][0])},
         "eval_ms_sum_of_kernels": eval_ms,
     }

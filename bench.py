@@ -217,7 +217,8 @@ def train_main(args):
     unet.use_cuda_graph = bool(args.graph)
     handle = P.DiffusionHandle(unet, two_cond=True).to(dev).train()
     opt = T.FusedAdamWEMA(unet, lr=2e-6)          # base_learning_rate of mead-128-ldm-f4.yaml
-    sync = T.GradAllReduce(unet) if world > 1 else None
+    wire = {"fp32": None, "bf16": torch.bfloat16}[args.grad_wire]
+    sync = T.GradAllReduce(unet, wire_dtype=wire) if world > 1 else None
     g = torch.Generator().manual_seed(2000 + rank)
     host = dict(x0=torch.randn(B, 3, HW, HW, generator=g), nz=torch.randn(B, 3, HW, HW, generator=g),
                 c12=torch.randn(B, 1, 1024, generator=g), c34=torch.randn(B, 6, HW, HW, generator=g))
@@ -323,7 +324,8 @@ def train_main(args):
         "config": {"workload": workload, "cuda_graph": bool(args.graph),
                    "l2": "per-step working set (saved activations, tens of GB) far exceeds the 126 MB L2",
                    "init": "synthetic non-zero weights, seed 0",
-                   "parallelism": f"data-parallel x{world}, flat-arena gradient all-reduce (2 buckets, first overlapped)"},
+                   "parallelism": f"data-parallel x{world}, flat-arena gradient all-reduce (2 buckets, first overlapped, "
+                                  f"{args.grad_wire} on the wire)"},
         "train_tflops_algorithmic": (value * gflop / 1e3) if gflop else None,
         "tensor_frac_of_measured_peak": (value / world * gflop / 1e3 / peak_tf) if gflop else None,
         "e2e": {"value": total / (ms_e2e * 1e-3), "unit": "samples/s", "ms_per_step": ms_e2e / args.steps,
@@ -638,6 +640,8 @@ def main():
     ap.add_argument("--precision", default="f16", choices=["f16", "bf16", "fp32"])
     ap.add_argument("--graph", type=int, default=int(os.environ.get("LDMB200_CUDA_GRAPH", "1")))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--grad-wire", default="fp32", choices=["fp32", "bf16"],
+                    help="train, N>1: dtype of the gradient all-reduce on the wire (fp32 = exact, default)")
     args = ap.parse_args()
     if args.batch is None:
         args.batch = 64 if args.workload == "sample" else 16 if args.workload == "decode" else 32

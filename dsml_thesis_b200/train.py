@@ -884,31 +884,47 @@ class GradAllReduce:
     model's backward; ``finish()`` must be called before the optimizer step.  ``flat`` may be given directly (CPU /
     gloo tests of the bucket logic)."""
 
-    def __init__(self, model=None, group=None, flat: Optional[torch.Tensor] = None):
+    def __init__(self, model=None, group=None, flat: Optional[torch.Tensor] = None,
+                 wire_dtype: Optional[torch.dtype] = None):
+        """``wire_dtype=torch.bfloat16`` halves the NVLink bytes (SURVEY §8e "bf16 grads optional"): each bucket is cast to a
+        bf16 staging buffer, pre-divided by the world size (so the sum cannot overflow where fp32 would not), summed in
+        bf16 by the collective and cast back into the fp32 arena.  Default: fp32 on the wire, exact."""
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.world = dist.get_world_size(group)
         self.flat = flat if flat is not None else train_state(model).flat
         self.side = torch.cuda.Stream(device=self.flat.device) if self.flat.is_cuda else None
+        self.wire_dtype = wire_dtype if wire_dtype not in (None, torch.float32) else None
+        self.wire = torch.empty_like(self.flat, dtype=self.wire_dtype) if self.wire_dtype is not None else None
         self.split = None
         if model is not None:
             model._grad_bucket_hook = self.bucket_ready
+
+    def _reduce(self, lo: int, hi: int):
+        if self.wire is None:
+            self.dist.all_reduce(self.flat[lo:hi], group=self.group)
+            return
+        w = self.wire[lo:hi]
+        torch.mul(self.flat[lo:hi], 1.0 / self.world, out=w)      # fp32 product, rounded once to the wire dtype
+        self.dist.all_reduce(w, group=self.group)
+        self.flat[lo:hi].copy_(w)
 
     def bucket_ready(self, lo: int, hi: int):
         """Elements [lo, hi) of the arena are final: start their all-reduce while the backward continues."""
         self.split = lo
         if self.side is None:
-            self.dist.all_reduce(self.flat[lo:hi], group=self.group)
+            self._reduce(lo, hi)
             return
         self.side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self.side):
-            self.dist.all_reduce(self.flat[lo:hi], group=self.group)
+            self._reduce(lo, hi)
 
     def finish(self):
         lo = self.split if self.split is not None else self.flat.numel()
         if lo > 0:
-            self.dist.all_reduce(self.flat[:lo], group=self.group)
+            self._reduce(0, lo)
         if self.side is not None:
             torch.cuda.current_stream().wait_stream(self.side)
-        self.flat.mul_(1.0 / self.world)
+        if self.wire is None:
+            self.flat.mul_(1.0 / self.world)
         self.split = None

@@ -51,6 +51,33 @@ def test_two_bucket_gradient_allreduce_is_the_mean_over_ranks(world, split, tmp_
         assert torch.allclose(got, ref, atol=1e-6), r
 
 
+def _worker_bf16(rank, world, port, n, split, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        flat = torch.randn(n, generator=torch.Generator().manual_seed(200 + rank))
+        ar = T.GradAllReduce(flat=flat, wire_dtype=torch.bfloat16)
+        if split is not None:
+            ar.bucket_ready(split, n)
+        ar.finish()
+        assert flat.dtype == torch.float32
+        torch.save(flat, os.path.join(out_dir, f"r{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,split", [(2, 300), (3, None)])
+def test_bf16_wire_gradient_allreduce(world, split, tmp_path):
+    """wire_dtype=bfloat16 (SURVEY 8e option): the mean over ranks to bf16 accuracy, identical on every rank, fp32 arena."""
+    n = 777
+    mp.spawn(_worker_bf16, args=(world, _free_port(), n, split, str(tmp_path)), nprocs=world, join=True)
+    ref = sum(torch.randn(n, generator=torch.Generator().manual_seed(200 + r)) for r in range(world)) / world
+    got = [torch.load(os.path.join(str(tmp_path), f"r{r}.pt")) for r in range(world)]
+    for r in range(world):
+        assert torch.equal(got[r], got[0])
+        assert float((got[r] - ref).norm() / ref.norm()) <= 1e-2
+
+
 def test_training_on_cpu_fails_loudly():
     unet = P.UNetModel(**O.TINY_UNET).train()
     x = torch.randn(1, 3, 16, 16)

@@ -171,7 +171,9 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
   }
 }
 
-template <int BN, int BK, int EW>
+// GG: the GEGLU-epilogue specialisation (no residual / NCHW / statistics code in it: the erf-GELU epilogue is the bound of
+// those GEMMs and needs the registers); GG == false handles every other epilogue.
+template <int BN, int BK, int EW, bool GG>
 __global__ void __launch_bounds__(64 + EW * 32, 1)
 igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                 const __grid_constant__ CUtensorMap tmB, const TcParams p) {
@@ -323,7 +325,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     constexpr int PITCH = Cfg::EPI_PITCH;
     float* st = epi + ew * 32 * PITCH;
     const bool out16 = p.out_dtype != LDMB200_F32;
-    const bool has_res = p.residual != nullptr;
+    const bool has_res = !GG && p.residual != nullptr;
     uint32_t t_iter = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
       const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
@@ -334,6 +336,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       float4 res[8];
       const int cc_first = par;
       // the residual tile does not depend on the accumulator: fetch it while the MMAs are still running
+      // (a second chunk of lookahead was measured r01u: slower by 15-45 % on the K <= 640 GEMMs - register spills)
       if (has_res && cc_first < NCH) {
         if (out16) epi_load_residual<true>(p, res, m0, n0 + cc_first * Cfg::CH, lane);
         else epi_load_residual<false>(p, res, m0, n0 + cc_first * Cfg::CH, lane);
@@ -360,7 +363,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[buf]);
         }
-        if (p.out_nchw) {
+        if (!GG && p.out_nchw) {
           // UNetModel.out conv: thread owns pixel m, writes the n_valid real channels as fp32 NCHW
           const int m = m0 + lane;
           if (m < p.M) {
@@ -374,7 +377,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
           }
           continue;
         }
-        if (p.geglu) {  // chunk = [16 value | 16 gate] columns (packed order), biases in the same order
+        if constexpr (GG) {  // chunk = [16 value | 16 gate] columns (packed order), biases in the same order
           if (Cfg::CH == 32) {
             const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + cc * 32);
             float bv[32];
@@ -396,6 +399,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
           }
           continue;
         }
+        if constexpr (!GG) {
 #pragma unroll
         for (int j = 0; j < Cfg::CH / 4; ++j)
           *reinterpret_cast<float4*>(&st[lane * PITCH + j * 4]) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
@@ -411,6 +415,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
 #pragma unroll
           for (int j = 0; j < 8; ++j) res[j] = res_next[j];
         }
+        }  // !GG
       }
       if (cc_first >= NCH) {  // this warp had no chunk in the tile (BN == CH): still release the buffer
         tc_fence_before();
@@ -428,13 +433,13 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   }
 }
 
-template <int BN, int BK, int EW>
+template <int BN, int BK, int EW, bool GG = false>
 static int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b, const TcParams& p,
                      cudaStream_t st) {
   using Cfg = TcCfg<BN, BK, EW>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::SMEM_BYTES);
     if (e != cudaSuccess) {
       set_error("igemm_tc: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
@@ -443,7 +448,7 @@ static int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtenso
     attr_set = true;
   }
   int grid = std::min(p.tiles_m * p.tiles_n, sm_count());
-  igemm_tc_kernel<BN, BK, EW><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(a1, a2, b, p);
+  igemm_tc_kernel<BN, BK, EW, GG><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(a1, a2, b, p);
   LDM_CHECK_LAUNCH("igemm_tc");
   return 0;
 }
@@ -514,7 +519,8 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   constexpr int BK = 64;
   // 128-wide tiles also serve the plain GEMMs whose n is a multiple of 128 but not of 160 (the first-stage decoder's
   // 128/256/512-channel convolutions and its n x n attention scores); no UNet shape falls in that class
-  int BN = (d->geglu && d->n % 128 == 0) ? 128 : (d->n % 160 == 0) ? 160 : (d->n % 128 == 0) ? 128 : (d->n % 32 == 0) ? 32 : 16;
+  int BN = d->geglu ? ((d->n % 128 == 0) ? 128 : 32)
+                    : (d->n % 160 == 0) ? 160 : (d->n % 128 == 0) ? 128 : (d->n % 32 == 0) ? 32 : 16;
   LDM_CHECK_ARG(BN != 16 || d->n == 16, "igemm_tc: n=%d unsupported (need multiple of 32, or exactly 16)", d->n);
   LDM_CHECK_ARG(!(d->geglu && BN == 16), "igemm_tc: geglu needs n %% 32 == 0");
   p.c1 = c1;
@@ -558,7 +564,9 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
     if (rc) return rc;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  if (BN == 128) return launch_tc<128, 64, 16>(tA1, tA2, tB, p, st);
+  if (BN == 128) return d->geglu ? launch_tc<128, 64, 16, true>(tA1, tA2, tB, p, st) : launch_tc<128, 64, 16>(tA1, tA2, tB, p, st);
+  LDM_CHECK_ARG(!d->geglu || d->n % 32 == 0, "igemm_tc: geglu needs n %% 32 == 0 (got n=%d)", d->n);
+  if (d->geglu) return launch_tc<32, 64, 8, true>(tA1, tA2, tB, p, st);
   // experiment switch (measured r01n: 16 epilogue warps on the plain 1x1 GEMMs are SLOWER, 32.1 vs 30.0 ms per UNet
   // eval — 5 chunks over 4 warps per quarter is unbalanced and the ring loses a stage — so the default stays 8)
   static const bool ew16 = getenv("LDMB200_TC_EW16") ? atoi(getenv("LDMB200_TC_EW16")) != 0 : false;

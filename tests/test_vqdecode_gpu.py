@@ -279,3 +279,46 @@ def test_handle_round_trips_latents_through_the_first_stage():
     assert O.rel_l2(lat.cpu(), ref_lat) <= 1e-4
     with pytest.raises(RuntimeError):
         P.DiffusionHandle(unet).cuda().decode_first_stage(z.cuda())
+
+
+def test_decode_and_encode_on_non_square_maps():
+    """H != W (both powers of two, as the tensor-core convolution requires): 8x32 latents <-> 32x128 images."""
+    sd, dec = _model(V.VQ_TINY)
+    sde, enc = _encoder(V.VQ_TINY)
+    z = torch.randn(2, 3, 8, 32, generator=torch.Generator().manual_seed(21))
+    ref, idx = V.vq_decode(sd, V.VQ_TINY, z)
+    for precision in ("fp32", "f16"):
+        dec.precision = enc.precision = precision
+        img = dec.decode(z.cuda())
+        assert img.shape == (2, 3, 32, 128) and torch.equal(dec.last_indices.cpu(), idx)
+        assert O.rel_l2(img.cpu(), ref) <= TOL[precision]
+        x = ref.clamp(-1, 1)
+        assert O.rel_l2(enc.encode(x.cuda()).cpu(), V.vq_encode(sde, V.VQ_TINY, x)) <= TOL[precision]
+
+
+def test_quantisation_is_idempotent_and_selects_codebook_rows():
+    """Size-independent properties of the lookup at full size (16384 codes, 64x64 latents, batch 8): every z_q is a codebook
+    row up to the straight-through rounding, and quantising z_q again returns the same indices."""
+    g = torch.Generator().manual_seed(33)
+    n_e, e, B, hw = 16384, 3, 8, 4096
+    cb = torch.randn(n_e, e, generator=g).cuda()
+    z = torch.randn(B, e, hw, generator=g).cuda()
+    w = torch.eye(3, device="cuda")
+    y = torch.empty(B * hw, 32, device="cuda")
+    idx = torch.empty(B * hw, dtype=torch.int64, device="cuda")
+    zq = torch.empty_like(z)
+    _cabi.call("ldmb200_vq_lookup_postconv", z.data_ptr(), cb.data_ptr(), n_e, e, w.data_ptr(), None, 3, y.data_ptr(), F32, 32,
+               idx.data_ptr(), zq.data_ptr(), B, hw, 0)
+    torch.cuda.synchronize()
+    rows = cb[idx].view(B, hw, e).permute(0, 2, 1)
+    assert float((zq - rows).abs().max()) <= 1e-6                       # z + (e - z) == e up to one rounding
+    assert torch.equal(y[:, :3], zq.permute(0, 2, 1).reshape(B * hw, e))  # identity post_quant_conv passes z_q through
+    d = torch.cdist(z.permute(0, 2, 1).reshape(-1, e).double(), cb.double())
+    best = d.min(dim=1).values
+    chosen = d.gather(1, idx[:, None]).squeeze(1)
+    assert float((chosen - best).max()) <= 1e-6                          # the chosen code is a nearest one
+    idx2 = torch.empty_like(idx)
+    _cabi.call("ldmb200_vq_lookup_postconv", zq.data_ptr(), cb.data_ptr(), n_e, e, w.data_ptr(), None, 3, y.data_ptr(), F32, 32,
+               idx2.data_ptr(), None, B, hw, 0)
+    torch.cuda.synchronize()
+    assert torch.equal(idx2, idx)

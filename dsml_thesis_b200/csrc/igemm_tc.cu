@@ -92,24 +92,34 @@ __device__ __forceinline__ void epi_load_residual(const TcParams& p, float4 (&re
   }
 }
 
+// bias (+ the per-sample row vector when a tile lies inside one sample) of this lane's columns of a chunk: loaded by
+// the caller BEFORE it waits for the accumulator so that the L1/L2 latency hides under the TMEM read
+template <bool OUT16, int COLS>
+__device__ __forceinline__ void epi_load_add(const TcParams& p, float4 (&add)[2], int col0, int lane, bool add_bias,
+                                             int tile_sample) {
+  constexpr int CPL = OUT16 ? 8 : 4, LPR = COLS / CPL, NQ = CPL / 4;
+  const int col = col0 + (lane % LPR) * CPL;
+  add[0] = add[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (col >= p.n_valid) return;
+#pragma unroll
+  for (int q = 0; q < NQ; ++q) {
+    if (add_bias && p.bias) add[q] = *reinterpret_cast<const float4*>(p.bias + col + 4 * q);
+    if (p.rowvec && p.rowvec_uniform) {
+      const float4 rv = *reinterpret_cast<const float4*>(p.rowvec + (size_t)tile_sample * p.rowvec_ld + col + 4 * q);
+      add[q].x += rv.x; add[q].y += rv.y; add[q].z += rv.z; add[q].w += rv.w;
+    }
+  }
+}
+
 template <bool OUT16, int COLS, bool STATS = false>
 __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, int pitch, int m0, int col0, int lane,
-                                          const float4 (&res)[8], bool has_res, bool add_bias, int tile_sample) {
+                                          const float4 (&res)[8], bool has_res, const float4 (&add)[2]) {
   static_assert(!(STATS && OUT16), "column statistics are taken of fp32 outputs only");
   float sx[4] = {0.f, 0.f, 0.f, 0.f}, sq[4] = {0.f, 0.f, 0.f, 0.f};
   constexpr int CPL = OUT16 ? 8 : 4, LPR = COLS / CPL, RPI = 32 / LPR, NQ = CPL / 4;
   const int lr = lane / LPR, lc = (lane % LPR) * CPL;
   const int col = col0 + lc;
   if (!STATS && col >= p.n_valid) return;  // (STATS: n_valid is a multiple of the chunk width, checked on the host)
-  float4 add[NQ];
-#pragma unroll
-  for (int q = 0; q < NQ; ++q) {
-    add[q] = (add_bias && p.bias) ? *reinterpret_cast<const float4*>(p.bias + col + 4 * q) : make_float4(0.f, 0.f, 0.f, 0.f);
-    if (p.rowvec && p.rowvec_uniform) {
-      const float4 rv = *reinterpret_cast<const float4*>(p.rowvec + (size_t)tile_sample * p.rowvec_ld + col + 4 * q);
-      add[q].x += rv.x; add[q].y += rv.y; add[q].z += rv.z; add[q].w += rv.w;
-    }
-  }
 #pragma unroll
   for (int it = 0; it < LPR; ++it) {
     const int r = it * RPI + lr;
@@ -357,6 +367,13 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
           if (out16) epi_load_residual<true>(p, res_next, m0, n0 + (cc + CSTEP) * Cfg::CH, lane);
           else epi_load_residual<false>(p, res_next, m0, n0 + (cc + CSTEP) * Cfg::CH, lane);
         }
+        float4 addv[2];
+        if constexpr (!GG) {
+          if (!p.out_nchw) {
+            if (out16) epi_load_add<true, Cfg::CH>(p, addv, n0 + cc * Cfg::CH, lane, true, tile_sample);
+            else epi_load_add<false, Cfg::CH>(p, addv, n0 + cc * Cfg::CH, lane, true, tile_sample);
+          }
+        }
         tmem_ld_wait();
         if (!more) {  // last TMEM read of this warp for this tile: hand the accumulator buffer back early
           tc_fence_before();
@@ -393,8 +410,9 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
               *reinterpret_cast<float4*>(&st[lane * PITCH + j * 4]) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
             __syncwarp();
             const int col0 = (n0 >> 1) + cc * 16;
-            if (out16) epi_store<true, 16>(p, st, PITCH, m0, col0, lane, res, false, false, tile_sample);
-            else epi_store<false, 16>(p, st, PITCH, m0, col0, lane, res, false, false, tile_sample);
+            const float4 zero_add[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+            if (out16) epi_store<true, 16>(p, st, PITCH, m0, col0, lane, res, false, zero_add);
+            else epi_store<false, 16>(p, st, PITCH, m0, col0, lane, res, false, zero_add);
             __syncwarp();
           }
           continue;
@@ -406,9 +424,9 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
         __syncwarp();
         {
           const int col0 = n0 + cc * Cfg::CH;
-          if (out16) epi_store<true, Cfg::CH>(p, st, PITCH, m0, col0, lane, res, has_res, true, tile_sample);
-          else if (p.colstats) epi_store<false, Cfg::CH, true>(p, st, PITCH, m0, col0, lane, res, has_res, true, tile_sample);
-          else epi_store<false, Cfg::CH>(p, st, PITCH, m0, col0, lane, res, has_res, true, tile_sample);
+          if (out16) epi_store<true, Cfg::CH>(p, st, PITCH, m0, col0, lane, res, has_res, addv);
+          else if (p.colstats) epi_store<false, Cfg::CH, true>(p, st, PITCH, m0, col0, lane, res, has_res, addv);
+          else epi_store<false, Cfg::CH>(p, st, PITCH, m0, col0, lane, res, has_res, addv);
         }
         __syncwarp();
         if (has_res && more) {

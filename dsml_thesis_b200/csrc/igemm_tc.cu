@@ -183,7 +183,9 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
 
 // GG: the GEGLU-epilogue specialisation (no residual / NCHW / statistics code in it: the erf-GELU epilogue is the bound of
 // those GEMMs and needs the registers); GG == false handles every other epilogue.
-template <int BN, int BK, int EW, bool GG>
+// O16: the output is a 16-bit type (bf16 / f16) — a template parameter, like GG, so that each instantiation carries one
+// store path only (the kernel was losing 8 % of its issue slots to instruction fetch, ncu r01v).
+template <int BN, int BK, int EW, bool GG, bool O16>
 __global__ void __launch_bounds__(64 + EW * 32, 1)
 igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                 const __grid_constant__ CUtensorMap tmB, const TcParams p) {
@@ -334,7 +336,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     constexpr int NCH = BN / Cfg::CH;
     constexpr int PITCH = Cfg::EPI_PITCH;
     float* st = epi + ew * 32 * PITCH;
-    const bool out16 = p.out_dtype != LDMB200_F32;
+    constexpr bool out16 = O16;
     const bool has_res = !GG && p.residual != nullptr;
     uint32_t t_iter = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
@@ -380,7 +382,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
           __syncwarp();
           if (lane == 0) mbar_arrive(&tempty[buf]);
         }
-        if (!GG && p.out_nchw) {
+        if (!GG && !O16 && p.out_nchw) {
           // UNetModel.out conv: thread owns pixel m, writes the n_valid real channels as fp32 NCHW
           const int m = m0 + lane;
           if (m < p.M) {
@@ -451,13 +453,13 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   }
 }
 
-template <int BN, int BK, int EW, bool GG = false>
-static int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b, const TcParams& p,
+template <int BN, int BK, int EW, bool GG, bool O16>
+static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b, const TcParams& p,
                      cudaStream_t st) {
   using Cfg = TcCfg<BN, BK, EW>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG, O16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::SMEM_BYTES);
     if (e != cudaSuccess) {
       set_error("igemm_tc: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
@@ -466,9 +468,16 @@ static int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtenso
     attr_set = true;
   }
   int grid = std::min(p.tiles_m * p.tiles_n, sm_count());
-  igemm_tc_kernel<BN, BK, EW, GG><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(a1, a2, b, p);
+  igemm_tc_kernel<BN, BK, EW, GG, O16><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(a1, a2, b, p);
   LDM_CHECK_LAUNCH("igemm_tc");
   return 0;
+}
+
+template <int BN, int BK, int EW, bool GG = false>
+static int launch_tc(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b, const TcParams& p,
+                     cudaStream_t st) {
+  if (p.out_dtype != LDMB200_F32) return launch_tc_impl<BN, BK, EW, GG, true>(a1, a2, b, p, st);
+  return launch_tc_impl<BN, BK, EW, GG, false>(a1, a2, b, p, st);
 }
 
 static bool is_pow2(int x) { return x > 0 && (x & (x - 1)) == 0; }
@@ -585,10 +594,8 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   if (BN == 128) return d->geglu ? launch_tc<128, 64, 16, true>(tA1, tA2, tB, p, st) : launch_tc<128, 64, 16>(tA1, tA2, tB, p, st);
   LDM_CHECK_ARG(!d->geglu || d->n % 32 == 0, "igemm_tc: geglu needs n %% 32 == 0 (got n=%d)", d->n);
   if (d->geglu) return launch_tc<32, 64, 8, true>(tA1, tA2, tB, p, st);
-  // experiment switch (measured r01n: 16 epilogue warps on the plain 1x1 GEMMs are SLOWER, 32.1 vs 30.0 ms per UNet
-  // eval — 5 chunks over 4 warps per quarter is unbalanced and the ring loses a stage — so the default stays 8)
-  static const bool ew16 = getenv("LDMB200_TC_EW16") ? atoi(getenv("LDMB200_TC_EW16")) != 0 : false;
-  if (BN == 160 && d->ksize == 1 && ew16) return launch_tc<160, 64, 16>(tA1, tA2, tB, p, st);
+  // (16 epilogue warps on the plain 160-wide tiles were measured r01n and are SLOWER, 32.1 vs 30.0 ms per UNet eval —
+  // 5 chunks over 4 warps per quarter is unbalanced and the ring loses a stage — so that instantiation is not built)
   if (BN == 160) return launch_tc<160, 64, 8>(tA1, tA2, tB, p, st);
   if (BN == 32) return launch_tc<32, 64, 8>(tA1, tA2, tB, p, st);
   return launch_tc<16, 64, 8>(tA1, tA2, tB, p, st);

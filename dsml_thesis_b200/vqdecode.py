@@ -28,7 +28,7 @@ import torch.nn as nn
 
 from . import _cabi
 from ._cabi import F32, GemmDesc
-from .unet import _Act, _Arena, _Buf, _Plan, _WeightPack, _tc_cpad
+from .unet import _Act, _Arena, _Plan, _WeightPack, _tc_cpad
 
 
 # ----------------------------------------------------------------------------------------------

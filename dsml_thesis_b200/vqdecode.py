@@ -1,4 +1,4 @@
-"""First-stage decode on the B200 kernels: drop-in for ``VQModelInterface.decode``
+"""First stage on the B200 kernels.  Decode: drop-in for ``VQModelInterface.decode``
 (ldm/models/autoencoder.py:274-283) = ``VectorQuantizer2`` nearest-code lookup (taming/modules/vqvae/quantize.py:285-312)
 → ``post_quant_conv`` → ``Decoder`` (ldm/modules/diffusionmodules/model.py:462-569).
 
@@ -14,6 +14,10 @@ quantize), a static launch list over the same channels-last arena, weight pack a
   S = q kᵀ and O = P v run through the SAME implicit-GEMM kernel with the sample's k and vᵀ as the "weight" operand
   (vᵀ = W_v · hᵀ is produced directly in that layout by swapping the operands of the v projection, and v's bias moves
   to the O epilogue because softmax rows sum to one); softmax rows by ``ldmb200_softmax_rows``.
+
+Encode (row n4, ``encode_first_stage`` of the masked frame in progressive sampling): ``VQEncoder`` =
+``quant_conv(Encoder(x))`` (autoencoder.py:269-272, model.py:368-459) as one more launch plan; its ``Downsample`` pads
+(0,1,0,1) and strides by 2, which the implicit GEMM takes as ``pad_mode = 1``.
 
 No CPU fallback: CPU tensors raise ``Ldmb200Error``.
 """

@@ -1,4 +1,4 @@
-"""CPU oracle of the first-stage decode — TEST INFRASTRUCTURE ONLY.
+"""CPU oracle of the first stage: decode and encode (row n4) — TEST INFRASTRUCTURE ONLY.
 
 Functional fp32 restatement (torch CPU ops over a plain state dict) of ``VQModelInterface.decode``
 (ldm/models/autoencoder.py:274-283): ``VectorQuantizer2.forward`` (taming/modules/vqvae/quantize.py:285-312) →
@@ -6,8 +6,11 @@ Functional fp32 restatement (torch CPU ops over a plain state dict) of ``VQModel
 ``ResnetBlock`` (model.py:120-142, temb=None), ``AttnBlock`` (172-198), ``Upsample`` (53-57), ``Normalize`` (38-39,
 GroupNorm 32 groups eps 1e-6) and the swish ``nonlinearity`` (33-35).
 
+The encode half restates ``VQModelInterface.encode`` (autoencoder.py:269-272): ``Encoder.forward`` (model.py:433-459) with
+the (0,1,0,1)-padded stride-2 ``Downsample`` (72-76) → ``quant_conv``.
+
 Pinned by ``tests/test_oracle_golden.py`` against outputs of the REAL reference modules
-(``tests/golden/make_golden.py: vq_goldens`` → ``tests/golden/vqdecode.npz``).  Only ``tests/``, ``smoke()`` and
+(``tests/golden/make_golden.py: vq_goldens / vq_encode_goldens`` → ``tests/golden/vqdecode.npz``, ``vqencode.npz``).  Only ``tests/``, ``smoke()`` and
 ``bench.py``'s CPU-baseline legs may import this module; the product never does.
 """
 from __future__ import annotations

@@ -534,6 +534,8 @@ def torch_eager_gpu_leg(args):
     B200 (the oracle's functional restatement, which is bit-identical to the reference modules on CPU; the reference tree
     itself does not travel to the GPU box): fp32 with TF32 off, fp32 with torch's defaults (cuDNN TF32 convolutions), and
     torch.autocast(bfloat16).  Times UNet evals only (the DDIM update is <0.1 % of a step) on config C2."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return                                   # a single-GPU baseline: under torchrun only rank 0 runs it
     import torch
     from oracle import ldm_oracle as O
     torch.cuda.set_device(0)

@@ -38,6 +38,11 @@ REF_GFLOP_PER_EVAL = {32: 46.0, 64: 230.0, 128: 1657.0}
 METRIC = "DDIM samples/s (64x64x3 latent, 50 steps)"
 
 
+def metric_name(hw, ddim):
+    """BASELINE.json's metric, with the latent size / step count actually run spelled out."""
+    return f"DDIM samples/s ({hw}x{hw}x3 latent, {ddim} steps)"
+
+
 def init_weights(unet, seed=0):
     """Deterministic non-zero synthetic weights (same recipe as oracle.ldm_oracle.init_state_dict, restated here
     because the product path must not import oracle/): U(-1,1)*sqrt(3/fan_in) weights, small biases, norm gains ~1."""
@@ -662,7 +667,7 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     workload = (f"C2: face_reenactment UNet (in 3, ctx 512, 156.8M params), {args.hw}x{args.hw}x3 latents, "
                 f"batch {args.batch}/GPU, {args.ddim}-step DDIM eta=0")
-    metric = METRIC
+    metric = metric_name(args.hw, args.ddim)
     if c3:
         workload = (f"C3: talking_face UNet (in 9 = latent + masked-frame + reference-frame latents, audio ctx 1024), "
                     f"{args.hw}x{args.hw} latents, {args.batch} streams/GPU, {args.frames} autoregressive frames x "
@@ -677,7 +682,8 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        value, cores, sample, per, n = cpu_reference_leg(args.hw, args.ddim, max(1, args.steps), max(0, args.warmup))
+        value, cores, sample, per, n = cpu_reference_leg(args.hw, args.ddim, max(10, args.steps), max(0, args.warmup),
+                                                         budget_s=120.0)
         line = {"impl": "reference", "metric": metric, "value": value, "unit": "samples/s", "n_gpus": args.gpus,
                 "steps": n, "warmup": args.warmup, "ms_per_step": per * 1e3, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -709,7 +715,7 @@ def main():
     smp = P.DDIMSampler2Cond(model) if c3 else P.DDIMSampler(model)
     ctx_dim = 1024 if c3 else 512
 
-    # per-rank synthetic inputs: seeds derive from the GLOBAL sample index, so results do not depend on N
+    # per-rank synthetic inputs (seed 1000 + rank: each rank draws its own batch; throughput does not depend on values)
     g = torch.Generator().manual_seed(1000 + rank)
     x_host = torch.randn(B, 3, HW, HW, generator=g).pin_memory()
     c_host = torch.randn(B, 1, ctx_dim, generator=g).pin_memory()
@@ -810,6 +816,37 @@ def main():
             sample_e2e()
         ms_e2e = timed(sample_e2e, args.steps)
 
+        # ---- strong scaling (N > 1): the SAME global batch as one GPU runs, split over the ranks by sample_sharded —
+        # the small-per-GPU-batch regime (8 samples per GPU at N = 8) where wave quantisation and per-tile epilogue
+        # latency, not a collective, limit scaling.  Global inputs are identical on every rank (seed 999).
+        strong = None
+        if world > 1 and not c3:
+            gg = torch.Generator().manual_seed(999)
+            xg = torch.randn(B, 3, HW, HW, generator=gg).to(dev)
+            cg = torch.randn(B, 1, ctx_dim, generator=gg).to(dev)
+
+            def sample_strong():
+                out, _ = P.sample_sharded(smp, T, B, [3, HW, HW], conditioning=cg, x_T=xg, eta=0.0)
+                return out
+            for _ in range(2):
+                sample_strong()
+            ms_strong = timed(sample_strong, args.steps)
+            lo, hi = P.shard_range(B, world, rank)
+            sp = unet._plans.get((hi - lo, HW, HW, 1, args.precision))
+            sfam = {}
+            if sp is not None:
+                sp.run_timed(torch.cuda.current_stream())
+                for name, t_ms, fl, by, _w in sp.run_timed(torch.cuda.current_stream()):
+                    f = sfam.setdefault(name, [0.0, 0.0])
+                    f[0] += t_ms
+                    f[1] += fl
+            strong = {"global_batch": B, "per_gpu_batch": hi - lo, "value": args.steps * B / (ms_strong * 1e-3),
+                      "unit": "samples/s", "ms_per_step": ms_strong / args.steps,
+                      "kernel_breakdown_ms_per_eval": {k: round(v[0], 4) for k, v in sorted(sfam.items(), key=lambda kv: -kv[1][0])},
+                      "kernel_tflops": {k: round(v[1] / (v[0] * 1e-3) / 1e12, 1) for k, v in sfam.items() if v[1] > 0 and v[0] > 0},
+                      "how": "sample_sharded: contiguous shards of one global batch, no data-path collective, final all_gather; "
+                             "device time, max over ranks; breakdown = rank 0's plan at its shard size"}
+
         # ---- roofline of the dominant kernel family, CUDA events around every launch of one UNet eval
         plan = next(iter(unet._plans.values()))
         if plan.pack is not None:
@@ -839,15 +876,18 @@ def main():
     peak_src = "MEASURED_PEAKS.json bf16_tflops_sustained (kernel timed inside a long step)" if peaks else \
         "fallback 1.4 PFLOP/s sustained (B200_PROFILING.md)"
     dom = "ldmb200_igemm_tc" if args.precision != "fp32" else "ldmb200_igemm_simt"
-    # DRAM traffic of the family's launches in one eval, from the committed ncu capture of the same workload
-    traffic, traffic_src = None, None
-    if dom == "ldmb200_igemm_tc" and B == 64 and HW == 64 and args.precision == "f16":
+    # DRAM traffic per kernel family in one eval, from the committed ncu capture of the same workload with the same
+    # kernels (profiles/traffic_r02*.json, tools/summarize_traffic.py)
+    traffic, traffic_src, traffic_fam = None, None, None
+    if B == 64 and HW == 64 and args.precision == "f16" and not c3:
         import glob
-        cand = sorted(glob.glob(os.path.join(ROOT, "profiles", "traffic_gemm_*.json")))
+        cand = sorted(glob.glob(os.path.join(ROOT, "profiles", "traffic_r*.json")))
         if cand:
             try:
                 tj = json.load(open(cand[-1]))
-                traffic, traffic_src = tj["dram_bytes_total"], os.path.relpath(cand[-1], ROOT)
+                traffic_src = os.path.relpath(cand[-1], ROOT)
+                traffic_fam = {k: v["dram_bytes_total"] for k, v in tj["families"].items()}
+                traffic = traffic_fam.get(dom)
             except Exception:
                 pass
     d = fam[dom]
@@ -900,11 +940,16 @@ def main():
                      "how": "sum of algorithmic FLOPs of the family's launches in one UNet eval / sum of their "
                             "CUDA-event durations on the launching stream"},
         "roofline_attention": attn_roof,
+        "traffic_by_family": ({k: {"dram_bytes_per_eval": traffic_fam.get(k), "algorithmic_bytes_per_eval": v[2] or None,
+                                   "ms_per_eval": round(v[0], 4)} for k, v in fam.items() if traffic_fam.get(k)}
+                              if traffic_fam else None),
         "kernel_breakdown_ms_per_eval": {k: round(v[0], 4) for k, v in sorted(fam.items(), key=lambda kv: -kv[1][0])},
         "eval_ms_sum_of_kernels": eval_ms,
     }
+    if strong is not None:
+        line["strong"] = strong
     if not args.no_cpu_baseline and not c3:
-        v, cores, sample, per, n = cpu_reference_leg(HW, T, 3, 1)
+        v, cores, sample, per, n = cpu_reference_leg(HW, T, 12, 1, budget_s=30.0)
         line["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample}
     print(json.dumps(line))
     if world > 1:

@@ -1,24 +1,28 @@
 // Fused flash-style self-attention for d_head = 32 on tcgen05 (K5): softmax(q k^T * scale) v per (sample, head)
 // without materialising the [N, N] score matrix the reference builds (attention.py:180-191).
 //
-// The op is MUFU / TMEM-read bound, not tensor-bound: every score needs one ex2 (16/clk/SM) and 4 bytes of TMEM
-// read (64 B/clk/SM) but only 128 tensor flops, so the design goal is to keep the exponent pipe busy all the time.
+// The op is MUFU / issue-slot bound, not tensor-bound: every score needs one ex2 (16/clk/SM) but only 128 tensor
+// flops, so the design goal is the fewest issue slots per score next to the exponential.
 // One CTA per (384-query block, head, sample), one CTA per SM, three 128-query tiles per CTA (three softmax
-// warpgroups = 3 warps per scheduler to hide the ex2 / TMEM latencies); keys advance in 64-key steps with S and P
+// warpgroups = 3 warps per scheduler to hide the ex2 / TMEM latencies); keys advance in 64-key steps with S
 // double-buffered per query tile, so the tensor pipe always works one step ahead of every softmax warpgroup.
 //   warps 0-11  : softmax warpgroup q = warp / 4   (thread r <-> query row r <-> TMEM lane r)
 //   warps 12-14 : MMA issuer of query tile q = warp - 12 (one elected lane) — one per scheduler, so no scheduler
 //                 carries two service warps:  S_q(i) = Q_q K(i)^T (M128 N64 K32) into TMEM cols q*128 + (i&1)*64;
-//                 O_q += P_q(i) V(i) (M128 N32 K64, V as MN-major B operand straight from the row-major tile) into
-//                 TMEM cols 384 + 32q.  Per step i: wait p_full_q(i) -> issue P.V_q(i), S_q(i+2), commit s_full_q.
+//                 O_q += P_q(i) V(i) (M128 N32 K64; A = P straight from TENSOR MEMORY, V as MN-major B operand from
+//                 the row-major smem tile) into TMEM cols 384 + 32q.  Per step i: wait p_full_q(i) -> issue
+//                 P.V_q(i), S_q(i+2), commit s_full_q.
 //   warp  15    : TMA producer — the Q tiles once, then K/V tiles (128 keys x 32) through a 3-stage ring, all from
 //                 the fused QKV matrix [B*N, 3C] through one 2-D tensor map (64B-swizzled K-major rows of 32 x 16
 //                 bit); also owns barrier initialisation and the TMEM allocation
-// Softmax: ONE pass over S in TMEM per KV tile (TMEM read bandwidth, ~64 B/clk/SM, and the ex2 pipe bound the
-// kernel): p = exp2(s*c - ref) against a per-row reference that is only re-based when a tile's row max outgrows it
-// by more than 2^8 (any finite reference is exact after normalisation); the running output accumulates in TMEM
-// across KV tiles (no per-tile read-back / rescale) and is re-based in place (tcgen05.ld/st) on that rare path.
-// P is written as bf16 into a 128B-swizzled K-major smem tile for the PV MMA.
+// Softmax: ONE pass over S in TMEM per 64-key step: p = exp2(s*c - ref) against a per-row reference that is only
+// re-based when a p outgrows 2^8 (any finite reference is exact after normalisation); the running output
+// accumulates in TMEM across KV tiles (no per-tile read-back / rescale) and is re-based in place (tcgen05.ld/st) on
+// that rare path.  Issue-slot diet of the inner loop (r02): s*c - ref and the row sum run on the packed fp32 pipe
+// (FFMA2 / FADD2: two scores per instruction); the per-step row max is NOT computed on the fast path — a step whose
+// row sum stays <= 2^8 cannot hold a p above 2^8, so the exact max is only taken when that gate trips; P (bf16) is
+// written back over the first 32 columns of its own S buffer with one tcgen05.st and consumed by the PV MMA as its
+// TMEM A operand, so there is no shared-memory restage, no swizzle arithmetic and no async-proxy fence.
 #include <algorithm>
 
 #include "common.cuh"
@@ -28,36 +32,22 @@ namespace ldm {
 constexpr int AT_NQ = 3;                      // 128-query tiles per CTA (softmax warpgroups)
 constexpr int AT_THREADS = 32 * (5 * AT_NQ + 1);  // 12 softmax warps, one MMA warp per query tile, one TMA warp
 constexpr int AT_MMA_WARP0 = 4 * AT_NQ, AT_TMA_WARP = 5 * AT_NQ;
-constexpr int AT_O_COL = AT_NQ * 128;          // TMEM: S_q buffers at q*128 + u*64, O_q at AT_O_COL + q*32
-constexpr int AT_STAGES = 3;
+constexpr int AT_O_COL = AT_NQ * 128;          // TMEM: S_q buffers at q*128 + u*64 (P_q(i) over cols 0..31), O_q at AT_O_COL + q*32
+constexpr int AT_STAGES = 4;
 constexpr int AT_TILE_BYTES = 128 * 32 * 2;  // 8 KiB: 128 rows x 32 16-bit values
-constexpr int AT_P_BYTES = 2 * 128 * 128;    // two K-major chunks of [128 x 64] bf16, 128B swizzle
-constexpr int AT_SMEM = AT_NQ * AT_TILE_BYTES + 2 * AT_STAGES * AT_TILE_BYTES + AT_NQ * AT_P_BYTES + 32 * 8 + 16 + 1024;
+constexpr int AT_SMEM = AT_NQ * AT_TILE_BYTES + 2 * AT_STAGES * AT_TILE_BYTES + 32 * 8 + 16 + 1024;
 constexpr int AT_TMEM_COLS = 512;
-#ifndef LDM_AT_POLY_PAIRS
-#define LDM_AT_POLY_PAIRS 0
+#ifndef LDM_AT_POLY
+#define LDM_AT_POLY 0
 #endif
-// 0..4: share (x 25 %) of the exponentials emulated on the FMA pipe.  Measured r01s (tools/attn_sweep.py, B=64 N=4096):
-// 0 -> 1.766 ms, 1 -> 1.831 ms, 2 -> 2.048 ms: the softmax warps are latency-bound (ex2 unit 70 % busy, issue slots
-// 36 %), the extra ~8 FMA-pipe instructions per emulated exponential only lengthen the critical path, so the default is 0.
-constexpr int AT_POLY_PAIRS = LDM_AT_POLY_PAIRS;
+// 0..8: of every 8 score pairs, this many take their exponentials on the FMA pipe (packed degree-3 polynomial)
+// instead of the ex2 unit.  Sweep with tools/attn_sweep.py; the shipped value is the measured optimum.
+constexpr int AT_POLY = LDM_AT_POLY;
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
-}
-// exp2 on the FMA pipe (FlashAttention-4 style): the ex2 unit (16/clk/SM) is the co-bound of this kernel with the TMEM
-// read port, so a fraction of the exponentials is emulated — round-to-nearest split x = n + f, |f| <= 0.5 (magic-number
-// add), degree-3 minimax 2^f (max rel. error 7.5e-5, far below the bf16 rounding of P), exponent add of n.
-__device__ __forceinline__ float ex2_poly(float x) {
-  x = fmaxf(x, -125.0f);
-  const float t = x + 12582912.0f;                 // 1.5 * 2^23: the integer part lands in the low mantissa bits
-  const float f = x - (t - 12582912.0f);
-  float p = fmaf(0.05517146f, f, 0.24261086f);
-  p = fmaf(p, f, 0.69326099f);
-  p = fmaf(p, f, 0.99992809f);
-  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
 }
 __device__ __forceinline__ float fmax3(float a, float b, float c) {
   float y;
@@ -78,9 +68,96 @@ __device__ __forceinline__ uint32_t pack_out16(float lo, float hi, int dt) {
   return r;
 }
 
-// row max of one 32-column chunk on 4 independent chains; MASK: columns >= valid are ignored
+// ---- packed fp32 (sm_100 FFMA2 / FADD2: two lanes per issue slot) ----
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpk2(f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+
+// exp2 of a score pair on the FMA pipe (FlashAttention-4 style): the ex2 unit (16/clk/SM) bounds this kernel, so a
+// share of the exponentials is emulated — round-to-nearest split x = n + f, |f| <= 0.5 (magic-number add), degree-3
+// minimax 2^f (max rel. error 7.5e-5, far below the bf16 rounding of P), exponent add of n.  x is clamped from below
+// (2^-125 ~ 0); the caller guards the upper side (x > 126 would wrap the exponent) through `gmax`.
+__device__ __forceinline__ void ex2_poly2(f32x2 x2, float& p0, float& p1, float& gmax) {
+  float x0, x1;
+  unpk2(x2, x0, x1);
+  x0 = fmaxf(x0, -125.0f);
+  x1 = fmaxf(x1, -125.0f);
+  gmax = fmax3(gmax, x0, x1);
+  x2 = pk2(x0, x1);
+  const f32x2 magic = pk2(12582912.0f, 12582912.0f);   // 1.5 * 2^23: the integer part lands in the low mantissa bits
+  const f32x2 t2 = add2(x2, magic);
+  const f32x2 f2 = sub2(x2, sub2(t2, magic));
+  f32x2 q2 = fma2(pk2(0.05517146f, 0.05517146f), f2, pk2(0.24261086f, 0.24261086f));
+  q2 = fma2(q2, f2, pk2(0.69326099f, 0.69326099f));
+  q2 = fma2(q2, f2, pk2(0.99992809f, 0.99992809f));
+  float q0, q1, t0, t1;
+  unpk2(q2, q0, q1);
+  unpk2(t2, t0, t1);
+  p0 = __int_as_float(__float_as_int(q0) + (__float_as_int(t0) << 23));
+  p1 = __int_as_float(__float_as_int(q1) + (__float_as_int(t1) << 23));
+}
+
+// tcgen05.wait::ld that also names the destination registers of the load it completes, so the compiler cannot
+// schedule a use of them above the wait (the asynchronous write is invisible to it otherwise)
+#define LDM_R8(v, o) "+f"(v[o]), "+f"(v[o + 1]), "+f"(v[o + 2]), "+f"(v[o + 3]), "+f"(v[o + 4]), "+f"(v[o + 5]), "+f"(v[o + 6]), "+f"(v[o + 7])
+__device__ __forceinline__ void tmem_wait_regs(float (&v)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : LDM_R8(v, 0), LDM_R8(v, 8), LDM_R8(v, 16), LDM_R8(v, 24)::"memory");
+}
+__device__ __forceinline__ void reg_fence(float (&v)[32]) {
+  asm volatile("" : LDM_R8(v, 0), LDM_R8(v, 8), LDM_R8(v, 16), LDM_R8(v, 24)::"memory");
+}
+
+// p = exp2(s*c - mb) for one 32-column chunk: packed FFMA2 for the argument, ex2 unit (or FMA-pipe polynomial for
+// AT_POLY of every 8 pairs), packed row sum on two chains, bf16 pack into 16 registers.  MASK: columns >= valid -> 0.
 template <bool MASK>
-__device__ __forceinline__ void chunk_max(const float (&v)[32], float (&mx)[4], int col0, int valid) {
+__device__ __forceinline__ void chunk_exp(const float (&v)[32], f32x2 (&ls)[2], f32x2 c2, f32x2 nmb2, int col0, int valid,
+                                          uint32_t* pk, float& gmax) {
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const f32x2 x2 = fma2(pk2(v[2 * j], v[2 * j + 1]), c2, nmb2);
+    float p0, p1;
+    if ((j & 7) < AT_POLY) {
+      ex2_poly2(x2, p0, p1, gmax);
+    } else {
+      float x0, x1;
+      unpk2(x2, x0, x1);
+      p0 = ex2_approx(x0);
+      p1 = ex2_approx(x1);
+    }
+    if (MASK) {
+      if (col0 + 2 * j >= valid) p0 = 0.f;
+      if (col0 + 2 * j + 1 >= valid) p1 = 0.f;
+    }
+    ls[j & 1] = add2(ls[j & 1], pk2(p0, p1));
+    pk[j] = pack_bf16x2(p0, p1);
+  }
+}
+
+// exact row max of one 64-key step (the slow path and the first step's reference); MASK: columns >= valid ignored
+template <bool MASK>
+__device__ __forceinline__ float chunk_max32(const float (&v)[32], int col0, int valid) {
+  float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
   if (MASK) {
 #pragma unroll
     for (int i = 0; i < 32; ++i)
@@ -94,77 +171,44 @@ __device__ __forceinline__ void chunk_max(const float (&v)[32], float (&mx)[4], 
       mx[3] = fmax3(mx[3], v[i + 6], v[i + 7]);
     }
   }
+  return fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
 }
-
-// p = exp2(s*c - mb) for one 32-column chunk, row sum on 4 chains, bf16 pack and swizzled store of the
-// thread's 64 bytes: chunk c of the row -> 64-key half (c>>1), 16-byte units (c&1)*4 .. +3
 template <bool MASK>
-__device__ __forceinline__ void chunk_exp_store(const float (&v)[32], float (&ls)[4], float c_, float mb, int c,
-                                                int valid, uint8_t* sP, int r) {
-  uint8_t* rowp = sP + (c >> 1) * (128 * 128) + r * 128;
-#pragma unroll
-  for (int u = 0; u < 4; ++u) {  // 8 columns -> one 16-byte unit
-    uint32_t pk[4];
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int i = u * 8 + e * 2;
-      // AT_POLY_PAIRS of every 4 column pairs go to the FMA pipe, the rest to the ex2 unit
-      float p0, p1;
-      if (e >= 4 - AT_POLY_PAIRS) {
-        p0 = ex2_poly(fmaf(v[i], c_, -mb));
-        p1 = ex2_poly(fmaf(v[i + 1], c_, -mb));
-      } else {
-        p0 = ex2_approx(fmaf(v[i], c_, -mb));
-        p1 = ex2_approx(fmaf(v[i + 1], c_, -mb));
-      }
-      if (MASK) {
-        if (c * 32 + i >= valid) p0 = 0.f;
-        if (c * 32 + i + 1 >= valid) p1 = 0.f;
-      }
-      ls[e] += p0 + p1;
-      pk[e] = pack_bf16x2(p0, p1);
-    }
-    const int unit = (c & 1) * 4 + u;
-    *reinterpret_cast<uint4*>(rowp + ((unit ^ (r & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-  }
-}
-
-// tcgen05.wait::ld that also names the destination registers of the load it completes, so the compiler cannot
-// schedule a use of them above the wait (the asynchronous write is invisible to it otherwise)
-#define LDM_R8(v, o) "+f"(v[o]), "+f"(v[o + 1]), "+f"(v[o + 2]), "+f"(v[o + 3]), "+f"(v[o + 4]), "+f"(v[o + 5]), "+f"(v[o + 6]), "+f"(v[o + 7])
-__device__ __forceinline__ void tmem_wait_regs(float (&v)[32]) {
-  asm volatile("tcgen05.wait::ld.sync.aligned;" : LDM_R8(v, 0), LDM_R8(v, 8), LDM_R8(v, 16), LDM_R8(v, 24)::"memory");
-}
-__device__ __forceinline__ void reg_fence(float (&v)[32]) {
-  asm volatile("" : LDM_R8(v, 0), LDM_R8(v, 8), LDM_R8(v, 16), LDM_R8(v, 24)::"memory");
-}
-
-// One 64-key step for query row r, ONE pass over S (64 fp32 columns at tS; TMEM reads are the scarce resource):
-// p = exp2(s*c - mb) against the row's current reference mb (= m_ref*c), the step's row max and row sum on the
-// side, P (bf16) into the swizzled smem tile.  FIRST: the reference is not known yet — take the max of the
-// first 32 keys (any finite reference is exact after normalisation; the caller re-references on overflow risk).
-template <bool MASK, bool FIRST>
-__device__ __forceinline__ void score_pass(uint32_t tS, int valid, float c_, float& mb, float& tmax, float& lsum,
-                                           uint8_t* sP, int r) {
+__device__ __noinline__ float step_rowmax(uint32_t tS, int valid) {
   float a[32], b[32];
-  float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-  float ls[4] = {0.f, 0.f, 0.f, 0.f};
   tmem_ld_32x32(tS, a);
   tmem_ld_32x32(tS + 32, b);
   tmem_wait_regs(a);
   reg_fence(b);
-  chunk_max<MASK>(a, mx, 0, valid);
-  if (FIRST) mb = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])) * c_;
-  chunk_exp_store<MASK>(a, ls, c_, mb, 0, valid, sP, r);
-  chunk_max<MASK>(b, mx, 32, valid);
-  chunk_exp_store<MASK>(b, ls, c_, mb, 1, valid, sP, r);
-  tmax = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
-  lsum = (ls[0] + ls[1]) + (ls[2] + ls[3]);
+  return fmaxf(chunk_max32<MASK>(a, 0, valid), chunk_max32<MASK>(b, 32, valid));
+}
+
+// One 64-key step for query row r, ONE pass over S (64 fp32 columns at tS): p = exp2(s*c - mb) against the row's
+// current reference mb (= m_ref*c), the step's row sum on the side, P (bf16 pairs) into pk[32] (stored to TMEM by the
+// caller once the overflow gate has passed).  FIRST: the reference is not known yet — take the max of the first 32
+// keys (any finite reference is exact after normalisation; the caller re-references on overflow risk).
+// gmax: largest exponent argument seen by the FMA-pipe exponentials (their upper-range guard).
+template <bool MASK, bool FIRST>
+__device__ __forceinline__ void score_pass(uint32_t tS, int valid, float c_, float& mb, float& lsum, float& gmax,
+                                           uint32_t (&pk)[32]) {
+  float a[32], b[32];
+  tmem_ld_32x32(tS, a);
+  tmem_ld_32x32(tS + 32, b);
+  tmem_wait_regs(a);
+  reg_fence(b);
+  if (FIRST) mb = chunk_max32<MASK>(a, 0, valid) * c_;
+  const f32x2 c2 = pk2(c_, c_), nmb2 = pk2(-mb, -mb);
+  f32x2 ls[2] = {0ull, 0ull};
+  gmax = -INFINITY;
+  chunk_exp<MASK>(a, ls, c2, nmb2, 0, valid, pk, gmax);
+  chunk_exp<MASK>(b, ls, c2, nmb2, 32, valid, pk + 16, gmax);
+  float s0, s1;
+  unpk2(add2(ls[0], ls[1]), s0, s1);
+  lsum = s0 + s1;
 }
 
 // 32 fp32 columns of this thread's TMEM lane <- registers (the rare re-referencing of the running output)
-__device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const float* v) {
-  const uint32_t* r = reinterpret_cast<const uint32_t*>(v);
+__device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t* r) {
   asm volatile(
       "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
       "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
@@ -177,25 +221,36 @@ __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const float* v) {
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
+// D[tmem] (+)= A[tmem] * B[smem desc]: A = bf16 pairs, lane = row, one 32-bit column per two K elements (K-major)
+__device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
 // how far (in exp2 units) a tile's row max may exceed the row's reference before the row is re-referenced:
 // p <= 2^8 per score, sums stay far inside the fp32 / bf16 exponent range
 constexpr float AT_REREF = 8.0f;
+constexpr float AT_GATE = 256.0f;           // 2^AT_REREF
 
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict__ out, int out_ld, int out_dtype,
                     int n_tok, int q_off, int k_off, int v_off, float scale_log2e, float* __restrict__ lse2) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint8_t* sQ = smem;                               // 2 tiles (256 rows), one TMA box
+  uint8_t* sQ = smem;                               // AT_NQ tiles of 128 query rows
   uint8_t* sK = sQ + AT_NQ * AT_TILE_BYTES;             // AT_STAGES tiles
   uint8_t* sV = sK + AT_STAGES * AT_TILE_BYTES;     // AT_STAGES tiles
-  uint8_t* sP = sV + AT_STAGES * AT_TILE_BYTES;     // 2 x 32 KiB, 1024-aligned (8 x 8 KiB offset)
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + AT_NQ * AT_P_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + AT_STAGES * AT_TILE_BYTES);
   uint64_t* q_full = bars;
   uint64_t* kv_full = bars + 1;                     // [AT_STAGES]
   uint64_t* kv_empty = kv_full + AT_STAGES;         // [AT_STAGES]
-  uint64_t* s_full = kv_empty + AT_STAGES;          // [2 q][2 buf]  S_q(i) ready (and every MMA issued before it)
-  uint64_t* p_full = s_full + 2 * AT_NQ;                    // [2 q][2 buf]  P_q(i) written, S_q(i) consumed
+  uint64_t* s_full = kv_empty + AT_STAGES;          // [q][2 buf]  S_q(i) ready (and every MMA issued before it)
+  uint64_t* p_full = s_full + 2 * AT_NQ;                    // [q][2 buf]  P_q(i) stored over S_q(i) in TMEM
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_full + 2 * AT_NQ);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -257,11 +312,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
       constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 64, 0, 0);
       constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 32, 0, 1);          // B = V is MN-major
       constexpr uint32_t hi_sw64 = (512u >> 4) | (1u << 14) | (4u << 29);    // Q, K (K-major) and V (MN-major) tiles
-      constexpr uint32_t hi_sw128 = (1024u >> 4) | (1u << 14) | (2u << 29);  // P tile
       const uint32_t q_lo = (((smem_u32(sQ) & 0x3FFFFu) >> 4) | (1u << 16)) + q * (AT_TILE_BYTES >> 4);
       const uint32_t k_lo = ((smem_u32(sK) & 0x3FFFFu) >> 4) | (1u << 16);
       const uint32_t v_lo = ((smem_u32(sV) & 0x3FFFFu) >> 4) | (1u << 16);
-      const uint32_t p_lo = (((smem_u32(sP) & 0x3FFFFu) >> 4) | (1u << 16)) + q * (AT_P_BYTES >> 4);
       const uint32_t dS = tmem_base + q * 128, dO = tmem_base + AT_O_COL + q * 32;
       // S_q(i) = Q_q . K(keys 64 i ..)^T -> TMEM columns q*128 + (i&1)*64;  st = smem stage of K/V tile i >> 1
       auto issue_s = [&](int i, int st) {
@@ -272,12 +325,13 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
                        ((uint64_t)hi_sw64 << 32) | (k_lo + st * (AT_TILE_BYTES >> 4) + hf * (4096 >> 4) + kk * 2),
                        idesc_qk, kk > 0);
       };
-      // O_q += P_q(i) . V(keys 64 i ..)   (the first step overwrites)
+      // O_q += P_q(i) . V(keys 64 i ..)   (the first step overwrites); P_q(i) = bf16 pairs in the first 32 columns of
+      // the S buffer it was computed from: 16 keys (one K step) = 8 columns
       auto issue_pv = [&](int i, int st) {
         const int hf = i & 1;
 #pragma unroll
         for (int t = 0; t < 4; ++t)
-          umma_bf16_ss(dO, ((uint64_t)hi_sw128 << 32) | (p_lo + hf * ((128 * 128) >> 4) + t * 2),
+          umma_bf16_ts(dO, dS + hf * 64 + t * 8,
                        ((uint64_t)hi_sw64 << 32) | (v_lo + st * (AT_TILE_BYTES >> 4) + (hf * 4 + t) * (1024 >> 4)),
                        idesc_pv, (i > 0 || t > 0) ? 1u : 0u);
       };
@@ -298,7 +352,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
         const int u = i & 1;
         const int st_next = (st + 1 == AT_STAGES) ? 0 : st + 1;
         const bool more = i + 2 < n_steps;
-        mbar_wait(&p_full[q * 2 + u], (i >> 1) & 1);  // all 128 rows of P_q(i) are in smem, S_q(i) is consumed
+        mbar_wait(&p_full[q * 2 + u], (i >> 1) & 1);  // all 128 rows of P_q(i) are in TMEM, S_q(i) is consumed
         tc_fence_after();
         if (elect_one()) issue_pv(i, st);
         __syncwarp();
@@ -322,7 +376,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
     const int r = threadIdx.x & 127;  // == TMEM lane
     const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
     const uint32_t tS = tmem_base + lane_sel + q * 128, tO = tmem_base + lane_sel + AT_O_COL + q * 32;
-    uint8_t* myP = sP + q * AT_P_BYTES;
     float mb = 0.f, l = 0.f;  // mb = (row reference) * c: the running output and l are relative to 2^mb
     const int last_valid = n_tok - (n_steps - 1) * 64;  // keys in the last step (1..64)
     const int my_steps = q < nq ? n_steps : 0;  // a query tile past the end of the sample does nothing
@@ -330,41 +383,48 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
       const int u = i & 1;
       const bool masked = (i == n_steps - 1) && last_valid < 64;
       const uint32_t tSu = tS + u * 64;
-      uint8_t* Pu = myP + u * (128 * 128);
-      mbar_wait(&s_full[q * 2 + u], (i >> 1) & 1);  // S_q(i) complete (and P_q.V(i-2): the P buffer is free again)
+      mbar_wait(&s_full[q * 2 + u], (i >> 1) & 1);  // S_q(i) complete (and P_q.V(i-2): the buffer's P half is free again)
       tc_fence_after();
-      float tmax, lsum;
+      float lsum, gmax;
+      uint32_t pk[32];
       if (i == 0) {
-        if (masked) score_pass<true, true>(tSu, last_valid, scale_log2e, mb, tmax, lsum, Pu, r);
-        else score_pass<false, true>(tSu, 64, scale_log2e, mb, tmax, lsum, Pu, r);
+        if (masked) score_pass<true, true>(tSu, last_valid, scale_log2e, mb, lsum, gmax, pk);
+        else score_pass<false, true>(tSu, 64, scale_log2e, mb, lsum, gmax, pk);
       } else {
-        if (masked) score_pass<true, false>(tSu, last_valid, scale_log2e, mb, tmax, lsum, Pu, r);
-        else score_pass<false, false>(tSu, 64, scale_log2e, mb, tmax, lsum, Pu, r);
+        if (masked) score_pass<true, false>(tSu, last_valid, scale_log2e, mb, lsum, gmax, pk);
+        else score_pass<false, false>(tSu, 64, scale_log2e, mb, lsum, gmax, pk);
       }
-      // lazy re-referencing: only when some row's scores outgrew its reference by more than 2^AT_REREF
-      const bool need = fmaf(tmax, scale_log2e, -mb) > AT_REREF;
-      if (__any_sync(0xffffffffu, need)) {
-        const float mb_new = need ? tmax * scale_log2e : mb;
-        const float f = ex2_approx(mb - mb_new);  // 1 for the rows that keep their reference
-        if (i > 0) {
-          // the output is rescaled in place: P.V(i-1) must have landed first (its commit is s_full of step i+1,
-          // issued even when there is no such step); P.V(i) cannot start before this thread arrives on p_full
-          mbar_wait(&s_full[q * 2 + (u ^ 1)], (((i - 1) >> 1) + 1) & 1);
-          tc_fence_after();
-          float t[32];
-          tmem_ld_32x32(tO, t);
-          tmem_wait_regs(t);
+      // overflow gate: every p is positive, so a row sum <= 2^AT_REREF bounds every p of the step; the comparison is
+      // written so that inf / NaN sums trip it.  FMA-pipe exponentials wrap above 2^126: their largest argument is
+      // tracked separately.  Only when the gate trips is the exact row max taken (S is still intact in TMEM).
+      const bool gate = !(lsum <= AT_GATE) || (AT_POLY > 0 && gmax > 100.0f);
+      if (__any_sync(0xffffffffu, gate)) {
+        const float tmax = masked ? step_rowmax<true>(tSu, last_valid) : step_rowmax<false>(tSu, 64);
+        // lazy re-referencing: only when some row's scores outgrew its reference by more than 2^AT_REREF
+        const bool need = fmaf(tmax, scale_log2e, -mb) > AT_REREF;
+        if (__any_sync(0xffffffffu, need)) {
+          const float mb_new = need ? tmax * scale_log2e : mb;
+          const float f = ex2_approx(mb - mb_new);  // 1 for the rows that keep their reference
+          if (i > 0) {
+            // the output is rescaled in place: P.V(i-1) must have landed first (its commit is s_full of step i+1,
+            // issued even when there is no such step); P.V(i) cannot start before this thread arrives on p_full
+            mbar_wait(&s_full[q * 2 + (u ^ 1)], (((i - 1) >> 1) + 1) & 1);
+            tc_fence_after();
+            float t[32];
+            tmem_ld_32x32(tO, t);
+            tmem_wait_regs(t);
 #pragma unroll
-          for (int d = 0; d < 32; ++d) t[d] *= f;
-          tmem_st_32x32(tO, t);
+            for (int d = 0; d < 32; ++d) t[d] *= f;
+            tmem_st_32x32(tO, reinterpret_cast<const uint32_t*>(t));
+          }
+          l *= f;
+          mb = mb_new;
+          if (masked) score_pass<true, false>(tSu, last_valid, scale_log2e, mb, lsum, gmax, pk);
+          else score_pass<false, false>(tSu, 64, scale_log2e, mb, lsum, gmax, pk);
         }
-        l *= f;
-        mb = mb_new;
-        if (masked) score_pass<true, false>(tSu, last_valid, scale_log2e, mb, tmax, lsum, Pu, r);
-        else score_pass<false, false>(tSu, 64, scale_log2e, mb, tmax, lsum, Pu, r);
       }
       l += lsum;
-      fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the UMMA (async proxy)
+      tmem_st_32x32(tSu, pk);  // P_q(i) over the first 32 columns of S_q(i) (incl. tcgen05.wait::st)
       tc_fence_before();
       mbar_arrive(&p_full[q * 2 + u]);
     }

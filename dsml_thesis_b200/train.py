@@ -728,32 +728,70 @@ class _UNetTrainFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, context, anchor, model, plan):
         ctx.model, ctx.plan = model, plan
+        # the plan owns every saved activation of the step: remember WHICH forward this node belongs to
+        ctx.gen, ctx.key = plan.steps, (plan.B, plan.H, plan.W, plan.L)
         return plan.out.clone()
 
     @staticmethod
     def backward(ctx, dout):
         model, plan = ctx.model, ctx.plan
         st = train_state(model)
+        if st.plans.get(ctx.key) is not plan or plan.steps != ctx.gen:
+            raise _cabi.Ldmb200Error(
+                "dsml_thesis_b200.UNetModel: backward of a training forward whose saved activations were overwritten by "
+                "a later training-mode forward (one live forward per model: run forward -> backward -> forward -> "
+                "backward; for several loss terms sum them before .backward(), for micro-batches call backward after "
+                "each forward)")
         with torch.cuda.device(dout.device):
             stream = torch.cuda.current_stream().cuda_stream
-            # p.grad is None (zero_grad(set_to_none=True)) -> fresh step: zero the arena; p.grad already a view of the
-            # arena -> the caller accumulates over micro-batches: keep adding (every kernel accumulates)
-            fresh = any(p.grad is None or p.grad.data_ptr() != st.views[id(p)].data_ptr() for p in st.params)
-            foreign = [(p, p.grad) for p in st.params
-                       if p.grad is not None and p.grad.data_ptr() != st.views[id(p)].data_ptr()]
-            if fresh:
-                st.flat.zero_()
+            # per parameter: p.grad is None (zero_grad(set_to_none=True)) -> its slot starts from zero; p.grad already the
+            # arena view -> the caller accumulates over micro-batches (every kernel adds); a foreign tensor (someone
+            # assigned p.grad) is folded into the slot.  Frozen parameters (requires_grad=False) never get a .grad and do
+            # not influence this decision; their slots are scratch.
+            live = [p for p in st.params if p.requires_grad]
+            is_view = {id(p): (p.grad is not None and p.grad.data_ptr() == st.views[id(p)].data_ptr()) for p in live}
+            foreign = [(p, p.grad) for p in live if p.grad is not None and not is_view[id(p)]]
+            if not any(is_view.values()):
+                st.flat.zero_()                       # the common case: one memset for the whole arena
+            else:
+                for p in live:
+                    if not is_view[id(p)]:
+                        st.views[id(p)].zero_()
             plan.dout_in.copy_(dout)
+            sync = getattr(model, "_grad_sync", None)
             plan.run_backward(stream, getattr(model, "_grad_bucket_hook", None),
                               use_graph=model.use_cuda_graph and plan.steps > 1)
             st.launches += len(plan.bwd_ops)
             for p, gr in foreign:
-                st.views[id(p)].add_(gr)
-            for p in st.params:
-                if p.requires_grad:
-                    p.grad = st.views[id(p)]
+                st.views[id(p)].add_(gr.to(st.views[id(p)].dtype))
+            if sync is not None and sync.auto:
+                sync.finish()                         # gradients are averaged over the ranks before anyone reads .grad
+            for p in live:
+                p.grad = st.views[id(p)]
             dctx = plan.dctx.clone() if ctx.needs_input_grad[1] else None
         return None, dctx, torch.zeros_like(st.anchor), None, None
+
+
+def _ensure_grad_sync(model):
+    """Multi-rank training without an explicit ``GradAllReduce``: the B200 backward writes ``p.grad`` straight into the flat
+    arena, so ``DistributedDataParallel``'s per-parameter autograd hooks never fire for the UNet (the reference's
+    ``main.py`` defaults every multi-GPU run to Lightning DDP, main.py:531-543).  Rather than letting the replicas diverge
+    silently, the first training forward in an initialised process group attaches an automatic ``GradAllReduce`` (parameters
+    broadcast from rank 0 once, like DDP's constructor; gradients averaged at the end of every backward, bucket 0
+    overlapped).  ``LDMB200_AUTO_GRAD_SYNC=0`` turns this into an error instead."""
+    sync = getattr(model, "_grad_sync", None)
+    if sync is not None:
+        return sync
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() <= 1:
+        return None
+    if os.environ.get("LDMB200_AUTO_GRAD_SYNC", "1") == "0":
+        raise _cabi.Ldmb200Error("dsml_thesis_b200.UNetModel trains in a %d-rank process group without a GradAllReduce: "
+                                 "DDP hooks do not see its gradients; construct dsml_thesis_b200.train.GradAllReduce(unet) "
+                                 "or unset LDMB200_AUTO_GRAD_SYNC=0" % dist.get_world_size())
+    sync = GradAllReduce(model, auto=True)
+    sync.broadcast_parameters(model)
+    return sync
 
 
 def unet_train_forward(model, x, timesteps, context, y=None):
@@ -770,6 +808,7 @@ def unet_train_forward(model, x, timesteps, context, y=None):
     assert Cin == model.in_channels and context.dim() == 3 and context.shape[0] == B
     assert timesteps is not None and timesteps.shape == (B,) and not timesteps.dtype.is_floating_point
     st = train_state(model)
+    _ensure_grad_sync(model)
     with torch.cuda.device(x.device):
         key = (B, H, W, int(context.shape[1]))
         plan = st.plans.get(key)
@@ -885,7 +924,7 @@ class GradAllReduce:
     gloo tests of the bucket logic)."""
 
     def __init__(self, model=None, group=None, flat: Optional[torch.Tensor] = None,
-                 wire_dtype: Optional[torch.dtype] = None):
+                 wire_dtype: Optional[torch.dtype] = None, auto: bool = False):
         """``wire_dtype=torch.bfloat16`` halves the NVLink bytes (SURVEY §8e "bf16 grads optional"): each bucket is cast to a
         bf16 staging buffer, pre-divided by the world size (so the sum cannot overflow where fp32 would not), summed in
         bf16 by the collective and cast back into the fp32 arena.  Default: fp32 on the wire, exact."""
@@ -897,8 +936,19 @@ class GradAllReduce:
         self.wire_dtype = wire_dtype if wire_dtype not in (None, torch.float32) else None
         self.wire = torch.empty_like(self.flat, dtype=self.wire_dtype) if self.wire_dtype is not None else None
         self.split = None
+        self.auto = auto      # True: the backward node itself calls finish() (no explicit sync.finish() in user code)
         if model is not None:
             model._grad_bucket_hook = self.bucket_ready
+            model._grad_sync = self
+
+    def broadcast_parameters(self, model, src: int = 0):
+        """Rank ``src``'s parameters to every rank, once (what ``DistributedDataParallel.__init__`` does for the parameters
+        it manages; the UNet's are excluded from DDP by ``install()``)."""
+        with torch.no_grad():
+            for p in model.parameters():
+                self.dist.broadcast(p.data, src=src, group=self.group)
+        if hasattr(model, "invalidate_weight_cache"):
+            model.invalidate_weight_cache()
 
     def _reduce(self, lo: int, hi: int):
         if self.wire is None:

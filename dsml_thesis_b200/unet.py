@@ -503,7 +503,13 @@ class _Plan:
                 d.colstats = res.stats.ptr
         self.keep.append(d)
         k_true = weight.shape[1] * ksize * ksize if weight.dim() >= 2 and n_true == weight.shape[0] else a.c
+        eb = lambda dt: 4 if dt == F32 else 2
+        # algorithmic bytes: the input map once, the weights once, the output once (+ the fp32 residual it adds)
+        abytes = (a.rows * a.c * eb(a.dtype) + n_true * k_true * (2 if tc else 4)
+                  + rows * n_cols * (4 if out_nchw_ptr is not None else eb(out_dtype))
+                  + (rows * n_cols * 4 if residual is not None else 0))
         self.emit("ldmb200_igemm_tc" if tc else "ldmb200_igemm_simt", C.byref(d), flops=2.0 * rows * n_true * k_true,
+                  bytes_=abytes,
                   what=f"M{rows} N{n_true} K{k_true} ks{ksize} s{stride}" + (" geglu" if geglu else "")
                   + (" res" if residual is not None else "") + ({BF16: " bf16out", F16: " f16out"}.get(out_dtype, "")))
         return res
@@ -554,7 +560,7 @@ class _Plan:
         o = self.new(t0.rows, Cc, self.act)
         if self.tc:
             self.emit("ldmb200_attention_tc", qkv.ptr, 3 * Cc, 0, Cc, 2 * Cc, o.ptr, Cc, self.act, B, heads, hw, scale,
-                      flops=4.0 * B * heads * hw * hw * dh, what=f"B{B} h{heads} N{hw}")
+                      flops=4.0 * B * heads * hw * hw * dh, bytes_=t0.rows * Cc * 2 * 4, what=f"B{B} h{heads} N{hw}")
         else:
             self.emit("ldmb200_attention_simt", qkv.ptr, 3 * Cc, 0, qkv.ptr, Cc, qkv.ptr, 2 * Cc, 3 * Cc, o.ptr, Cc, B,
                       heads, hw, hw, scale, flops=4.0 * B * heads * hw * hw * dh)
@@ -838,13 +844,17 @@ class UNetModel(nn.Module):
 
         # ---- runtime state (not parameters / buffers: state_dict stays identical to the reference)
         self.precision = os.environ.get("LDMB200_PRECISION", "f16")
-        self.use_cuda_graph = os.environ.get("LDMB200_CUDA_GRAPH", "0") == "1"
+        # CUDA-graph replay of the static launch plan is the default (the benchmarked configuration); the first call of a
+        # plan runs eagerly (lazy per-kernel setup), the second captures.  LDMB200_CUDA_GRAPH=0 launches eagerly.
+        self.use_cuda_graph = os.environ.get("LDMB200_CUDA_GRAPH", "1") == "1"
         self._plans: Dict[tuple, _Plan] = {}
         self._packs: Dict[int, _WeightPack] = {}   # operand dtype -> packed weights
         self._frozen = 0
         self._pack_valid: set = set()              # dtypes whose pack matches the current parameters
         self.launches = 0   # kernels launched by forward() so far (bench.py's gpu_launches)
         self._train_state = None  # dsml_thesis_b200.train._TrainState (gradient arena, training plans)
+        self._grad_sync = None    # dsml_thesis_b200.train.GradAllReduce attached to this model (explicit or automatic)
+        self._grad_bucket_hook = None
 
     # ---- reference API stubs (openaimodel.py:694-708): the fp16 conversion is a no-op there too -------
     def convert_to_fp16(self):
@@ -860,6 +870,8 @@ class UNetModel(nn.Module):
     def _apply(self, fn, *a, **k):
         # .to()/.cuda()/.float() may move parameter storage: drop everything that holds raw pointers
         self._train_state = None
+        self._grad_sync = None          # holds views of the old gradient arena
+        self._grad_bucket_hook = None
         self._plans = {}
         self._packs = {}
         self._pack_valid = set()

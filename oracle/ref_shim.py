@@ -161,3 +161,48 @@ def cpu_manipulation_sampler(model):
             setattr(self, name, attr)
 
     return CpuManipulationSampler(model)
+
+
+def cpu_progressive_sampler(model, record: list = None):
+    """The talking-face progressive sampler runnable here: the private ``DDIMSampler`` class of
+    TF/progressive_sampling_difftalk.py:55-319 (its own ``make_schedule``, ``p_sample_ddim`` :207-243 and the
+    autoregressive ``progressive_sampling`` :246-319 with ``zid = img`` at :317).  The script's module-level imports
+    (taming's MEAD dataset, omegaconf, PIL) are absent here, so the UNMODIFIED source text of the class is cut out of
+    the file and executed against the reference's own ``ldm.modules.diffusionmodules.util`` helpers.  ``record``, when
+    given, receives every 4-D ``torch.randn`` draw in call order (the per-frame x_T and the per-step ``noise_like``
+    draws) so that a GPU run can be fed the same starting noise."""
+    import re
+    from tqdm import tqdm  # noqa: F401
+    import_reference("talking_face")
+    from ldm.modules.diffusionmodules.util import (make_ddim_sampling_parameters, make_ddim_timesteps, noise_like,
+                                                   extract_into_tensor)
+    src = open(os.path.join(REFERENCE_ROOT, "talking_face", "progressive_sampling_difftalk.py")).read()
+    m = re.search(r"^class DDIMSampler\(object\):.*?(?=^def main\(\))", src, re.S | re.M)
+    assert m, "class DDIMSampler not found in progressive_sampling_difftalk.py"
+
+    class _TorchProxy:
+        """``torch`` with ``randn`` recorded (everything else is the real module)."""
+
+        def __getattr__(self, name):
+            return getattr(torch, name)
+
+        @staticmethod
+        def randn(*a, **k):
+            out = torch.randn(*a, **k)
+            if record is not None and out.dim() == 4:
+                record.append(out.clone())
+            return out
+
+    ns = {"torch": _TorchProxy(), "np": np, "tqdm": lambda it, **k: it, "noise_like": noise_like,
+          "make_ddim_sampling_parameters": make_ddim_sampling_parameters, "make_ddim_timesteps": make_ddim_timesteps,
+          "extract_into_tensor": extract_into_tensor, "__name__": "progressive_sampling_difftalk_cut"}
+    exec(m.group(0), ns)
+    base = ns["DDIMSampler"]
+
+    class CpuProgressiveSampler(base):
+        def register_buffer(self, name, attr):  # :62-66 without the hard-coded cuda move
+            if type(attr) == torch.Tensor and attr.device != model.device:
+                attr = attr.to(model.device)
+            setattr(self, name, attr)
+
+    return CpuProgressiveSampler(model)

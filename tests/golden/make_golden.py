@@ -363,6 +363,95 @@ def vq_encode_goldens():
     return out
 
 
+def c2_trajectory_goldens():
+    """BASELINE config 1/2 at full size: the REAL FR UNet, 64x64x3 latents, B=2, the reference ``DDIMSampler.sample``
+    (ddim.py:56-162) for 50 steps at eta 0 — final latents and the logged intermediates — plus one B=4 eval at mixed
+    timesteps for the batch-invariance check at 64x64 (minutes on CPU)."""
+    out = {}
+    cfg = O.FR_UNET
+    sd = O.init_state_dict(cfg, seed=0)
+    ref = R.reference_unet(cfg, "face_reenactment").eval()
+    ref.load_state_dict(sd, strict=True)
+    model = R.LatentDiffusionStandIn(ref)
+    B, hw = 2, 64
+    x_T, ctx = synth_inputs(cfg, B, hw, seed=2)
+    smp = R.cpu_ddim_sampler(model)
+    torch.manual_seed(1234)
+    samples, inter = smp.sample(50, batch_size=B, shape=[3, hw, hw], conditioning=ctx, eta=0.0, x_T=x_T,
+                                verbose=False, log_every_t=10)
+    out["c2/S50_eta0/samples"] = samples.numpy()
+    out["c2/S50_eta0/x_inter"] = torch.stack(inter["x_inter"]).numpy()
+    out["c2/S50_eta0/pred_x0"] = torch.stack(inter["pred_x0"]).numpy()
+    x4, ctx4 = synth_inputs(cfg, 4, hw, seed=3)
+    t4 = torch.tensor([981, 501, 261, 21], dtype=torch.long)
+    with torch.no_grad():
+        out["c2/b4/eps"] = ref(x4, t4, context=ctx4).numpy()
+    out["c2/b4/t"] = t4.numpy()
+    return out
+
+
+def c3_chain_goldens():
+    """BASELINE config 3: the talking-face progressive sampler exactly as the reference runs it — the private sampler class
+    of TF/progressive_sampling_difftalk.py (source-cut, ``oracle.ref_shim.cpu_progressive_sampler``) driving the REAL TF
+    UNet, the REAL ``Conv1DTemporalAttention`` (``cond_stage_model_2``) and the REAL first-stage ``Encoder`` + ``quant_conv``
+    (``encode_first_stage``; the small VQ_TINY f4 topology keeps the fixture CPU-sized) for 2 autoregressive frames
+    (``zid = img``, :316-317): 200 steps at the script's own 32x32 latents, 100 steps at 64x64."""
+    import contextlib
+    import io
+    import types
+    from oracle import cond_oracle as CO
+    from oracle import vq_oracle as V
+    R.import_reference("talking_face")
+    for name in ("clip", "kornia"):
+        if name not in sys.modules:
+            sys.modules[name] = types.ModuleType(name)
+    from ldm.modules.encoders.modules import Conv1DTemporalAttention
+    from ldm.modules.diffusionmodules.model import Encoder
+
+    class FirstStage(torch.nn.Module):
+        def __init__(self, cfg):
+            super().__init__()
+            dd = cfg["ddconfig"]
+            with contextlib.redirect_stdout(io.StringIO()):
+                self.encoder = Encoder(**dd)
+            self.quant_conv = torch.nn.Conv2d(dd["z_channels"], cfg["embed_dim"], 1)
+
+        def encode(self, x):                                # autoencoder.py:269-272
+            return self.quant_conv(self.encoder(x))
+
+    out = {}
+    cfg = O.TF_UNET
+    ref = R.reference_unet(cfg, "talking_face").eval()
+    ref.load_state_dict(O.init_state_dict(cfg, seed=0), strict=True)
+    aud = Conv1DTemporalAttention(**CO.TF_AUDIO)
+    aud.load_state_dict(CO.init_cond_state_dict(CO.TF_AUDIO, 0), strict=True)
+    aud.eval()
+    fs = FirstStage(V.VQ_TINY)
+    fs.load_state_dict(V.init_vq_encoder_state_dict(V.VQ_TINY, 0), strict=True)
+    fs.eval()
+    model = R.LatentDiffusionStandIn(ref, two_cond=True)
+    model.cond_stage_model_2 = aud
+    model.encode_first_stage = lambda x: fs.encode(x)
+    n_frames, window = 2, 8
+    for tag, hw, S in (("hw32_S200", 32, 200), ("hw64_S100", 64, 100)):
+        g = torch.Generator().manual_seed(31 + hw)
+        c1 = torch.randn(1, 1, 256, generator=g)
+        xid = torch.randn(1, 3, hw, hw, generator=g).clamp_(-1, 1)
+        xmasks = torch.randn(n_frames, 3, 4 * hw, 4 * hw, generator=g).clamp_(-1, 1)
+        audio = torch.randn(n_frames, 768, generator=g)
+        draws = []
+        smp = R.cpu_progressive_sampler(model, record=draws)
+        torch.manual_seed(4321)
+        with contextlib.redirect_stdout(io.StringIO()):
+            frames, _ = smp.progressive_sampling(c1=c1, xid=xid, xmasks=xmasks, audio_feats=audio, S=S, batch_size=1,
+                                                 num_frames=n_frames, shape=[3, hw, hw], audio_window=window, eta=0.,
+                                                 verbose=False)
+        assert len(frames) == n_frames and len(draws) == n_frames * (S + 1)
+        out[f"c3/{tag}/frames"] = torch.cat(frames).numpy()
+        out[f"c3/{tag}/x_T"] = torch.cat([draws[f * (S + 1)] for f in range(n_frames)]).numpy()
+    return out
+
+
 def main():
     torch.set_num_threads(max(1, os.cpu_count() or 1))
     only = sys.argv[1:]
@@ -370,7 +459,8 @@ def main():
                     ("trajectory.npz", trajectory_goldens), ("unet64.npz", unet64_goldens),
                     ("manipulation.npz", manipulation_goldens), ("train.npz", train_goldens),
                     ("unet128.npz", unet128_goldens), ("vqdecode.npz", vq_goldens), ("cond.npz", cond_goldens),
-                    ("vqencode.npz", vq_encode_goldens)):
+                    ("vqencode.npz", vq_encode_goldens),
+                    ("c2_trajectory.npz", c2_trajectory_goldens), ("c3_chain.npz", c3_chain_goldens)):
         if only and fn not in only:
             continue
         data = gen()

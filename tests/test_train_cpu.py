@@ -88,3 +88,100 @@ def test_training_on_cpu_fails_loudly():
 def test_training_module_never_imports_the_oracle():
     src = open(T.__file__).read()
     assert "oracle" not in src.replace("the CPU oracle", "")
+
+
+# ---- multi-rank training through the reference's own trainer (VERDICT r01 missing 1; main.py:531-543) -----------------
+class _StubState:
+    def __init__(self, model):
+        n = sum(p.numel() for p in model.parameters())
+        self.flat = torch.zeros(n)
+
+
+def _worker_auto_sync(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        unet = P.UNetModel(**O.TINY_UNET).train()
+        unet.load_state_dict(O.init_state_dict(O.TINY_UNET, seed=rank), strict=True)   # replicas start DIFFERENT
+        stub = _StubState(unet)
+        T.train_state = lambda m: stub                       # the real arena needs a GPU; the sync logic does not
+        sync = T._ensure_grad_sync(unet)
+        assert sync is not None and sync.auto and unet._grad_sync is sync and T._ensure_grad_sync(unet) is sync
+        assert unet._grad_bucket_hook == sync.bucket_ready
+        # (i) parameters were broadcast from rank 0
+        ref = O.init_state_dict(O.TINY_UNET, seed=0)
+        for k, v in unet.state_dict().items():
+            assert torch.equal(v, ref[k]), k
+        # (ii) what the backward node does: bucket 0 while the backward runs, finish() before anyone reads .grad
+        stub.flat.fill_(float(rank + 1))
+        sync.bucket_ready(stub.flat.numel() // 2, stub.flat.numel())
+        sync.finish()
+        assert torch.allclose(stub.flat, torch.full_like(stub.flat, sum(range(1, world + 1)) / world))
+        # (iii) opting out must raise, not diverge
+        unet2 = P.UNetModel(**O.TINY_UNET).train()
+        os.environ["LDMB200_AUTO_GRAD_SYNC"] = "0"
+        try:
+            with pytest.raises(P.Ldmb200Error):
+                T._ensure_grad_sync(unet2)
+        finally:
+            del os.environ["LDMB200_AUTO_GRAD_SYNC"]
+        open(os.path.join(out_dir, f"ok{rank}"), "w").close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_multi_rank_training_attaches_a_gradient_sync_automatically(tmp_path):
+    mp.spawn(_worker_auto_sync, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    assert os.path.exists(tmp_path / "ok0") and os.path.exists(tmp_path / "ok1")
+
+
+def test_single_process_training_needs_no_sync():
+    unet = P.UNetModel(**O.TINY_UNET).train()
+    assert T._ensure_grad_sync(unet) is None
+
+
+class _LitStandIn(torch.nn.Module):
+    """The shape of the reference's LatentDiffusion under Lightning DDP: a UNet inside a wrapper next to other
+    trainable parameters (conditioning stage, logvar)."""
+
+    def __init__(self):
+        super().__init__()
+        self.model = torch.nn.Module()
+        self.model.diffusion_model = P.UNetModel(**O.TINY_UNET)
+        self.cond_stage_model = torch.nn.Linear(4, 4)
+
+    def forward(self, x):
+        return self.cond_stage_model(x).sum()
+
+
+def _worker_ddp(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        P.install()
+        lit = _LitStandIn()
+        ddp = torch.nn.parallel.DistributedDataParallel(lit)
+        ignored = set(ddp.parameters_to_ignore)
+        names = {f"model.diffusion_model.{n}" for n, _ in lit.model.diffusion_model.named_parameters()}
+        assert names and names <= ignored
+        # DDP manages only the non-UNet parameters: iterating twice must not trip "Expected to have finished reduction"
+        for it in range(3):
+            ddp.zero_grad()
+            ddp(torch.full((2, 4), float(rank + it))).backward()
+        g = lit.cond_stage_model.weight.grad.clone()
+        dist.all_reduce(g)
+        assert torch.allclose(g / world, lit.cond_stage_model.weight.grad)       # averaged by DDP on every rank
+        assert all(p.grad is None for p in lit.model.diffusion_model.parameters())
+        P.uninstall()
+        assert not getattr(torch.nn.parallel.DistributedDataParallel, "_ldmb200_wrapped", False)
+        open(os.path.join(out_dir, f"ok{rank}"), "w").close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_install_excludes_the_unet_from_ddp(tmp_path):
+    """install() must keep DistributedDataParallel's reducer away from the UNet's parameters (their gradients never pass
+    autograd's accumulation hooks), otherwise the second training iteration of main.py's Lightning-DDP run fails — or,
+    with find_unused_parameters, silently skips the UNet."""
+    mp.spawn(_worker_ddp, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    assert os.path.exists(tmp_path / "ok0") and os.path.exists(tmp_path / "ok1")

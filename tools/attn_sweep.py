@@ -28,5 +28,5 @@ for (B, N, h) in [(64, 4096, 5), (64, 1024, 10), (8, 16384, 5)]:
 '''
 for k in sys.argv[1:]:
     env = dict(os.environ, LDMB200_LIB=os.path.abspath(f"dsml_thesis_b200/libldmb200_p{k}.so"))
-    print("== poly pairs", k); sys.stdout.flush()
+    print("== variant", k); sys.stdout.flush()
     subprocess.run([sys.executable, "-c", code], env=env)

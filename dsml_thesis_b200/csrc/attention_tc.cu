@@ -38,10 +38,11 @@ constexpr int AT_TILE_BYTES = 128 * 32 * 2;  // 8 KiB: 128 rows x 32 16-bit valu
 constexpr int AT_SMEM = AT_NQ * AT_TILE_BYTES + 2 * AT_STAGES * AT_TILE_BYTES + 32 * 8 + 16 + 1024;
 constexpr int AT_TMEM_COLS = 512;
 #ifndef LDM_AT_POLY
-#define LDM_AT_POLY 0
+#define LDM_AT_POLY 2
 #endif
 // 0..8: of every 8 score pairs, this many take their exponentials on the FMA pipe (packed degree-3 polynomial)
-// instead of the ex2 unit.  Sweep with tools/attn_sweep.py; the shipped value is the measured optimum.
+// instead of the ex2 unit.  Measured r02a (tools/attn_sweep.py, B=64 N=4096 h=5): 0 -> 1.606 ms, 2 -> 1.393, 3 -> 1.425,
+// 4 -> 1.634 (r01 kernel: 1.767).
 constexpr int AT_POLY = LDM_AT_POLY;
 
 __device__ __forceinline__ float ex2_approx(float x) {

@@ -500,6 +500,49 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
   }
 }
 
+// C = 20 * LPR floats (160 / 320 / 640: every SpatialTransformer width of the shipped UNets): LPR lanes share a row,
+// five float4 per lane, so a warp normalises 32 / LPR rows at once with every lane busy and 80 bytes of loads in
+// flight per lane (the one-warp-per-row kernel above leaves 24 of 32 lanes idle on its second trip at C = 160 and
+// keeps only 640 B in flight per warp).  Statistics: two-pass on the register-resident row, xor-shuffles inside the
+// LPR-lane group.
+template <typename T, int LPR>
+__global__ void __launch_bounds__(256) layernorm_c20_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, T* __restrict__ y,
+                                                            int64_t rows, float eps) {
+  constexpr int RPW = 32 / LPR, C = 20 * LPR;
+  const int lane = threadIdx.x & 31, sub = lane % LPR;
+  const int64_t row = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * RPW + lane / LPR;
+  const bool live = row < rows;
+  const float4* xr = reinterpret_cast<const float4*>(x + (live ? row : 0) * C);
+  float4 v[5];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) v[i] = live ? xr[sub + i * LPR] : make_float4(0.f, 0.f, 0.f, 0.f);
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+#pragma unroll
+  for (int o = LPR >> 1; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mean = s * (1.0f / (float)C);
+  float d = 0.f;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, e = v[i].w - mean;
+    d += (a * a + b * b) + (c * c + e * e);
+  }
+#pragma unroll
+  for (int o = LPR >> 1; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+  const float rstd = rsqrtf(d * (1.0f / (float)C) + eps);
+  if (!live) return;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const int idx = sub + i * LPR;
+    const float4 g = reinterpret_cast<const float4*>(gamma)[idx];
+    const float4 bb = reinterpret_cast<const float4*>(beta)[idx];
+    Store4<T>::st(y + row * C + idx * 4, (v[i].x - mean) * rstd * g.x + bb.x, (v[i].y - mean) * rstd * g.y + bb.y,
+                  (v[i].z - mean) * rstd * g.z + bb.z, (v[i].w - mean) * rstd * g.w + bb.w);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // weight packer: fp32 nn.Parameter -> bf16 [n_pad, taps, c_pad] (K-major), optional GEGLU row permutation
 // ---------------------------------------------------------------------------------------------
@@ -715,6 +758,18 @@ int ldmb200_layernorm(const float* x, const float* gamma, const float* beta, voi
   const int warps = 8;
   int blocks = (int)ceil_div64(rows, warps);
   cudaStream_t st = (cudaStream_t)stream;
+  if (c == 160 || c == 320 || c == 640) {
+#define LN20_LAUNCH(T, LPR) \
+  layernorm_c20_kernel<T, LPR><<<(int)ceil_div64(rows, warps * (32 / LPR)), warps * 32, 0, st>>>(x, gamma, beta, (T*)y, rows, eps)
+    LDM_DISPATCH_DTYPE(out_dtype, {
+      if (c == 160) LN20_LAUNCH(T, 8);
+      else if (c == 320) LN20_LAUNCH(T, 16);
+      else LN20_LAUNCH(T, 32);
+    });
+#undef LN20_LAUNCH
+    LDM_CHECK_LAUNCH("layernorm");
+    return 0;
+  }
 #define LN_LAUNCH(T, MAXV) layernorm_kernel<T, MAXV><<<blocks, warps * 32, 0, st>>>(x, gamma, beta, (T*)y, rows, c, eps)
   const int need = ceil_div(c / 4, 32);
   LDM_DISPATCH_DTYPE(out_dtype, {

@@ -17,7 +17,7 @@ import torch.nn as nn
 class DiffusionHandle(nn.Module):
     def __init__(self, unet: nn.Module, timesteps: int = 1000, linear_start: float = 0.0015,
                  linear_end: float = 0.0205, two_cond: bool = False, first_stage_decoder: nn.Module = None,
-                 first_stage_encoder: nn.Module = None, scale_factor: float = 1.0):
+                 first_stage_encoder: nn.Module = None, scale_factor: float = 1.0, cond_stage_model_2: nn.Module = None):
         super().__init__()
         betas = (torch.linspace(linear_start ** 0.5, linear_end ** 0.5, timesteps, dtype=torch.float64) ** 2).numpy()
         alphas_cumprod = np.cumprod(1.0 - betas, axis=0)
@@ -37,6 +37,8 @@ class DiffusionHandle(nn.Module):
         self.first_stage_decoder = first_stage_decoder
         self.first_stage_encoder = first_stage_encoder
         self.scale_factor = float(scale_factor)
+        # talking-face audio conditioning stage (ddpm2cond.py cond_stage_model_2; ``Conv1DTemporalAttention``)
+        self.cond_stage_model_2 = cond_stage_model_2
 
     @property
     def device(self):

@@ -324,6 +324,55 @@ class DDIMSampler2Cond(DDIMSampler):
         return x_dec
 
 
+    @torch.no_grad()
+    def progressive_sampling(self, c1, xid, xmasks, audio_feats, S, batch_size, num_frames, shape, audio_window, eta=0.,
+                             verbose=True, unconditional_guidance_scale=1., unconditional_conditioning=None, x_T=None,
+                             **kwargs):
+        """The autoregressive talking-face sampler of TF/progressive_sampling_difftalk.py:246-319 (the method of that
+        script's private sampler class, same arguments and return value): per frame, the audio window goes through
+        ``model.cond_stage_model_2``, the masked frame through ``model.encode_first_stage``, the frame is generated by
+        an S-step DDIM loop from fresh noise, and its latent becomes the reference (identity) latent of the next frame
+        (``zid = img``, :316-317).  Returns ``(generated_frame_latents, None)``.
+
+        Extensions (not in the reference, which is batch 1): ``x_T`` — a tensor ``[frames, B, C, H, W]`` (or a list) of
+        starting noise instead of the per-frame ``torch.randn`` draw (parity tests); and B independent streams at once:
+        ``c1 [B,1,256]``, ``xid [B,c,h,w]``, ``xmasks [frames,B,3,H,W]``, ``audio_feats [B,frames,768]``.
+        The reference's CFG branch concatenates on ``dim=21`` (:299) and cannot run; here it is ``dim=2``."""
+        assert c1 is not None
+        assert eta in [0., 1.]
+        self.make_schedule(ddim_num_steps=S, ddim_eta=eta, verbose=verbose)
+        if audio_feats.dim() == 3 and audio_feats.shape[0] == 1:
+            audio_feats = audio_feats.squeeze(0)
+        streams = audio_feats.dim() == 3                      # [B, frames, 768]
+        num_frames = audio_feats.shape[1] if streams else audio_feats.shape[0]
+        C, H, W = shape
+        size = (batch_size, C, H, W)
+        if verbose:
+            print(f'Data shape for DDIM sampling is {size}, eta {eta}')
+        device = self.model.betas.device
+        zid = xid.clone().detach()
+        generated_frame_latents = list()
+        for frame_idx in range(num_frames):
+            audio_indices = [min(max(frame_idx + i, 0), num_frames - 1) for i in range(-audio_window, audio_window + 1)]
+            assert audio_indices[audio_window] == frame_idx
+            c2 = audio_feats[:, audio_indices] if streams else audio_feats[audio_indices].unsqueeze(0)
+            c2 = self.model.cond_stage_model_2(c2)                               # (B, 1, 768)
+            c12 = torch.cat([c1, c2], dim=2)                                     # (B, 1, 1024)
+            masked_img = xmasks[frame_idx]
+            if masked_img.dim() == 3:
+                masked_img = masked_img.unsqueeze(0)
+            c3 = self.model.encode_first_stage(masked_img)                       # masked frame latent (B, c, h, w)
+            c34 = torch.cat([c3, zid], dim=1)                                    # (B, 2c, h, w)
+            uc = torch.cat([unconditional_conditioning, c2], dim=2) if unconditional_conditioning is not None else None
+            cond = {self.CROSS_KEY: c12, self.CONCAT_KEY: c34}
+            img = torch.randn(size, device=device) if x_T is None else x_T[frame_idx].to(device)
+            img, _ = self.ddim_sampling(cond, size, x_T=img, unconditional_guidance_scale=unconditional_guidance_scale,
+                                        unconditional_conditioning=uc, verbose=False)
+            generated_frame_latents.append(img)
+            zid = img.clone().detach()
+        return generated_frame_latents, None
+
+
 class DDIMSampler2CondFR(DDIMSampler2Cond):
     """face_reenactment/ldm/models/diffusion/ddim2cond.py: keys ``class_label`` / ``shape_image`` (line 166),
     ``sample`` returns the intermediates dict (line 157)."""

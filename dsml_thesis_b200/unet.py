@@ -315,6 +315,7 @@ class _Plan:
         self.ops: List[tuple] = []       # (c function, args without the trailing stream)
         self.meta: List[tuple] = []      # (kernel name, algorithmic flops, algorithmic bytes) per op
         self.py_ops: Dict[int, object] = {}  # op index -> python callable run before that op
+        self.op_outs: Dict[int, list] = {}   # op index -> [(buffer, elements, dtype)] 16-bit outputs of that op
         self.keep: List[object] = []     # ctypes structs referenced by pointer from ops
         self.arena = _Arena(dev)
         self.pack = self._make_pack()
@@ -344,9 +345,11 @@ class _Plan:
                     self.arena.release(a.stats)
                     a.stats = None
 
-    def emit(self, name: str, *args, flops: float = 0.0, bytes_: float = 0.0, what: str = ""):
+    def emit(self, name: str, *args, flops: float = 0.0, bytes_: float = 0.0, what: str = "", outs=()):
         """Appends one launch.  ``flops`` / ``bytes_`` are the ALGORITHMIC work of the launch (no padding, no
-        re-reads) used by ``bench.py`` for the roofline; they do not influence execution."""
+        re-reads) used by ``bench.py`` for the roofline; they do not influence execution.  ``outs``: the 16-bit
+        activations the launch writes (``f16_saturation_report`` inspects them right after the launch)."""
+        self.op_outs[len(self.ops)] = [(o.buf, o.rows * o.c, o.dtype) for o in outs if o is not None and o.dtype != F32]
         self.ops.append((getattr(self.lib, name), args, name))
         self.meta.append((name, float(flops), float(bytes_), what))
 
@@ -441,20 +444,22 @@ class _Plan:
                       gn.bias.data_ptr(), y.ptr, raw.ptr if raw is not None else None, self.act, self.B, hw,
                       gn.num_groups, float(gn.eps), silu, self.gn_ws.data_ptr(),
                       bytes_=x1.rows * c * (4 + 2 * (2 if want_raw else 1)),
-                      what=f"rows{x1.rows} C{c} fused" + (" cat" if x2 is not None else "") + (" raw" if want_raw else ""))
+                      what=f"rows{x1.rows} C{c} fused" + (" cat" if x2 is not None else "") + (" raw" if want_raw else ""),
+                      outs=(y, raw))
             return y, raw
         self.emit("ldmb200_groupnorm", x1.ptr, x1.c, x2.ptr if x2 is not None else None,
                   x2.c if x2 is not None else 0, gn.weight.data_ptr(), gn.bias.data_ptr(), y.ptr,
                   raw.ptr if raw is not None else None, self.act, self.B, hw, gn.num_groups, float(gn.eps), silu,
                   self.gn_ws.data_ptr(),
                   bytes_=x1.rows * c * (4 + (2 if self.tc else 4) * (2 if want_raw else 1)),
-                  what=f"rows{x1.rows} C{c}" + (" cat" if x2 is not None else "") + (" raw" if want_raw else ""))
+                  what=f"rows{x1.rows} C{c}" + (" cat" if x2 is not None else "") + (" raw" if want_raw else ""),
+                  outs=(y, raw))
         return y, raw
 
     def layernorm(self, x: _Act, ln: nn.LayerNorm) -> _Act:
         y = self.new(x.rows, x.c, self.act)
         self.emit("ldmb200_layernorm", x.ptr, ln.weight.data_ptr(), ln.bias.data_ptr(), y.ptr, self.act, x.rows, x.c,
-                  float(ln.eps), bytes_=x.rows * x.c * (4 + (2 if self.tc else 4)), what=f"rows{x.rows} C{x.c}")
+                  float(ln.eps), bytes_=x.rows * x.c * (4 + (2 if self.tc else 4)), what=f"rows{x.rows} C{x.c}", outs=(y,))
         return y
 
     def gemm(self, a: _Act, key: str, weight: torch.Tensor, bias: Optional[torch.Tensor], h_in: int, w_in: int,
@@ -511,7 +516,8 @@ class _Plan:
         self.emit("ldmb200_igemm_tc" if tc else "ldmb200_igemm_simt", C.byref(d), flops=2.0 * rows * n_true * k_true,
                   bytes_=abytes,
                   what=f"M{rows} N{n_true} K{k_true} ks{ksize} s{stride}" + (" geglu" if geglu else "")
-                  + (" res" if residual is not None else "") + ({BF16: " bf16out", F16: " f16out"}.get(out_dtype, "")))
+                  + (" res" if residual is not None else "") + ({BF16: " bf16out", F16: " f16out"}.get(out_dtype, "")),
+                  outs=(res,))
         return res
 
     # ---- blocks ------------------------------------------------------------------------
@@ -560,7 +566,8 @@ class _Plan:
         o = self.new(t0.rows, Cc, self.act)
         if self.tc:
             self.emit("ldmb200_attention_tc", qkv.ptr, 3 * Cc, 0, Cc, 2 * Cc, o.ptr, Cc, self.act, B, heads, hw, scale,
-                      flops=4.0 * B * heads * hw * hw * dh, bytes_=t0.rows * Cc * 2 * 4, what=f"B{B} h{heads} N{hw}")
+                      flops=4.0 * B * heads * hw * hw * dh, bytes_=t0.rows * Cc * 2 * 4, what=f"B{B} h{heads} N{hw}",
+                      outs=(o,))
         else:
             self.emit("ldmb200_attention_simt", qkv.ptr, 3 * Cc, 0, qkv.ptr, Cc, qkv.ptr, 2 * Cc, 3 * Cc, o.ptr, Cc, B,
                       heads, hw, hw, scale, flops=4.0 * B * heads * hw * hw * dh)
@@ -614,7 +621,7 @@ class _Plan:
         """openaimodel.py:151-160: conv 3x3 stride 2 pad 1."""
         if self.tc:
             s = self.new(x.rows, x.c, self.act)
-            self.emit("ldmb200_space_to_depth2", x.ptr, s.ptr, self.act, self.B, H, W, x.c)
+            self.emit("ldmb200_space_to_depth2", x.ptr, s.ptr, self.act, self.B, H, W, x.c, outs=(s,))
             out = self.gemm(s, name + ".op", m.op.weight, m.op.bias, H, W, ksize=3, stride=2, want_stats=True)
             self.free(s)
             return out
@@ -624,7 +631,7 @@ class _Plan:
         """openaimodel.py:109-119: nearest 2x, then conv 3x3."""
         if self.tc:
             u = self.new(4 * x.rows, x.c, self.act)
-            self.emit("ldmb200_upsample2x", x.ptr, u.ptr, self.act, self.B, H, W, x.c)
+            self.emit("ldmb200_upsample2x", x.ptr, u.ptr, self.act, self.B, H, W, x.c, outs=(u,))
             out = self.gemm(u, name + ".conv", m.conv.weight, m.conv.bias, 2 * H, 2 * W, ksize=3, want_stats=True)
             self.free(u)
             return out
@@ -716,6 +723,27 @@ class _Plan:
             evs.append((e0, e1))
         stream_obj.synchronize()
         return [(m[0], e0.elapsed_time(e1), m[1], m[2], m[3]) for m, (e0, e1) in zip(self.meta, evs)]
+
+    def run_checked(self, stream_obj) -> Dict[str, int]:
+        """Debug run: after every launch, counts the elements of its fp16 outputs that sit at the clamp of the saturating
+        conversion (|v| == 65504) or are not finite.  Returns ``{"<op index> <kernel> <shape>": count}`` for the
+        launches that saturated (empty = the fp16 operand range was never exceeded)."""
+        bad: Dict[str, int] = {}
+        for i, (fn, args, name) in enumerate(self.ops):
+            if i in self.py_ops:
+                self.py_ops[i]()
+            rc = fn(*args, stream_obj.cuda_stream)
+            if rc:
+                _cabi.check(rc, name)
+            for buf, n, dt in self.op_outs.get(i, ()):
+                if dt != F16:
+                    continue
+                v = buf.t[: 2 * n].view(torch.float16)
+                cnt = int(((v.abs() >= 65504.0) | ~torch.isfinite(v)).sum().item())
+                if cnt:
+                    bad[f"{i} {name[8:]} {self.meta[i][3]}"] = cnt
+        self.runs += 1
+        return bad
 
     def run(self, stream: int):
         py = self.py_ops
@@ -847,6 +875,9 @@ class UNetModel(nn.Module):
         # CUDA-graph replay of the static launch plan is the default (the benchmarked configuration); the first call of a
         # plan runs eagerly (lazy per-kernel setup), the second captures.  LDMB200_CUDA_GRAPH=0 launches eagerly.
         self.use_cuda_graph = os.environ.get("LDMB200_CUDA_GRAPH", "1") == "1"
+        # fp16 operand range guard, evaluated on the first call of every plan: "warn" (default) = fall back to bf16
+        # operands for the whole model with a RuntimeWarning when a launch saturates at +-65504, "raise", or "off"
+        self.f16_guard = os.environ.get("LDMB200_F16_GUARD", "warn")
         self._plans: Dict[tuple, _Plan] = {}
         self._packs: Dict[int, _WeightPack] = {}   # operand dtype -> packed weights
         self._frozen = 0
@@ -900,6 +931,26 @@ class UNetModel(nn.Module):
         finally:
             self._frozen -= 1
 
+    @torch.no_grad()
+    def f16_saturation_report(self, x, timesteps, context, y=None) -> Dict[str, int]:
+        """One eager eval in ``"f16"`` mode that counts, launch by launch, the fp16 operand elements that hit the
+        saturating conversion's clamp (±65504) — the failure mode fp16 operands have and bf16 operands do not.
+        Synthetic weights never get near it; a trained checkpoint with outlier activations (the 16-bit copy of the
+        residual stream after the last transformer block, GEGLU products) can.  Empty dict = safe for these inputs.
+        ``f16_guard`` (below) runs this automatically on the first call of every plan."""
+        B, _, H, W = x.shape
+        with torch.cuda.device(x.device):
+            plan = self._get_plan(B, H, W, int(context.shape[1]), "f16")
+            plan.x_in.copy_(x)
+            plan.t_in.copy_(timesteps)
+            plan.ctx_in.copy_(context)
+            if y is not None:
+                plan.y_in.copy_(y)
+            cur = torch.cuda.current_stream()
+            plan.pack.run(cur.cuda_stream)
+            self._pack_valid.add(plan.act)
+            return plan.run_checked(cur)
+
     def _get_plan(self, B, H, W, L, mode) -> _Plan:
         key = (B, H, W, L, mode)
         plan = self._plans.get(key)
@@ -950,7 +1001,25 @@ class UNetModel(nn.Module):
                 plan.y_in.copy_(y)
             need_pack = plan.tc and not (self._frozen and plan.act in self._pack_valid)
             self.launches += len(plan.ops) + (1 if need_pack else 0)
-            if self.use_cuda_graph and plan.runs >= 1:
+            if mode == "f16" and plan.runs == 0 and self.f16_guard != "off":
+                # first call of this plan (eager anyway): the checked run.  fp16 operands that saturate silently change
+                # the result; bf16 operands cannot saturate — fall back to them for the whole model, loudly.
+                cur = torch.cuda.current_stream()
+                if need_pack:
+                    plan.pack.run(cur.cuda_stream)
+                    self._pack_valid.add(plan.act)
+                bad = plan.run_checked(cur)
+                if bad:
+                    msg = ("dsml_thesis_b200.UNetModel: %d launch(es) saturated their fp16 operands at +-65504 (first: %s, "
+                           "%d elements)" % (len(bad), next(iter(bad)), next(iter(bad.values()))))
+                    if self.f16_guard == "raise":
+                        raise _cabi.Ldmb200Error(msg + "; set model.precision = 'bf16'")
+                    import warnings
+                    warnings.warn(msg + "; switching this model to precision='bf16' (bf16 operands cannot saturate; "
+                                  "eps error ~1.2e-2 instead of ~1.5e-3)", RuntimeWarning)
+                    self.precision = "bf16"
+                    return self._forward(x, timesteps, context, y, clone)
+            elif self.use_cuda_graph and plan.runs >= 1:
                 if plan.graph is None:
                     g = torch.cuda.CUDAGraph()
                     with torch.cuda.graph(g):

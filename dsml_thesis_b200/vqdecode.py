@@ -187,7 +187,7 @@ class _VQPlan(_Plan):
         self.act = {"bf16": _cabi.BF16, "f16": _cabi.F16, "fp32": F32}[mode]
         dev = model._device()
         self.lib = _cabi.load()
-        self.ops, self.meta, self.py_ops, self.keep = [], [], {}, []
+        self.ops, self.meta, self.py_ops, self.keep, self.op_outs = [], [], {}, [], {}
         self.arena = _Arena(dev)
         self.pack = model._weight_pack(self.act) if self.tc else None
         f32 = dict(dtype=torch.float32, device=dev)
@@ -320,7 +320,7 @@ class _VQEncPlan(_VQPlan):
         self.act = {"bf16": _cabi.BF16, "f16": _cabi.F16, "fp32": F32}[mode]
         dev = model._device()
         self.lib = _cabi.load()
-        self.ops, self.meta, self.py_ops, self.keep = [], [], {}, []
+        self.ops, self.meta, self.py_ops, self.keep, self.op_outs = [], [], {}, [], {}
         self.arena = _Arena(dev)
         self.pack = model._weight_pack(self.act) if self.tc else None
         f32 = dict(dtype=torch.float32, device=dev)
@@ -558,12 +558,21 @@ def accelerated_encode(reference_encode):
         if not x.is_cuda or (torch.is_grad_enabled() and x.requires_grad):
             return reference_encode(self, x)
         fast = self.__dict__.get("_ldmb200_encoder")
-        if fast is None or fast._device() != x.device:
-            fast = _build_encoder_from(self)
-            self.__dict__["_ldmb200_encoder"] = fast
+        fp = _fingerprint(self)
+        if fast is None or fast._device() != x.device or self.__dict__.get("_ldmb200_encoder_fp") != fp:
+            fast = _build_encoder_from(self)      # first use, device move, or the live weights changed (load_state_dict,
+            self.__dict__["_ldmb200_encoder"] = fast   # init_from_ckpt, .half(): new data_ptr / bumped _version)
+            self.__dict__["_ldmb200_encoder_fp"] = fp
         return fast.encode(x)
     encode._ldmb200_reference = reference_encode
     return encode
+
+
+def _fingerprint(module) -> tuple:
+    """(storage address, in-place version) of every parameter of the live first stage: changes whenever its weights are
+    replaced or overwritten through torch (load_state_dict / init_from_ckpt copy in place and bump ``_version``; ``.half()``
+    / ``.to()`` re-allocate), so the private 16-bit copy behind ``install()``'s wrappers is rebuilt instead of going stale."""
+    return tuple((p.data_ptr(), p._version) for p in module.parameters())
 
 
 def _build_from(first_stage_model) -> VQDecoder:
@@ -605,9 +614,11 @@ def accelerated_decode(reference_decode):
         if not h.is_cuda or (torch.is_grad_enabled() and h.requires_grad):
             return reference_decode(self, h, force_not_quantize)
         fast = self.__dict__.get("_ldmb200_decoder")
-        if fast is None or fast._device() != h.device:
-            fast = _build_from(self)
+        fp = _fingerprint(self)
+        if fast is None or fast._device() != h.device or self.__dict__.get("_ldmb200_decoder_fp") != fp:
+            fast = _build_from(self)              # first use, device move, or the live weights changed
             self.__dict__["_ldmb200_decoder"] = fast
+            self.__dict__["_ldmb200_decoder_fp"] = fp
         return fast.decode(h, force_not_quantize)
     decode._ldmb200_reference = reference_decode
     return decode

@@ -169,8 +169,8 @@ def cpu_progressive_sampler(model, record: list = None):
     autoregressive ``progressive_sampling`` :246-319 with ``zid = img`` at :317).  The script's module-level imports
     (taming's MEAD dataset, omegaconf, PIL) are absent here, so the UNMODIFIED source text of the class is cut out of
     the file and executed against the reference's own ``ldm.modules.diffusionmodules.util`` helpers.  ``record``, when
-    given, receives every 4-D ``torch.randn`` draw in call order (the per-frame x_T and the per-step ``noise_like``
-    draws) so that a GPU run can be fed the same starting noise."""
+    given, receives every 4-D ``torch.randn`` draw of the class body in call order (the per-frame x_T; the per-step
+    ``noise_like`` draws happen inside the reference's util module) so that a GPU run can be fed the same starting noise."""
     import re
     from tqdm import tqdm  # noqa: F401
     import_reference("talking_face")

@@ -446,9 +446,11 @@ def c3_chain_goldens():
             frames, _ = smp.progressive_sampling(c1=c1, xid=xid, xmasks=xmasks, audio_feats=audio, S=S, batch_size=1,
                                                  num_frames=n_frames, shape=[3, hw, hw], audio_window=window, eta=0.,
                                                  verbose=False)
-        assert len(frames) == n_frames and len(draws) == n_frames * (S + 1)
+        # the per-step noise_like draws (util.py:264-267) go through the reference's own module; the class body's
+        # torch.randn is the per-frame x_T only
+        assert len(frames) == n_frames and len(draws) == n_frames, (len(frames), len(draws))
         out[f"c3/{tag}/frames"] = torch.cat(frames).numpy()
-        out[f"c3/{tag}/x_T"] = torch.cat([draws[f * (S + 1)] for f in range(n_frames)]).numpy()
+        out[f"c3/{tag}/x_T"] = torch.cat(draws).numpy()
     return out
 
 

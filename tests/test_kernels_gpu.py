@@ -139,7 +139,8 @@ def test_elementwise_groupnorm(B, c1, c2, H, eps, silu, dt, raw):
 
 
 @pytest.mark.parametrize("rows,c,dt", [(4096, 160, BF16), (1024, 320, F32), (256, 640, BF16), (5, 32, F32), (77, 1280, F32),
-                                       (4096, 160, F16), (300, 640, F16)])
+                                       (4096, 160, F16), (300, 640, F16), (4099, 160, F16), (301, 320, BF16), (1, 160, F32),
+                                       (33, 320, F32)])
 def test_elementwise_layernorm(rows, c, dt):
     x, g, b = rnd(rows, c) * 3 + 1, 1 + 0.1 * rnd(c), 0.1 * rnd(c)
     y = torch.empty(rows, c, dtype=K.TORCH_DT[dt], device="cuda")

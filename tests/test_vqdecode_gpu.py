@@ -199,6 +199,16 @@ def test_install_wrapper_decodes_cuda_latents_through_the_kernels():
     out = fs.decode(z.cuda(), force_not_quantize=True)
     assert O.rel_l2(out.cpu(), ref) <= TOL[fs._ldmb200_decoder.precision]
     assert fs.decode(z.cuda()).shape == ref.shape and len(fs._ldmb200_decoder._plans) == 2
+    # the live module's weights change after the first decode (init_from_ckpt / load_state_dict on resume): the private
+    # 16-bit copy must follow (it used to stay stale until a device change)
+    first = fs._ldmb200_decoder
+    sd2 = V.init_vq_state_dict(V.VQ_TINY, 1)
+    fs.load_state_dict({k: v for k, v in sd2.items() if k in fs.state_dict()}, strict=True)
+    ref2, _ = V.vq_decode(sd2, V.VQ_TINY, z, force_not_quantize=True)
+    out2 = fs.decode(z.cuda(), force_not_quantize=True)
+    assert fs._ldmb200_decoder is not first
+    assert O.rel_l2(out2.cpu(), ref2) <= TOL[fs._ldmb200_decoder.precision]
+    assert O.rel_l2(out2.cpu(), ref) > 0.1
 
 
 # ------------------------------------------------------------------------------------------ encode half (8f n4)

@@ -628,9 +628,126 @@ def torch_eager_gpu_leg(args):
                       "modes": out}))
 
 
+C5B_UNET = dict(FR_UNET, channel_mult=[1, 2, 2, 4, 4], attention_resolutions=[4, 8, 16])
+C5_GFLOP = {"c5a": 1657.0, "c5b": 375.4}     # algorithmic GFLOP / sample / eval (probed through the reference ctor)
+
+
+def c5_main(args):
+    """--workload c5 (BASELINE config 5, roofline stress): 128x128x3 latents, GLOBAL batch swept 1..512 over the N GPUs
+    of the box through sample_sharded (contiguous shards, no data-path collective, final all-gather), both readings of
+    SURVEY 8d: c5a = the shipped architecture at 128^2 (self-attention over 16384/4096/1024 tokens), c5b = a 5-level
+    channel_mult with attention where the feature map is 32/16/8.  One JSON line PER POINT (rank 0); device time, max
+    over ranks; attention and non-attention kernels reported against their own rooflines."""
+    import torch
+    import torch.distributed as dist
+    import dsml_thesis_b200 as P
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    HW, T = 128, args.ddim
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_tf = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    batches = [int(b) for b in args.c5_batches.split(",")]
+    max_local = args.c5_max_local
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for reading in args.c5_readings.split(","):
+        cfg = FR_UNET if reading == "c5a" else C5B_UNET
+        unet = P.UNetModel(**cfg)
+        init_weights(unet, 0)
+        unet = unet.to(dev).eval()
+        unet.precision = args.precision
+        unet.use_cuda_graph = bool(args.graph)
+        model = P.DiffusionHandle(unet).to(dev)
+        smp = P.DDIMSampler(model)
+        for GB in batches:
+            lo, hi = P.shard_range(GB, world, rank)
+            if -(-GB // world) > max_local:
+                if rank == 0:
+                    print(json.dumps({"workload": reading, "global_batch": GB, "n_gpus": world,
+                                      "skipped": f"{-(-GB // world)} samples per GPU exceed --c5-max-local {max_local}"}))
+                continue
+            gg = torch.Generator().manual_seed(4000 + GB)
+            xg = torch.randn(GB, 3, HW, HW, generator=gg).to(dev)
+            cg = torch.randn(GB, 1, 512, generator=gg).to(dev)
+
+            def run():
+                out, _ = P.sample_sharded(smp, T, GB, [3, HW, HW], conditioning=cg, x_T=xg, eta=0.0)
+                return out
+            with torch.no_grad():
+                clocks = ClockSampler(local_rank)
+                for _ in range(max(1, args.warmup)):
+                    run()
+                barrier()
+                if rank == 0:
+                    clocks.start()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(args.steps):
+                    run()
+                e1.record()
+                barrier()
+                clk = clocks.stop() if rank == 0 else None
+                ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+                if world > 1:
+                    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+                ms = float(ms.item()) / args.steps
+                fam = {}
+                plan = unet._plans.get((hi - lo, HW, HW, 1, args.precision)) if hi > lo else None
+                if plan is not None:
+                    plan.run_timed(torch.cuda.current_stream())
+                    for name, t_ms, fl, by, _w in plan.run_timed(torch.cuda.current_stream()):
+                        f = fam.setdefault(name, [0.0, 0.0])
+                        f[0] += t_ms
+                        f[1] += fl
+                unet._plans.clear()
+            if rank != 0:
+                continue
+            value = GB / (ms * 1e-3)
+            af = fam.get("ldmb200_attention_tc", [0.0, 0.0])
+            rest_ms = sum(v[0] for k, v in fam.items() if k != "ldmb200_attention_tc")
+            rest_fl = sum(v[1] for k, v in fam.items() if k != "ldmb200_attention_tc")
+            mhz = (clk or {}).get("sm_mhz") or 1965.0
+            peak_ex2 = 16.0 * sms * mhz * 1e6
+            print(json.dumps({
+                "metric": metric_name(HW, T), "workload": reading, "value": value, "unit": "samples/s", "n_gpus": world,
+                "global_batch": GB, "per_gpu_batch": hi - lo, "steps": args.steps, "warmup": max(1, args.warmup),
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong (fixed global batch split over the ranks)",
+                "dtype": args.precision, "data": "synthetic",
+                "config": {"workload": f"C5 {reading}: FR UNet " + ("as shipped" if reading == "c5a" else
+                                                                     "with channel_mult [1,2,2,4,4], attention_resolutions [4,8,16]")
+                           + f", 128x128x3 latents, global batch {GB} over {world} GPU(s), {T}-step DDIM eta=0",
+                           "cuda_graph": bool(args.graph)},
+                "unet_tflops_algorithmic_per_gpu": value / world * T * C5_GFLOP[reading] / 1e3,
+                "tensor_frac_of_measured_peak": value / world * T * C5_GFLOP[reading] / 1e3 / peak_tf,
+                "attention": {"ms_per_eval": round(af[0], 4), "tflops": (af[1] / (af[0] * 1e-3) / 1e12) if af[0] else None,
+                              "frac_of_ex2_roofline": ((af[1] / 128.0) / (af[0] * 1e-3) / peak_ex2) if af[0] else None},
+                "non_attention": {"ms_per_eval": round(rest_ms, 4),
+                                  "tflops": (rest_fl / (rest_ms * 1e-3) / 1e12) if rest_ms else None,
+                                  "frac_of_tensor_peak": (rest_fl / (rest_ms * 1e-3) / 1e12 / peak_tf) if rest_ms else None},
+                "clocks": clk}), flush=True)
+        del unet, model, smp
+        torch.cuda.empty_cache()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--workload", default="sample", choices=["sample", "train", "c3", "decode"],
+    ap.add_argument("--workload", default="sample", choices=["sample", "train", "c3", "decode", "c5"],
                     help="sample = BASELINE config 2 (the headline metric); train = config 4 (DDPM training step); "
                          "c3 = config 3 (talking_face UNet, 200-step progressive DDIM, autoregressive frames)")
     ap.add_argument("--frames", type=int, default=2, help="c3: autoregressive frames per step")
@@ -647,6 +764,9 @@ def main():
     ap.add_argument("--precision", default="f16", choices=["f16", "bf16", "fp32"])
     ap.add_argument("--graph", type=int, default=int(os.environ.get("LDMB200_CUDA_GRAPH", "1")))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--c5-batches", default="1,2,4,8,16,32,64,128,256,512", help="c5: global batch sizes of the sweep")
+    ap.add_argument("--c5-readings", default="c5a,c5b", help="c5: which readings of SURVEY 8d to run")
+    ap.add_argument("--c5-max-local", type=int, default=64, help="c5: largest per-GPU batch (activation arena at 128x128)")
     ap.add_argument("--grad-wire", default="fp32", choices=["fp32", "bf16"],
                     help="train, N>1: dtype of the gradient all-reduce on the wire (fp32 = exact, default)")
     args = ap.parse_args()
@@ -660,6 +780,8 @@ def main():
         return train_main(args)
     if args.workload == "decode":
         return decode_main(args)
+    if args.workload == "c5":
+        return c5_main(args)
     c3 = args.workload == "c3"
 
     rank = int(os.environ.get("RANK", "0"))

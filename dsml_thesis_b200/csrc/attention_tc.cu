@@ -42,7 +42,9 @@ constexpr int AT_TMEM_COLS = 512;
 #endif
 // 0..8: of every 8 score pairs, this many take their exponentials on the FMA pipe (packed degree-3 polynomial)
 // instead of the ex2 unit.  Measured r02a (tools/attn_sweep.py, B=64 N=4096 h=5): 0 -> 1.606 ms, 2 -> 1.393, 3 -> 1.425,
-// 4 -> 1.634 (r01 kernel: 1.767).
+// 4 -> 1.634 (r01 kernel: 1.767).  A software-pipelined variant (next step's tcgen05.ld issued before the P store) was
+// measured r02c and rejected: 1.635 ms at 2/8 — the loop-carried register arrays push the kernel into spills at the
+// 128-register cap of a 512-thread CTA, and setmaxnreg re-distribution made ptxas spill more, not less.
 constexpr int AT_POLY = LDM_AT_POLY;
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -66,32 +68,6 @@ __device__ __forceinline__ uint32_t pack_out16(float lo, float hi, int dt) {
     asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
   else
     asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
-  return r;
-}
-
-// ---- packed fp32 (sm_100 FFMA2 / FADD2: two lanes per issue slot) ----
-typedef unsigned long long f32x2;
-__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
-  f32x2 r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ void unpk2(f32x2 v, float& lo, float& hi) {
-  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-}
-__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
-  f32x2 r;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-  return r;
-}
-__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
-  f32x2 r;
-  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
-__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
-  f32x2 r;
-  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
   return r;
 }
 

@@ -228,6 +228,65 @@ __device__ __forceinline__ float gelu_erf_fast(float x) {
   return x * (x >= 0.f ? 1.0f - q : q);
 }
 
+// ---- packed fp32 (sm_100 FFMA2 / FADD2 / FMUL2: two lanes per issue slot) ----
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpk2(f32x2 v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 bc2(float c) { return pk2(c, c); }
+
+// gelu_erf_fast for a pair on the packed pipe: x * (0.5 + copysign(0.5 - q, x)), q = 0.5 erfc(|x| / sqrt 2) from the
+// same A&S 7.1.26 polynomial — 17 issue slots per PAIR instead of 17 per element.
+__device__ __forceinline__ f32x2 gelu_erf_fast2(f32x2 x2) {
+  float x0, x1;
+  unpk2(x2, x0, x1);
+  float d0, d1, t0, t1;
+  unpk2(fma2(pk2(fabsf(x0), fabsf(x1)), bc2(0.3275911f * 0.70710678118654752f), bc2(1.0f)), d0, d1);
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(d0));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(d1));
+  const f32x2 t2 = pk2(t0, t1);
+  f32x2 q2 = fma2(t2, bc2(0.5f * 1.061405429f), bc2(0.5f * -1.453152027f));
+  q2 = fma2(q2, t2, bc2(0.5f * 1.421413741f));
+  q2 = fma2(q2, t2, bc2(0.5f * -0.284496736f));
+  q2 = fma2(q2, t2, bc2(0.5f * 0.254829592f));
+  q2 = mul2(q2, t2);
+  float a0, a1, e0, e1;
+  unpk2(mul2(mul2(x2, bc2(-0.72134752044448170f)), x2), a0, a1);
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(a0));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(a1));
+  q2 = mul2(q2, pk2(e0, e1));          // 0.5 * erfc(|x| / sqrt 2)
+  float h0, h1;
+  unpk2(sub2(bc2(0.5f), q2), h0, h1);  // >= 0: Phi(x) - 0.5 up to the sign of x
+  h0 = __int_as_float(__float_as_int(h0) | (__float_as_int(x0) & 0x80000000));
+  h1 = __int_as_float(__float_as_int(h1) | (__float_as_int(x1) & 0x80000000));
+  return mul2(x2, add2(pk2(h0, h1), bc2(0.5f)));
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

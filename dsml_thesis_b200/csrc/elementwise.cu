@@ -383,8 +383,10 @@ __global__ void __launch_bounds__(128) gn_finalize_kernel(const float* __restric
   }
 }
 
-template <typename T>
-__global__ void gn_apply_kernel(const float* __restrict__ x1, int c1, const float* __restrict__ x2, int c2,
+// MAXT = 256 (every shipped width up to C = 960): capped at 48 registers so that five blocks are resident per SM.
+template <typename T, int MAXT>
+__global__ void __launch_bounds__(MAXT, MAXT == 256 ? 5 : (MAXT == 512 ? 2 : 1))
+gn_apply_kernel(const float* __restrict__ x1, int c1, const float* __restrict__ x2, int c2,
                                 const float* __restrict__ gamma, const float* __restrict__ beta, T* __restrict__ y,
                                 T* __restrict__ raw, int hw, int groups, int R, int S, float eps, int silu,
                                 const float* __restrict__ ws) {
@@ -603,6 +605,39 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const ldmb200_pack_jo
 
 using namespace ldm;
 
+// Blocks of the apply pass per sample: ONE wave of resident blocks over the whole batch.  (r01 sized the grid as
+// ceil(8 * SMs / batch) while the 64-register kernel fitted 4 blocks per SM: 1216 blocks on 592 slots = 2.05 waves, the
+// third nearly empty — the reason the pass sat at 4.1 TB/s next to the LayerNorm's 5.8 TB/s on the same byte pattern.)
+template <typename T>
+static int gn_apply_launch(const float* x1, int c1, const float* x2, int c2, const float* gamma, const float* beta, void* y,
+                           void* raw, int batch, int hw, int groups, int R, int S, float eps, int silu, const float* ws,
+                           cudaStream_t st) {
+  const int threads = ((c1 + c2) / 4) * R;
+  static int occ_small = 0, occ_big = 0;
+  int& occ = threads <= 256 ? occ_small : occ_big;
+  if (occ == 0) {
+    cudaError_t e = threads <= 256
+        ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gn_apply_kernel<T, 256>, 256, 0)
+        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gn_apply_kernel<T, 512>, 512, 0);
+    if (e != cudaSuccess || occ < 1) occ = 1;
+  }
+  static const int per_sm_env = getenv("LDMB200_GN_BLOCKS_PER_SM") ? atoi(getenv("LDMB200_GN_BLOCKS_PER_SM")) : 0;
+  const int slots = sm_count() * (per_sm_env > 0 ? per_sm_env : occ);
+  int nblk = hw / (R * 4);
+  if (nblk > slots / batch) nblk = slots / batch;
+  if (nblk < 1) nblk = 1;
+  if (threads <= 256)
+    gn_apply_kernel<T, 256><<<dim3(nblk, batch), threads, 0, st>>>(x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw, hw, groups, R,
+                                                                 S, eps, silu, ws);
+  else if (threads <= 512)
+    gn_apply_kernel<T, 512><<<dim3(nblk, batch), threads, 0, st>>>(x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw, hw, groups,
+                                                                  R, S, eps, silu, ws);
+  else  // C > 2048: one block per SM slot
+    gn_apply_kernel<T, 1024><<<dim3(nblk, batch), threads, 0, st>>>(x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw, hw, groups,
+                                                                   R, S, eps, silu, ws);
+  return 0;
+}
+
 extern "C" {
 
 int ldmb200_ddim_step(const float* x, const float* e_cond, const float* e_uncond, const float* noise, float* x_prev,
@@ -711,14 +746,8 @@ int ldmb200_groupnorm(const float* x1, int c1, const float* x2, int c2, const fl
   cudaStream_t st = (cudaStream_t)stream;
   gn_stats_kernel<<<dim3(S, batch), threads, smem, st>>>(x1, c1, x2, c2, hw, groups, R, stats_ws);
   LDM_CHECK_LAUNCH("groupnorm stats");
-  int T = hw / (R * 4);
-  int want = ceil_div(sm_count() * 4, batch);
-  if (T > want) T = want;
-  if (T < 1) T = 1;
-  const int nblk = T;
-  LDM_DISPATCH_DTYPE(out_dtype, (gn_apply_kernel<T><<<dim3(nblk, batch), threads, 0, st>>>(
-                                    x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw_copy, hw, groups, R, S, eps, silu,
-                                    stats_ws)));
+  LDM_DISPATCH_DTYPE(out_dtype, (gn_apply_launch<T>(x1, c1, x2, c2, gamma, beta, y, raw_copy, batch, hw, groups, R, S, eps,
+                                                    silu, stats_ws, st)));
   LDM_CHECK_LAUNCH("groupnorm apply");
   return 0;
 }
@@ -738,15 +767,8 @@ int ldmb200_groupnorm_fused(const float* x1, int c1, const float* colstats1, con
   gn_finalize_kernel<<<dim3(groups, batch), 128, 0, st>>>(colstats1, c1, colstats2, c2, hw, groups, eps, stats_ws);
   LDM_CHECK_LAUNCH("groupnorm finalize");
   const int R = gn_rows_per_block(C);
-  const int threads = (C / 4) * R;
-  int nblk = hw / (R * 4);
-  static const int per_sm = getenv("LDMB200_GN_BLOCKS_PER_SM") ? atoi(getenv("LDMB200_GN_BLOCKS_PER_SM")) : 8;  // measured r01t: 4 -> 2.68, 8 -> 2.47, 16 -> 2.47, 32 -> 2.56 ms of GroupNorm per UNet eval
-  int want = ceil_div(sm_count() * per_sm, batch);
-  if (nblk > want) nblk = want;
-  if (nblk < 1) nblk = 1;
-  LDM_DISPATCH_DTYPE(out_dtype, (gn_apply_kernel<T><<<dim3(nblk, batch), threads, 0, st>>>(
-                                    x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw_copy, hw, groups, R, 0, eps, silu,
-                                    stats_ws)));
+  LDM_DISPATCH_DTYPE(out_dtype, (gn_apply_launch<T>(x1, c1, x2, c2, gamma, beta, y, raw_copy, batch, hw, groups, R, 0, eps,
+                                                    silu, stats_ws, st)));
   LDM_CHECK_LAUNCH("groupnorm apply");
   return 0;
 }

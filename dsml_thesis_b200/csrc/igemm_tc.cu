@@ -18,6 +18,10 @@
 
 #include "common.cuh"
 
+#ifndef LDM_TC_RES_PREFETCH
+#define LDM_TC_RES_PREFETCH 1
+#endif
+
 namespace ldm {
 
 struct TcParams {
@@ -347,6 +351,23 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       const int tile_sample = (tm * Cfg::BM) / p.rows_per_sample;
       float4 res[8];
       const int cc_first = par;
+#if LDM_TC_RES_PREFETCH
+      // The +residual GEMMs with K <= 640 are bound by the latency of the residual read (ncu r01s: 80 KB of fp32
+      // residual per tile with at most one 4 KB chunk per warp in flight = 7.4 us per tile): pull the NEXT tile's
+      // residual rows into L2 now, a whole tile time ahead; fire-and-forget, no registers held.
+      if (has_res) {
+        const int tile_n = tile + gridDim.x;
+        if (tile_n < ntiles) {
+          const int m = (tile_n / p.tiles_n) * Cfg::BM + qw * 32 + lane;
+          if (m < p.M) {
+            const char* rp = reinterpret_cast<const char*>(p.residual + (size_t)m * p.residual_ld + (tile_n % p.tiles_n) * BN);
+#pragma unroll
+            for (int l = par; l < (BN * 4 + 127) / 128; l += CSTEP)
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + l * 128));
+          }
+        }
+      }
+#endif
       // the residual tile does not depend on the accumulator: fetch it while the MMAs are still running
       // (a second chunk of lookahead was measured r01u: slower by 15-45 % on the K <= 640 GEMMs - register spills)
       if (has_res && cc_first < NCH) {
@@ -406,7 +427,11 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
               bv[4 * j] = t.x; bv[4 * j + 1] = t.y; bv[4 * j + 2] = t.z; bv[4 * j + 3] = t.w;
             }
 #pragma unroll
-            for (int j = 0; j < 16; ++j) v[j] = (v[j] + bv[j]) * gelu_erf_fast(v[16 + j] + bv[16 + j]);
+            for (int j = 0; j < 16; j += 2) {  // packed fp32 pairs: half the issue slots of the epilogue's bound
+              const f32x2 val2 = add2(pk2(v[j], v[j + 1]), pk2(bv[j], bv[j + 1]));
+              const f32x2 g2 = add2(pk2(v[16 + j], v[17 + j]), pk2(bv[16 + j], bv[17 + j]));
+              unpk2(mul2(val2, gelu_erf_fast2(g2)), v[j], v[j + 1]);
+            }
 #pragma unroll
             for (int j = 0; j < 4; ++j)
               *reinterpret_cast<float4*>(&st[lane * PITCH + j * 4]) = make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);

@@ -174,9 +174,9 @@ class _TrainPlan(_Plan):
         if self.building_bwd:
             super().free(*acts)
 
-    def emit(self, name: str, *args, flops: float = 0.0, bytes_: float = 0.0, what: str = ""):
+    def emit(self, name: str, *args, flops: float = 0.0, bytes_: float = 0.0, what: str = "", outs=()):
         if not self.building_bwd:
-            return super().emit(name, *args, flops=flops, bytes_=bytes_, what=what)
+            return super().emit(name, *args, flops=flops, bytes_=bytes_, what=what, outs=outs)
         # weight gradients are leaves of the dependency graph (nothing downstream reads them before the step ends):
         # they run on a side stream and fill the SMs the latency-bound main chain leaves idle
         self.bwd_ops.append((getattr(self.lib, name), args, name, name == "ldmb200_wgrad"))

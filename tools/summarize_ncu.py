@@ -107,6 +107,23 @@ def main(paths):
             print(f"| {r[0]} | `{short(r[kname])}` | {r[grid] if grid is not None else ''} | "
                   f"{r[block] if block is not None else ''} | " + " | ".join(cells) + tail)
         print()
+        # warp-stall breakdown (stall cycles per issue-active cycle): what the warps wait for
+        stall = [(h.split("issue_stalled_")[1].split("_per_issue")[0], j) for j, h in enumerate(hdr)
+                 if "average_warps_issue_stalled_" in h and h.endswith("_per_issue_active.ratio")]
+        if stall:
+            keep = [n for n, _ in stall if n not in ("selected",)]
+            print("| # | kernel | " + " | ".join(keep) + " |")
+            print("|---:|---|" + "---:|" * len(keep))
+            for r in body:
+                if len(r) <= kname:
+                    continue
+                cells = []
+                for n, j in stall:
+                    if n in keep:
+                        v = num(r[j])
+                        cells.append("-" if v is None else f"{v:.2f}")
+                print(f"| {r[0]} | `{short(r[kname])}` | " + " | ".join(cells) + " |")
+            print()
 
 
 if __name__ == "__main__":

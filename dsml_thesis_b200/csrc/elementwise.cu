@@ -279,6 +279,15 @@ __global__ void upsample2x_kernel(const float* __restrict__ x, T* __restrict__ y
   }
 }
 
+// x fp32 [n] -> y [n] (16-bit GEMM operand of a map that is consumed as it is: the folded upsample convolution)
+template <typename T>
+__global__ void cast_rows_kernel(const float* __restrict__ x, T* __restrict__ y, int64_t n4) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 v = reinterpret_cast<const float4*>(x)[i];
+    Store4<T>::st(y + i * 4, v.x, v.y, v.z, v.w);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // K7 GroupNorm (+SiLU) over channels-last [B, HW, C1 (+C2)].  Two launches:
 //   stats: grid (S, B); thread owns one channel quad, sums x and x^2 over its rows; block reduces channel
@@ -587,6 +596,29 @@ __global__ void __launch_bounds__(256) pack_weights_kernel(const ldmb200_pack_jo
     }
     return;
   }
+  if (j.kind == 4) {
+    // K10 folded into the conv: nearest-2x + 3x3 (pad 1) = per output parity (py, px) a 2x2 convolution on the low-res
+    // map whose tap (a, b) sums the 3x3 taps that land on the same low-res pixel: rows {py=0: a0 <- kh 0, a1 <- kh 1,2;
+    // py=1: a0 <- kh 0,1, a1 <- kh 2}, columns alike.  dst = [4 parities][n_pad][4 taps][c_pad]; sums in fp32.
+    const int64_t kp4 = 4 * (int64_t)j.c_pad, per = (int64_t)j.n_pad * kp4;
+    for (int64_t i = i0; i < 4 * per; i += stride) {
+      const int par = (int)(i / per);
+      const int64_t r = i % per;
+      const int rp = (int)(r / kp4), rem = (int)(r % kp4), tap = rem / j.c_pad, c = rem % j.c_pad;
+      const int py = par >> 1, px = par & 1, a = tap >> 1, b = tap & 1;
+      const int kh0 = (py == 0) ? (a == 0 ? 0 : 1) : (a == 0 ? 0 : 2), kh1 = (py == 0) ? (a == 0 ? 0 : 2) : (a == 0 ? 1 : 2);
+      const int kw0 = (px == 0) ? (b == 0 ? 0 : 1) : (b == 0 ? 0 : 2), kw1 = (px == 0) ? (b == 0 ? 0 : 2) : (b == 0 ? 1 : 2);
+      float v = 0.f;
+      if (rp < j.n && c < j.c) {
+        const float* w = j.src + ((size_t)rp * j.c + c) * 9;
+        for (int kh = kh0; kh <= kh1; ++kh)
+          for (int kw = kw0; kw <= kw1; ++kw) v += w[kh * 3 + kw];
+      }
+      dst[i] = j.dst_dtype == LDMB200_F16 ? __half_as_ushort(__float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f)))
+                                          : __bfloat16_as_ushort(__float2bfloat16_rn(v));
+    }
+    return;
+  }
   const int64_t total = (int64_t)j.n_pad * kp;
   for (int64_t i = i0; i < total; i += stride) {
     int rp = (int)(i / kp);
@@ -722,6 +754,14 @@ int ldmb200_upsample2x(const float* x, void* y, int out_dtype, int batch, int h,
   int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), (int64_t)sm_count() * 16);
   LDM_DISPATCH_DTYPE(out_dtype, (upsample2x_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (T*)y, batch, h, w, c)));
   LDM_CHECK_LAUNCH("upsample2x");
+  return 0;
+}
+
+int ldmb200_cast_rows(const float* x, void* y, int out_dtype, int64_t n, void* stream) {
+  LDM_CHECK_ARG(x && y && n > 0 && n % 4 == 0, "cast_rows: bad arguments (n %% 4 == 0)");
+  int blocks = (int)std::min<int64_t>(ceil_div64(n / 4, 256), (int64_t)sm_count() * 16);
+  LDM_DISPATCH_DTYPE(out_dtype, (cast_rows_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (T*)y, n / 4)));
+  LDM_CHECK_LAUNCH("cast_rows");
   return 0;
 }
 

@@ -42,6 +42,11 @@ struct TcParams {
   void* out;
   int out_dtype, out_ld, out_nchw, n_valid;
   float* colstats;  // optional [M/32][n_valid][2]: per 32-row block column sums / sums of squares of the stored values
+  // K10 folded into the conv (nearest-2x upsample + 3x3 = four 2x2 convolutions on the LOW-RES map, one per output
+  // parity, with tap-summed weights): the GEMM's M space is the low-res pixel grid, row m = (n, y, x) is stored at
+  // output pixel (n, 2y + up_py, 2x + up_px).  up_w == 0: off.
+  int up_w, up_hw, up_py, up_px;
+  int b_row0;  // first row of this launch's weight set inside the B tensor map
   uint32_t idesc;  // tcgen05 instruction descriptor (operand format bf16 or f16, M = 128, N = BN)
 };
 
@@ -150,15 +155,20 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
         t[q].x += rs.x; t[q].y += rs.y; t[q].z += rs.z; t[q].w += rs.w;
       }
     }
+    size_t mo = (size_t)m;
+    if (p.up_w) {  // folded upsample: low-res pixel -> its output pixel of this launch's parity
+      const int n = m / p.up_hw, rem = m - n * p.up_hw, y = rem / p.up_w, x = rem - y * p.up_w;
+      mo = (size_t)n * 4 * p.up_hw + (size_t)(2 * y + p.up_py) * (2 * p.up_w) + 2 * x + p.up_px;
+    }
     if (OUT16) {
       uint4 u;
       u.x = pack16(t[0].x, t[0].y, p.out_dtype);
       u.y = pack16(t[0].z, t[0].w, p.out_dtype);
       u.z = pack16(t[NQ - 1].x, t[NQ - 1].y, p.out_dtype);
       u.w = pack16(t[NQ - 1].z, t[NQ - 1].w, p.out_dtype);
-      *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out) + (size_t)m * p.out_ld + col) = u;
+      *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out) + mo * p.out_ld + col) = u;
     } else {
-      *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)m * p.out_ld + col) = t[0];
+      *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + mo * p.out_ld + col) = t[0];
       if (STATS) {
         sx[0] += t[0].x; sx[1] += t[0].y; sx[2] += t[0].z; sx[3] += t[0].w;
         sq[0] = fmaf(t[0].x, t[0].x, sq[0]); sq[1] = fmaf(t[0].y, t[0].y, sq[1]);
@@ -178,7 +188,12 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
       }
     }
     if (lr == 0 && m0 < p.M) {  // (M % 32 == 0: a 32-row block is entirely inside or outside the matrix)
-      float4* dst = reinterpret_cast<float4*>(p.colstats + ((size_t)(m0 >> 5) * p.n_valid + col) * 2);
+      size_t blk = (size_t)(m0 >> 5);
+      if (p.up_w) {  // folded upsample: the output sample's blocks are [4 parities][low-res blocks] (any order sums alike)
+        const int n = m0 / p.up_hw;
+        blk = (size_t)n * (p.up_hw >> 3) + (size_t)(p.up_py * 2 + p.up_px) * (p.up_hw >> 5) + ((m0 - n * p.up_hw) >> 5);
+      }
+      float4* dst = reinterpret_cast<float4*>(p.colstats + (blk * p.n_valid + col) * 2);
       dst[0] = make_float4(sx[0], sq[0], sx[1], sq[1]);
       dst[1] = make_float4(sx[2], sq[2], sx[3], sq[3]);
     }
@@ -250,7 +265,10 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       }
       for (int tap = 0; tap < p.taps; ++tap) {
         int dh = 0, dw = 0, plane = 0;
-        if (p.ks == 3) {
+        if (p.ks == 2) {  // folded upsample: tap (a, b) reads low-res pixel (y + a - 1 + py, x + b - 1 + px)
+          dh = (tap >> 1) - 1 + p.up_py;
+          dw = (tap & 1) - 1 + p.up_px;
+        } else if (p.ks == 3) {
           const int kh = tap / 3, kw = tap % 3;
           if (p.stride == 1) {
             dh = kh - 1;
@@ -284,7 +302,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
               tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, w0 + dw, h0 + dh, plane, n_img);
             else
               tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, 0, m0, 0, 0);
-            tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &full[s], tap * p.ctot + (second ? p.c1 : 0) + c0, tn * BN);
+            tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &full[s], tap * p.ctot + (second ? p.c1 : 0) + c0, p.b_row0 + tn * BN);
           }
           __syncwarp();
         }
@@ -515,7 +533,11 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   LDM_CHECK_ARG(d && d->a && d->w && d->out, "igemm_tc: null pointer");
   LDM_CHECK_ARG(d->a_dtype == LDMB200_BF16 || d->a_dtype == LDMB200_F16,
                 "igemm_tc: A operand must be bf16 or f16 (and the packed weights of the same type)");
-  LDM_CHECK_ARG(!d->upsample, "igemm_tc: upsample must be materialised (ldmb200_upsample2x) on the tensor-core path");
+  const bool fold = d->upsample != 0;
+  LDM_CHECK_ARG(!fold || (d->ksize == 3 && d->stride == 1 && !d->a2 && !d->residual && !d->rowvec && !d->geglu &&
+                          !d->out_nchw && d->pad_mode == 0),
+                "igemm_tc: upsample=1 is the folded nearest-2x + 3x3 convolution (one input, bias only, row-major output); "
+                "w must be the four tap-summed 2x2 weight sets of ldmb200_pack_weights kind 4");
   LDM_CHECK_ARG(d->ksize == 1 || d->ksize == 3, "igemm_tc: ksize must be 1 or 3");
   LDM_CHECK_ARG(d->stride == 1 || (d->stride == 2 && d->ksize == 3), "igemm_tc: stride 2 only for 3x3");
   const int c1 = d->c1, c2 = d->a2 ? d->c2 : 0;
@@ -526,9 +548,14 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   TcParams p;
   memset(&p, 0, sizeof(p));
   LDM_CHECK_ARG((int64_t)d->batch * hw_out > 0 && (int64_t)d->batch * hw_out < (1ll << 31), "igemm_tc: M out of range");
-  p.M = d->batch * hw_out;
-  p.ks = d->ksize;
-  p.taps = d->ksize * d->ksize;
+  p.M = d->batch * hw_out;          // (folded upsample: h_in x w_in IS the low-res grid the GEMM runs on)
+  p.ks = fold ? 2 : d->ksize;
+  p.taps = p.ks * p.ks;
+  if (fold) {
+    p.up_w = d->w_in;
+    p.up_hw = hw_out;
+    LDM_CHECK_ARG(!d->colstats || hw_out % 32 == 0, "igemm_tc: folded upsample with colstats needs h_in*w_in %% 32 == 0");
+  }
   p.stride = d->stride;
   p.is_conv = d->ksize == 3;
   LDM_CHECK_ARG(d->pad_mode == 0 || (d->pad_mode == 1 && d->ksize == 3 && d->stride == 2),
@@ -609,13 +636,25 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   }
   if (!c2) tA2 = tA1;
   {
-    uint64_t dims[2] = {(uint64_t)p.taps * p.ctot, (uint64_t)d->n};
+    uint64_t dims[2] = {(uint64_t)p.taps * p.ctot, (uint64_t)d->n * (fold ? 4 : 1)};
     uint64_t str[1] = {(uint64_t)p.taps * p.ctot * 2};
     uint32_t box[2] = {(uint32_t)BK, (uint32_t)BN};
     int rc = make_tensor_map_bf16(&tB, d->w, 2, dims, str, box, BK * 2);
     if (rc) return rc;
   }
   cudaStream_t st = (cudaStream_t)stream;
+  if (fold) {  // four launches, one per output parity; each reads its own weight set and writes its own pixels
+    for (int par = 0; par < 4; ++par) {
+      p.up_py = par >> 1;
+      p.up_px = par & 1;
+      p.b_row0 = par * d->n;
+      int rc = (BN == 160) ? launch_tc<160, 64, 8>(tA1, tA2, tB, p, st)
+               : (BN == 128) ? launch_tc<128, 64, 16>(tA1, tA2, tB, p, st)
+               : (BN == 32) ? launch_tc<32, 64, 8>(tA1, tA2, tB, p, st) : launch_tc<16, 64, 8>(tA1, tA2, tB, p, st);
+      if (rc) return rc;
+    }
+    return 0;
+  }
   if (BN == 128) return d->geglu ? launch_tc<128, 64, 16, true>(tA1, tA2, tB, p, st) : launch_tc<128, 64, 16>(tA1, tA2, tB, p, st);
   LDM_CHECK_ARG(!d->geglu || d->n % 32 == 0, "igemm_tc: geglu needs n %% 32 == 0 (got n=%d)", d->n);
   if (d->geglu) return launch_tc<32, 64, 8, true>(tA1, tA2, tB, p, st);

@@ -206,7 +206,19 @@ class _WeightPack:
             off += n_pad * ksize * ksize * c_pad * 2
             off = (off + 255) // 256 * 256
 
+        def add_fold(key, w):
+            """Upsample.conv folded with the nearest-2x upsample (K10): four tap-summed 2x2 weight sets (pack kind 4)."""
+            nonlocal off
+            n, c = w.shape[0], w.shape[1]
+            n_pad, c_pad = _tc_npad(n), _tc_cpad(c)
+            jobs.append((w, off, 4, n, c, 3, n_pad, c_pad, 0, _tc_bn(n_pad)))
+            self.entries[key] = (off, n_pad, c_pad)
+            off += 4 * n_pad * 4 * c_pad * 2
+            off = (off + 255) // 256 * 256
+
         for name, m in model.named_modules():
+            if isinstance(m, Upsample):
+                add_fold(name + ".conv.fold", m.conv.weight)
             if isinstance(m, nn.Conv2d):
                 add(name, [m.weight], m.kernel_size[0])
             elif isinstance(m, BasicTransformerBlock):
@@ -328,6 +340,7 @@ class _Plan:
         self.gn_ws = torch.empty(int(self.lib.ldmb200_groupnorm_ws_floats(B, H * W, 0)), **f32)
         self.graph = None
         self.runs = 0
+        self.fold_upsample = getattr(self, "fold_upsample", os.environ.get("LDMB200_FOLD_UPSAMPLE", "1") == "1")
         self._build()
 
     # ---- small helpers -------------------------------------------------------------------
@@ -508,6 +521,8 @@ class _Plan:
                 d.colstats = res.stats.ptr
         self.keep.append(d)
         k_true = weight.shape[1] * ksize * ksize if weight.dim() >= 2 and n_true == weight.shape[0] else a.c
+        if upsample and tc:
+            k_true = weight.shape[1] * 4        # executed: four 2x2 convolutions on rows/4 pixels each = rows x 4C
         eb = lambda dt: 4 if dt == F32 else 2
         # algorithmic bytes: the input map once, the weights once, the output once (+ the fp32 residual it adds)
         abytes = (a.rows * a.c * eb(a.dtype) + n_true * k_true * (2 if tc else 4)
@@ -515,7 +530,7 @@ class _Plan:
                   + (rows * n_cols * 4 if residual is not None else 0))
         self.emit("ldmb200_igemm_tc" if tc else "ldmb200_igemm_simt", C.byref(d), flops=2.0 * rows * n_true * k_true,
                   bytes_=abytes,
-                  what=f"M{rows} N{n_true} K{k_true} ks{ksize} s{stride}" + (" geglu" if geglu else "")
+                  what=f"M{rows} N{n_true} K{k_true} ks{ksize} s{stride}" + (" geglu" if geglu else "") + (" upfold" if upsample and tc else "")
                   + (" res" if residual is not None else "") + ({BF16: " bf16out", F16: " f16out"}.get(out_dtype, "")),
                   outs=(res,))
         return res
@@ -629,6 +644,15 @@ class _Plan:
 
     def upsample(self, m: Upsample, name: str, x: _Act, H: int, W: int) -> _Act:
         """openaimodel.py:109-119: nearest 2x, then conv 3x3."""
+        if self.tc and self.fold_upsample and H & (H - 1) == 0 and W & (W - 1) == 0:
+            # K10 folded into the conv: the 16-bit copy of the LOW-RES map is the operand of four 2x2 convolutions (one per
+            # output parity, tap-summed weights): 4/9 of the flops, no materialised 4x larger map
+            lo = self.new(x.rows, x.c, self.act)
+            self.emit("ldmb200_cast_rows", x.ptr, lo.ptr, self.act, x.rows * x.c, bytes_=x.rows * x.c * 6, outs=(lo,))
+            out = self.gemm(lo, name + ".conv.fold", m.conv.weight, m.conv.bias, H, W, ksize=3, upsample=1,
+                            want_stats=(H * W) % 32 == 0)
+            self.free(lo)
+            return out
         if self.tc:
             u = self.new(4 * x.rows, x.c, self.act)
             self.emit("ldmb200_upsample2x", x.ptr, u.ptr, self.act, self.B, H, W, x.c, outs=(u,))

@@ -128,6 +128,9 @@ int ldmb200_layernorm(const float* x, const float* gamma, const float* beta, voi
  */
 int ldmb200_space_to_depth2(const float* x, void* y, int out_dtype, int batch, int h, int w, int c, void* stream);
 int ldmb200_upsample2x(const float* x, void* y, int out_dtype, int batch, int h, int w, int c, void* stream);
+/* x fp32 [n] -> y [n] in out_dtype (n % 4 == 0): the 16-bit operand copy of a residual-stream map that a GEMM reads as it
+ * is — the low-res input of the folded Upsample convolution (ldmb200_igemm_tc with upsample = 1). */
+int ldmb200_cast_rows(const float* x, void* y, int out_dtype, int64_t n, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * K1-K4 (+K8,K10,K11)  Convolution / linear as (implicit) GEMM with fused epilogue.
@@ -139,8 +142,11 @@ int ldmb200_upsample2x(const float* x, void* y, int out_dtype, int batch, int h,
  *   out[m, j] = geglu ? v[value col] * gelu_erf(v[gate col]) : v           (attention.py:43-44)
  *
  * A is read from one or two channels-last maps (virtual concat, c1 + c2 channels per tap) of spatial size
- * h_in x w_in; ksize 1 or 3 (padding 1); stride 1 or 2; upsample=1 reads the nearest-2x upsampled map
- * (SIMT path only — the tensor-core path takes a materialised ldmb200_upsample2x / space_to_depth2 input).
+ * h_in x w_in; ksize 1 or 3 (padding 1); stride 1 or 2; upsample=1 = Upsample.forward (openaimodel.py:109-119):
+ * F.interpolate(x, scale_factor=2, mode="nearest") followed by the 3x3 convolution, h_in x w_in being the LOW-RES map.
+ * The SIMT path folds the upsample into its input index map; the tensor-core path runs it as FOUR 2x2 convolutions on
+ * the low-res map, one per output parity, with tap-summed weights (w = the kind-4 pack of ldmb200_pack_weights:
+ * [4][n][4 taps][c]) — 4/9 of the flops and no materialised 4x larger map.
  */
 typedef struct ldmb200_gemm_desc {
   const void* a;         /* first map  [B, h_in, w_in, c1] (plain GEMM: [M, c1] with h_in = M/batch, w_in = 1) */
@@ -176,7 +182,7 @@ typedef struct ldmb200_gemm_desc {
 /* fp32-exact SIMT path (precision mode "fp32": per-step eps rel-L2 <= 1e-4 vs the fp32 reference). */
 int ldmb200_igemm_simt(const ldmb200_gemm_desc* d, void* stream);
 /* tcgen05 / TMEM / TMA path: bf16 operands, fp32 accumulation in tensor memory.
- * Requirements: a_dtype bf16, c1 % 32 == 0, c2 % 32 == 0, w packed, upsample == 0. */
+ * Requirements: a_dtype bf16 / f16, c1 % 16 == 0, c2 % 16 == 0, w packed; upsample = 1 needs the kind-4 pack. */
 int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream);
 
 /* Weight packing for the tensor-core path (one launch for the whole model, re-run whenever weights change —
@@ -190,6 +196,9 @@ int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream);
  *           dX = conv(dY, dst) through the same ldmb200_igemm_tc (autograd's conv2d / linear input gradient).
  *           n_pad = padded row count (from c), c_pad = padded column count (from n); row_offset here offsets the
  *           destination COLUMN (fused QKV: the q, k, v blocks sit side by side along K)
+ *   kind 4  folded Upsample convolution (K10): [n, c, 3, 3] -> [4 parities][n_pad][4 taps][c_pad], parity = py*2 + px of
+ *           the output pixel, tap = a*2 + b of the 2x2 window on the low-res map; each tap is the fp32 sum of the 3x3 taps
+ *           that read the same low-res pixel (py=0: a0 <- kh 0, a1 <- kh 1+2; py=1: a0 <- kh 0+1, a1 <- kh 2; kw alike)
  * jobs is a DEVICE array of n_jobs ldmb200_pack_job.
  */
 typedef struct ldmb200_pack_job {

@@ -55,6 +55,17 @@ def pack_weight(w, kind=0, bias=None, parts=None, dtype=BF16):
     c = ws[0].shape[1]
     n_tot = sum(p.shape[0] for p in ws)
     n_pad, c_pad = _tc_npad(n_tot), _tc_cpad(c)
+    if kind == 4:   # folded Upsample conv: four tap-summed 2x2 weight sets [4][n_pad][4][c_pad]
+        dst = torch.full((4, n_pad, 4, c_pad), float("nan"), dtype=TORCH_DT[dtype], device=DEV)
+        arr = (PackJob * 1)()
+        j = arr[0]
+        (j.src, j.dst, j.kind, j.n, j.c, j.ksize, j.n_pad, j.c_pad, j.row_offset, j.block_n) = (
+            ws[0].data_ptr(), dst.data_ptr(), 4, n_tot, c, 3, n_pad, c_pad, 0, _tc_bn(n_pad))
+        j.dst_dtype = dtype
+        dev_jobs = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(DEV)
+        _cabi.call("ldmb200_pack_weights", dev_jobs.data_ptr(), 1, stream())
+        torch.cuda.synchronize()
+        return dst, None, n_pad, c_pad
     dst = torch.full((n_pad, ks * ks, c_pad), float("nan"), dtype=TORCH_DT[dtype], device=DEV)
     fb = torch.full((n_tot,), float("nan"), dtype=torch.float32, device=DEV) if (kind == 1 and bias is not None) else None
     jobs = []
@@ -99,7 +110,7 @@ def igemm(mode, a, B, h_in, w_in, w, bias=None, ksize=1, stride=1, upsample=0, a
     d.batch, d.h_in, d.w_in = B, h_in, w_in
     d.ksize, d.stride, d.upsample = ksize, stride, upsample
     if mode == "tc":
-        wp, fb, n_pad, c_pad = pack_weight(w, kind=1 if geglu else 0, bias=bias, dtype=d.a_dtype)
+        wp, fb, n_pad, c_pad = pack_weight(w, kind=4 if upsample else (1 if geglu else 0), bias=bias, dtype=d.a_dtype)
         assert c_pad == d.c1 + d.c2 or d.c2 == 0, "test harness: concat inputs must be multiples of 32"
         keep += [wp, fb]
         d.w, d.n = wp.data_ptr(), n_pad

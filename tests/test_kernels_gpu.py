@@ -373,3 +373,26 @@ def test_attn_tc_rereference(N, growth):
     ref = K.attention_reference(q, k, v, heads, 32 ** -0.5)
     assert torch.isfinite(out).all()
     assert K.rel_l2(out, ref) <= 6e-3
+
+
+# ------------------------------------------------------------------------------------------ K10 folded into the conv
+@pytest.mark.parametrize("B,H,cin,cout", [(2, 16, 32, 32), (1, 32, 64, 160), (3, 8, 160, 320), (2, 4, 32, 64)])
+@pytest.mark.parametrize("dt", [BF16, F16])
+def test_tc_upsample_fold(B, H, cin, cout, dt):
+    """Upsample.forward (openaimodel.py:109-119) on the tensor-core path: nearest-2x + 3x3 conv as four 2x2 convolutions on
+    the low-res map with tap-summed weights (pack kind 4), against F.interpolate + conv2d on the same 16-bit-rounded
+    input; the epilogue's GroupNorm column statistics must describe the tensor it wrote."""
+    x = r16(rnd(B, cin, H, H), dt)
+    w, b = rnd(cout, cin, 3, 3) / (3 * cin ** 0.5), 0.1 * rnd(cout)
+    a = K.to_cl(x).to(K.TORCH_DT[dt])
+    M = B * 4 * H * H
+    cs = torch.full((M // 32, cout, 2), float("nan"), device="cuda") if (H * H) % 32 == 0 else None
+    out = K.igemm("tc", a, B, H, H, w, b, ksize=3, upsample=1, colstats=cs)
+    ref = K.to_cl(K.igemm_reference(x, w, b, upsample=1))
+    # the four tap sums are rounded to 16 bits once each (instead of nine separately rounded taps): operand-rounding noise
+    assert K.rel_l2(out, ref) <= OUT_TOL[dt]
+    if cs is not None:
+        o = out.reshape(B, 4 * H * H, cout).double()
+        tot = cs.reshape(B, 4 * H * H // 32, cout, 2).double().sum(1)
+        assert torch.allclose(tot[..., 0], o.sum(1), rtol=1e-4, atol=1e-3)
+        assert torch.allclose(tot[..., 1], (o * o).sum(1), rtol=1e-4, atol=1e-3)

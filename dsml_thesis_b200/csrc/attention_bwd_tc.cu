@@ -40,7 +40,7 @@ constexpr int AX_ACC = 256;                    // TMEM: T1_u at u*128, T2_u at u
 
 struct AxParams {
   uint16_t* dqkv;
-  const float2* ld;     // [B, heads, n_pad] {lse2, D}
+  const float2* ld;     // [B, heads, n_pad] x 2 floats: {-lse2, -D scale}, pair-interleaved (attention_bwd_prep_kernel)
   int ld_qkv, q_off, k_off, v_off;
   int n_tok, n_pad, heads;
   float scale, scale_log2e;
@@ -221,12 +221,12 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv128, const __g
     const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
     const int grow = row0 + r;                      // row index inside the sample
     float lse_r = 0.f, d_r = 0.f;
-    if (!KV && grow < p.n_tok) {
-      const float2 v = p.ld[((size_t)b * p.heads + h) * p.n_pad + grow];
-      lse_r = v.x;
-      d_r = v.y;
+    if (!KV && grow < p.n_tok) {  // (already negated: the stage only adds)
+      const float* lp = reinterpret_cast<const float*>(p.ld + ((size_t)b * p.heads + h) * p.n_pad) + (size_t)(grow >> 1) * 4 + (grow & 1);
+      lse_r = lp[0];
+      d_r = lp[2];
     }
-    const float c_ = p.scale_log2e, sc = p.scale;
+    const f32x2 c2 = pk2(p.scale_log2e, p.scale_log2e), sc2 = pk2(p.scale, p.scale);
     for (int i = set; i < n_slabs; i += AX_SETS) {
       const int u = i & 1, s = i % AX_ST;
       if (KV) mbar_wait(&st_full[s], (i / AX_ST) & 1);     // the slab's {lse2, D}
@@ -248,19 +248,25 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv128, const __g
         for (int q4 = 0; q4 < 4; ++q4) {            // 8 columns -> one 16-byte unit of each operand row
           uint32_t pk[4], dk[4];
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
+          for (int e = 0; e < 4; ++e) {  // one column pair on the packed fp32 pipe: 2 FFMA2 + 2 ex2 + FMUL2 + packs
             const int j = q4 * 8 + e * 2;
-            float l0 = lse_r, l1 = lse_r, dd0 = d_r, dd1 = d_r;
-            if (KV) {
-              const float4 v = *reinterpret_cast<const float4*>(ldp + j);   // {lse, D} of columns j, j+1 (broadcast read)
-              l0 = v.x; dd0 = v.y; l1 = v.z; dd1 = v.w;
+            f32x2 nl2 = pk2(lse_r, lse_r), nd2 = pk2(d_r, d_r);
+            if (KV) {   // {-lse_j, -lse_j+1 | -D_j, -D_j+1}: the two halves of one 16-byte word (broadcast read)
+              const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(ldp + j);
+              nl2 = v.x;
+              nd2 = v.y;
             }
-            float p0 = ax_ex2(fmaf(t1[j], c_, -l0)), p1 = ax_ex2(fmaf(t1[j + 1], c_, -l1));
+            float p0, p1, x0, x1;
+            unpk2(fma2(pk2(t1[j], t1[j + 1]), c2, nl2), x0, x1);
+            p0 = ax_ex2(x0);
+            p1 = ax_ex2(x1);
             if (CHECK) {
               if (col0 + j >= p.n_tok) p0 = 0.f;
               if (col0 + j + 1 >= p.n_tok) p1 = 0.f;
             }
-            dk[e] = ax_pack(p0 * fmaf(t2[j], sc, -dd0), p1 * fmaf(t2[j + 1], sc, -dd1));
+            float s0, s1;
+            unpk2(mul2(pk2(p0, p1), fma2(pk2(t2[j], t2[j + 1]), sc2, nd2)), s0, s1);
+            dk[e] = ax_pack(s0, s1);
             if (KV) pk[e] = ax_pack(p0, p1);
           }
           const int unit = wg * 4 + q4;
@@ -304,7 +310,9 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv128, const __g
   }
 }
 
-// D_i = sum_d dO_id O_id and the forward's lse2 -> ld[b, h, i] = {lse2, D * scale}   (thread per (row, head))
+// D_i = sum_d dO_id O_id and the forward's lse2 -> {-lse2, -D * scale} of row i, stored PAIR-INTERLEAVED per (b, h):
+// floats [(i >> 1) * 4 + (i & 1)] = -lse2_i and [(i >> 1) * 4 + 2 + (i & 1)] = -D_i * scale, so that the softmax stage reads
+// the two 64-bit halves of one 16-byte word as ready-made packed-fp32 addends of a column pair (thread per (row, head))
 __global__ void __launch_bounds__(256) attention_bwd_prep_kernel(const uint16_t* __restrict__ o, const uint16_t* __restrict__ dout,
                                                                  int o_ld, const float* __restrict__ lse2,
                                                                  float2* __restrict__ ld, int batch, int heads, int n_tok,
@@ -331,9 +339,11 @@ __global__ void __launch_bounds__(256) attention_bwd_prep_kernel(const uint16_t*
         acc = fmaf(__uint_as_float(xs[e] & 0xffff0000u), __uint_as_float(ys[e] & 0xffff0000u), acc);
       }
     }
-    out = make_float2(lse2[((size_t)b * heads + h) * n_tok + i], acc * scale);
+    out = make_float2(-lse2[((size_t)b * heads + h) * n_tok + i], -acc * scale);
   }
-  ld[((size_t)b * heads + h) * n_pad + i] = out;
+  float* dst = reinterpret_cast<float*>(ld + ((size_t)b * heads + h) * n_pad) + (size_t)(i >> 1) * 4 + (i & 1);
+  dst[0] = out.x;
+  dst[2] = out.y;
 }
 
 int attention_bwd_tc_launch(const void* qkv, int ld, int q_off, int k_off, int v_off, const void* out, const void* dout,

@@ -107,6 +107,7 @@ SIGNATURES = {
     "ldmb200_space_to_depth2": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "ldmb200_upsample2x": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "ldmb200_cast_rows": (_i, [_p, _p, _i, _i64, _p]),
+    "ldmb200_count_f16_saturated": (_i, [_p, _i64, _p, _p]),
     "ldmb200_igemm_simt": (_i, [C.POINTER(GemmDesc), _p]),
     "ldmb200_igemm_tc": (_i, [C.POINTER(GemmDesc), _p]),
     "ldmb200_pack_weights": (_i, [_p, _i, _p]),

@@ -288,6 +288,15 @@ __global__ void cast_rows_kernel(const float* __restrict__ x, T* __restrict__ y,
   }
 }
 
+// fp16 operand range guard: elements at the clamp of the saturating conversion (|v| >= 65504) or not finite
+__global__ void count_f16_saturated_kernel(const uint16_t* __restrict__ x, int64_t n, unsigned long long* __restrict__ counter) {
+  unsigned int c = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    c += (x[i] & 0x7fffu) >= 0x7bffu;
+  c = __reduce_add_sync(0xffffffffu, c);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(counter, (unsigned long long)c);
+}
+
 // ---------------------------------------------------------------------------------------------
 // K7 GroupNorm (+SiLU) over channels-last [B, HW, C1 (+C2)].  Two launches:
 //   stats: grid (S, B); thread owns one channel quad, sums x and x^2 over its rows; block reduces channel
@@ -762,6 +771,14 @@ int ldmb200_cast_rows(const float* x, void* y, int out_dtype, int64_t n, void* s
   int blocks = (int)std::min<int64_t>(ceil_div64(n / 4, 256), (int64_t)sm_count() * 16);
   LDM_DISPATCH_DTYPE(out_dtype, (cast_rows_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (T*)y, n / 4)));
   LDM_CHECK_LAUNCH("cast_rows");
+  return 0;
+}
+
+int ldmb200_count_f16_saturated(const void* x, int64_t n, void* counter_u64, void* stream) {
+  LDM_CHECK_ARG(x && counter_u64 && n > 0, "count_f16_saturated: bad arguments");
+  int blocks = (int)std::min<int64_t>(ceil_div64(n, 256 * 8), (int64_t)sm_count() * 8);
+  count_f16_saturated_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const uint16_t*)x, n, (unsigned long long*)counter_u64);
+  LDM_CHECK_LAUNCH("count_f16_saturated");
   return 0;
 }
 

@@ -120,7 +120,7 @@ __device__ __forceinline__ void epi_load_add(const TcParams& p, float4 (&add)[2]
   }
 }
 
-template <bool OUT16, int COLS, bool STATS = false>
+template <bool OUT16, int COLS, bool STATS = false, bool UP = false>
 __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, int pitch, int m0, int col0, int lane,
                                           const float4 (&res)[8], bool has_res, const float4 (&add)[2]) {
   static_assert(!(STATS && OUT16), "column statistics are taken of fp32 outputs only");
@@ -156,7 +156,8 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
       }
     }
     size_t mo = (size_t)m;
-    if (p.up_w) {  // folded upsample: low-res pixel -> its output pixel of this launch's parity
+    if (UP) {  // folded upsample: low-res pixel -> its output pixel of this launch's parity (compile-time: the r02g build
+               // carried this as a runtime branch in every instantiation and lost 15 % on all 1x1 GEMMs to code size)
       const int n = m / p.up_hw, rem = m - n * p.up_hw, y = rem / p.up_w, x = rem - y * p.up_w;
       mo = (size_t)n * 4 * p.up_hw + (size_t)(2 * y + p.up_py) * (2 * p.up_w) + 2 * x + p.up_px;
     }
@@ -189,7 +190,7 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
     }
     if (lr == 0 && m0 < p.M) {  // (M % 32 == 0: a 32-row block is entirely inside or outside the matrix)
       size_t blk = (size_t)(m0 >> 5);
-      if (p.up_w) {  // folded upsample: the output sample's blocks are [4 parities][low-res blocks] (any order sums alike)
+      if (UP) {  // folded upsample: the output sample's blocks are [4 parities][low-res blocks] (any order sums alike)
         const int n = m0 / p.up_hw;
         blk = (size_t)n * (p.up_hw >> 3) + (size_t)(p.up_py * 2 + p.up_px) * (p.up_hw >> 5) + ((m0 - n * p.up_hw) >> 5);
       }
@@ -204,7 +205,7 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
 // those GEMMs and needs the registers); GG == false handles every other epilogue.
 // O16: the output is a 16-bit type (bf16 / f16) — a template parameter, like GG, so that each instantiation carries one
 // store path only (the kernel was losing 8 % of its issue slots to instruction fetch, ncu r01v).
-template <int BN, int BK, int EW, bool GG, bool O16>
+template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false>
 __global__ void __launch_bounds__(64 + EW * 32, 1)
 igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                 const __grid_constant__ CUtensorMap tmB, const TcParams p) {
@@ -253,6 +254,8 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   const int nchunks = p.c1_chunks + p.c2_chunks;
   if (warp == 0) {
     // ===================== TMA producer (whole warp converged, one elected lane issues) =====================
+    // (a single-thread producer / MMA loop with running stage counters was measured r02l and is SLOWER: big-K convolutions
+    // 0.753 -> 0.934 ms at K = 5760, implicit GEMMs 13.6 -> 14.9 ms per eval; the converged-warp form stays)
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
@@ -392,6 +395,16 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
         if (out16) epi_load_residual<true>(p, res, m0, n0 + cc_first * Cfg::CH, lane);
         else epi_load_residual<false>(p, res, m0, n0 + cc_first * Cfg::CH, lane);
       }
+      // bias / per-sample row vector of the first chunk: fetched before the accumulator wait, and one chunk ahead from then
+      // on (ncu r02j: the FADD that folds the row vector into the bias stalled on these loads — 8 % of the epilogue warps'
+      // samples on the K = 160 GEMMs — because they were issued in the chunk that consumes them)
+      float4 addv[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+      if constexpr (!GG) {
+        if (!p.out_nchw && cc_first < NCH) {
+          if (out16) epi_load_add<true, Cfg::CH>(p, addv, n0 + cc_first * Cfg::CH, lane, true, tile_sample);
+          else epi_load_add<false, Cfg::CH>(p, addv, n0 + cc_first * Cfg::CH, lane, true, tile_sample);
+        }
+      }
       mbar_wait(&tfull[buf], (t_iter >> 1) & 1);
       tc_fence_after();
 #pragma unroll 1
@@ -408,11 +421,11 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
           if (out16) epi_load_residual<true>(p, res_next, m0, n0 + (cc + CSTEP) * Cfg::CH, lane);
           else epi_load_residual<false>(p, res_next, m0, n0 + (cc + CSTEP) * Cfg::CH, lane);
         }
-        float4 addv[2];
+        float4 addv_next[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
         if constexpr (!GG) {
-          if (!p.out_nchw) {
-            if (out16) epi_load_add<true, Cfg::CH>(p, addv, n0 + cc * Cfg::CH, lane, true, tile_sample);
-            else epi_load_add<false, Cfg::CH>(p, addv, n0 + cc * Cfg::CH, lane, true, tile_sample);
+          if (!p.out_nchw && more) {
+            if (out16) epi_load_add<true, Cfg::CH>(p, addv_next, n0 + (cc + CSTEP) * Cfg::CH, lane, true, tile_sample);
+            else epi_load_add<false, Cfg::CH>(p, addv_next, n0 + (cc + CSTEP) * Cfg::CH, lane, true, tile_sample);
           }
         }
         tmem_ld_wait();
@@ -470,14 +483,16 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
         {
           const int col0 = n0 + cc * Cfg::CH;
           if (out16) epi_store<true, Cfg::CH>(p, st, PITCH, m0, col0, lane, res, has_res, addv);
-          else if (p.colstats) epi_store<false, Cfg::CH, true>(p, st, PITCH, m0, col0, lane, res, has_res, addv);
-          else epi_store<false, Cfg::CH>(p, st, PITCH, m0, col0, lane, res, has_res, addv);
+          else if (p.colstats) epi_store<false, Cfg::CH, true, UP>(p, st, PITCH, m0, col0, lane, res, has_res, addv);
+          else epi_store<false, Cfg::CH, false, UP>(p, st, PITCH, m0, col0, lane, res, has_res, addv);
         }
         __syncwarp();
         if (has_res && more) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) res[j] = res_next[j];
         }
+        addv[0] = addv_next[0];
+        addv[1] = addv_next[1];
         }  // !GG
       }
       if (cc_first >= NCH) {  // this warp had no chunk in the tile (BN == CH): still release the buffer
@@ -496,13 +511,13 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   }
 }
 
-template <int BN, int BK, int EW, bool GG, bool O16>
+template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false>
 static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b, const TcParams& p,
                      cudaStream_t st) {
   using Cfg = TcCfg<BN, BK, EW>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG, O16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG, O16, UP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::SMEM_BYTES);
     if (e != cudaSuccess) {
       set_error("igemm_tc: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
@@ -511,7 +526,7 @@ static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CU
     attr_set = true;
   }
   int grid = std::min(p.tiles_m * p.tiles_n, sm_count());
-  igemm_tc_kernel<BN, BK, EW, GG, O16><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(a1, a2, b, p);
+  igemm_tc_kernel<BN, BK, EW, GG, O16, UP><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(a1, a2, b, p);
   LDM_CHECK_LAUNCH("igemm_tc");
   return 0;
 }
@@ -534,6 +549,7 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   LDM_CHECK_ARG(d->a_dtype == LDMB200_BF16 || d->a_dtype == LDMB200_F16,
                 "igemm_tc: A operand must be bf16 or f16 (and the packed weights of the same type)");
   const bool fold = d->upsample != 0;
+  LDM_CHECK_ARG(!fold || d->out_dtype == LDMB200_F32, "igemm_tc: the folded upsample convolution writes fp32");
   LDM_CHECK_ARG(!fold || (d->ksize == 3 && d->stride == 1 && !d->a2 && !d->residual && !d->rowvec && !d->geglu &&
                           !d->out_nchw && d->pad_mode == 0),
                 "igemm_tc: upsample=1 is the folded nearest-2x + 3x3 convolution (one input, bias only, row-major output); "
@@ -648,9 +664,10 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
       p.up_py = par >> 1;
       p.up_px = par & 1;
       p.b_row0 = par * d->n;
-      int rc = (BN == 160) ? launch_tc<160, 64, 8>(tA1, tA2, tB, p, st)
-               : (BN == 128) ? launch_tc<128, 64, 16>(tA1, tA2, tB, p, st)
-               : (BN == 32) ? launch_tc<32, 64, 8>(tA1, tA2, tB, p, st) : launch_tc<16, 64, 8>(tA1, tA2, tB, p, st);
+      int rc = (BN == 160) ? launch_tc_impl<160, 64, 8, false, false, true>(tA1, tA2, tB, p, st)
+               : (BN == 128) ? launch_tc_impl<128, 64, 16, false, false, true>(tA1, tA2, tB, p, st)
+               : (BN == 32) ? launch_tc_impl<32, 64, 8, false, false, true>(tA1, tA2, tB, p, st)
+                            : launch_tc_impl<16, 64, 8, false, false, true>(tA1, tA2, tB, p, st);
       if (rc) return rc;
     }
     return 0;

@@ -131,6 +131,10 @@ int ldmb200_upsample2x(const float* x, void* y, int out_dtype, int batch, int h,
 /* x fp32 [n] -> y [n] in out_dtype (n % 4 == 0): the 16-bit operand copy of a residual-stream map that a GEMM reads as it
  * is — the low-res input of the folded Upsample convolution (ldmb200_igemm_tc with upsample = 1). */
 int ldmb200_cast_rows(const float* x, void* y, int out_dtype, int64_t n, void* stream);
+/* fp16 operand range guard (UNetModel.f16_guard): *counter_u64 += number of the n fp16 values at x that sit at the clamp of
+ * the saturating conversions (|v| >= 65504) or are not finite.  Replaces no reference call site: fp16 operands are this
+ * implementation's choice, the counter is what keeps that choice from changing results silently. */
+int ldmb200_count_f16_saturated(const void* x, int64_t n, void* counter_u64, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * K1-K4 (+K8,K10,K11)  Convolution / linear as (implicit) GEMM with fused epilogue.

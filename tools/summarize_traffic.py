@@ -14,8 +14,7 @@ import sys
 
 FAMILY = [  # kernel-name regex -> C-ABI family as bench.py names it
     (r"igemm_tc_kernel", "ldmb200_igemm_tc"), (r"attention_tc_kernel", "ldmb200_attention_tc"),
-    (r"gn_fused_apply|gn_finalize|gn_apply|gn_stats", "ldmb200_groupnorm"), (r"layernorm_kernel", "ldmb200_layernorm"),
-    (r"ln_apply", "ldmb200_layernorm"), (r"cast_rows|upsample2x|space_to_depth2|nchw_to_nhwc|nhwc_to_nchw", "layout"),
+    (r"gn_fused_apply|gn_finalize|gn_apply|gn_stats", "ldmb200_groupnorm_fused"), (r"layernorm", "ldmb200_layernorm"), (r"cast_rows|upsample2x|space_to_depth2|nchw_to_nhwc|nhwc_to_nchw", "layout"),
     (r"small_linear|timestep_embedding", "small dense"),
 ]
 

@@ -217,7 +217,7 @@ class _WeightPack:
             off = (off + 255) // 256 * 256
 
         for name, m in model.named_modules():
-            if isinstance(m, Upsample):
+            if isinstance(m, Upsample) or getattr(m, "_ldmb200_fold_upsample", False):   # (first-stage UpsampleConv too)
                 add_fold(name + ".conv.fold", m.conv.weight)
             if isinstance(m, nn.Conv2d):
                 add(name, [m.weight], m.kernel_size[0])

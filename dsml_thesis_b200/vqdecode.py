@@ -71,6 +71,8 @@ class AttnBlock(nn.Module):
 class UpsampleConv(nn.Module):
     """model.py:42-57 (with_conv=True)."""
 
+    _ldmb200_fold_upsample = True   # the weight pack adds the four tap-summed 2x2 weight sets (pack kind 4)
+
     def __init__(self, c: int):
         super().__init__()
         self.conv = nn.Conv2d(c, c, 3, padding=1)
@@ -198,6 +200,7 @@ class _VQPlan(_Plan):
         self.gn_ws = torch.empty(int(self.lib.ldmb200_groupnorm_ws_floats(B, H * W, 0)), **f32)
         self.graph = None
         self.runs = 0
+        self.fold_upsample = os.environ.get("LDMB200_FOLD_UPSAMPLE", "1") == "1"
         self.pinned = set()
         self._build()
 
@@ -260,6 +263,14 @@ class _VQPlan(_Plan):
 
     def up2x(self, m: UpsampleConv, name: str, x: _Act, H: int, W: int) -> _Act:
         """model.py:53-57: nearest 2x, conv 3x3."""
+        if self.tc and self.fold_upsample and H & (H - 1) == 0 and W & (W - 1) == 0 and W <= 128:
+            # folded into the convolution like the UNet's Upsample (four tap-summed 2x2 convolutions on the low-res map)
+            lo = self.new(x.rows, x.c, self.act)
+            self.emit("ldmb200_cast_rows", x.ptr, lo.ptr, self.act, x.rows * x.c, bytes_=x.rows * x.c * 6, outs=(lo,))
+            out = self.gemm(lo, name + ".conv.fold", m.conv.weight, m.conv.bias, H, W, ksize=3, upsample=1,
+                            want_stats=(H * W) % 32 == 0)
+            self.free(lo)
+            return out
         if self.tc:
             u = self.new(4 * x.rows, x.c, self.act)
             self.emit("ldmb200_upsample2x", x.ptr, u.ptr, self.act, self.B, H, W, x.c,
@@ -334,6 +345,7 @@ class _VQEncPlan(_VQPlan):
         self.gn_ws = torch.empty(int(self.lib.ldmb200_groupnorm_ws_floats(B, H * W, 0)), **f32)
         self.graph = None
         self.runs = 0
+        self.fold_upsample = os.environ.get("LDMB200_FOLD_UPSAMPLE", "1") == "1"
         self.pinned = set()
         self._build()
 

@@ -731,6 +731,14 @@ class _Plan:
         self.gemm(y, "out.2", oc.weight, oc.bias, H, W, ksize=3, out_nchw_ptr=self.out.data_ptr())
         self.free(y)
 
+    def kernel_launches(self) -> int:
+        """CUDA kernels one replay of the plan launches (a C-ABI call is one kernel, except: GroupNorm = statistics /
+        finalize + apply, the folded Upsample convolution = four parity launches)."""
+        n = 0
+        for name, _fl, _by, what in self.meta:
+            n += 2 if name.startswith("ldmb200_groupnorm") else 4 if "upfold" in what else 1
+        return n
+
     def run_timed(self, stream_obj) -> List[tuple]:
         """Runs the plan once with a CUDA event pair around every launch on ``stream_obj`` (the launching stream);
         returns ``[(kernel name, ms, algorithmic flops, algorithmic bytes)]``.  Measurement aid for bench.py."""
@@ -1021,7 +1029,7 @@ class UNetModel(nn.Module):
                 assert y.shape == (B,)
                 plan.y_in.copy_(y)
             need_pack = plan.tc and not (self._frozen and plan.act in self._pack_valid)
-            self.launches += len(plan.ops) + (1 if need_pack else 0)
+            self.launches += plan.kernel_launches() + (1 if need_pack else 0)
             if mode == "f16" and plan.runs == 0 and self.f16_guard != "off":
                 # first call of this plan (eager anyway): the checked run.  fp16 operands that saturate silently change
                 # the result; bf16 operands cannot saturate — fall back to them for the whole model, loudly.

@@ -238,6 +238,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
 
   // query tiles of this CTA that hold real rows (the last CTA of a sample may have fewer than AT_NQ)
   const int nq = min(AT_NQ, (n_tok - qb * (AT_NQ * 128) + 127) / 128);
+  pdl_launch_dependents();
   if (warp == AT_TMA_WARP) {
     if (lane == 0) {
       prefetch_tmap(&tm);
@@ -259,6 +260,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // q / k / v of the predecessor are visible from here (barriers and TMEM were set up under its tail)
 
   if (warp == AT_TMA_WARP) {
     // ===================== TMA producer (warp converged, one elected lane issues) =====================
@@ -465,8 +467,12 @@ static int attention_tc_launch(const void* qkv, int ld, int q_off, int k_off, in
   if (rc) return rc;
   dim3 grid(ceil_div(n_tokens, AT_NQ * 128), heads, batch);
   const float scale_log2e = scale * 1.4426950408889634f;
-  attention_tc_kernel<<<grid, AT_THREADS, AT_SMEM, (cudaStream_t)stream>>>(tm, (uint16_t*)out, out_ld, out_dtype,
-                                                                           n_tokens, q_off, k_off, v_off, scale_log2e, lse2);
+  cudaError_t le = launch_pdl(attention_tc_kernel, grid, dim3(AT_THREADS), AT_SMEM, (cudaStream_t)stream, tm, (uint16_t*)out, out_ld,
+                              out_dtype, n_tokens, q_off, k_off, v_off, scale_log2e, lse2);
+  if (le != cudaSuccess) {
+    set_error("attention_tc: launch failed: %s", cudaGetErrorString(le));
+    return LDMB200_ERR_CUDA;
+  }
   LDM_CHECK_LAUNCH("attention_tc");
   return 0;
 }

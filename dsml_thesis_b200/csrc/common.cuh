@@ -42,10 +42,37 @@ int sm_count();
 int make_tensor_map_bf16(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
                          const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
 
+// Programmatic dependent launch (PDL): the kernels of the UNet forward are launched with the programmatic-stream-
+// serialization attribute, call pdl_launch_dependents() first thing and pdl_wait() before they touch anything a predecessor
+// wrote.  The next kernel's CTAs are then scheduled as soon as every CTA of the current one has started (and resources
+// free up), so barrier initialisation, TMEM allocation, tensor-map prefetch and the launch latency itself overlap the tail
+// of the predecessor instead of following its drain — 257 graph nodes x ~3 us per DDIM step otherwise.  EVERY kernel
+// launched with the attribute must execute pdl_wait() (completion is transitive only then); kernels launched without
+// it (<<<>>>) are ordinary full dependencies, and both instructions are no-ops there.  Measured and NOT the default
+// (runtime.cu: pdl_enabled): opt in with LDMB200_PDL=1.
+bool pdl_enabled();
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 #ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                     Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---------------------------------------------------------------------------------------------
 // device helpers
 // ---------------------------------------------------------------------------------------------

@@ -124,6 +124,8 @@ __global__ void __launch_bounds__(256) ddim_step_kernel(const float* __restrict_
 // ---------------------------------------------------------------------------------------------
 __global__ void timestep_embedding_kernel(const int64_t* __restrict__ t, float* __restrict__ out, int batch, int dim,
                                           float neg_log_period) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int half = dim / 2;
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= batch * half) return;
@@ -203,11 +205,15 @@ __device__ __forceinline__ void small_linear_tile(const ldmb200_linear_job& j, i
 }
 
 __global__ void __launch_bounds__(256) small_linear_kernel(const __grid_constant__ ldmb200_linear_job job) {
+  pdl_launch_dependents();
+  pdl_wait();
   small_linear_tile(job, blockIdx.x);
 }
 
 __global__ void __launch_bounds__(256) small_linear_batched_kernel(const ldmb200_linear_job* __restrict__ jobs,
                                                                    int n_jobs) {
+  pdl_launch_dependents();
+  pdl_wait();
   int lo = 0;  // last job whose first_block <= blockIdx.x (tables are a few dozen entries)
   for (int i = 1; i < n_jobs; ++i)
     if (jobs[i].first_block <= (int)blockIdx.x) lo = i;
@@ -221,6 +227,8 @@ __global__ void __launch_bounds__(256) small_linear_batched_kernel(const ldmb200
 template <typename T>
 __global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__ y, int batch, int C, int HW,
                                     int c_pad) {
+  pdl_launch_dependents();
+  pdl_wait();
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (int64_t)batch * HW) return;
   int b = idx / HW, p = idx % HW;
@@ -243,6 +251,8 @@ __global__ void nhwc_to_nchw_kernel(const float* __restrict__ y, int ld, float* 
 template <typename T>
 __global__ void space_to_depth2_kernel(const float* __restrict__ x, T* __restrict__ y, int batch, int H, int W,
                                        int C) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int c4n = C >> 2, Ho = H >> 1, Wo = W >> 1;
   int64_t total = (int64_t)batch * H * W * c4n;
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
@@ -282,6 +292,8 @@ __global__ void upsample2x_kernel(const float* __restrict__ x, T* __restrict__ y
 // x fp32 [n] -> y [n] (16-bit GEMM operand of a map that is consumed as it is: the folded upsample convolution)
 template <typename T>
 __global__ void cast_rows_kernel(const float* __restrict__ x, T* __restrict__ y, int64_t n4) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
     const float4 v = reinterpret_cast<const float4*>(x)[i];
     Store4<T>::st(y + i * 4, v.x, v.y, v.z, v.w);
@@ -367,6 +379,8 @@ __global__ void gn_stats_kernel(const float* __restrict__ x1, int c1, const floa
 __global__ void __launch_bounds__(128) gn_finalize_kernel(const float* __restrict__ cs1, int c1,
                                                           const float* __restrict__ cs2, int c2, int hw, int groups,
                                                           float eps, float* __restrict__ ws) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ double red[2][4];
   const int g = blockIdx.x, b = blockIdx.y;
   const int C = c1 + c2, cpg = C / groups, nrb = hw >> 5;
@@ -408,6 +422,8 @@ gn_apply_kernel(const float* __restrict__ x1, int c1, const float* __restrict__ 
                                 const float* __restrict__ gamma, const float* __restrict__ beta, T* __restrict__ y,
                                 T* __restrict__ raw, int hw, int groups, int R, int S, float eps, int silu,
                                 const float* __restrict__ ws) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float s_mean[64], s_rstd[64];
   const int C = c1 + c2, q = C >> 2, cpg = C / groups;
   const int b = blockIdx.y;
@@ -482,6 +498,8 @@ template <typename T, int MAXV>
 __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, T* __restrict__ y,
                                                         int64_t rows, int C, float eps) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
@@ -529,6 +547,8 @@ template <typename T, int LPR>
 __global__ void __launch_bounds__(256) layernorm_c20_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                                             const float* __restrict__ beta, T* __restrict__ y,
                                                             int64_t rows, float eps) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int RPW = 32 / LPR, C = 20 * LPR;
   const int lane = threadIdx.x & 31, sub = lane % LPR;
   const int64_t row = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * RPW + lane / LPR;
@@ -668,14 +688,14 @@ static int gn_apply_launch(const float* x1, int c1, const float* x2, int c2, con
   if (nblk > slots / batch) nblk = slots / batch;
   if (nblk < 1) nblk = 1;
   if (threads <= 256)
-    gn_apply_kernel<T, 256><<<dim3(nblk, batch), threads, 0, st>>>(x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw, hw, groups, R,
-                                                                 S, eps, silu, ws);
+    launch_pdl(gn_apply_kernel<T, 256>, dim3(nblk, batch), dim3(threads), 0, st, x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw, hw,
+               groups, R, S, eps, silu, ws);
   else if (threads <= 512)
-    gn_apply_kernel<T, 512><<<dim3(nblk, batch), threads, 0, st>>>(x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw, hw, groups,
-                                                                  R, S, eps, silu, ws);
+    launch_pdl(gn_apply_kernel<T, 512>, dim3(nblk, batch), dim3(threads), 0, st, x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw, hw,
+               groups, R, S, eps, silu, ws);
   else  // C > 2048: one block per SM slot
-    gn_apply_kernel<T, 1024><<<dim3(nblk, batch), threads, 0, st>>>(x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw, hw, groups,
-                                                                   R, S, eps, silu, ws);
+    launch_pdl(gn_apply_kernel<T, 1024>, dim3(nblk, batch), dim3(threads), 0, st, x1, c1, x2, c2, gamma, beta, (T*)y, (T*)raw, hw,
+               groups, R, S, eps, silu, ws);
   return 0;
 }
 
@@ -704,7 +724,7 @@ int ldmb200_timestep_embedding(const int64_t* t, float* out, int batch, int dim,
   int total = batch * (dim / 2);
   // -math.log(max_period) is a python float rounded to fp32 when it multiplies the fp32 arange (util.py:162-164)
   float neg_log = (float)(-log((double)max_period));
-  timestep_embedding_kernel<<<ceil_div(total, 128), 128, 0, (cudaStream_t)stream>>>(t, out, batch, dim, neg_log);
+  launch_pdl(timestep_embedding_kernel, dim3(ceil_div(total, 128)), dim3(128), 0, (cudaStream_t)stream, t, out, batch, dim, neg_log);
   LDM_CHECK_LAUNCH("timestep_embedding");
   return 0;
 }
@@ -716,7 +736,7 @@ int ldmb200_small_linear(const float* in, int in_ld, const float* w, const float
   j.in = in; j.w = w; j.bias = bias; j.out = out;
   j.in_ld = in_ld; j.out_ld = out_ld; j.rows = rows; j.k = k; j.n = n; j.silu_in = silu_in; j.first_block = 0;
   const int blocks = ceil_div(n, SL_BN) * ceil_div(rows, SL_BM);
-  small_linear_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(j);
+  launch_pdl(small_linear_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, j);
   LDM_CHECK_LAUNCH("small_linear");
   return 0;
 }
@@ -725,7 +745,7 @@ int ldmb200_small_linear_blocks(int rows, int n) { return ceil_div(n, SL_BN) * c
 
 int ldmb200_small_linear_batched(const ldmb200_linear_job* jobs, int n_jobs, int total_blocks, void* stream) {
   LDM_CHECK_ARG(jobs && n_jobs > 0 && total_blocks > 0, "small_linear_batched: bad arguments");
-  small_linear_batched_kernel<<<total_blocks, 256, 0, (cudaStream_t)stream>>>(jobs, n_jobs);
+  launch_pdl(small_linear_batched_kernel, dim3(total_blocks), dim3(256), 0, (cudaStream_t)stream, jobs, n_jobs);
   LDM_CHECK_LAUNCH("small_linear_batched");
   return 0;
 }
@@ -734,7 +754,7 @@ int ldmb200_nchw_to_nhwc(const float* x, void* y, int batch, int c, int hw, int 
   LDM_CHECK_ARG(x && y && batch > 0 && c > 0 && hw > 0 && c_pad >= c, "nchw_to_nhwc: bad arguments");
   int64_t total = (int64_t)batch * hw;
   int blocks = (int)ceil_div64(total, 256);
-  LDM_DISPATCH_DTYPE(out_dtype, (nchw_to_nhwc_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (T*)y, batch, c, hw, c_pad)));
+  LDM_DISPATCH_DTYPE(out_dtype, (launch_pdl(nchw_to_nhwc_kernel<T>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, x, (T*)y, batch, c, hw, c_pad)));
   LDM_CHECK_LAUNCH("nchw_to_nhwc");
   return 0;
 }
@@ -752,7 +772,7 @@ int ldmb200_space_to_depth2(const float* x, void* y, int out_dtype, int batch, i
                 "space_to_depth2: bad arguments (h, w even; c %% 4 == 0)");
   int64_t total = (int64_t)batch * h * w * (c / 4);
   int blocks = (int)std::min<int64_t>(ceil_div64(total, 256), (int64_t)sm_count() * 16);
-  LDM_DISPATCH_DTYPE(out_dtype, (space_to_depth2_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (T*)y, batch, h, w, c)));
+  LDM_DISPATCH_DTYPE(out_dtype, (launch_pdl(space_to_depth2_kernel<T>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, x, (T*)y, batch, h, w, c)));
   LDM_CHECK_LAUNCH("space_to_depth2");
   return 0;
 }
@@ -769,7 +789,7 @@ int ldmb200_upsample2x(const float* x, void* y, int out_dtype, int batch, int h,
 int ldmb200_cast_rows(const float* x, void* y, int out_dtype, int64_t n, void* stream) {
   LDM_CHECK_ARG(x && y && n > 0 && n % 4 == 0, "cast_rows: bad arguments (n %% 4 == 0)");
   int blocks = (int)std::min<int64_t>(ceil_div64(n / 4, 256), (int64_t)sm_count() * 16);
-  LDM_DISPATCH_DTYPE(out_dtype, (cast_rows_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(x, (T*)y, n / 4)));
+  LDM_DISPATCH_DTYPE(out_dtype, (launch_pdl(cast_rows_kernel<T>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, x, (T*)y, n / 4)));
   LDM_CHECK_LAUNCH("cast_rows");
   return 0;
 }
@@ -821,7 +841,7 @@ int ldmb200_groupnorm_fused(const float* x1, int c1, const float* colstats1, con
   LDM_CHECK_ARG(groups > 0 && groups <= 64 && C % groups == 0, "groupnorm_fused: C=%d not divisible by groups=%d", C, groups);
   LDM_CHECK_ARG(c1 % 4 == 0 && c2 % 4 == 0 && C / 4 <= 1024, "groupnorm_fused: channel counts must be multiples of 4");
   cudaStream_t st = (cudaStream_t)stream;
-  gn_finalize_kernel<<<dim3(groups, batch), 128, 0, st>>>(colstats1, c1, colstats2, c2, hw, groups, eps, stats_ws);
+  launch_pdl(gn_finalize_kernel, dim3(groups, batch), dim3(128), 0, st, colstats1, c1, colstats2, c2, hw, groups, eps, stats_ws);
   LDM_CHECK_LAUNCH("groupnorm finalize");
   const int R = gn_rows_per_block(C);
   LDM_DISPATCH_DTYPE(out_dtype, (gn_apply_launch<T>(x1, c1, x2, c2, gamma, beta, y, raw_copy, batch, hw, groups, R, 0, eps,
@@ -839,7 +859,7 @@ int ldmb200_layernorm(const float* x, const float* gamma, const float* beta, voi
   cudaStream_t st = (cudaStream_t)stream;
   if (c == 160 || c == 320 || c == 640) {
 #define LN20_LAUNCH(T, LPR) \
-  layernorm_c20_kernel<T, LPR><<<(int)ceil_div64(rows, warps * (32 / LPR)), warps * 32, 0, st>>>(x, gamma, beta, (T*)y, rows, eps)
+  launch_pdl(layernorm_c20_kernel<T, LPR>, dim3((int)ceil_div64(rows, warps * (32 / LPR))), dim3(warps * 32), 0, st, x, gamma, beta, (T*)y, rows, eps)
     LDM_DISPATCH_DTYPE(out_dtype, {
       if (c == 160) LN20_LAUNCH(T, 8);
       else if (c == 320) LN20_LAUNCH(T, 16);
@@ -849,7 +869,7 @@ int ldmb200_layernorm(const float* x, const float* gamma, const float* beta, voi
     LDM_CHECK_LAUNCH("layernorm");
     return 0;
   }
-#define LN_LAUNCH(T, MAXV) layernorm_kernel<T, MAXV><<<blocks, warps * 32, 0, st>>>(x, gamma, beta, (T*)y, rows, c, eps)
+#define LN_LAUNCH(T, MAXV) launch_pdl(layernorm_kernel<T, MAXV>, dim3(blocks), dim3(warps * 32), 0, st, x, gamma, beta, (T*)y, rows, c, eps)
   const int need = ceil_div(c / 4, 32);
   LDM_DISPATCH_DTYPE(out_dtype, {
     if (need <= 2) LN_LAUNCH(T, 2);

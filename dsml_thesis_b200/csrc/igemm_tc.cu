@@ -223,6 +223,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ntiles = p.tiles_m * p.tiles_n;
+  pdl_launch_dependents();  // PDL: everything up to pdl_wait() below overlaps the predecessor's tail
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA1);
@@ -248,6 +249,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // the predecessor's writes (activations, packed weights, residual, statistics buffers) are visible from here
 
   // K loop: taps x channel chunks of BK; the last chunk of each channel range may be partial (multiple of 16):
   // TMA zero-fills the out-of-range channels of the A box, and only `valid/16` MMAs are issued for it.
@@ -526,7 +528,12 @@ static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CU
     attr_set = true;
   }
   int grid = std::min(p.tiles_m * p.tiles_n, sm_count());
-  igemm_tc_kernel<BN, BK, EW, GG, O16, UP><<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(a1, a2, b, p);
+  cudaError_t le = launch_pdl(igemm_tc_kernel<BN, BK, EW, GG, O16, UP>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, st, a1,
+                              a2, b, p);
+  if (le != cudaSuccess) {
+    set_error("igemm_tc: launch failed: %s", cudaGetErrorString(le));
+    return LDMB200_ERR_CUDA;
+  }
   LDM_CHECK_LAUNCH("igemm_tc");
   return 0;
 }

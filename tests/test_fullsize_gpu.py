@@ -284,3 +284,35 @@ def test_inference_is_bit_reproducible_run_to_run():
         outs.append(m(x.cuda(), t, context=ctx.cuda()))
     for o in outs[1:]:
         assert torch.equal(o, outs[0])
+
+
+@pytest.mark.parametrize("precision", ["fp32", "f16"])
+@pytest.mark.parametrize("H,W", [(32, 64), (64, 16)])
+def test_unet_non_square_maps_vs_oracle(H, W, precision):
+    """Non-square latents (the reference takes any H, W divisible by 2^(levels-1), openaimodel.py:710-742): attention over
+    H*W tokens, the folded Upsample and the stride-2 planes with different row / column extents.  (The tensor-core
+    convolutions need power-of-two H and W — anything else raises loudly; the fp32 mode has no such limit.)"""
+    cfg = O.FR_UNET
+    m = build(cfg, precision)
+    g = torch.Generator().manual_seed(H * 1000 + W)
+    x = torch.randn(1, 3, H, W, generator=g)
+    ctx = torch.randn(1, 1, cfg["context_dim"], generator=g)
+    t = torch.tensor([333])
+    ref = O.unet_forward(O.init_state_dict(cfg, 0), cfg, x, t, ctx)
+    with torch.no_grad():
+        eps = m(x.cuda(), t.cuda(), context=ctx.cuda())
+    err = O.rel_l2(eps, ref)
+    record_parity(f"eps/fr_{H}x{W}/{precision}", err)
+    assert err <= EPS_TOL[precision], err
+
+
+def test_unet_rejects_non_power_of_two_maps_in_tensor_core_mode_loudly():
+    m = build(O.FR_UNET, "f16")
+    x = torch.randn(1, 3, 24, 40).cuda()
+    with pytest.raises(P.Ldmb200Error, match="power-of-two"), torch.no_grad():
+        m(x, torch.tensor([5]).cuda(), context=torch.randn(1, 1, 512).cuda())
+    m._plans.clear()
+    m.precision = "fp32"                       # the parity mode takes the same map
+    with torch.no_grad():
+        out = m(x, torch.tensor([5]).cuda(), context=torch.randn(1, 1, 512).cuda())
+    assert out.shape == (1, 3, 24, 40) and torch.isfinite(out).all()

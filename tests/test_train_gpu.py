@@ -61,7 +61,10 @@ def _compare(tag, sd, unet, grads, dctx, ctx_grad):
 
 
 @pytest.mark.parametrize("tag,cfg,two_cond,B,hw", [("tiny16", O.TINY_UNET, False, 2, 16), ("tiny32", O.TINY_UNET, False, 3, 32),
-                                                   ("fr16", O.FR_UNET, False, 2, 16), ("tf16", O.TF_UNET, True, 2, 16)])
+                                                   ("fr16", O.FR_UNET, False, 2, 16), ("tf16", O.TF_UNET, True, 2, 16),
+                                                   # BASELINE config 4 at its own latent sizes (32x32 shipped, 64x64): the
+                                                   # N = 1024 / 4096 attention backward, full-size weight gradients
+                                                   ("tf32", O.TF_UNET, True, 2, 32), ("tf64", O.TF_UNET, True, 1, 64)])
 def test_training_step_gradients_vs_oracle(tag, cfg, two_cond, B, hw):
     sd, unet, handle = _build(cfg, two_cond)
     x0, noise, ctx, c34, t = _inputs(cfg, two_cond, B, hw)

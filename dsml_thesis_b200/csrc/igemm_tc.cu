@@ -401,6 +401,21 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       // on (ncu r02j: the FADD that folds the row vector into the bias stalled on these loads — 8 % of the epilogue warps'
       // samples on the K = 160 GEMMs — because they were issued in the chunk that consumes them)
       float4 addv[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+      // GEGLU: every warp owns at most one 32-column chunk per tile; its 32 biases ([16 value | 16 gate], packed order) are
+      // fetched here, before the accumulator wait (they used to be loaded after it: an exposed L1/L2 round trip per chunk,
+      // the long-scoreboard share of the r02e profile of this specialisation)
+      float bv[32];
+      if constexpr (GG) {
+        static_assert(NCH <= CSTEP, "the GEGLU epilogue prefetches the bias of ONE chunk per warp and tile");
+        if (Cfg::CH == 32 && cc_first < NCH) {
+          const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + cc_first * 32);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 t = bp[j];
+            bv[4 * j] = t.x; bv[4 * j + 1] = t.y; bv[4 * j + 2] = t.z; bv[4 * j + 3] = t.w;
+          }
+        }
+      }
       if constexpr (!GG) {
         if (!p.out_nchw && cc_first < NCH) {
           if (out16) epi_load_add<true, Cfg::CH>(p, addv, n0 + cc_first * Cfg::CH, lane, true, tile_sample);
@@ -452,13 +467,6 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
         }
         if constexpr (GG) {  // chunk = [16 value | 16 gate] columns (packed order), biases in the same order
           if (Cfg::CH == 32) {
-            const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + cc * 32);
-            float bv[32];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 t = bp[j];
-              bv[4 * j] = t.x; bv[4 * j + 1] = t.y; bv[4 * j + 2] = t.z; bv[4 * j + 3] = t.w;
-            }
 #pragma unroll
             for (int j = 0; j < 16; j += 2) {  // packed fp32 pairs: half the issue slots of the epilogue's bound
               const f32x2 val2 = add2(pk2(v[j], v[j + 1]), pk2(bv[j], bv[j + 1]));

@@ -139,65 +139,69 @@ __global__ void timestep_embedding_kernel(const int64_t* __restrict__ t, float* 
 
 // ---------------------------------------------------------------------------------------------
 // small dense layers on per-sample vectors (fp32 FMA, exact-parity path): out = act(in) W^T + bias.
-// These layers have 1..64 rows (one per sample) and hundreds of columns: the work is streaming the weights.  r02: a warp
-// owns ONE output column and up to 64 rows — lane <-> k, the weight row is read coalesced once per 64 rows, the activations
-// of the block's rows are staged per 32-wide k chunk in shared memory (conflict-free row reads), every lane keeps 64
-// row accumulators and the column is finished by warp sums in a fixed order (deterministic).  Block = 8 warps = 8 columns:
-// n/8 blocks per layer instead of n/32 (time_embed.2 at batch 64: 80 blocks instead of 20; the r01 64x32 register tile
-// left 128 of 148 SMs idle on it).  One launch serves a whole table of independent layers: block -> job by first_block.
+// Block = 256 threads, output tile 64 rows x 32 columns, K in chunks of 32 staged in shared memory with the
+// next chunk prefetched into registers; thread (ty, tx) owns rows 4ty..4ty+3, columns 2tx..2tx+1.
+// One launch serves a whole table of independent layers (all ResBlock emb projections of a UNet eval, or all
+// cross-attention value projections): block -> job by the job's first block index.
+// (r02s: a warp-per-output-column variant with 64 row accumulators per lane and n/8 blocks per layer was measured and is
+// 2x SLOWER — one shared-memory read per FMA; this register tile does 8 FMAs per 2 reads.)
 // ---------------------------------------------------------------------------------------------
-constexpr int SL_BM = 64, SL_BN = 8, SL_BK = 32;
+constexpr int SL_BM = 64, SL_BN = 32, SL_BK = 32, SL_XP = 68, SL_WP = 34;
 
 __device__ __forceinline__ void small_linear_tile(const ldmb200_linear_job& j, int blk) {
-  __shared__ float xs[SL_BM][SL_BK];
+  __shared__ __align__(16) float xs[SL_BK][SL_XP];
+  __shared__ __align__(16) float ws[SL_BK][SL_WP];
   const int nb = (j.n + SL_BN - 1) / SL_BN;
-  const int r0 = (blk / nb) * SL_BM;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int n = (blk % nb) * SL_BN + warp;
-  const int rows = min(SL_BM, j.rows - r0);
-  const bool col_ok = n < j.n;
-  const float* wrow = j.w + (size_t)(col_ok ? n : 0) * j.k;
-  float acc[SL_BM];
-#pragma unroll
-  for (int r = 0; r < SL_BM; ++r) acc[r] = 0.f;
-  float xn[8], wn;
-  auto fetch = [&](int k0) {   // next chunk into registers: the global latency hides under the FMAs of the current one
-    const int k = k0 + lane;
+  const int r0 = (blk / nb) * SL_BM, n0 = (blk % nb) * SL_BN;
+  const int tid = threadIdx.x, lk = tid & 31, lr = tid >> 5;  // loader: k = lk, rows / columns lr + 8i
+  const int ty = tid >> 4, tx = tid & 15;
+  float acc[4][2] = {};
+  float xr[8], wr[4];
+  auto fetch = [&](int k0) {
+    const int k = k0 + lk;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const int r = warp + 8 * i;
+      const int r = r0 + lr + 8 * i;
       float v = 0.f;
-      if (r < rows && k < j.k) {
-        v = j.in[(size_t)(r0 + r) * j.in_ld + k];
+      if (r < j.rows && k < j.k) {
+        v = j.in[(size_t)r * j.in_ld + k];
         if (j.silu_in) v = silu_f(v);
       }
-      xn[i] = v;
+      xr[i] = v;
     }
-    wn = (col_ok && k < j.k) ? wrow[k] : 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int n = n0 + lr + 8 * i;
+      wr[i] = (n < j.n && k < j.k) ? j.w[(size_t)n * j.k + k] : 0.f;
+    }
   };
   fetch(0);
   for (int k0 = 0; k0 < j.k; k0 += SL_BK) {
     __syncthreads();
 #pragma unroll
-    for (int i = 0; i < 8; ++i) xs[warp + 8 * i][lane] = xn[i];   // rows past `rows` are zeros
-    const float w = wn;
+    for (int i = 0; i < 8; ++i) xs[lk][lr + 8 * i] = xr[i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) ws[lk][lr + 8 * i] = wr[i];
     __syncthreads();
     if (k0 + SL_BK < j.k) fetch(k0 + SL_BK);
-    if (rows > 8) {
 #pragma unroll
-      for (int r = 0; r < SL_BM; ++r) acc[r] = fmaf(xs[r][lane], w, acc[r]);
-    } else {
-#pragma unroll
-      for (int r = 0; r < 8; ++r) acc[r] = fmaf(xs[r][lane], w, acc[r]);
+    for (int kk = 0; kk < SL_BK; ++kk) {
+      const float4 xv = *reinterpret_cast<const float4*>(&xs[kk][ty * 4]);
+      const float2 wv = *reinterpret_cast<const float2*>(&ws[kk][tx * 2]);
+      acc[0][0] = fmaf(xv.x, wv.x, acc[0][0]); acc[0][1] = fmaf(xv.x, wv.y, acc[0][1]);
+      acc[1][0] = fmaf(xv.y, wv.x, acc[1][0]); acc[1][1] = fmaf(xv.y, wv.y, acc[1][1]);
+      acc[2][0] = fmaf(xv.z, wv.x, acc[2][0]); acc[2][1] = fmaf(xv.z, wv.y, acc[2][1]);
+      acc[3][0] = fmaf(xv.w, wv.x, acc[3][0]); acc[3][1] = fmaf(xv.w, wv.y, acc[3][1]);
     }
   }
-  if (!col_ok) return;
-  const float bias = j.bias ? j.bias[n] : 0.f;
 #pragma unroll
-  for (int r = 0; r < SL_BM; ++r) {
-    if (r < rows) {                 // uniform across the warp
-      const float v = warp_sum(acc[r]);
-      if (lane == (r & 31)) j.out[(size_t)(r0 + r) * j.out_ld + n] = v + bias;
+  for (int a = 0; a < 4; ++a) {
+    const int r = r0 + ty * 4 + a;
+    if (r >= j.rows) continue;
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      const int n = n0 + tx * 2 + b;
+      if (n < j.n) j.out[(size_t)r * j.out_ld + n] = acc[a][b] + (j.bias ? j.bias[n] : 0.f);
     }
   }
 }

@@ -73,7 +73,7 @@ attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv128, const __g
                         const __grid_constant__ CUtensorMap tm_do128, const __grid_constant__ CUtensorMap tm_do64,
                         const AxParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // (offset, not uintptr_t: keeps the shared address space)
   uint8_t* sR1 = smem;
   uint8_t* sR2 = sR1 + AX_RES;
   uint8_t* sOp = sR2 + AX_RES;                 // [2 buffers][Ds | Pw] 4 x 16 KiB, 1024-aligned

@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(AT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict__ out, int out_ld, int out_dtype,
                     int n_tok, int q_off, int k_off, int v_off, float scale_log2e, float* __restrict__ lse2) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // (offset, not uintptr_t: keeps the shared address space)
   uint8_t* sQ = smem;                               // AT_NQ tiles of 128 query rows
   uint8_t* sK = sQ + AT_NQ * AT_TILE_BYTES;             // AT_STAGES tiles
   uint8_t* sV = sK + AT_STAGES * AT_TILE_BYTES;     // AT_STAGES tiles

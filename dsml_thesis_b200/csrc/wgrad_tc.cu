@@ -37,7 +37,7 @@ struct WtParams {
 __global__ void __launch_bounds__(WT_THREADS, 1)
 wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX, const WtParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // (offset, not uintptr_t: keeps the shared address space)
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + WT_STAGES * WT_STAGE);
   uint64_t* empty = full + WT_STAGES;
   uint64_t* tfull = empty + WT_STAGES;

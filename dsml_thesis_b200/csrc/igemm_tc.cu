@@ -21,6 +21,9 @@
 #ifndef LDM_TC_RES_PREFETCH
 #define LDM_TC_RES_PREFETCH 1
 #endif
+#ifndef LDM_TC_GG_PIPE
+#define LDM_TC_GG_PIPE 1   // software-pipelined GEGLU epilogue (halves of the chunk; see the epilogue branch)
+#endif
 
 namespace ldm {
 
@@ -368,6 +371,79 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     constexpr bool out16 = O16;
     const bool has_res = !GG && p.residual != nullptr;
     uint32_t t_iter = 0;
+    if constexpr (GG && Cfg::CH == 32 && LDM_TC_GG_PIPE) {
+      // ---- GEGLU epilogue, software-pipelined over the two 16-column halves of the warp's chunk ----
+      // All 16 epilogue warps wait for the same accumulator and have identical work, so they ran in lock step: first
+      // everyone reads tensor memory (a 128x128 fp32 tile = 64 KB through a 64 B/clk read port = ~1000 clk with nothing
+      // else to do), then everyone evaluates GELUs (issue-bound, the read port idle) — ~3100 clk per tile of which the two
+      // phases explain 2500.  Here the second half's tcgen05.ld is in flight while the first half is evaluated, and the
+      // NEXT tile's first half is fetched (other accumulator buffer, complete long ago) while the second half is evaluated.
+      static_assert(!GG || NCH <= CSTEP, "one chunk per warp and tile");
+      const int cc = par;
+      if (cc < NCH) {
+        float va[16], vb[16];  // half h: [8 value | 8 gate] columns 8h..8h+7 and 16+8h..16+8h+7 of the chunk
+        const uint32_t lane_base = tmem_base + ((uint32_t)(qw * 32) << 16) + cc * 32;
+        int tile = blockIdx.x;
+        if (tile < ntiles) {
+          mbar_wait(&tfull[0], 0);
+          tc_fence_after();
+          tmem_ld_32x8(lane_base, va);
+          tmem_ld_32x8(lane_base + 16, va + 8);
+        }
+        for (; tile < ntiles; tile += gridDim.x, ++t_iter) {
+          const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
+          const int m0 = tm * Cfg::BM + qw * 32;
+          const int n0 = tn * BN;
+          const uint32_t buf = t_iter & 1;
+          const float4* bp = reinterpret_cast<const float4*>(p.bias + n0 + cc * 32);
+          float4 b4[4] = {bp[0], bp[1], bp[4], bp[5]};          // half 0: value biases 0..7, gate biases 16..23
+          tmem_ld_wait16(va);
+          tmem_ld_32x8(lane_base + buf * BN + 8, vb);           // half 1 in flight while half 0 is evaluated
+          tmem_ld_32x8(lane_base + buf * BN + 24, vb + 8);
+          auto half = [&](const float (&v)[16], const float4 (&b)[4], int h) {
+            const float bb[16] = {b[0].x, b[0].y, b[0].z, b[0].w, b[1].x, b[1].y, b[1].z, b[1].w,
+                                  b[2].x, b[2].y, b[2].z, b[2].w, b[3].x, b[3].y, b[3].z, b[3].w};
+            float o[8];
+#pragma unroll
+            for (int j = 0; j < 8; j += 2) {
+              const f32x2 val2 = add2(pk2(v[j], v[j + 1]), pk2(bb[j], bb[j + 1]));
+              const f32x2 g2 = add2(pk2(v[8 + j], v[9 + j]), pk2(bb[8 + j], bb[9 + j]));
+              unpk2(mul2(val2, gelu_erf_fast2(g2)), o[j], o[j + 1]);
+            }
+            *reinterpret_cast<float4*>(&st[lane * PITCH + 8 * h]) = make_float4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<float4*>(&st[lane * PITCH + 8 * h + 4]) = make_float4(o[4], o[5], o[6], o[7]);
+          };
+          half(va, b4, 0);
+          const float4 c4[4] = {bp[2], bp[3], bp[6], bp[7]};    // half 1: value biases 8..15, gate biases 24..31
+          tmem_ld_wait16(vb);
+          tc_fence_before();                                    // the whole chunk has left tensor memory
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[buf]);
+          if (tile + (int)gridDim.x < ntiles) {                 // next tile's half 0 (other buffer) during half 1's GELUs
+            mbar_wait(&tfull[buf ^ 1], ((t_iter + 1) >> 1) & 1);
+            tc_fence_after();
+            tmem_ld_32x8(lane_base + (buf ^ 1) * BN, va);
+            tmem_ld_32x8(lane_base + (buf ^ 1) * BN + 16, va + 8);
+          }
+          half(vb, c4, 1);
+          __syncwarp();
+          const int col0 = (n0 >> 1) + cc * 16;
+          const float4 zero_add[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+          float4 res0[8];
+          if (out16) epi_store<true, 16>(p, st, PITCH, m0, col0, lane, res0, false, zero_add);
+          else epi_store<false, 16>(p, st, PITCH, m0, col0, lane, res0, false, zero_add);
+          __syncwarp();
+        }
+      } else {  // a warp without a chunk (BN == 32): it still hands every accumulator buffer back
+        for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
+          const uint32_t buf = t_iter & 1;
+          mbar_wait(&tfull[buf], (t_iter >> 1) & 1);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty[buf]);
+        }
+      }
+    } else
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
       const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
       const int m0 = tm * Cfg::BM + qw * 32;

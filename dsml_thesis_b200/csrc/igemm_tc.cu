@@ -378,6 +378,9 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       // else to do), then everyone evaluates GELUs (issue-bound, the read port idle) — ~3100 clk per tile of which the two
       // phases explain 2500.  Here the second half's tcgen05.ld is in flight while the first half is evaluated, and the
       // NEXT tile's first half is fetched (other accumulator buffer, complete long ago) while the second half is evaluated.
+      // Measured on top of this and rejected (r02w / r02x, same-run A/B/A/B on the N = 1280 GEMMs): the biases fetched a whole
+      // tile ahead + no zero-add in the store (1.079 -> 1.135 ms), and a rows-fastest lane map that removes the 2-way bank
+      // conflicts of the 16-column staging read (1.07 -> 1.17 ms: the stores lose their lane-pair-contiguous 32-byte sectors).
       static_assert(!GG || NCH <= CSTEP, "one chunk per warp and tile");
       const int cc = par;
       if (cc < NCH) {

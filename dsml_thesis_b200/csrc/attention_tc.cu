@@ -33,7 +33,10 @@ constexpr int AT_NQ = 3;                      // 128-query tiles per CTA (softma
 constexpr int AT_THREADS = 32 * (5 * AT_NQ + 1);  // 12 softmax warps, one MMA warp per query tile, one TMA warp
 constexpr int AT_MMA_WARP0 = 4 * AT_NQ, AT_TMA_WARP = 5 * AT_NQ;
 constexpr int AT_O_COL = AT_NQ * 128;          // TMEM: S_q buffers at q*128 + u*64 (P_q(i) over cols 0..31), O_q at AT_O_COL + q*32
-constexpr int AT_STAGES = 4;
+#ifndef LDM_AT_STAGES
+#define LDM_AT_STAGES 4
+#endif
+constexpr int AT_STAGES = LDM_AT_STAGES;   // K/V tile ring depth (128 keys x 32 each)
 constexpr int AT_TILE_BYTES = 128 * 32 * 2;  // 8 KiB: 128 rows x 32 16-bit values
 constexpr int AT_SMEM = AT_NQ * AT_TILE_BYTES + 2 * AT_STAGES * AT_TILE_BYTES + 32 * 8 + 16 + 1024;
 constexpr int AT_TMEM_COLS = 512;

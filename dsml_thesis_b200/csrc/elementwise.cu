@@ -319,6 +319,10 @@ __global__ void count_f16_saturated_kernel(const uint16_t* __restrict__ x, int64
 //          registers, streams the slab once: y = silu(x*scale + shift)  (+ raw cast copy)
 // ---------------------------------------------------------------------------------------------
 constexpr int GN_MAX_SPLITS = 64;
+#ifndef LDM_GN_UNR
+#define LDM_GN_UNR 4
+#endif
+constexpr int GN_UNR = LDM_GN_UNR;   // rows per thread in flight in the apply pass
 
 static inline int gn_rows_per_block(int C) {
   int q = C / 4;
@@ -419,7 +423,7 @@ __global__ void __launch_bounds__(128) gn_finalize_kernel(const float* __restric
 
 // MAXT = 256 (every shipped width up to C = 960): capped at 48 registers so that five blocks are resident per SM.
 template <typename T, int MAXT>
-__global__ void __launch_bounds__(MAXT, MAXT == 256 ? 5 : (MAXT == 512 ? 2 : 1))
+__global__ void __launch_bounds__(MAXT, MAXT == 256 ? (GN_UNR > 4 ? 4 : 5) : (MAXT == 512 ? 2 : 1))
 gn_apply_kernel(const float* __restrict__ x1, int c1, const float* __restrict__ x2, int c2,
                                 const float* __restrict__ gamma, const float* __restrict__ beta, T* __restrict__ y,
                                 T* __restrict__ raw, int hw, int groups, int R, int S, float eps, int silu,
@@ -462,14 +466,14 @@ gn_apply_kernel(const float* __restrict__ x1, int c1, const float* __restrict__ 
   const int T_ = gridDim.x;
   const int rows_per = (hw + T_ - 1) / T_;
   const int r0 = blockIdx.x * rows_per, r1 = min(hw, r0 + rows_per);
-  // four rows per thread in flight: the pass is a pure stream and needs the memory-level parallelism
+  // GN_UNR rows per thread in flight: the pass is a pure stream and needs the memory-level parallelism
   int r = r0 + rl;
-  for (; r + 3 * R < r1; r += 4 * R) {
-    float4 v[4];
+  for (; r + (GN_UNR - 1) * R < r1; r += GN_UNR * R) {
+    float4 v[GN_UNR];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) v[u] = gn_load(x1, c1, x2, c2, (int64_t)b * hw + r + u * R, cq * 4);
+    for (int u = 0; u < GN_UNR; ++u) v[u] = gn_load(x1, c1, x2, c2, (int64_t)b * hw + r + u * R, cq * 4);
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < GN_UNR; ++u) {
       const int64_t row = (int64_t)b * hw + r + u * R;
       float o0 = fmaf(v[u].x, sc[0], sh[0]), o1 = fmaf(v[u].y, sc[1], sh[1]);
       float o2 = fmaf(v[u].z, sc[2], sh[2]), o3 = fmaf(v[u].w, sc[3], sh[3]);
@@ -686,7 +690,7 @@ static int gn_apply_launch(const float* x1, int c1, const float* x2, int c2, con
   }
   static const int per_sm_env = getenv("LDMB200_GN_BLOCKS_PER_SM") ? atoi(getenv("LDMB200_GN_BLOCKS_PER_SM")) : 0;
   const int slots = sm_count() * (per_sm_env > 0 ? per_sm_env : occ);
-  int nblk = hw / (R * 4);
+  int nblk = hw / (R * GN_UNR);
   if (nblk > slots / batch) nblk = slots / batch;
   if (nblk < 1) nblk = 1;
   if (threads <= 256)

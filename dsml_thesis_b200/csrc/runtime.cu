@@ -64,8 +64,12 @@ int make_tensor_map_bf16(CUtensorMap* map, const void* base, int rank, const uin
                           : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
                           : swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B
                                                 : CU_TENSOR_MAP_SWIZZLE_NONE;
+  // L2 promotion of the TMA requests: 256 B measured best or equal (LDMB200_TMAP_L2 = 0 none | 1 64B | 2 128B | 3 256B)
+  static const int l2sel = getenv("LDMB200_TMAP_L2") ? atoi(getenv("LDMB200_TMAP_L2")) : 3;
+  const CUtensorMapL2promotion l2promo = l2sel == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE : l2sel == 1 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+                                         : l2sel == 2 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
   CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx,
-                   es, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   es, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, l2promo,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed (CUresult %d) rank %d dims [%llu %llu %llu %llu %llu] box [%u %u %u %u %u]",

@@ -153,3 +153,31 @@ def test_cuda_graph_replay_matches_eager_training_step():
     big = lambda t_: float(t_.norm()) > 1e-5 * t_.numel() ** 0.5
     for n, p in unet.named_parameters():
         assert O.rel_l2(p.grad, g0[n]) <= 3e-2 or not big(g0[n]), n
+
+
+def test_backward_of_an_overwritten_forward_raises():
+    """One live training forward per model (the plan owns the saved activations): forward, forward, backward of the FIRST
+    output must raise instead of silently using the second forward's activations."""
+    sd, unet, handle = _build(O.TINY_UNET, False)
+    x0, noise, ctx, _, t = _inputs(O.TINY_UNET, False, 2, 16)
+    l1, _ = T.p_losses(handle, x0.cuda(), ctx.cuda(), t.cuda(), noise.cuda())
+    l2, _ = T.p_losses(handle, (x0 * 0.5).cuda(), ctx.cuda(), t.cuda(), noise.cuda())
+    with pytest.raises(P.Ldmb200Error, match="overwritten"):
+        l1.backward()
+    l2.backward()                                   # the live forward still works
+    assert all(p.grad is not None for p in unet.parameters())
+
+
+def test_frozen_parameters_do_not_break_accumulation():
+    """A frozen UNet parameter never receives a .grad; that must not reset the arena on every backward."""
+    sd, unet, handle = _build(O.TINY_UNET, False)
+    frozen = next(unet.parameters())
+    frozen.requires_grad_(False)
+    x0, noise, ctx, _, t = _inputs(O.TINY_UNET, False, 2, 16)
+    args = (x0.cuda(), ctx.cuda(), t.cuda(), noise.cuda())
+    T.p_losses(handle, *args)[0].backward()
+    name, p = [(n, q) for n, q in unet.named_parameters() if q.requires_grad and q.dim() == 4][3]
+    g1 = p.grad.clone()
+    T.p_losses(handle, *args)[0].backward()         # accumulates
+    assert frozen.grad is None
+    assert O.rel_l2(p.grad, 2 * g1) <= 3e-2, name

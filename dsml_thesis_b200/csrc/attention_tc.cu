@@ -241,7 +241,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
 
   // query tiles of this CTA that hold real rows (the last CTA of a sample may have fewer than AT_NQ)
   const int nq = min(AT_NQ, (n_tok - qb * (AT_NQ * 128) + 127) / 128);
-  pdl_launch_dependents();
   if (warp == AT_TMA_WARP) {
     if (lane == 0) {
       prefetch_tmap(&tm);
@@ -433,6 +432,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm, uint16_t* __restrict
     }
   }
 
+  pdl_launch_dependents();
   tc_fence_before();
   __syncthreads();
   if (warp == AT_TMA_WARP) {

@@ -43,8 +43,8 @@ int make_tensor_map_bf16(CUtensorMap* map, const void* base, int rank, const uin
                          const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
 
 // Programmatic dependent launch (PDL): the kernels of the UNet forward are launched with the programmatic-stream-
-// serialization attribute, call pdl_launch_dependents() first thing and pdl_wait() before they touch anything a predecessor
-// wrote.  The next kernel's CTAs are then scheduled as soon as every CTA of the current one has started (and resources
+// serialization attribute, call pdl_wait() before they touch anything a predecessor wrote and (the tensor-core kernels)
+// pdl_launch_dependents() when their own work is issued.  The next kernel's CTAs are then scheduled as soon as every CTA of the current one has started (and resources
 // free up), so barrier initialisation, TMEM allocation, tensor-map prefetch and the launch latency itself overlap the tail
 // of the predecessor instead of following its drain — 257 graph nodes x ~3 us per DDIM step otherwise.  EVERY kernel
 // launched with the attribute must execute pdl_wait() (completion is transitive only then); kernels launched without

@@ -124,7 +124,6 @@ __global__ void __launch_bounds__(256) ddim_step_kernel(const float* __restrict_
 // ---------------------------------------------------------------------------------------------
 __global__ void timestep_embedding_kernel(const int64_t* __restrict__ t, float* __restrict__ out, int batch, int dim,
                                           float neg_log_period) {
-  pdl_launch_dependents();
   pdl_wait();
   const int half = dim / 2;
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -207,14 +206,12 @@ __device__ __forceinline__ void small_linear_tile(const ldmb200_linear_job& j, i
 }
 
 __global__ void __launch_bounds__(256) small_linear_kernel(const __grid_constant__ ldmb200_linear_job job) {
-  pdl_launch_dependents();
   pdl_wait();
   small_linear_tile(job, blockIdx.x);
 }
 
 __global__ void __launch_bounds__(256) small_linear_batched_kernel(const ldmb200_linear_job* __restrict__ jobs,
                                                                    int n_jobs) {
-  pdl_launch_dependents();
   pdl_wait();
   int lo = 0;  // last job whose first_block <= blockIdx.x (tables are a few dozen entries)
   for (int i = 1; i < n_jobs; ++i)
@@ -229,7 +226,6 @@ __global__ void __launch_bounds__(256) small_linear_batched_kernel(const ldmb200
 template <typename T>
 __global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__ y, int batch, int C, int HW,
                                     int c_pad) {
-  pdl_launch_dependents();
   pdl_wait();
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (int64_t)batch * HW) return;
@@ -253,7 +249,6 @@ __global__ void nhwc_to_nchw_kernel(const float* __restrict__ y, int ld, float* 
 template <typename T>
 __global__ void space_to_depth2_kernel(const float* __restrict__ x, T* __restrict__ y, int batch, int H, int W,
                                        int C) {
-  pdl_launch_dependents();
   pdl_wait();
   const int c4n = C >> 2, Ho = H >> 1, Wo = W >> 1;
   int64_t total = (int64_t)batch * H * W * c4n;
@@ -294,7 +289,6 @@ __global__ void upsample2x_kernel(const float* __restrict__ x, T* __restrict__ y
 // x fp32 [n] -> y [n] (16-bit GEMM operand of a map that is consumed as it is: the folded upsample convolution)
 template <typename T>
 __global__ void cast_rows_kernel(const float* __restrict__ x, T* __restrict__ y, int64_t n4) {
-  pdl_launch_dependents();
   pdl_wait();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
     const float4 v = reinterpret_cast<const float4*>(x)[i];
@@ -385,7 +379,6 @@ __global__ void gn_stats_kernel(const float* __restrict__ x1, int c1, const floa
 __global__ void __launch_bounds__(128) gn_finalize_kernel(const float* __restrict__ cs1, int c1,
                                                           const float* __restrict__ cs2, int c2, int hw, int groups,
                                                           float eps, float* __restrict__ ws) {
-  pdl_launch_dependents();
   pdl_wait();
   __shared__ double red[2][4];
   const int g = blockIdx.x, b = blockIdx.y;
@@ -428,7 +421,6 @@ gn_apply_kernel(const float* __restrict__ x1, int c1, const float* __restrict__ 
                                 const float* __restrict__ gamma, const float* __restrict__ beta, T* __restrict__ y,
                                 T* __restrict__ raw, int hw, int groups, int R, int S, float eps, int silu,
                                 const float* __restrict__ ws) {
-  pdl_launch_dependents();
   pdl_wait();
   __shared__ float s_mean[64], s_rstd[64];
   const int C = c1 + c2, q = C >> 2, cpg = C / groups;
@@ -504,7 +496,6 @@ template <typename T, int MAXV>
 __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                                         const float* __restrict__ beta, T* __restrict__ y,
                                                         int64_t rows, int C, float eps) {
-  pdl_launch_dependents();
   pdl_wait();
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -553,7 +544,6 @@ template <typename T, int LPR>
 __global__ void __launch_bounds__(256) layernorm_c20_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
                                                             const float* __restrict__ beta, T* __restrict__ y,
                                                             int64_t rows, float eps) {
-  pdl_launch_dependents();
   pdl_wait();
   constexpr int RPW = 32 / LPR, C = 20 * LPR;
   const int lane = threadIdx.x & 31, sub = lane % LPR;

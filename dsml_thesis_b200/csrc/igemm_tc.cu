@@ -228,7 +228,6 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ntiles = p.tiles_m * p.tiles_n;
-  pdl_launch_dependents();  // PDL: everything up to pdl_wait() below overlaps the predecessor's tail
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA1);
@@ -597,6 +596,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     }
   }
 
+  pdl_launch_dependents();  // PDL (opt-in): this CTA's work is issued; the successor may start being scheduled
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {

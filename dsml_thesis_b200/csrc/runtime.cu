@@ -83,8 +83,10 @@ int make_tensor_map_bf16(CUtensorMap* map, const void* base, int rank, const uin
 }
 
 bool pdl_enabled() {
-  // measured r02 (same run, CUDA-graph replay): 47.98 samples/s without, 46.54 with (batch 64); 34.03 / 33.70 at batch 8 —
-  // the early-scheduled dependents cost more than the launch gaps they hide, so it is opt-in (LDMB200_PDL=1)
+  // measured r02 (same run, CUDA-graph replay).  Trigger at kernel start: 47.98 samples/s without, 46.54 with (batch 64);
+  // 34.03 / 33.70 at batch 8 — the early-scheduled dependents cost more than the launch gaps they hide.  Trigger at the end of
+  // each CTA's work (the shipped form): 48.93 without, 48.46 with (batch 64); 34.04 / 34.14 at batch 8 — no gain either.
+  // Opt-in only (LDMB200_PDL=1)
   static const bool on = getenv("LDMB200_PDL") && atoi(getenv("LDMB200_PDL")) == 1;
   return on;
 }

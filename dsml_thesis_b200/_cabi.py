@@ -11,7 +11,7 @@ import ctypes as C
 import os
 
 F32, BF16, F16 = 0, 1, 2
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("LDMB200_LIB", os.path.join(_HERE, "libldmb200.so"))
@@ -39,7 +39,12 @@ class GemmDesc(C.Structure):
         ("out_dtype", C.c_int32), ("out_ld", C.c_int32), ("out_nchw", C.c_int32), ("n_valid", C.c_int32),
         ("colstats", C.c_void_p),
         ("pad_mode", C.c_int32), ("pad_", C.c_int32),
+        ("splitk_ws", C.c_void_p), ("splitk_ws_bytes", C.c_int64),
+        ("prefetch", C.c_void_p), ("prefetch_bytes", C.c_int64),
     ]
+
+
+SPLITK_COUNTER_BYTES = 1024   # LDMB200_SPLITK_COUNTER_BYTES
 
 
 class PackJob(C.Structure):

@@ -14,6 +14,8 @@
 // smem operand tiles are K-major with the hardware 64B (BK=32) or 128B (BK=64) swizzle, written by TMA and
 // read by the UMMA descriptors (cute/arch/mma_sm100_desc.hpp bit layout).
 #include <algorithm>
+#include <math.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -50,6 +52,16 @@ struct TcParams {
   // output pixel (n, 2y + up_py, 2x + up_px).  up_w == 0: off.
   int up_w, up_hw, up_py, up_px;
   int b_row0;  // first row of this launch's weight set inside the B tensor map
+  // split-K for grids that would leave most SMs idle (small M, deep K): `splits` CTAs share one output tile, each reduces
+  // kiters_per_split of the tile's taps x channel-chunk iterations and leaves its fp32 partial in sk_part; the CTA that
+  // arrives last at the tile's counter folds the partials in split order (deterministic) and runs the fused epilogue.
+  int splits, kiters_per_split;
+  float* sk_part;          // [tile][split][chunk][CH/4][128 rows] float4
+  unsigned int* sk_cnt;    // [tile] arrival counters: zero before the launch, reset to zero by the last arrival
+  // weights of a LATER launch to pull into L2 while this one runs (ldmb200_gemm_desc.prefetch): at batch 1-4 a GEMM's
+  // 2-15 MB of weights are read once, cold, by 8-32 CTAs whose 5 TMA stages cannot cover the DRAM latency
+  const char* pf_ptr;
+  unsigned long long pf_bytes;
   uint32_t idesc;  // tcgen05 instruction descriptor (operand format bf16 or f16, M = 128, N = BN)
 };
 
@@ -208,7 +220,8 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
 // those GEMMs and needs the registers); GG == false handles every other epilogue.
 // O16: the output is a 16-bit type (bf16 / f16) — a template parameter, like GG, so that each instantiation carries one
 // store path only (the kernel was losing 8 % of its issue slots to instruction fetch, ncu r01v).
-template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false>
+// SK: split-K specialisation (see TcParams::splits); plain epilogues only.
+template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false>
 __global__ void __launch_bounds__(64 + EW * 32, 1)
 igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                 const __grid_constant__ CUtensorMap tmB, const TcParams p) {
@@ -226,9 +239,20 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
+  static_assert(!SK || (!GG && !UP), "split-K serves the plain epilogues");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ntiles = p.tiles_m * p.tiles_n;
+  // work units of the persistent loop: output tiles, or (tile, split) pairs with the split index fastest
+  const int ntiles = p.tiles_m * p.tiles_n * (SK ? p.splits : 1);
 
+  if (p.pf_bytes && warp == 2 && lane == 0) {
+    // constant data, nothing of the predecessor is touched: issued before the dependency wait.  CTA b takes slice b.
+    const unsigned long long per = (((p.pf_bytes + gridDim.x - 1) / gridDim.x) + 4095ull) & ~4095ull;
+    const unsigned long long b0 = blockIdx.x * per, b1 = b0 + per < p.pf_bytes ? b0 + per : p.pf_bytes;
+    for (unsigned long long o = b0; o < b1; o += 16384ull) {
+      const unsigned int n = (unsigned int)(b1 - o < 16384ull ? b1 - o : 16384ull);
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.pf_ptr + o), "r"(n) : "memory");
+    }
+  }
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA1);
     prefetch_tmap(&tmB);
@@ -263,16 +287,20 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     // (a single-thread producer / MMA loop with running stage counters was measured r02l and is SLOWER: big-K convolutions
     // 0.753 -> 0.934 ms at K = 5760, implicit GEMMs 13.6 -> 14.9 ms per eval; the converged-warp form stays)
     uint32_t it = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (int unit = blockIdx.x; unit < ntiles; unit += gridDim.x) {
+      const int tile = SK ? unit / p.splits : unit;
       const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
       const int m0 = tm * Cfg::BM;
+      // this unit's range [k0, k1) of the flattened (tap, chunk) iterations
+      const int k0 = SK ? (unit - tile * p.splits) * p.kiters_per_split : 0;
+      const int k1 = SK ? min(p.taps * nchunks, k0 + p.kiters_per_split) : p.taps * nchunks;
       int n_img = 0, h0 = 0, w0 = 0;
       if (p.is_conv) {
         n_img = m0 / p.hw_out;
         h0 = (m0 % p.hw_out) / p.w_out;
         w0 = m0 % p.w_out;  // non-zero only for maps wider than one 128-pixel tile (first-stage decoder at 256x256)
       }
-      for (int tap = 0; tap < p.taps; ++tap) {
+      for (int tap = SK ? k0 / nchunks : 0; tap < (SK ? (k1 + nchunks - 1) / nchunks : p.taps); ++tap) {
         int dh = 0, dw = 0, plane = 0;
         if (p.ks == 2) {  // folded upsample: tap (a, b) reads low-res pixel (y + a - 1 + py, x + b - 1 + px)
           dh = (tap >> 1) - 1 + p.up_py;
@@ -298,7 +326,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
             plane = ph * 2 + pw;
           }
         }
-        for (int j = 0; j < nchunks; ++j, ++it) {
+        for (int j = SK ? max(k0 - tap * nchunks, 0) : 0; j < (SK ? min(k1 - tap * nchunks, nchunks) : nchunks); ++j, ++it) {
           const int s = it % Cfg::STAGES;
           const uint32_t ph_ = (it / Cfg::STAGES) & 1;
           mbar_wait(&empty[s], ph_ ^ 1);
@@ -326,14 +354,16 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     const uint32_t idesc = p.idesc;
     const int kmax1 = p.c1_tail_k, kmax2 = p.c2_tail_k;
     uint32_t it = 0, t_iter = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
+    for (int unit = blockIdx.x; unit < ntiles; unit += gridDim.x, ++t_iter) {
       const uint32_t buf = t_iter & 1;
       mbar_wait(&tempty[buf], ((t_iter >> 1) & 1) ^ 1);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + buf * BN;
       uint32_t acc = 0;
-      for (int tap = 0; tap < p.taps; ++tap) {
-        for (int j = 0; j < nchunks; ++j, ++it) {
+      const int k0 = SK ? (unit % p.splits) * p.kiters_per_split : 0;
+      const int k1 = SK ? min(p.taps * nchunks, k0 + p.kiters_per_split) : p.taps * nchunks;
+      for (int tap = SK ? k0 / nchunks : 0; tap < (SK ? (k1 + nchunks - 1) / nchunks : p.taps); ++tap) {
+        for (int j = SK ? max(k0 - tap * nchunks, 0) : 0; j < (SK ? min(k1 - tap * nchunks, nchunks) : nchunks); ++j, ++it) {
           const int s = it % Cfg::STAGES;
           const uint32_t ph_ = (it / Cfg::STAGES) & 1;
           const int kmax = (j == p.c1_chunks - 1) ? kmax1 : (j == nchunks - 1) ? kmax2 : BK / 16;
@@ -446,7 +476,8 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
         }
       }
     } else
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
+    for (int unit = blockIdx.x; unit < ntiles; unit += gridDim.x, ++t_iter) {
+      const int tile = SK ? unit / p.splits : unit;
       const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
       const int m0 = tm * Cfg::BM + qw * 32;
       const int n0 = tn * BN;
@@ -454,11 +485,47 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       const int tile_sample = (tm * Cfg::BM) / p.rows_per_sample;
       float4 res[8];
       const int cc_first = par;
+      // partials of this tile: [split][chunk][CH/4][128 rows] float4 — a warp's store of one float4 index is 512 contiguous bytes
+      const float4* sk_tile = nullptr;
+      if constexpr (SK) {
+        sk_tile = reinterpret_cast<const float4*>(p.sk_part) + (size_t)tile * p.splits * (NCH * (Cfg::CH / 4) * 128);
+        float4* mine = const_cast<float4*>(sk_tile) + (size_t)(unit - tile * p.splits) * (NCH * (Cfg::CH / 4) * 128) + qw * 32 + lane;
+        mbar_wait(&tfull[buf], (t_iter >> 1) & 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int cc = cc_first; cc < NCH; cc += CSTEP) {
+          float v[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16) + buf * BN + cc * Cfg::CH;
+          if (Cfg::CH == 32) tmem_ld_32x32(taddr, v);
+          else tmem_ld_32x16(taddr, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < Cfg::CH / 4; ++j)
+            __stcg(mine + (cc * (Cfg::CH / 4) + j) * 128, make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]));
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[buf]);
+        // every epilogue thread's partial is visible device-wide before the tile's counter moves (threadFenceReduction pattern)
+        __threadfence();
+        asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
+        if (ew == 0 && lane == 0) {
+          const unsigned int prev = atomicAdd(p.sk_cnt + tile, 1u);
+          const bool last = prev == (unsigned int)p.splits - 1u;
+          if (last) p.sk_cnt[tile] = 0u;  // every split of the tile has arrived: the counter is ready for the next launch
+          tmem_slot[1] = last ? 1u : 0u;
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
+        const bool last = reinterpret_cast<volatile uint32_t*>(tmem_slot)[1] != 0u;
+        asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");  // (the flag is rewritten by the next unit)
+        if (!last) continue;
+        __threadfence();
+      }
 #if LDM_TC_RES_PREFETCH
       // The +residual GEMMs with K <= 640 are bound by the latency of the residual read (ncu r01s: 80 KB of fp32
       // residual per tile with at most one 4 KB chunk per warp in flight = 7.4 us per tile): pull the NEXT tile's
       // residual rows into L2 now, a whole tile time ahead; fire-and-forget, no registers held.
-      if (has_res) {
+      if (!SK && has_res) {
         const int tile_n = tile + gridDim.x;
         if (tile_n < ntiles) {
           const int m = (tile_n / p.tiles_n) * Cfg::BM + qw * 32 + lane;
@@ -502,13 +569,29 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
           else epi_load_add<false, Cfg::CH>(p, addv, n0 + cc_first * Cfg::CH, lane, true, tile_sample);
         }
       }
-      mbar_wait(&tfull[buf], (t_iter >> 1) & 1);
-      tc_fence_after();
+      if constexpr (!SK) {
+        mbar_wait(&tfull[buf], (t_iter >> 1) & 1);
+        tc_fence_after();
+      }
 #pragma unroll 1
       for (int cc = cc_first; cc < NCH; cc += CSTEP) {
         float v[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16) + buf * BN + cc * Cfg::CH;
-        if (Cfg::CH == 32)
+        if constexpr (SK) {  // accumulator = the splits' partials, folded in split order whichever CTA arrived last
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0.f;
+          const float4* src = sk_tile + cc * (Cfg::CH / 4) * 128 + qw * 32 + lane;
+#pragma unroll 1
+          for (int sp = 0; sp < p.splits; ++sp, src += NCH * (Cfg::CH / 4) * 128) {
+            float4 t[Cfg::CH / 4];
+#pragma unroll
+            for (int j = 0; j < Cfg::CH / 4; ++j) t[j] = __ldcg(src + j * 128);
+#pragma unroll
+            for (int j = 0; j < Cfg::CH / 4; ++j) {
+              v[4 * j] += t[j].x; v[4 * j + 1] += t[j].y; v[4 * j + 2] += t[j].z; v[4 * j + 3] += t[j].w;
+            }
+          }
+        } else if (Cfg::CH == 32)
           tmem_ld_32x32(taddr, v);
         else
           tmem_ld_32x16(taddr, v);
@@ -525,11 +608,13 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
             else epi_load_add<false, Cfg::CH>(p, addv_next, n0 + (cc + CSTEP) * Cfg::CH, lane, true, tile_sample);
           }
         }
-        tmem_ld_wait();
-        if (!more) {  // last TMEM read of this warp for this tile: hand the accumulator buffer back early
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty[buf]);
+        if constexpr (!SK) {
+          tmem_ld_wait();
+          if (!more) {  // last TMEM read of this warp for this tile: hand the accumulator buffer back early
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[buf]);
+          }
         }
         if (!GG && !O16 && p.out_nchw) {
           // UNetModel.out conv: thread owns pixel m, writes the n_valid real channels as fp32 NCHW
@@ -588,7 +673,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
         addv[1] = addv_next[1];
         }  // !GG
       }
-      if (cc_first >= NCH) {  // this warp had no chunk in the tile (BN == CH): still release the buffer
+      if (!SK && cc_first >= NCH) {  // this warp had no chunk in the tile (BN == CH): still release the buffer
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tempty[buf]);
@@ -605,13 +690,13 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   }
 }
 
-template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false>
+template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false>
 static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b, const TcParams& p,
                      cudaStream_t st) {
   using Cfg = TcCfg<BN, BK, EW>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG, O16, UP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::SMEM_BYTES);
     if (e != cudaSuccess) {
       set_error("igemm_tc: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
@@ -619,8 +704,8 @@ static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CU
     }
     attr_set = true;
   }
-  int grid = std::min(p.tiles_m * p.tiles_n, sm_count());
-  cudaError_t le = launch_pdl(igemm_tc_kernel<BN, BK, EW, GG, O16, UP>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, st, a1,
+  int grid = std::min(p.tiles_m * p.tiles_n * (SK ? p.splits : 1), sm_count());
+  cudaError_t le = launch_pdl(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, st, a1,
                               a2, b, p);
   if (le != cudaSuccess) {
     set_error("igemm_tc: launch failed: %s", cudaGetErrorString(le));
@@ -692,6 +777,12 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   p.out_ld = d->out_ld;
   p.out_nchw = d->out_nchw;
   p.colstats = d->colstats;
+  if (d->prefetch && d->prefetch_bytes > 0) {
+    LDM_CHECK_ARG(((uintptr_t)d->prefetch & 15) == 0 && d->prefetch_bytes % 16 == 0,
+                  "igemm_tc: prefetch range must be 16-byte aligned and a multiple of 16 bytes");
+    p.pf_ptr = reinterpret_cast<const char*>(d->prefetch);
+    p.pf_bytes = (unsigned long long)d->prefetch_bytes;
+  }
   LDM_CHECK_ARG(!d->colstats || (d->out_dtype == LDMB200_F32 && !d->geglu && !d->out_nchw && p.M % 32 == 0 &&
                                  d->n % 32 == 0 && (d->n_valid <= 0 || d->n_valid == d->n)),
                 "igemm_tc: colstats needs an fp32 row-major output with M %% 32 == 0 and n %% 32 == 0, unpadded");
@@ -770,6 +861,42 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
       if (rc) return rc;
     }
     return 0;
+  }
+  // ---- split-K (opt-in: the caller passes a workspace): a grid that would occupy at most half of the SMs with a deep
+  // reduction per tile (batch 1-4 sampling: M = 256 ... 4096 rows against K = 2560 ... 11520).  S ~ sqrt(0.6 kiters) splits,
+  // at most 8, at most SMs / tiles, at least 4 iterations each, K >= 2560 (40 chunks of 64).  Measured r02 (ncu, batch 1,
+  // 64x64 latents): M256 N640 K5760 32.0 -> 29.4 us with 7 splits, K11520 54 -> 33 us with 8; K <= 2880 LOSES (18 -> 23 us).
+  // The main loops do shrink to ~8 us, but the CTA that arrives last then pulls S x 80 KB of partials through ONE SM's
+  // load path in S dependent rounds (~20 us at S = 7: sm__cycles_active shows 48 of the 56 CTAs done after 15 K of the
+  // 56 K cycles).  Whole eval under CUDA-graph replay: 3.98 -> 3.89 ms at batch 1, 6.85 -> 6.65 ms at batch 1 / 128x128
+  // (tools/eval_time.py) — a 2-3 % gain, hence not the default; a cluster / DSMEM reduce-scatter fold is the next step.
+  if (d->splitk_ws && BN == 160 && !d->geglu && !d->out_nchw) {
+    const int kiters = p.taps * (p.c1_chunks + p.c2_chunks), tiles = p.tiles_m * p.tiles_n, sms = sm_count();
+    static int tune_mink = 40, tune_max = 8;
+    static double tune_coef = 0.6;
+    static bool tune_read = false;
+    if (!tune_read) {  // LDMB200_SPLITK_TUNE="min_kiters,coef,max_splits" (measurement knob)
+      if (const char* e = getenv("LDMB200_SPLITK_TUNE")) sscanf(e, "%d,%lf,%d", &tune_mink, &tune_coef, &tune_max);
+      tune_read = true;
+    }
+    if (tiles * 2 <= sms && kiters >= tune_mink) {
+      const int64_t tile_bytes = (int64_t)128 * BN * 4;
+      const int64_t cap = (d->splitk_ws_bytes - LDMB200_SPLITK_COUNTER_BYTES) / (tile_bytes * tiles);
+      int s = (int)(sqrt(tune_coef * (double)kiters) + 0.5);
+      s = std::min(std::min(s, tune_max), std::min(sms / tiles, kiters / 4));
+      s = (int)std::min<int64_t>(s, cap);
+      if (s >= 2 && tiles * 4 <= LDMB200_SPLITK_COUNTER_BYTES) {
+        LDM_CHECK_ARG(((uintptr_t)d->splitk_ws & 15) == 0, "igemm_tc: splitk_ws must be 16-byte aligned");
+        p.kiters_per_split = ceil_div(kiters, s);
+        p.splits = ceil_div(kiters, p.kiters_per_split);
+        p.sk_cnt = reinterpret_cast<unsigned int*>(d->splitk_ws);
+        p.sk_part = reinterpret_cast<float*>(reinterpret_cast<char*>(d->splitk_ws) + LDMB200_SPLITK_COUNTER_BYTES);
+        if (p.splits >= 2)
+          return out16 ? launch_tc_impl<160, 64, 8, false, true, false, true>(tA1, tA2, tB, p, st)
+                       : launch_tc_impl<160, 64, 8, false, false, false, true>(tA1, tA2, tB, p, st);
+        p.splits = 0;
+      }
+    }
   }
   if (BN == 128) return d->geglu ? launch_tc<128, 64, 16, true>(tA1, tA2, tB, p, st) : launch_tc<128, 64, 16>(tA1, tA2, tB, p, st);
   LDM_CHECK_ARG(!d->geglu || d->n % 32 == 0, "igemm_tc: geglu needs n %% 32 == 0 (got n=%d)", d->n);

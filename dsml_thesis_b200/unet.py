@@ -185,6 +185,7 @@ class _WeightPack:
         self.dtype = dtype
         self.entries: Dict[str, Tuple[int, int, int]] = {}   # key -> (byte offset, n_pad, c_pad)
         self.f32_entries: Dict[str, int] = {}                 # key -> float offset (GEGLU biases)
+        self.nbytes: Dict[str, int] = {}                      # key -> bytes of the packed matrix
         jobs: List[tuple] = []
         off = 0
         foff = 0
@@ -203,6 +204,7 @@ class _WeightPack:
                 jobs.append((p, base, kind, p.shape[0], c, ksize, rows, c_pad, row, _tc_bn(n_pad, kind == 1)))
                 row += p.shape[0]
             self.entries[key] = (base, n_pad, c_pad)
+            self.nbytes[key] = n_pad * ksize * ksize * c_pad * 2
             off += n_pad * ksize * ksize * c_pad * 2
             off = (off + 255) // 256 * 256
 
@@ -213,6 +215,7 @@ class _WeightPack:
             n_pad, c_pad = _tc_npad(n), _tc_cpad(c)
             jobs.append((w, off, 4, n, c, 3, n_pad, c_pad, 0, _tc_bn(n_pad)))
             self.entries[key] = (off, n_pad, c_pad)
+            self.nbytes[key] = 4 * n_pad * 4 * c_pad * 2
             off += 4 * n_pad * 4 * c_pad * 2
             off = (off + 255) // 256 * 256
 
@@ -338,10 +341,26 @@ class _Plan:
         self.y_in = torch.empty(B, dtype=torch.int64, device=dev) if model.num_classes is not None else None
         self.out = torch.empty(B, model.out_channels, H, W, **f32)
         self.gn_ws = torch.empty(int(self.lib.ldmb200_groupnorm_ws_floats(B, H * W, 0)), **f32)
+        # split-K scratch of the tensor-core GEMMs (ldmb200_gemm_desc.splitk_ws): arrival counters (zero) + fp32 partials.
+        # The launcher only splits grids of <= 74 tiles with K >= 2560 (batch 1-4 sampling); UNetModel.split_k turns it on
+        self.splitk_ws = None
+        if self.tc and getattr(model, "split_k", False):
+            self.splitk_ws = torch.zeros((_cabi.SPLITK_COUNTER_BYTES + (16 << 20)) // 4, **f32)
         self.graph = None
         self.runs = 0
         self.fold_upsample = getattr(self, "fold_upsample", os.environ.get("LDMB200_FOLD_UPSAMPLE", "1") == "1")
+        self.tc_gemms: List[tuple] = []   # (desc, bytes of its packed weights, GEMM rows) in launch order
         self._build()
+        self._link_weight_prefetch()
+
+    def _link_weight_prefetch(self):
+        """Small-batch evals read every GEMM's weights once, cold, through a few CTAs: each tensor-core GEMM pulls the
+        weights of the NEXT one into L2 while it runs (``ldmb200_gemm_desc.prefetch``) when that next GEMM has at most
+        ``LDMB200_WPREFETCH_ROWS`` rows — above that its many M tiles share the weights through L2 anyway."""
+        max_rows = int(os.environ.get("LDMB200_WPREFETCH_ROWS", "16384"))
+        for (d, _, _), (nxt, nbytes, rows) in zip(self.tc_gemms, self.tc_gemms[1:]):
+            if nbytes and rows <= max_rows and nbytes % 16 == 0:
+                d.prefetch, d.prefetch_bytes = nxt.w, nbytes
 
     # ---- small helpers -------------------------------------------------------------------
     def _make_pack(self):
@@ -502,6 +521,9 @@ class _Plan:
         d.rowvec, d.rowvec_ld = rowvec if rowvec is not None else (None, 0)
         d.residual, d.residual_ld = (residual.ptr, residual.c) if residual is not None else (None, 0)
         d.geglu = 1 if geglu else 0
+        ws = getattr(self, "splitk_ws", None)   # (the first-stage plans of vqdecode.py carry none)
+        if tc and ws is not None and not geglu:
+            d.splitk_ws, d.splitk_ws_bytes = ws.data_ptr(), ws.numel() * 4
         n_cols = n_true // 2 if geglu else n_true
         h_eff, w_eff = (2 * h_in, 2 * w_in) if upsample else (h_in, w_in)
         h_out, w_out = (h_eff // 2, w_eff // 2) if stride == 2 else (h_eff, w_eff)
@@ -520,6 +542,8 @@ class _Plan:
                 res.stats = self.arena.alloc((rows // 32) * n_true * 2 * 4)
                 d.colstats = res.stats.ptr
         self.keep.append(d)
+        if tc and hasattr(self, "tc_gemms"):
+            self.tc_gemms.append((d, self.pack.nbytes.get(key, 0), rows))
         k_true = weight.shape[1] * ksize * ksize if weight.dim() >= 2 and n_true == weight.shape[0] else a.c
         # (folded upsample: `flops` stays the ALGORITHMIC count of the reference's op list, 2 M N 9C — SURVEY 8d — although
         # the four 2x2 convolutions execute 4/9 of it; bench.py reports the executed rate next to the algorithmic one)
@@ -907,6 +931,11 @@ class UNetModel(nn.Module):
         # fp16 operand range guard, evaluated on the first call of every plan: "warn" (default) = fall back to bf16
         # operands for the whole model with a RuntimeWarning when a launch saturates at +-65504, "raise", or "off"
         self.f16_guard = os.environ.get("LDMB200_F16_GUARD", "warn")
+        # split-K of the tensor-core GEMMs whose grid would leave most SMs idle (batch 1-4 sampling).  Opt-in (split_k = True
+        # or LDMB200_SPLITK=1): measured 2-3 % per eval at batch 1-2 (igemm_tc.cu), and it gives up the bit-identity of a
+        # sample's eps BETWEEN batch sizes that take different split decisions (fp32 summation order; every batch shape stays
+        # bit-reproducible run to run).  Off, a sample's eps is bit-identical under any sharding of the batch.
+        self._split_k = os.environ.get("LDMB200_SPLITK", "0") == "1"
         self._plans: Dict[tuple, _Plan] = {}
         self._packs: Dict[int, _WeightPack] = {}   # operand dtype -> packed weights
         self._frozen = 0
@@ -979,6 +1008,16 @@ class UNetModel(nn.Module):
             plan.pack.run(cur.cuda_stream)
             self._pack_valid.add(plan.act)
             return plan.run_checked(cur)
+
+    @property
+    def split_k(self) -> bool:
+        return self._split_k
+
+    @split_k.setter
+    def split_k(self, on: bool):
+        if bool(on) != self._split_k:
+            self._split_k = bool(on)
+            self._plans.clear()   # the workspace pointer is part of the recorded launches
 
     def _get_plan(self, B, H, W, L, mode) -> _Plan:
         key = (B, H, W, L, mode)

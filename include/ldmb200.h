@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define LDMB200_ABI_VERSION 4
+#define LDMB200_ABI_VERSION 5
 
 #define LDMB200_F32 0
 #define LDMB200_BF16 1
@@ -181,7 +181,21 @@ typedef struct ldmb200_gemm_desc {
                           * row below and one zero column right, none above / left - the Downsample of the first-stage
                           * Encoder (ldm/modules/diffusionmodules/model.py:72-76)                                    */
   int32_t pad_;
+  /* TC path, optional split-K scratch (NULL: never split).  Batch 1-4 sampling leaves GEMMs of 8-74 output tiles with K
+   * up to 11520 on 148 SMs; with a workspace the launcher splits such a tile's reduction over up to 8 CTAs, which leave fp32
+   * partials here and fold them in split order (bit-reproducible) in whichever CTA arrives last, before the same fused
+   * epilogue.  Layout: LDMB200_SPLITK_COUNTER_BYTES of arrival counters — ZERO before the first use, left zero by every
+   * launch — followed by the partials.  16-byte aligned; one workspace per stream (launches that may overlap must not
+   * share it).  16 MiB + the counters covers every shape the heuristic picks. */
+  void* splitk_ws;
+  int64_t splitk_ws_bytes;
+  /* TC path, optional: a read-only range (the packed weights of a LATER launch) that this launch pulls into L2 with bulk
+   * prefetches while it runs.  Small-batch sampling reads each GEMM's weights exactly once per eval, cold, from a handful of
+   * CTAs; the launch before it has the HBM idle.  16-byte aligned, multiple of 16 bytes; NULL / 0: none. */
+  const void* prefetch;
+  int64_t prefetch_bytes;
 } ldmb200_gemm_desc;
+#define LDMB200_SPLITK_COUNTER_BYTES 1024
 
 /* fp32-exact SIMT path (precision mode "fp32": per-step eps rel-L2 <= 1e-4 vs the fp32 reference). */
 int ldmb200_igemm_simt(const ldmb200_gemm_desc* d, void* stream);

@@ -98,7 +98,7 @@ def geglu_perm(n_total, block_n):
 
 
 def igemm(mode, a, B, h_in, w_in, w, bias=None, ksize=1, stride=1, upsample=0, a2=None, rowvec=None,
-          residual=None, geglu=False, out_dtype=F32, out_nchw=False, colstats=None):
+          residual=None, geglu=False, out_dtype=F32, out_nchw=False, colstats=None, splitk_ws=None):
     """mode 'simt' | 'tc'.  a / a2: channels-last matrices [B*h*w, c] (fp32 for simt, bf16 for tc; for tc+stride 2
     ``a`` is the space-to-depth layout).  w: fp32 [n, c1+c2, k, k].  Returns the output tensor."""
     d = GemmDesc()
@@ -135,6 +135,8 @@ def igemm(mode, a, B, h_in, w_in, w, bias=None, ksize=1, stride=1, upsample=0, a
         d.out, d.out_dtype, d.out_ld, d.out_nchw, d.n_valid = out.data_ptr(), out_dtype, n_cols, 0, n_cols
     if colstats is not None:
         d.colstats = colstats.data_ptr()
+    if splitk_ws is not None:   # float32 tensor: LDMB200_SPLITK_COUNTER_BYTES of zeroed counters + partials
+        d.splitk_ws, d.splitk_ws_bytes = splitk_ws.data_ptr(), splitk_ws.numel() * 4
     _cabi.call("ldmb200_igemm_tc" if mode == "tc" else "ldmb200_igemm_simt", C.byref(d), stream())
     torch.cuda.synchronize()
     return out

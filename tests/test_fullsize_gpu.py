@@ -91,11 +91,28 @@ def test_fr_unet_64_batch4_vs_reference_and_batch_invariance(precision, golden_c
         err = O.rel_l2(full, torch.from_numpy(golden_c2["c2/b4/eps"]))
         record_parity(f"eps/fr_64_b4/{precision}", err)
         assert err <= EPS_TOL[precision], err
-        singles = torch.cat([m(x[i:i + 1].cuda(), t[i:i + 1].cuda(), context=ctx[i:i + 1].cuda()) for i in range(4)])
-        halves = torch.cat([m(x[:2].cuda(), t[:2].cuda(), context=ctx[:2].cuda()),
-                            m(x[2:].cuda(), t[2:].cuda(), context=ctx[2:].cuda())])
-    # a sample's eps does not depend on its batch-mates: bit-identical under any sharding of the batch
-    assert torch.equal(full, singles) and torch.equal(full, halves)
+        shard = lambda: (torch.cat([m(x[i:i + 1].cuda(), t[i:i + 1].cuda(), context=ctx[i:i + 1].cuda()) for i in range(4)]),
+                         torch.cat([m(x[:2].cuda(), t[:2].cuda(), context=ctx[:2].cuda()),
+                                    m(x[2:].cuda(), t[2:].cuda(), context=ctx[2:].cuda())]))
+        singles, halves = shard()
+        # a sample's eps does not depend on its batch-mates: bit-identical under any sharding of the batch
+        assert torch.equal(full, singles) and torch.equal(full, halves)
+        # opt-in split-K (batch 1 / 2 / 4 split the deep reductions of the 8x8 ... 32x32 levels differently): the same holds
+        # up to fp32 summation order, and every batch shape stays bit-reproducible run to run
+        bound = {"fp32": 0.0, "f16": 3e-3, "bf16": 2e-2}[precision]   # (fp32 mode = SIMT kernels, never split)
+        m.split_k = True
+        try:
+            full1 = m(x.cuda(), t.cuda(), context=ctx.cuda())
+            singles1, halves1 = shard()
+            again = shard()
+            full1b = m(x.cuda(), t.cuda(), context=ctx.cuda())
+        finally:
+            m.split_k = False
+    assert O.rel_l2(singles1, full) <= bound and O.rel_l2(halves1, full) <= bound and O.rel_l2(full1, full) <= bound
+    assert torch.equal(again[0], singles1) and torch.equal(again[1], halves1) and torch.equal(full1b, full1)
+    err = O.rel_l2(singles1, torch.from_numpy(golden_c2["c2/b4/eps"]))
+    record_parity(f"eps/fr_64_b4_splitk_singles/{precision}", err)
+    assert err <= EPS_TOL[precision], err
 
 
 @pytest.mark.parametrize("precision", ["fp32", "f16"])

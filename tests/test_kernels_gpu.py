@@ -301,6 +301,72 @@ def test_tc_epilogues():
     assert K.rel_l2(out, K.igemm_reference(x, bf(wo), bo)) <= 1e-5
 
 
+@pytest.mark.parametrize("B,H,c,n,ksize,extras", [
+    (1, 16, 640, 640, 3, "res+rowvec+stats"),    # M = 256, K = 5760: the FR UNet's 8x8..16x16 levels at batch 1
+    (1, 32, 320, 320, 3, "res"),                 # M = 1024, K = 2880
+    (4, 16, 288, 160, 3, "stats"),               # M = 1024, K = 2592: partial last channel chunk (288 = 4 x 64 + 32) inside a split
+    (1, 16, 2560, 640, 1, "res+f16out"),         # ff.net.2 at batch 1: K = 2560, 16-bit output
+    (3, 8, 1280, 1280, 3, "rowvec"),             # M = 192 (ragged last tile), K = 11520, 2 x 8 tiles
+    (1, 16, 2880, 640, 1, "plain"),              # plain 1x1, K = 2880
+])
+def test_tc_split_k(B, H, c, n, ksize, extras):
+    """ldmb200_gemm_desc.splitk_ws: the split-K launch (small grids, deep K) equals the single-CTA-per-tile launch up to
+    fp32 summation order, is bit-reproducible run to run, leaves its counters zero, and never writes outside the
+    workspace it was given."""
+    hw = H * H
+    M = B * hw
+    a = bf(rnd(M, c)).to(torch.bfloat16)
+    w, b = rnd(n, c, ksize, ksize, scale=(ksize * ksize * c) ** -0.5), rnd(n)
+    kw = dict(ksize=ksize)
+    if "res" in extras:
+        kw["residual"] = rnd(M, n) + 0.3
+    if "rowvec" in extras:
+        kw["rowvec"] = rnd(B, n)
+    if "f16out" in extras:
+        kw["out_dtype"] = F16
+    mk_cs = lambda: torch.full((M // 32, n, 2), float("nan"), device=a.device) if "stats" in extras else None
+    cs0 = mk_cs()
+    ref = K.igemm("tc", a, B, H, H, w, b, colstats=cs0, **kw)
+    words = (1024 + (16 << 20)) // 4
+    guard = torch.full((words + 1024,), 777.0, device=a.device)
+    ws = guard[:words]
+    ws.zero_()
+    outs = []
+    for _ in range(3):
+        cs = mk_cs()
+        outs.append((K.igemm("tc", a, B, H, H, w, b, colstats=cs, splitk_ws=ws, **kw), cs))
+        assert bool((ws[:256].view(torch.int32) == 0).all()), "arrival counters must be left at zero"
+    assert bool((guard[words:] == 777.0).all())
+    assert float(ws[256:].abs().max()) > 0.0, "the shape was expected to take the split-K path (partials untouched)"
+    out, cs = outs[0]
+    assert torch.isfinite(out.float()).all()
+    assert K.rel_l2(out, ref) <= (2e-3 if "f16out" in extras else 1e-5)
+    for o2, c2 in outs[1:]:
+        assert torch.equal(o2, out)
+        if cs is not None:
+            assert torch.equal(c2, cs)
+    if cs is not None:
+        blk = out.reshape(M // 32, 32, n).double()
+        assert K.rel_l2(cs[..., 0], blk.sum(1).float()) <= 1e-5
+        assert K.rel_l2(cs[..., 1], (blk * blk).sum(1).float()) <= 1e-5
+    x = K.from_cl(a.float(), B, H, H)
+    tgt = K.igemm_reference(x, bf(w), b, rowvec=kw.get("rowvec"),
+                            residual_nchw=K.from_cl(kw["residual"], B, H, H) if "residual" in kw else None)
+    assert K.rel_l2(out.float(), K.to_cl(tgt).float()) <= (2e-3 if "f16out" in extras else 1e-5)
+
+
+def test_tc_split_k_not_taken_without_workspace_or_on_large_grids():
+    """No workspace -> never split; a grid that already fills the SMs ignores the workspace (partials stay untouched)."""
+    B, H, c, n = 8, 32, 320, 320     # M = 8192 -> 64 x 2 tiles
+    a = bf(rnd(B * H * H, c)).to(torch.bfloat16)
+    w, b = rnd(n, c, 3, 3, scale=(9 * c) ** -0.5), rnd(n)
+    ws = torch.zeros((1024 + (16 << 20)) // 4, device=a.device)
+    ref = K.igemm("tc", a, B, H, H, w, b, ksize=3)
+    out = K.igemm("tc", a, B, H, H, w, b, ksize=3, splitk_ws=ws)
+    assert torch.equal(out, ref)
+    assert float(ws.abs().max()) == 0.0
+
+
 @pytest.mark.parametrize("B,H,c1,c2,n1,n2", [(2, 16, 64, 0, 160, 0), (2, 8, 96, 64, 640, 320), (1, 32, 32, 48, 320, 160),
                                                   (3, 8, 32, 0, 64, 0)])
 def test_tc_colstats_groupnorm_fused(B, H, c1, c2, n1, n2):

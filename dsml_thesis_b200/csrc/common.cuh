@@ -40,7 +40,7 @@ int sm_count();
 // cuTensorMapEncodeTiled via cudaGetDriverEntryPoint (no link-time dependency on libcuda).
 // dims/strides are innermost-first; strides[i] is the byte stride of dim i+1 (rank-1 entries).
 int make_tensor_map_bf16(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
-                         const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
+                         const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes, int elem_bytes = 2);
 
 // Programmatic dependent launch (PDL): the kernels of the UNet forward are launched with the programmatic-stream-
 // serialization attribute, call pdl_wait() before they touch anything a predecessor wrote and (the tensor-core kernels)
@@ -150,6 +150,18 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* m, uin
       ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+// shared -> global tile store (bulk async group of the issuing thread); rows / columns past the tensor's extent are clipped
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {  // at most N groups still READING their shared source
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void tma_load_5d(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
                                             int c3, int c4) {
   asm volatile(

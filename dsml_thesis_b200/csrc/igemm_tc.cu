@@ -221,10 +221,13 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
 // O16: the output is a 16-bit type (bf16 / f16) — a template parameter, like GG, so that each instantiation carries one
 // store path only (the kernel was losing 8 % of its issue slots to instruction fetch, ncu r01v).
 // SK: split-K specialisation (see TcParams::splits); plain epilogues only.
-template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false>
+// TS: nothing but a bias / per-tile row vector to add and no statistics (fused QKV, proj_in, 1x1 skip convolutions): each
+// thread finishes its row of the 32 x 32 chunk in registers, writes it into a swizzled shared-memory tile, and a TMA store
+// (tmO) moves the tile — no transposing read-back through shared memory, no per-lane global stores.
+template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false, bool TS = false>
 __global__ void __launch_bounds__(64 + EW * 32, 1)
 igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
-                const __grid_constant__ CUtensorMap tmB, const TcParams p) {
+                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO, const TcParams p) {
   using Cfg = TcCfg<BN, BK, EW>;
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment as an OFFSET from the shared array (not through uintptr_t): the compiler keeps the shared address
@@ -240,6 +243,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   static_assert(!SK || (!GG && !UP), "split-K serves the plain epilogues");
+  static_assert(!TS || (!GG && !UP && !SK && BN % 32 == 0 && BN / 32 >= EW / 4), "TMA-store epilogue: plain output");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // work units of the persistent loop: output tiles, or (tile, split) pairs with the split index fastest
   const int ntiles = p.tiles_m * p.tiles_n * (SK ? p.splits : 1);
@@ -400,6 +404,87 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     constexpr bool out16 = O16;
     const bool has_res = !GG && p.residual != nullptr;
     uint32_t t_iter = 0;
+    if constexpr (TS) {
+      // ---- bias / uniform row vector only: TMA-store epilogue.  Staging per warp: 16-bit output = two 2 KB tiles (32 rows
+      // x 64 B, 64B swizzle), fp32 output = one 4 KB tile (32 rows x 128 B, 128B swizzle); the 16-byte piece c of a row sits
+      // at piece c ^ (bits 7.. of the row's shared address), so the row owners' 16-byte writes are bank-conflict-free ----
+      constexpr int ROWB = O16 ? 64 : 128, NBUF = O16 ? 2 : 1;
+      uint8_t* stb = reinterpret_cast<uint8_t*>(epi) + ew * 4096;      // 1024-byte aligned (the staging area is)
+      if (warp == 2 && lane == 0) prefetch_tmap(&tmO);
+      uint32_t nstore = 0;
+      const int sw = O16 ? ((lane >> 1) & 3) : (lane & 7);
+      const int odt = p.out_dtype;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
+        const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
+        const int m0 = tm * Cfg::BM + qw * 32;
+        const int n0 = tn * BN;
+        const uint32_t buf = t_iter & 1;
+        const float* rvp = p.rowvec ? p.rowvec + (size_t)((tm * Cfg::BM) / p.rows_per_sample) * p.rowvec_ld : nullptr;
+        float4 bq[8];
+        auto load_add = [&](float4 (&b)[8], int cc) {  // the same 32 column addends for every row of the tile
+          const int col = n0 + cc * 32;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            b[j] = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + col) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+            if (rvp) {
+              const float4 r = __ldg(reinterpret_cast<const float4*>(rvp + col) + j);
+              b[j].x += r.x; b[j].y += r.y; b[j].z += r.z; b[j].w += r.w;
+            }
+          }
+        };
+        load_add(bq, par);
+        mbar_wait(&tfull[buf], (t_iter >> 1) & 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int cc = par; cc < NCH; cc += CSTEP) {
+          float v[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(qw * 32) << 16) + buf * BN + cc * 32, v);
+          const bool more = cc + CSTEP < NCH;
+          float4 bn[8];
+          if (more) load_add(bn, cc + CSTEP);
+          tmem_ld_wait();
+          if (!more) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[buf]);
+          }
+          // the store that last read this staging tile has finished reading it
+          if (lane == 0) tma_store_wait_read<NBUF - 1>();
+          __syncwarp();
+          uint8_t* tile_s = stb + (nstore % NBUF) * 2048;
+          uint8_t* row_s = tile_s + lane * ROWB;
+          if constexpr (O16) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const float4 b0 = bq[2 * c], b1 = bq[2 * c + 1];
+              uint4 o;
+              o.x = pack16(v[8 * c] + b0.x, v[8 * c + 1] + b0.y, odt);
+              o.y = pack16(v[8 * c + 2] + b0.z, v[8 * c + 3] + b0.w, odt);
+              o.z = pack16(v[8 * c + 4] + b1.x, v[8 * c + 5] + b1.y, odt);
+              o.w = pack16(v[8 * c + 6] + b1.z, v[8 * c + 7] + b1.w, odt);
+              *reinterpret_cast<uint4*>(row_s + ((c ^ sw) << 4)) = o;
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+              *reinterpret_cast<float4*>(row_s + ((c ^ sw) << 4)) =
+                  make_float4(v[4 * c] + bq[c].x, v[4 * c + 1] + bq[c].y, v[4 * c + 2] + bq[c].z, v[4 * c + 3] + bq[c].w);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmO, tile_s, n0 + cc * 32, m0);
+            tma_store_commit();
+          }
+          ++nstore;
+          if (more) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) bq[j] = bn[j];
+          }
+        }
+      }
+      if (lane == 0) tma_store_wait_all();
+    } else
     if constexpr (GG && Cfg::CH == 32 && LDM_TC_GG_PIPE) {
       // ---- GEGLU epilogue, software-pipelined over the two 16-column halves of the warp's chunk ----
       // All 16 epilogue warps wait for the same accumulator and have identical work, so they ran in lock step: first
@@ -690,13 +775,13 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   }
 }
 
-template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false>
+template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false, bool TS = false>
 static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b, const TcParams& p,
-                     cudaStream_t st) {
+                     cudaStream_t st, const CUtensorMap* o = nullptr) {
   using Cfg = TcCfg<BN, BK, EW>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::SMEM_BYTES);
     if (e != cudaSuccess) {
       set_error("igemm_tc: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
@@ -705,8 +790,8 @@ static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CU
     attr_set = true;
   }
   int grid = std::min(p.tiles_m * p.tiles_n * (SK ? p.splits : 1), sm_count());
-  cudaError_t le = launch_pdl(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, st, a1,
-                              a2, b, p);
+  cudaError_t le = launch_pdl(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, st, a1,
+                              a2, b, o ? *o : b, p);
   if (le != cudaSuccess) {
     set_error("igemm_tc: launch failed: %s", cudaGetErrorString(le));
     return LDMB200_ERR_CUDA;
@@ -897,6 +982,20 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
         p.splits = 0;
       }
     }
+  }
+  // ---- TMA-store epilogue: bias / per-tile row vector only, no statistics (fused QKV, proj_in, 1x1 skip convolutions)
+  static const bool tma_store_on = !(getenv("LDMB200_TMA_STORE") && atoi(getenv("LDMB200_TMA_STORE")) == 0);
+  if (tma_store_on && BN == 160 && !d->geglu && !d->residual && (!d->rowvec || p.rowvec_uniform) && !d->colstats &&
+      !d->out_nchw && p.n_valid == d->n && d->out_ld % 8 == 0 && ((uintptr_t)d->out & 15) == 0) {
+    CUtensorMap tO;
+    const int eb = out16 ? 2 : 4;
+    uint64_t dims[2] = {(uint64_t)d->n, (uint64_t)p.M};
+    uint64_t str[1] = {(uint64_t)d->out_ld * eb};
+    uint32_t box[2] = {32u, 32u};
+    int rc = make_tensor_map_bf16(&tO, d->out, 2, dims, str, box, out16 ? 64 : 128, eb);
+    if (rc) return rc;
+    return out16 ? launch_tc_impl<160, 64, 8, false, true, false, false, true>(tA1, tA2, tB, p, st, &tO)
+                 : launch_tc_impl<160, 64, 8, false, false, false, false, true>(tA1, tA2, tB, p, st, &tO);
   }
   if (BN == 128) return d->geglu ? launch_tc<128, 64, 16, true>(tA1, tA2, tB, p, st) : launch_tc<128, 64, 16>(tA1, tA2, tB, p, st);
   LDM_CHECK_ARG(!d->geglu || d->n % 32 == 0, "igemm_tc: geglu needs n %% 32 == 0 (got n=%d)", d->n);

@@ -45,7 +45,7 @@ static encode_tiled_fn get_encode() {
 }
 
 int make_tensor_map_bf16(CUtensorMap* map, const void* base, int rank, const uint64_t* dims,
-                         const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes) {
+                         const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes, int elem_bytes) {
   encode_tiled_fn enc = get_encode();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled entry point not available (driver too old?)");
@@ -68,7 +68,7 @@ int make_tensor_map_bf16(CUtensorMap* map, const void* base, int rank, const uin
   static const int l2sel = getenv("LDMB200_TMAP_L2") ? atoi(getenv("LDMB200_TMAP_L2")) : 3;
   const CUtensorMapL2promotion l2promo = l2sel == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE : l2sel == 1 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
                                          : l2sel == 2 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
-  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx,
+  CUresult r = enc(map, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx,
                    es, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, l2promo,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {

@@ -131,7 +131,11 @@ def igemm(mode, a, B, h_in, w_in, w, bias=None, ksize=1, stride=1, upsample=0, a
         out = torch.full((B, n_true, h_out, w_out), float("nan"), dtype=torch.float32, device=DEV)
         d.out, d.out_dtype, d.out_ld, d.out_nchw, d.n_valid = out.data_ptr(), F32, 0, 1, n_true
     else:
-        out = torch.full((M, n_cols), float("nan"), dtype=tdt, device=DEV)
+        # 64 guard rows behind the output: a store past row M (ragged last tile) would show up in them
+        whole = torch.full((M + 64, n_cols), float("nan"), dtype=tdt, device=DEV)
+        whole[M:] = 7.0
+        igemm.guard = whole[M:]
+        out = whole[:M]
         d.out, d.out_dtype, d.out_ld, d.out_nchw, d.n_valid = out.data_ptr(), out_dtype, n_cols, 0, n_cols
     if colstats is not None:
         d.colstats = colstats.data_ptr()
@@ -139,6 +143,8 @@ def igemm(mode, a, B, h_in, w_in, w, bias=None, ksize=1, stride=1, upsample=0, a
         d.splitk_ws, d.splitk_ws_bytes = splitk_ws.data_ptr(), splitk_ws.numel() * 4
     _cabi.call("ldmb200_igemm_tc" if mode == "tc" else "ldmb200_igemm_simt", C.byref(d), stream())
     torch.cuda.synchronize()
+    if not out_nchw:
+        assert bool((igemm.guard == 7.0).all()), "igemm wrote past the last output row"
     return out
 
 

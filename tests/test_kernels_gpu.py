@@ -301,6 +301,33 @@ def test_tc_epilogues():
     assert K.rel_l2(out, K.igemm_reference(x, bf(wo), bo)) <= 1e-5
 
 
+@pytest.mark.parametrize("B,H,c,n,ksize,bias,rowvec", [
+    (2, 16, 160, 480, 1, True, False),      # fused QKV of the 160-channel level
+    (3, 8, 160, 480, 1, True, False),       # M = 192: ragged last tile, rows 192..255 must be clipped by the TMA store
+    (1, 8, 320, 960, 1, False, False),      # M = 64 < one tile, no bias
+    (2, 16, 96, 160, 3, True, True),        # 3x3 convolution + per-sample row vector (hw = 256: uniform per tile)
+    (3, 8, 96, 160, 3, True, True),         # hw = 64: a tile spans two samples -> the launcher keeps the per-lane store path
+    (5, 16, 640, 1920, 1, True, False),     # M = 1280, 12 N tiles: several tiles per CTA through both staging tiles
+])
+def test_tc_tma_store_epilogue(B, H, c, n, ksize, bias, rowvec):
+    """Outputs with only a bias / per-tile row vector to add and no statistics take the TMA-store epilogue
+    (igemm_tc_kernel<..., TS>): fp32 bit-identical to the per-lane store path (forced by asking for column statistics),
+    16-bit bit-identical to that rounded to the same type, nothing written past row M (harness guard rows)."""
+    hw = H * H
+    a = bf(rnd(B * hw, c)).to(torch.bfloat16)
+    w, b = rnd(n, c, ksize, ksize, scale=(ksize * ksize * c) ** -0.5), (rnd(n) if bias else None)
+    rv = rnd(B, n) if rowvec else None
+    cs = torch.empty(B * hw // 32, n, 2, device=a.device)
+    old32 = K.igemm("tc", a, B, H, H, w, b, ksize=ksize, rowvec=rv, colstats=cs)      # per-lane store path
+    new32 = K.igemm("tc", a, B, H, H, w, b, ksize=ksize, rowvec=rv)
+    assert torch.equal(new32, old32)
+    tgt = K.to_cl(K.igemm_reference(K.from_cl(a.float(), B, H, H), bf(w), b, rowvec=rv))
+    assert K.rel_l2(new32, tgt) <= 1e-5
+    for odt, tdt in ((BF16, torch.bfloat16), (F16, torch.float16)):
+        out = K.igemm("tc", a, B, H, H, w, b, ksize=ksize, rowvec=rv, out_dtype=odt)
+        assert out.dtype == tdt and torch.equal(out, old32.to(tdt))
+
+
 @pytest.mark.parametrize("B,H,c,n,ksize,extras", [
     (1, 16, 640, 640, 3, "res+rowvec+stats"),    # M = 256, K = 5760: the FR UNet's 8x8..16x16 levels at batch 1
     (1, 32, 320, 320, 3, "res"),                 # M = 1024, K = 2880

@@ -543,7 +543,7 @@ class _Plan:
                 d.colstats = res.stats.ptr
         self.keep.append(d)
         if tc and hasattr(self, "tc_gemms"):
-            self.tc_gemms.append((d, self.pack.nbytes.get(key, 0), rows))
+            self.tc_gemms.append((d, getattr(self.pack, "nbytes", {}).get(key, 0), rows))   # (the training pack records no sizes: no prefetch)
         k_true = weight.shape[1] * ksize * ksize if weight.dim() >= 2 and n_true == weight.shape[0] else a.c
         # (folded upsample: `flops` stays the ALGORITHMIC count of the reference's op list, 2 M N 9C — SURVEY 8d — although
         # the four 2x2 convolutions execute 4/9 of it; bench.py reports the executed rate next to the algorithmic one)

@@ -107,6 +107,7 @@ SIGNATURES = {
     "ldmb200_nhwc_to_nchw": (_i, [_p, _i, _p, _i, _i, _i, _p]),
     "ldmb200_groupnorm_ws_floats": (_i64, [_i, _i, _i]),
     "ldmb200_groupnorm": (_i, [_p, _i, _p, _i, _p, _p, _p, _p, _i, _i, _i, _i, _f, _i, _p, _p]),
+    "ldmb200_groupnorm_static": (_i, [_p, _i, _p, _i, _p, _p, _p, _p, _i, _i, _i, _i, _f, _i, _p]),
     "ldmb200_groupnorm_fused": (_i, [_p, _i, _p, _p, _i, _p, _p, _p, _p, _p, _i, _i, _i, _i, _f, _i, _p, _p]),
     "ldmb200_layernorm": (_i, [_p, _p, _p, _p, _i, _i64, _i, _f, _p]),
     "ldmb200_space_to_depth2": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),

@@ -885,3 +885,59 @@ int ldmb200_pack_weights(const ldmb200_pack_job* jobs, int n_jobs, void* stream)
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free GroupNorm (ldmb200_groupnorm_static): ldmb200_groupnorm with the statistics workspace in a file-scope
+// device array instead of a caller buffer.  The array is part of the module image: every GPU that loads the library
+// holds its 2 MiB until exit.  Every call on a device shares it, so calls that overlap on that GPU (two streams, two host
+// threads) race on the partial sums; the statistics kernel overwrites every entry the apply kernel reads, so nothing has
+// to start at zero and the previous call's contents are harmless.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_gn_static_ws[(size_t)LDMB200_GN_STATIC_MAX_BATCH * GN_MAX_SPLITS * 64 * 2];
+
+// In host code `g_gn_static_ws` is a host-side stand-in, not a device address: resolved once per device, that device current.
+static float* gn_static_ws_ptr() {
+  constexpr int MAX_DEV = 64;
+  static float* ptrs[MAX_DEV] = {};
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+    set_error("groupnorm_static: cudaGetDevice failed or device index %d out of range", dev);
+    return nullptr;
+  }
+  if (!ptrs[dev]) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_gn_static_ws);
+    if (e != cudaSuccess || !p) {
+      set_error("groupnorm_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return nullptr;
+    }
+    ptrs[dev] = p;
+  }
+  return ptrs[dev];
+}
+
+extern "C" int ldmb200_groupnorm_static(const float* x1, int c1, const float* x2, int c2, const float* gamma,
+                                        const float* beta, void* y, void* raw_copy, int out_dtype, int batch, int hw,
+                                        int groups, float eps, int silu, void* stream) {
+  const int C = c1 + (x2 ? c2 : 0);
+  if (!x2) c2 = 0;
+  LDM_CHECK_ARG(x1 && gamma && beta && y && batch > 0 && hw > 0, "groupnorm_static: null pointer / empty");
+  LDM_CHECK_ARG(batch <= LDMB200_GN_STATIC_MAX_BATCH,
+                "groupnorm_static: batch=%d exceeds the built-in workspace (LDMB200_GN_STATIC_MAX_BATCH = %d); "
+                "use ldmb200_groupnorm with a caller workspace", batch, LDMB200_GN_STATIC_MAX_BATCH);
+  LDM_CHECK_ARG(groups > 0 && groups <= 64 && C % groups == 0, "groupnorm_static: C=%d not divisible by groups=%d", C, groups);
+  LDM_CHECK_ARG(c1 % 4 == 0 && c2 % 4 == 0 && C / 4 <= 1024, "groupnorm_static: channel counts must be multiples of 4");
+  float* ws = gn_static_ws_ptr();
+  if (!ws) return LDMB200_ERR_CUDA;
+  const int R = gn_rows_per_block(C);
+  const int S = gn_splits(hw, C);
+  const int threads = (C / 4) * R;
+  const size_t smem = (size_t)2 * R * C * sizeof(float);
+  cudaStream_t st = (cudaStream_t)stream;
+  gn_stats_kernel<<<dim3(S, batch), threads, smem, st>>>(x1, c1, x2, c2, hw, groups, R, ws);
+  LDM_CHECK_LAUNCH("groupnorm_static stats");
+  LDM_DISPATCH_DTYPE(out_dtype, (gn_apply_launch<T>(x1, c1, x2, c2, gamma, beta, y, raw_copy, batch, hw, groups, R, S, eps,
+                                                    silu, ws, st)));
+  LDM_CHECK_LAUNCH("groupnorm_static apply");
+  return 0;
+}

@@ -108,6 +108,19 @@ int ldmb200_groupnorm(const float* x1, int c1, const float* x2, int c2, const fl
                       void* y, void* raw_copy, int out_dtype, int batch, int hw, int groups, float eps, int silu,
                       float* stats_ws, void* stream);
 
+/* Allocation-free variant of ldmb200_groupnorm.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments and results as ldmb200_groupnorm without stats_ws: the statistics workspace is a
+ * file-scope device array inside the library (LDMB200_GN_STATIC_MAX_BATCH x 32 KiB = 2 MiB, held by every GPU that loads
+ * the library until exit; its device address is resolved with cudaGetSymbolAddress once per device).  The call
+ * allocates nothing (no cudaMalloc / cudaFree / allocating library routine).  batch > LDMB200_GN_STATIC_MAX_BATCH is
+ * rejected with LDMB200_ERR_INVALID.  All calls on a GPU share the array: calls that overlap on the GPU (different
+ * streams or host threads) RACE — serialise them on one stream.  Nothing needs to start at zero between calls. */
+#define LDMB200_GN_STATIC_MAX_BATCH 64
+int ldmb200_groupnorm_static(const float* x1, int c1, const float* x2, int c2, const float* gamma, const float* beta,
+                             void* y, void* raw_copy, int out_dtype, int batch, int hw, int groups, float eps, int silu,
+                             void* stream);
+
 /* K7 with the statistics pass fused into the producers: colstats1 / colstats2 are the ldmb200_gemm_desc.colstats
  * buffers the tensor-core GEMMs that wrote x1 / x2 filled ([B*hw/32][c][2] floats); the statistics never re-read
  * x.  hw % 32 == 0.  Launches: finalize (float64 fold -> stats_ws[b][g] = {mean, rstd}) + apply. */

@@ -69,7 +69,9 @@ struct TcParams {
 // epilogues; 16 for GEGLU, whose per-element work (erf GELU) makes the epilogue the bound: 128-wide tiles = 4 chunks
 // = exactly one chunk per warp, 4 warps per scheduler to hide the MUFU / TMEM / smem latencies.
 
-template <int BN, int BK, int EW>
+// RS: the TMA-store epilogue with an fp32 residual (igemm_tc_kernel<..., TS, RS>): 12 KB of residual / output staging
+// tiles per epilogue warp instead of the 4.5 KB transpose tile, paid for with two operand stages (K <= 640 linears only).
+template <int BN, int BK, int EW, bool RS = false>
 struct TcCfg {
   static constexpr int THREADS = 64 + EW * 32;
   static constexpr int BM = 128;
@@ -77,10 +79,10 @@ struct TcCfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = ((BN * BK * 2 + 1023) / 1024) * 1024;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN >= 128) ? (EW > 8 ? 4 : 5) : 8;
+  static constexpr int STAGES = RS ? 3 : (BN >= 128) ? (EW > 8 ? 4 : 5) : 8;
   static constexpr int TX_BYTES = BM * BK * 2 + BN * BK * 2;
   static constexpr int EPI_PITCH = 36;  // floats; 144 B row pitch: conflict-free 16 B row-owner writes + row reads
-  static constexpr int EPI_BYTES = EW * 32 * EPI_PITCH * 4;
+  static constexpr int EPI_BYTES = RS ? EW * 12288 + 256 : EW * 32 * EPI_PITCH * 4;
   static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + (2 * STAGES + 4) * 8 + 16 + 1024;
   static constexpr int CH = BN >= 32 ? 32 : 16;  // epilogue column chunk
@@ -224,11 +226,15 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
 // TS: nothing but a bias / per-tile row vector to add and no statistics (fused QKV, proj_in, 1x1 skip convolutions): each
 // thread finishes its row of the 32 x 32 chunk in registers, writes it into a swizzled shared-memory tile, and a TMA store
 // (tmO) moves the tile — no transposing read-back through shared memory, no per-lane global stores.
-template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false, bool TS = false>
+// RS (with TS): + an fp32 residual, TMA-loaded into a per-warp ring of swizzled tiles one chunk ahead (tmR); every thread adds
+// its own row in shared memory and the tile goes out through the TMA store — attn1.to_out, ff.net.2 (no statistics).
+template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false, bool TS = false, bool RS = false>
 __global__ void __launch_bounds__(64 + EW * 32, 1)
 igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
-                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO, const TcParams p) {
-  using Cfg = TcCfg<BN, BK, EW>;
+                const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
+                const __grid_constant__ CUtensorMap tmR, const TcParams p) {
+  using Cfg = TcCfg<BN, BK, EW, RS>;
+  static_assert(!RS || TS, "RS extends the TMA-store epilogue");
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment as an OFFSET from the shared array (not through uintptr_t): the compiler keeps the shared address
   // space and emits STS / LDS for the epilogue's staging tile instead of generic ST / LD
@@ -243,7 +249,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   static_assert(!SK || (!GG && !UP), "split-K serves the plain epilogues");
-  static_assert(!TS || (!GG && !UP && !SK && BN % 32 == 0 && BN / 32 >= EW / 4), "TMA-store epilogue: plain output");
+  static_assert(!TS || (!UP && !SK && BN % 32 == 0 && (GG ? O16 && BN == 128 : BN / 32 >= EW / 4)), "TMA-store epilogue: plain or GEGLU output");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // work units of the persistent loop: output tiles, or (tile, split) pairs with the split index fastest
   const int ntiles = p.tiles_m * p.tiles_n * (SK ? p.splits : 1);
@@ -404,7 +410,123 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     constexpr bool out16 = O16;
     const bool has_res = !GG && p.residual != nullptr;
     uint32_t t_iter = 0;
-    if constexpr (TS) {
+    if constexpr (RS) {
+      // ---- fp32 residual + bias / uniform row vector: TMA-load / TMA-store epilogue.  Per warp 12 KB: fp32 output = three
+      // 4 KB tiles used IN PLACE (residual lands, every thread adds its row, the same tile is stored); 16-bit output = two
+      // residual tiles + two 2 KB output tiles.  Work items of the warp = its chunks, tile after tile; item i + 1's residual
+      // is requested when item i starts (it does not depend on the accumulator), so the load has a whole chunk to land. ----
+      constexpr int NRB = O16 ? 2 : 3;                                  // residual (fp32: residual == output) tiles
+      uint8_t* stb = reinterpret_cast<uint8_t*>(epi) + ew * 12288;      // 1024-byte aligned
+      uint8_t* outb = stb + 8192;                                       // 16-bit output tiles (2 x 2 KB)
+      uint64_t* rfull = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(epi) + EW * 12288) + ew * 3;
+      if (lane == 0) {
+        for (int b = 0; b < NRB; ++b) mbar_init(&rfull[b], 1);
+        fence_mbar_init();
+        prefetch_tmap(&tmO);
+        prefetch_tmap(&tmR);
+      }
+      __syncwarp();
+      const int sw = lane & 7, sw16 = (lane >> 1) & 3;
+      const int odt = p.out_dtype;
+      uint32_t item = 0;
+      auto request = [&](uint32_t it, int tile_, int cc_) {  // lane 0: residual chunk (tile_, cc_) -> ring slot it % NRB
+        const int tm_ = tile_ / p.tiles_n, tn_ = tile_ - tm_ * p.tiles_n;
+        uint64_t* bar = &rfull[it % NRB];
+        mbar_expect_tx(bar, 4096);
+        tma_load_2d(stb + (it % NRB) * 4096, &tmR, bar, tn_ * BN + cc_ * 32, tm_ * Cfg::BM + qw * 32);
+      };
+      if (par < NCH && (int)blockIdx.x < ntiles && lane == 0) request(0, blockIdx.x, par);
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
+        const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
+        const int m0 = tm * Cfg::BM + qw * 32;
+        const int n0 = tn * BN;
+        const uint32_t buf = t_iter & 1;
+        const float* rvp = p.rowvec ? p.rowvec + (size_t)((tm * Cfg::BM) / p.rows_per_sample) * p.rowvec_ld : nullptr;
+        float4 bq[8];
+        auto load_add = [&](float4 (&b)[8], int cc) {
+          const int col = n0 + cc * 32;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            b[j] = p.bias ? __ldg(reinterpret_cast<const float4*>(p.bias + col) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+            if (rvp) {
+              const float4 r = __ldg(reinterpret_cast<const float4*>(rvp + col) + j);
+              b[j].x += r.x; b[j].y += r.y; b[j].z += r.z; b[j].w += r.w;
+            }
+          }
+        };
+        if (par < NCH) load_add(bq, par);
+        mbar_wait(&tfull[buf], (t_iter >> 1) & 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int cc = par; cc < NCH; cc += CSTEP, ++item) {
+          const bool more = cc + CSTEP < NCH;
+          if (lane == 0) {  // next item's residual
+            const int ntile = more ? tile : tile + (int)gridDim.x, ncc = more ? cc + CSTEP : par;
+            if (ntile < ntiles) {
+              // fp32: the slot was item - 2's tile; its store (one of the last two groups) has finished READING it
+              if constexpr (!O16) tma_store_wait_read<1>();
+              request(item + 1, ntile, ncc);
+            }
+          }
+          float v[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(qw * 32) << 16) + buf * BN + cc * 32, v);
+          float4 bn[8];
+          if (more) load_add(bn, cc + CSTEP);
+          tmem_ld_wait();
+          if (!more) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[buf]);
+          }
+          mbar_wait(&rfull[item % NRB], (item / NRB) & 1);
+          uint8_t* rrow = stb + (item % NRB) * 4096 + lane * 128;
+          if constexpr (O16) {
+            if (lane == 0) tma_store_wait_read<1>();    // the output tile used two items ago has been read
+            __syncwarp();
+            uint8_t* tile_o = outb + (item & 1) * 2048;
+            uint8_t* orow = tile_o + lane * 64;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const float4 r0 = *reinterpret_cast<const float4*>(rrow + (((2 * c) ^ sw) << 4));
+              const float4 r1 = *reinterpret_cast<const float4*>(rrow + (((2 * c + 1) ^ sw) << 4));
+              const float4 b0 = bq[2 * c], b1 = bq[2 * c + 1];
+              uint4 o;
+              o.x = pack16(v[8 * c] + b0.x + r0.x, v[8 * c + 1] + b0.y + r0.y, odt);
+              o.y = pack16(v[8 * c + 2] + b0.z + r0.z, v[8 * c + 3] + b0.w + r0.w, odt);
+              o.z = pack16(v[8 * c + 4] + b1.x + r1.x, v[8 * c + 5] + b1.y + r1.y, odt);
+              o.w = pack16(v[8 * c + 6] + b1.z + r1.z, v[8 * c + 7] + b1.w + r1.w, odt);
+              *reinterpret_cast<uint4*>(orow + ((c ^ sw16) << 4)) = o;
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmO, tile_o, n0 + cc * 32, m0);
+              tma_store_commit();
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              float4* q = reinterpret_cast<float4*>(rrow + ((c ^ sw) << 4));
+              const float4 r = *q;
+              *q = make_float4(v[4 * c] + bq[c].x + r.x, v[4 * c + 1] + bq[c].y + r.y, v[4 * c + 2] + bq[c].z + r.z,
+                               v[4 * c + 3] + bq[c].w + r.w);
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmO, stb + (item % NRB) * 4096, n0 + cc * 32, m0);
+              tma_store_commit();
+            }
+          }
+          if (more) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) bq[j] = bn[j];
+          }
+        }
+      }
+      if (lane == 0) tma_store_wait_all();
+    } else
+    if constexpr (TS && !GG) {
       // ---- bias / uniform row vector only: TMA-store epilogue.  Staging per warp: 16-bit output = two 2 KB tiles (32 rows
       // x 64 B, 64B swizzle), fp32 output = one 4 KB tile (32 rows x 128 B, 128B swizzle); the 16-byte piece c of a row sits
       // at piece c ^ (bits 7.. of the row's shared address), so the row owners' 16-byte writes are bank-conflict-free ----
@@ -500,6 +622,12 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       if (cc < NCH) {
         float va[16], vb[16];  // half h: [8 value | 8 gate] columns 8h..8h+7 and 16+8h..16+8h+7 of the chunk
         const uint32_t lane_base = tmem_base + ((uint32_t)(qw * 32) << 16) + cc * 32;
+        // TS: each half is exactly one 16-byte piece (8 x 16-bit) of the thread's output row: two 1 KB tiles (32 rows x 32 B,
+        // 32B swizzle: piece ^= bit 2 of the row) per warp, one TMA store per chunk instead of the transposing read-back
+        uint8_t* gtile = reinterpret_cast<uint8_t*>(st);
+        [[maybe_unused]] const int gsw = (lane >> 2) & 1;
+        [[maybe_unused]] const int godt = p.out_dtype;
+        if (TS && warp == 2 && lane == 0) prefetch_tmap(&tmO);
         int tile = blockIdx.x;
         if (tile < ntiles) {
           mbar_wait(&tfull[0], 0);
@@ -527,9 +655,20 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
               const f32x2 g2 = add2(pk2(v[8 + j], v[9 + j]), pk2(bb[8 + j], bb[9 + j]));
               unpk2(mul2(val2, gelu_erf_fast2(g2)), o[j], o[j + 1]);
             }
-            *reinterpret_cast<float4*>(&st[lane * PITCH + 8 * h]) = make_float4(o[0], o[1], o[2], o[3]);
-            *reinterpret_cast<float4*>(&st[lane * PITCH + 8 * h + 4]) = make_float4(o[4], o[5], o[6], o[7]);
+            if constexpr (TS) {
+              uint4 u;
+              u.x = pack16(o[0], o[1], godt); u.y = pack16(o[2], o[3], godt);
+              u.z = pack16(o[4], o[5], godt); u.w = pack16(o[6], o[7], godt);
+              *reinterpret_cast<uint4*>(gtile + (t_iter & 1) * 1024 + lane * 32 + ((h ^ gsw) << 4)) = u;
+            } else {
+              *reinterpret_cast<float4*>(&st[lane * PITCH + 8 * h]) = make_float4(o[0], o[1], o[2], o[3]);
+              *reinterpret_cast<float4*>(&st[lane * PITCH + 8 * h + 4]) = make_float4(o[4], o[5], o[6], o[7]);
+            }
           };
+          if constexpr (TS) {  // the store that read this staging tile two tiles ago has finished reading it
+            if (lane == 0) tma_store_wait_read<1>();
+            __syncwarp();
+          }
           half(va, b4, 0);
           const float4 c4[4] = {bp[2], bp[3], bp[6], bp[7]};    // half 1: value biases 8..15, gate biases 24..31
           tmem_ld_wait16(vb);
@@ -543,14 +682,24 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
             tmem_ld_32x8(lane_base + (buf ^ 1) * BN + 16, va + 8);
           }
           half(vb, c4, 1);
-          __syncwarp();
           const int col0 = (n0 >> 1) + cc * 16;
-          const float4 zero_add[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
-          float4 res0[8];
-          if (out16) epi_store<true, 16>(p, st, PITCH, m0, col0, lane, res0, false, zero_add);
-          else epi_store<false, 16>(p, st, PITCH, m0, col0, lane, res0, false, zero_add);
-          __syncwarp();
+          if constexpr (TS) {
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmO, gtile + (t_iter & 1) * 1024, col0, m0);
+              tma_store_commit();
+            }
+          } else {
+            __syncwarp();
+            const float4 zero_add[2] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
+            float4 res0[8];
+            if (out16) epi_store<true, 16>(p, st, PITCH, m0, col0, lane, res0, false, zero_add);
+            else epi_store<false, 16>(p, st, PITCH, m0, col0, lane, res0, false, zero_add);
+            __syncwarp();
+          }
         }
+        if (TS && lane == 0) tma_store_wait_all();
       } else {  // a warp without a chunk (BN == 32): it still hands every accumulator buffer back
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++t_iter) {
           const uint32_t buf = t_iter & 1;
@@ -775,13 +924,13 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   }
 }
 
-template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false, bool TS = false>
+template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false, bool TS = false, bool RS = false>
 static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b, const TcParams& p,
-                     cudaStream_t st, const CUtensorMap* o = nullptr) {
-  using Cfg = TcCfg<BN, BK, EW>;
+                     cudaStream_t st, const CUtensorMap* o = nullptr, const CUtensorMap* r = nullptr) {
+  using Cfg = TcCfg<BN, BK, EW, RS>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::SMEM_BYTES);
     if (e != cudaSuccess) {
       set_error("igemm_tc: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
@@ -790,8 +939,8 @@ static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CU
     attr_set = true;
   }
   int grid = std::min(p.tiles_m * p.tiles_n * (SK ? p.splits : 1), sm_count());
-  cudaError_t le = launch_pdl(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, st, a1,
-                              a2, b, o ? *o : b, p);
+  cudaError_t le = launch_pdl(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS, RS>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, st, a1,
+                              a2, b, o ? *o : b, r ? *r : b, p);
   if (le != cudaSuccess) {
     set_error("igemm_tc: launch failed: %s", cudaGetErrorString(le));
     return LDMB200_ERR_CUDA;
@@ -996,6 +1145,39 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
     if (rc) return rc;
     return out16 ? launch_tc_impl<160, 64, 8, false, true, false, false, true>(tA1, tA2, tB, p, st, &tO)
                  : launch_tc_impl<160, 64, 8, false, false, false, false, true>(tA1, tA2, tB, p, st, &tO);
+  }
+  // ---- the same with an fp32 residual (attn1.to_out, ff.net.2 of the 160-channel level), K <= 640 only: the 96 KB of
+  // staging leave three operand stages.  Measured r02s, same run: M262144 N160 K160 0.926 -> 0.853 ms (10 launches),
+  // N160 K640 0.559 -> 0.529, M65536 N320 K320 0.511 -> 0.486, M16384 N640 K640 0.426 -> 0.412; K = 1280 / 2560 LOSE on
+  // three stages (0.350 -> 0.401, 0.383 -> 0.469 ms) and stay on the per-lane path.
+  static const bool tma_res_on = !(getenv("LDMB200_TMA_RES") && atoi(getenv("LDMB200_TMA_RES")) == 0);
+  if (tma_store_on && tma_res_on && BN == 160 && d->ksize == 1 && d->residual && !d->geglu && (!d->rowvec || p.rowvec_uniform) &&
+      !d->colstats && !d->out_nchw && p.n_valid == d->n && d->out_ld % 8 == 0 && ((uintptr_t)d->out & 15) == 0 &&
+      ((uintptr_t)d->residual & 15) == 0 && d->residual_ld % 4 == 0 && p.ctot <= 640) {
+    CUtensorMap tO, tR;
+    const int eb = out16 ? 2 : 4;
+    uint64_t dims[2] = {(uint64_t)d->n, (uint64_t)p.M};
+    uint64_t str[1] = {(uint64_t)d->out_ld * eb};
+    uint32_t box[2] = {32u, 32u};
+    int rc = make_tensor_map_bf16(&tO, d->out, 2, dims, str, box, out16 ? 64 : 128, eb);
+    if (rc) return rc;
+    uint64_t rstr[1] = {(uint64_t)d->residual_ld * 4};
+    rc = make_tensor_map_bf16(&tR, d->residual, 2, dims, rstr, box, 128, 4);
+    if (rc) return rc;
+    return out16 ? launch_tc_impl<160, 64, 8, false, true, false, false, true, true>(tA1, tA2, tB, p, st, &tO, &tR)
+                 : launch_tc_impl<160, 64, 8, false, false, false, false, true, true>(tA1, tA2, tB, p, st, &tO, &tR);
+  }
+  // ---- GEGLU with a 16-bit output: TMA store of each warp's 32 x 16 chunk
+  static const bool tma_gg_on = !(getenv("LDMB200_TMA_GEGLU") && atoi(getenv("LDMB200_TMA_GEGLU")) == 0);
+  if (tma_store_on && tma_gg_on && BN == 128 && d->geglu && out16 && p.n_valid == d->n / 2 && d->out_ld % 8 == 0 &&
+      ((uintptr_t)d->out & 15) == 0) {
+    CUtensorMap tO;
+    uint64_t dims[2] = {(uint64_t)(d->n / 2), (uint64_t)p.M};
+    uint64_t str[1] = {(uint64_t)d->out_ld * 2};
+    uint32_t box[2] = {16u, 32u};
+    int rc = make_tensor_map_bf16(&tO, d->out, 2, dims, str, box, 32, 2);
+    if (rc) return rc;
+    return launch_tc_impl<128, 64, 16, true, true, false, false, true>(tA1, tA2, tB, p, st, &tO);
   }
   if (BN == 128) return d->geglu ? launch_tc<128, 64, 16, true>(tA1, tA2, tB, p, st) : launch_tc<128, 64, 16>(tA1, tA2, tB, p, st);
   LDM_CHECK_ARG(!d->geglu || d->n % 32 == 0, "igemm_tc: geglu needs n %% 32 == 0 (got n=%d)", d->n);

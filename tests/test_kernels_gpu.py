@@ -301,30 +301,51 @@ def test_tc_epilogues():
     assert K.rel_l2(out, K.igemm_reference(x, bf(wo), bo)) <= 1e-5
 
 
-@pytest.mark.parametrize("B,H,c,n,ksize,bias,rowvec", [
-    (2, 16, 160, 480, 1, True, False),      # fused QKV of the 160-channel level
-    (3, 8, 160, 480, 1, True, False),       # M = 192: ragged last tile, rows 192..255 must be clipped by the TMA store
-    (1, 8, 320, 960, 1, False, False),      # M = 64 < one tile, no bias
-    (2, 16, 96, 160, 3, True, True),        # 3x3 convolution + per-sample row vector (hw = 256: uniform per tile)
-    (3, 8, 96, 160, 3, True, True),         # hw = 64: a tile spans two samples -> the launcher keeps the per-lane store path
-    (5, 16, 640, 1920, 1, True, False),     # M = 1280, 12 N tiles: several tiles per CTA through both staging tiles
+@pytest.mark.parametrize("rows,cc", [(512, 160), (200, 160), (20480, 320), (64, 640)])
+def test_tc_geglu_tma_store(rows, cc):
+    """GEGLU epilogue with a 16-bit output (TMA store of each warp's 32 x 16 chunk, 32B-swizzled staging) == the fp32-output
+    epilogue (per-lane stores) rounded to the same type, bit for bit; ragged last tile clipped (harness guard rows)."""
+    xg = bf(rnd(rows, cc))
+    wg, bg = rnd(8 * cc, cc, 1, 1, scale=cc ** -0.5), rnd(8 * cc)
+    out32 = K.igemm("tc", xg.to(torch.bfloat16), 1, rows, 1, wg, bg, geglu=True, out_dtype=F32)
+    y = F.linear(xg.double(), bf(wg.reshape(8 * cc, cc)).double(), bg.double())
+    va, ga = y.chunk(2, dim=1)
+    assert K.rel_l2(out32, (va * F.gelu(ga)).float()) <= OUT_TOL[F32]
+    for odt, tdt in ((BF16, torch.bfloat16), (F16, torch.float16)):
+        out = K.igemm("tc", xg.to(torch.bfloat16), 1, rows, 1, wg, bg, geglu=True, out_dtype=odt)
+        assert torch.equal(out, out32.to(tdt))
+
+
+@pytest.mark.parametrize("B,H,c,n,ksize,bias,rowvec,res", [
+    (2, 16, 160, 480, 1, True, False, False),      # fused QKV of the 160-channel level
+    (3, 8, 160, 480, 1, True, False, False),       # M = 192: ragged last tile, rows 192..255 must be clipped by the TMA store
+    (1, 8, 320, 960, 1, False, False, False),      # M = 64 < one tile, no bias
+    (2, 16, 96, 160, 3, True, True, False),        # 3x3 convolution + per-sample row vector (hw = 256: uniform per tile)
+    (3, 8, 96, 160, 3, True, True, False),         # hw = 64: a tile spans two samples -> the launcher keeps the per-lane store path
+    (5, 16, 640, 1920, 1, True, False, False),     # M = 1280, 12 N tiles: several tiles per CTA through both staging tiles
+    (2, 16, 160, 160, 1, True, True, True),        # attn1.to_out: + cross-attention row vector + fp32 residual (TMA-loaded ring)
+    (3, 8, 640, 160, 1, True, False, True),        # ff.net.2 of the 160 level, ragged last tile: residual rows past M are zero-filled
+    (40, 32, 320, 320, 1, True, True, True),       # M = 40960 = 320 x 2 tiles on 148 CTAs: the ring wraps across tiles
+    (1, 8, 2560, 640, 1, True, False, True),       # ff.net.2 of the 640 level: K > 640 stays on the per-lane path
 ])
-def test_tc_tma_store_epilogue(B, H, c, n, ksize, bias, rowvec):
-    """Outputs with only a bias / per-tile row vector to add and no statistics take the TMA-store epilogue
-    (igemm_tc_kernel<..., TS>): fp32 bit-identical to the per-lane store path (forced by asking for column statistics),
-    16-bit bit-identical to that rounded to the same type, nothing written past row M (harness guard rows)."""
+def test_tc_tma_store_epilogue(B, H, c, n, ksize, bias, rowvec, res):
+    """Outputs with only a bias / per-tile row vector (and, for linears, an fp32 residual) to add and no statistics take the
+    TMA-store epilogue (igemm_tc_kernel<..., TS[, RS]>): fp32 bit-identical to the per-lane store path (forced by asking for
+    column statistics), 16-bit bit-identical to that rounded to the same type, nothing written past row M (guard rows)."""
     hw = H * H
     a = bf(rnd(B * hw, c)).to(torch.bfloat16)
     w, b = rnd(n, c, ksize, ksize, scale=(ksize * ksize * c) ** -0.5), (rnd(n) if bias else None)
     rv = rnd(B, n) if rowvec else None
+    rs = rnd(B * hw, n) + 0.25 if res else None
     cs = torch.empty(B * hw // 32, n, 2, device=a.device)
-    old32 = K.igemm("tc", a, B, H, H, w, b, ksize=ksize, rowvec=rv, colstats=cs)      # per-lane store path
-    new32 = K.igemm("tc", a, B, H, H, w, b, ksize=ksize, rowvec=rv)
+    old32 = K.igemm("tc", a, B, H, H, w, b, ksize=ksize, rowvec=rv, residual=rs, colstats=cs)      # per-lane store path
+    new32 = K.igemm("tc", a, B, H, H, w, b, ksize=ksize, rowvec=rv, residual=rs)
     assert torch.equal(new32, old32)
-    tgt = K.to_cl(K.igemm_reference(K.from_cl(a.float(), B, H, H), bf(w), b, rowvec=rv))
+    tgt = K.to_cl(K.igemm_reference(K.from_cl(a.float(), B, H, H), bf(w), b, rowvec=rv,
+                                    residual_nchw=K.from_cl(rs, B, H, H) if res else None))
     assert K.rel_l2(new32, tgt) <= 1e-5
     for odt, tdt in ((BF16, torch.bfloat16), (F16, torch.float16)):
-        out = K.igemm("tc", a, B, H, H, w, b, ksize=ksize, rowvec=rv, out_dtype=odt)
+        out = K.igemm("tc", a, B, H, H, w, b, ksize=ksize, rowvec=rv, residual=rs, out_dtype=odt)
         assert out.dtype == tdt and torch.equal(out, old32.to(tdt))
 
 

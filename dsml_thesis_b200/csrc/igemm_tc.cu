@@ -71,16 +71,19 @@ struct TcParams {
 
 // RS: the TMA-store epilogue with an fp32 residual (igemm_tc_kernel<..., TS, RS>): 12 KB of residual / output staging
 // tiles per epilogue warp instead of the 4.5 KB transpose tile, paid for with two operand stages (K <= 640 linears only).
-template <int BN, int BK, int EW, bool RS = false>
+// C2: CTA pair (cta_group::2, M = 256 per MMA): each CTA stages its own A rows and HALF of the B tile -> 26 KB instead of
+// 36 KB per stage through each SM's L2 port, and seven stages instead of five.
+template <int BN, int BK, int EW, bool RS = false, bool C2 = false>
 struct TcCfg {
   static constexpr int THREADS = 64 + EW * 32;
   static constexpr int BM = 128;
   static constexpr int SW = BK * 2;  // swizzle span in bytes == one K-major row
   static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int B_BYTES = ((BN * BK * 2 + 1023) / 1024) * 1024;
+  static constexpr int BN_CTA = C2 ? BN / 2 : BN;          // B rows staged by one CTA
+  static constexpr int B_BYTES = ((BN_CTA * BK * 2 + 1023) / 1024) * 1024;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = RS ? 3 : (BN >= 128) ? (EW > 8 ? 4 : 5) : 8;
-  static constexpr int TX_BYTES = BM * BK * 2 + BN * BK * 2;
+  static constexpr int STAGES = C2 ? 7 : RS ? 3 : (BN >= 128) ? (EW > 8 ? 4 : 5) : 8;
+  static constexpr int TX_BYTES = (BM * BK * 2 + BN_CTA * BK * 2) * (C2 ? 2 : 1);   // C2: both CTAs' bytes land on rank 0's barrier
   static constexpr int EPI_PITCH = 36;  // floats; 144 B row pitch: conflict-free 16 B row-owner writes + row reads
   static constexpr int EPI_BYTES = RS ? EW * 12288 + 256 : EW * 32 * EPI_PITCH * 4;
   static constexpr int TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64) ? 64 : (2 * BN <= 128) ? 128 : (2 * BN <= 256) ? 256 : 512;
@@ -228,13 +231,16 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
 // (tmO) moves the tile — no transposing read-back through shared memory, no per-lane global stores.
 // RS (with TS): + an fp32 residual, TMA-loaded into a per-warp ring of swizzled tiles one chunk ahead (tmR); every thread adds
 // its own row in shared memory and the tile goes out through the TMA store — attn1.to_out, ff.net.2 (no statistics).
-template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false, bool TS = false, bool RS = false>
+// C2: CTA-pair main loop (launched as 2-clusters; plain epilogue only): unit = a pair of vertically adjacent M tiles.
+template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false, bool TS = false, bool RS = false,
+          bool C2 = false>
 __global__ void __launch_bounds__(64 + EW * 32, 1)
 igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                 const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
                 const __grid_constant__ CUtensorMap tmR, const TcParams p) {
-  using Cfg = TcCfg<BN, BK, EW, RS>;
+  using Cfg = TcCfg<BN, BK, EW, RS, C2>;
   static_assert(!RS || TS, "RS extends the TMA-store epilogue");
+  static_assert(!C2 || (!GG && !UP && !SK && !TS && BN % 32 == 0), "CTA pair: plain epilogue");
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment as an OFFSET from the shared array (not through uintptr_t): the compiler keeps the shared address
   // space and emits STS / LDS for the epilogue's staging tile instead of generic ST / LD
@@ -252,7 +258,11 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   static_assert(!TS || (!UP && !SK && BN % 32 == 0 && (GG ? O16 && BN == 128 : BN / 32 >= EW / 4)), "TMA-store epilogue: plain or GEGLU output");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // work units of the persistent loop: output tiles, or (tile, split) pairs with the split index fastest
-  const int ntiles = p.tiles_m * p.tiles_n * (SK ? p.splits : 1);
+  // (C2: units are PAIRS of M tiles — tiles_m is even — walked by the cluster; rank r takes the pair's r-th tile)
+  const int ntiles = C2 ? (p.tiles_m >> 1) * p.tiles_n : p.tiles_m * p.tiles_n * (SK ? p.splits : 1);
+  const int crank = C2 ? (int)cluster_ctarank() : 0;
+  const int unit0 = C2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, ustep = C2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  auto pair_tile = [&](int unit) { return (2 * (unit / p.tiles_n) + crank) * p.tiles_n + unit % p.tiles_n; };
 
   if (p.pf_bytes && warp == 2 && lane == 0) {
     // constant data, nothing of the predecessor is touched: issued before the dependency wait.  CTA b takes slice b.
@@ -276,15 +286,17 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       }
       for (int b = 0; b < 2; ++b) {
         mbar_init(&tfull[b], 1);
-        mbar_init(&tempty[b], EW);
+        mbar_init(&tempty[b], C2 ? 2 * EW : EW);   // C2: rank 0's barrier collects both CTAs' epilogue warps
       }
       fence_mbar_init();
     }
     __syncwarp();
-    tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    if constexpr (C2) tmem_alloc_pair(tmem_slot, Cfg::TMEM_COLS);
+    else tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
   }
   tc_fence_before();
   __syncthreads();
+  if constexpr (C2) cluster_sync_all();   // the peer's barriers exist before anything is signalled across the pair
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();  // the predecessor's writes (activations, packed weights, residual, statistics buffers) are visible from here
@@ -297,8 +309,9 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     // (a single-thread producer / MMA loop with running stage counters was measured r02l and is SLOWER: big-K convolutions
     // 0.753 -> 0.934 ms at K = 5760, implicit GEMMs 13.6 -> 14.9 ms per eval; the converged-warp form stays)
     uint32_t it = 0;
-    for (int unit = blockIdx.x; unit < ntiles; unit += gridDim.x) {
-      const int tile = SK ? unit / p.splits : unit;
+    [[maybe_unused]] const uint32_t full0 = C2 ? mapa_u32(smem_u32(full), 0) : 0u;   // rank 0's full[] barriers
+    for (int unit = unit0; unit < ntiles; unit += ustep) {
+      const int tile = C2 ? pair_tile(unit) : SK ? unit / p.splits : unit;
       const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
       const int m0 = tm * Cfg::BM;
       // this unit's range [k0, k1) of the flattened (tap, chunk) iterations
@@ -341,22 +354,33 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
           const uint32_t ph_ = (it / Cfg::STAGES) & 1;
           mbar_wait(&empty[s], ph_ ^ 1);
           if (elect_one()) {
-            mbar_expect_tx(&full[s], Cfg::TX_BYTES);
             const bool second = j >= p.c1_chunks;
             const CUtensorMap* tm_a = second ? &tmA2 : &tmA1;
             const int c0 = (second ? j - p.c1_chunks : j) * BK;
+            if constexpr (C2) {
+              if (crank == 0) mbar_expect_tx(&full[s], Cfg::TX_BYTES);
+              const uint32_t bar = full0 + s * 8;
+              if (p.is_conv)
+                tma_load_5d_pair(sA + s * Cfg::A_BYTES, tm_a, bar, c0, w0 + dw, h0 + dh, plane, n_img);
+              else
+                tma_load_5d_pair(sA + s * Cfg::A_BYTES, tm_a, bar, c0, 0, m0, 0, 0);
+              tma_load_2d_pair(sB + s * Cfg::B_BYTES, &tmB, bar, tap * p.ctot + (second ? p.c1 : 0) + c0,
+                               p.b_row0 + tn * BN + crank * (BN / 2));
+            } else {
+            mbar_expect_tx(&full[s], Cfg::TX_BYTES);
             if (p.is_conv)
               tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, w0 + dw, h0 + dh, plane, n_img);
             else
               tma_load_5d(sA + s * Cfg::A_BYTES, tm_a, &full[s], c0, 0, m0, 0, 0);
             tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &full[s], tap * p.ctot + (second ? p.c1 : 0) + c0, p.b_row0 + tn * BN);
+            }
           }
           __syncwarp();
         }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (whole warp converged, one elected lane issues) =====================
+  } else if (warp == 1 && (!C2 || crank == 0)) {
+    // ===================== MMA issuer (whole warp converged, one elected lane issues; C2: rank 0 for the pair) ==========
     // descriptors: the high word is constant, the low word is (address >> 4) | LBO; K advances by 32 B = +2
     constexpr uint32_t desc_hi = (uint32_t)((8u * Cfg::SW) >> 4) | (1u << 14) | ((Cfg::SW == 128 ? 2u : 4u) << 29);
     const uint32_t a_lo0 = ((smem_u32(sA) & 0x3FFFFu) >> 4) | (1u << 16);
@@ -364,7 +388,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     const uint32_t idesc = p.idesc;
     const int kmax1 = p.c1_tail_k, kmax2 = p.c2_tail_k;
     uint32_t it = 0, t_iter = 0;
-    for (int unit = blockIdx.x; unit < ntiles; unit += gridDim.x, ++t_iter) {
+    for (int unit = unit0; unit < ntiles; unit += ustep, ++t_iter) {
       const uint32_t buf = t_iter & 1;
       mbar_wait(&tempty[buf], ((t_iter >> 1) & 1) ^ 1);
       tc_fence_after();
@@ -384,21 +408,29 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
 #pragma unroll
             for (int kk = 0; kk < BK / 16; ++kk) {
               if (kk < kmax) {
+                if constexpr (C2)
+                  umma_bf16_ss_pair(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo + 2 * kk),
+                                    ((uint64_t)desc_hi << 32) | (b_lo + 2 * kk), idesc, acc);
+                else
                 umma_bf16_ss(d_tmem, ((uint64_t)desc_hi << 32) | (a_lo + 2 * kk), ((uint64_t)desc_hi << 32) | (b_lo + 2 * kk),
                              idesc, acc);
                 acc = 1;
               }
             }
-            umma_commit(&empty[s]);  // frees the smem stage once these MMAs retire
+            if constexpr (C2) umma_commit_pair(&empty[s]);  // frees the stage in BOTH CTAs
+            else umma_commit(&empty[s]);  // frees the smem stage once these MMAs retire
           }
           __syncwarp();
           acc = 1;
         }
       }
-      if (elect_one()) umma_commit(&tfull[buf]);  // accumulator complete -> epilogue
+      if (elect_one()) {  // accumulator complete -> epilogue (C2: of both CTAs)
+        if constexpr (C2) umma_commit_pair(&tfull[buf]);
+        else umma_commit(&tfull[buf]);
+      }
       __syncwarp();
     }
-  } else {
+  } else if (warp >= 2) {
     // ===================== epilogue (EW warps) =====================
     const int ew = warp - 2;
     const int qw = warp & 3;          // TMEM lane quarter accessible to this warp (hardware: warp id % 4)
@@ -410,6 +442,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     constexpr bool out16 = O16;
     const bool has_res = !GG && p.residual != nullptr;
     uint32_t t_iter = 0;
+    [[maybe_unused]] const uint32_t tempty0 = C2 ? mapa_u32(smem_u32(tempty), 0) : 0u;   // rank 0's tempty[] barriers
     if constexpr (RS) {
       // ---- fp32 residual + bias / uniform row vector: TMA-load / TMA-store epilogue.  Per warp 12 KB: fp32 output = three
       // 4 KB tiles used IN PLACE (residual lands, every thread adds its row, the same tile is stored); 16-bit output = two
@@ -710,8 +743,8 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
         }
       }
     } else
-    for (int unit = blockIdx.x; unit < ntiles; unit += gridDim.x, ++t_iter) {
-      const int tile = SK ? unit / p.splits : unit;
+    for (int unit = unit0; unit < ntiles; unit += ustep, ++t_iter) {
+      const int tile = C2 ? pair_tile(unit) : SK ? unit / p.splits : unit;
       const int tm = tile / p.tiles_n, tn = tile % p.tiles_n;
       const int m0 = tm * Cfg::BM + qw * 32;
       const int n0 = tn * BN;
@@ -760,8 +793,8 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       // residual per tile with at most one 4 KB chunk per warp in flight = 7.4 us per tile): pull the NEXT tile's
       // residual rows into L2 now, a whole tile time ahead; fire-and-forget, no registers held.
       if (!SK && has_res) {
-        const int tile_n = tile + gridDim.x;
-        if (tile_n < ntiles) {
+        const int tile_n = C2 ? pair_tile(unit + ustep) : tile + (int)gridDim.x;
+        if (unit + ustep < ntiles) {
           const int m = (tile_n / p.tiles_n) * Cfg::BM + qw * 32 + lane;
           if (m < p.M) {
             const char* rp = reinterpret_cast<const char*>(p.residual + (size_t)m * p.residual_ld + (tile_n % p.tiles_n) * BN);
@@ -847,7 +880,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
           if (!more) {  // last TMEM read of this warp for this tile: hand the accumulator buffer back early
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[buf]);
+            if (lane == 0) { if constexpr (C2) mbar_arrive_cluster(tempty0 + buf * 8); else mbar_arrive(&tempty[buf]); }
           }
         }
         if (!GG && !O16 && p.out_nchw) {
@@ -910,7 +943,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       if (!SK && cc_first >= NCH) {  // this warp had no chunk in the tile (BN == CH): still release the buffer
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty[buf]);
+        if (lane == 0) { if constexpr (C2) mbar_arrive_cluster(tempty0 + buf * 8); else mbar_arrive(&tempty[buf]); }
       }
     }
   }
@@ -918,19 +951,22 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
   pdl_launch_dependents();  // PDL (opt-in): this CTA's work is issued; the successor may start being scheduled
   tc_fence_before();
   __syncthreads();
+  if constexpr (C2) cluster_sync_all();   // the peer has finished reading this CTA's operands and signalling its barriers
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    if constexpr (C2) tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS);
+    else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
   }
 }
 
-template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false, bool TS = false, bool RS = false>
+template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false, bool TS = false, bool RS = false,
+          bool C2 = false>
 static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& b, const TcParams& p,
                      cudaStream_t st, const CUtensorMap* o = nullptr, const CUtensorMap* r = nullptr) {
-  using Cfg = TcCfg<BN, BK, EW, RS>;
+  using Cfg = TcCfg<BN, BK, EW, RS, C2>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS, RS, C2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          Cfg::SMEM_BYTES);
     if (e != cudaSuccess) {
       set_error("igemm_tc: cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
@@ -939,7 +975,26 @@ static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CU
     attr_set = true;
   }
   int grid = std::min(p.tiles_m * p.tiles_n * (SK ? p.splits : 1), sm_count());
-  cudaError_t le = launch_pdl(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS, RS>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, st, a1,
+  cudaError_t le;
+  if constexpr (C2) {  // 2-clusters: one per pair of M tiles, at most one per pair of SMs
+    grid = 2 * std::min((p.tiles_m / 2) * p.tiles_n, sm_count() / 2);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(Cfg::THREADS);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 2;
+    le = cudaLaunchKernelEx(&cfg, igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS, RS, C2>, a1, a2, b, b, b, p);
+  } else
+  le = launch_pdl(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS, RS>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, st, a1,
                               a2, b, o ? *o : b, r ? *r : b, p);
   if (le != cudaSuccess) {
     set_error("igemm_tc: launch failed: %s", cudaGetErrorString(le));
@@ -1178,6 +1233,20 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
     int rc = make_tensor_map_bf16(&tO, d->out, 2, dims, str, box, 32, 2);
     if (rc) return rc;
     return launch_tc_impl<128, 64, 16, true, true, false, false, true>(tA1, tA2, tB, p, st, &tO);
+  }
+  // ---- CTA pair (cta_group::2, M = 256): the deep reductions (3x3 convolutions, K >= 1280 linears) on 160-wide tiles
+  static const int c2_on = getenv("LDMB200_C2") ? atoi(getenv("LDMB200_C2")) : 1;
+  static const int c2_mink = getenv("LDMB200_C2_MINK") ? atoi(getenv("LDMB200_C2_MINK")) : 1280;
+  if (c2_on && BN == 160 && !d->geglu && !d->out_nchw && p.tiles_m % 2 == 0 && p.taps * p.ctot >= c2_mink && sm_count() >= 2) {
+    CUtensorMap tBh;  // half of the B tile per CTA
+    uint64_t dims[2] = {(uint64_t)p.taps * p.ctot, (uint64_t)d->n};
+    uint64_t str[1] = {(uint64_t)p.taps * p.ctot * 2};
+    uint32_t box[2] = {(uint32_t)BK, (uint32_t)(BN / 2)};
+    int rc = make_tensor_map_bf16(&tBh, d->w, 2, dims, str, box, BK * 2);
+    if (rc) return rc;
+    p.idesc = umma_idesc_f16(256, BN, d->a_dtype == LDMB200_F16 ? 0 : 1);
+    return out16 ? launch_tc_impl<160, 64, 8, false, true, false, false, false, false, true>(tA1, tA2, tBh, p, st)
+                 : launch_tc_impl<160, 64, 8, false, false, false, false, false, false, true>(tA1, tA2, tBh, p, st);
   }
   if (BN == 128) return d->geglu ? launch_tc<128, 64, 16, true>(tA1, tA2, tB, p, st) : launch_tc<128, 64, 16>(tA1, tA2, tB, p, st);
   LDM_CHECK_ARG(!d->geglu || d->n % 32 == 0, "igemm_tc: geglu needs n %% 32 == 0 (got n=%d)", d->n);

@@ -301,6 +301,45 @@ def test_tc_epilogues():
     assert K.rel_l2(out, K.igemm_reference(x, bf(wo), bo)) <= 1e-5
 
 
+@pytest.mark.parametrize("B,H,c1,c2,n,ksize,stride,extras", [
+    (1, 16, 160, 0, 160, 3, 1, "res+rowvec+stats"),     # M = 256: one pair of M tiles, K = 1440 with a partial last chunk
+    (8, 32, 320, 0, 320, 3, 1, "res+stats"),            # M = 8192: 32 pairs x 2 N tiles
+    (2, 16, 640, 320, 320, 3, 1, "rowvec+stats"),       # virtual concat (second tensor map), K = 8640
+    (4, 32, 160, 0, 160, 3, 2, "stats"),                # stride 2 on the space-to-depth planes (M = 1024)
+    (2, 16, 2560, 0, 640, 1, 1, "res+f16out"),          # ff.net.2 of the 640 level: linear, K = 2560, 16-bit output
+    (40, 32, 160, 0, 160, 3, 1, "res+rowvec+stats"),    # M = 40960: 160 pairs on 74 clusters — the pipeline wraps across units
+])
+def test_tc_cta_pair(B, H, c1, c2, n, ksize, stride, extras):
+    """The CTA-pair main loop (cta_group::2, M = 256 per MMA, half of the weight tile per CTA; taken for K >= 1280 on an even
+    number of M tiles) against the float64 convolution of the same bf16-rounded operands, every fused epilogue term on."""
+    x1, x2 = bf(rnd(B, c1, H, H)), (bf(rnd(B, c2, H, H)) if c2 else None)
+    c = c1 + c2
+    w, b = rnd(n, c, ksize, ksize, scale=(ksize * ksize * c) ** -0.5), rnd(n)
+    Ho = H // stride
+    M = B * Ho * Ho
+    assert (M + 127) // 128 % 2 == 0 and ksize * ksize * c >= 1280, "shape would not take the CTA-pair path"
+    kw = dict(ksize=ksize, stride=stride)
+    res = rnd(B, n, Ho, Ho) + 0.3 if "res" in extras else None
+    rv = rnd(B, n) if "rowvec" in extras else None
+    cs = torch.full((M // 32, n, 2), float("nan"), device=K.DEV) if "stats" in extras else None
+    odt = F16 if "f16out" in extras else F32
+    if stride == 2:
+        a = K.space_to_depth(x1, torch.bfloat16)
+    else:
+        a = K.to_cl(x1, torch.bfloat16)
+    a2 = K.to_cl(x2, torch.bfloat16) if c2 else None
+    outs = [K.igemm("tc", a, B, H, H, w, b, a2=a2, rowvec=rv, residual=K.to_cl(res) if res is not None else None,
+                    colstats=cs, out_dtype=odt, **kw) for _ in range(2)]
+    assert torch.equal(outs[0], outs[1])
+    xin = torch.cat([x1, x2], 1) if c2 else x1
+    ref = K.to_cl(K.igemm_reference(xin, bf(w), b, stride=stride, rowvec=rv, residual_nchw=res))
+    assert K.rel_l2(outs[0].float(), ref) <= (OUT_TOL[F16] if odt == F16 else 1e-5)
+    if cs is not None:
+        blk = outs[0].reshape(M // 32, 32, n).double()
+        assert K.rel_l2(cs[..., 0], blk.sum(1).float()) <= 1e-5
+        assert K.rel_l2(cs[..., 1], (blk * blk).sum(1).float()) <= 1e-5
+
+
 @pytest.mark.parametrize("rows,cc", [(512, 160), (200, 160), (20480, 320), (64, 640)])
 def test_tc_geglu_tma_store(rows, cc):
     """GEGLU epilogue with a 16-bit output (TMA store of each warp's 32 x 16 chunk, 32B-swizzled staging) == the fp32-output

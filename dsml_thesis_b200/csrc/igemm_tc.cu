@@ -1236,8 +1236,13 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
   }
   // ---- CTA pair (cta_group::2, M = 256): the deep reductions (3x3 convolutions, K >= 1280 linears) on 160-wide tiles
   static const int c2_on = getenv("LDMB200_C2") ? atoi(getenv("LDMB200_C2")) : 1;
-  static const int c2_mink = getenv("LDMB200_C2_MINK") ? atoi(getenv("LDMB200_C2_MINK")) : 1280;
-  if (c2_on && BN == 160 && !d->geglu && !d->out_nchw && p.tiles_m % 2 == 0 && p.taps * p.ctot >= c2_mink && sm_count() >= 2) {
+  // Measured r02s (same run, one eval at batch 64): 25.41 -> 24.91 ms with K >= 1280, 24.78 with K >= 640 (every shape gains
+  // 3-12 %: N=160 K=1440 757 -> 854 TFLOP/s).  Below two waves of tiles the pairs lose (batch 1-8: +2 % per eval: half as
+  // many independent schedulable units and a cluster barrier at both ends), so small grids stay on single CTAs.
+  static const int c2_mink = getenv("LDMB200_C2_MINK") ? atoi(getenv("LDMB200_C2_MINK")) : 640;
+  static const int c2_waves = getenv("LDMB200_C2_WAVES") ? atoi(getenv("LDMB200_C2_WAVES")) : 2;
+  if (c2_on && BN == 160 && !d->geglu && !d->out_nchw && p.tiles_m % 2 == 0 && p.taps * p.ctot >= c2_mink && sm_count() >= 2 &&
+      p.tiles_m * p.tiles_n >= c2_waves * sm_count()) {
     CUtensorMap tBh;  // half of the B tile per CTA
     uint64_t dims[2] = {(uint64_t)p.taps * p.ctot, (uint64_t)d->n};
     uint64_t str[1] = {(uint64_t)p.taps * p.ctot * 2};

@@ -302,22 +302,24 @@ def test_tc_epilogues():
 
 
 @pytest.mark.parametrize("B,H,c1,c2,n,ksize,stride,extras", [
-    (1, 16, 160, 0, 160, 3, 1, "res+rowvec+stats"),     # M = 256: one pair of M tiles, K = 1440 with a partial last chunk
-    (8, 32, 320, 0, 320, 3, 1, "res+stats"),            # M = 8192: 32 pairs x 2 N tiles
-    (2, 16, 640, 320, 320, 3, 1, "rowvec+stats"),       # virtual concat (second tensor map), K = 8640
-    (4, 32, 160, 0, 160, 3, 2, "stats"),                # stride 2 on the space-to-depth planes (M = 1024)
-    (2, 16, 2560, 0, 640, 1, 1, "res+f16out"),          # ff.net.2 of the 640 level: linear, K = 2560, 16-bit output
-    (40, 32, 160, 0, 160, 3, 1, "res+rowvec+stats"),    # M = 40960: 160 pairs on 74 clusters — the pipeline wraps across units
+    (40, 32, 160, 0, 160, 3, 1, "res+rowvec+stats"),    # M = 40960: 160 pairs on 74 clusters, K = 1440 with a partial last chunk
+    (40, 32, 320, 0, 320, 3, 1, "res+stats"),           # two N tiles per pair, K = 2880
+    (20, 32, 320, 160, 320, 3, 1, "rowvec+stats"),      # virtual concat (second tensor map), K = 4320
+    (40, 64, 160, 0, 160, 3, 2, "stats"),               # stride 2 on the space-to-depth planes
+    (40, 16, 2560, 0, 640, 1, 1, "res+f16out"),         # ff.net.2 of the 640 level: linear, K = 2560, 16-bit output
+    (1, 101, 1280, 0, 640, 1, 1, "res"),                # M = 10201: ragged last tile of the last pair
+    (40, 16, 640, 0, 640, 1, 1, "res+stats"),           # proj_out of the 640 level: K = 640, the shallowest reduction taken
 ])
 def test_tc_cta_pair(B, H, c1, c2, n, ksize, stride, extras):
-    """The CTA-pair main loop (cta_group::2, M = 256 per MMA, half of the weight tile per CTA; taken for K >= 1280 on an even
-    number of M tiles) against the float64 convolution of the same bf16-rounded operands, every fused epilogue term on."""
+    """The CTA-pair main loop (cta_group::2, M = 256 per MMA, half of the weight tile per CTA; taken for K >= 640 on an even
+    number of M tiles filling at least two waves of the SMs) against the float64 convolution of the same bf16-rounded operands, every fused epilogue term on."""
     x1, x2 = bf(rnd(B, c1, H, H)), (bf(rnd(B, c2, H, H)) if c2 else None)
     c = c1 + c2
     w, b = rnd(n, c, ksize, ksize, scale=(ksize * ksize * c) ** -0.5), rnd(n)
     Ho = H // stride
     M = B * Ho * Ho
-    assert (M + 127) // 128 % 2 == 0 and ksize * ksize * c >= 1280, "shape would not take the CTA-pair path"
+    tiles_m = (M + 127) // 128
+    assert tiles_m % 2 == 0 and ksize * ksize * c >= 640 and tiles_m * (n // 160) >= 2 * 148, "shape would not take the CTA-pair path"
     kw = dict(ksize=ksize, stride=stride)
     res = rnd(B, n, Ho, Ho) + 0.3 if "res" in extras else None
     rv = rnd(B, n) if "rowvec" in extras else None

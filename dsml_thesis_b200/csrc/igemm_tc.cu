@@ -82,7 +82,7 @@ struct TcCfg {
   static constexpr int BN_CTA = C2 ? BN / 2 : BN;          // B rows staged by one CTA
   static constexpr int B_BYTES = ((BN_CTA * BK * 2 + 1023) / 1024) * 1024;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = C2 ? 7 : RS ? 3 : (BN >= 128) ? (EW > 8 ? 4 : 5) : 8;
+  static constexpr int STAGES = C2 ? (EW > 8 ? 6 : 7) : RS ? 3 : (BN >= 128) ? (EW > 8 ? 4 : 5) : 8;
   static constexpr int TX_BYTES = (BM * BK * 2 + BN_CTA * BK * 2) * (C2 ? 2 : 1);   // C2: both CTAs' bytes land on rank 0's barrier
   static constexpr int EPI_PITCH = 36;  // floats; 144 B row pitch: conflict-free 16 B row-owner writes + row reads
   static constexpr int EPI_BYTES = RS ? EW * 12288 + 256 : EW * 32 * EPI_PITCH * 4;
@@ -240,7 +240,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
                 const __grid_constant__ CUtensorMap tmR, const TcParams p) {
   using Cfg = TcCfg<BN, BK, EW, RS, C2>;
   static_assert(!RS || TS, "RS extends the TMA-store epilogue");
-  static_assert(!C2 || (!GG && !UP && !SK && !TS && BN % 32 == 0), "CTA pair: plain epilogue");
+  static_assert(!C2 || (!UP && !SK && !RS && BN % 32 == 0 && (GG ? TS : !TS)), "CTA pair: plain epilogue, or GEGLU with the TMA store");
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment as an OFFSET from the shared array (not through uintptr_t): the compiler keeps the shared address
   // space and emits STS / LDS for the epilogue's staging tile instead of generic ST / LD
@@ -661,14 +661,15 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
         [[maybe_unused]] const int gsw = (lane >> 2) & 1;
         [[maybe_unused]] const int godt = p.out_dtype;
         if (TS && warp == 2 && lane == 0) prefetch_tmap(&tmO);
-        int tile = blockIdx.x;
-        if (tile < ntiles) {
+        int unit = unit0;
+        if (unit < ntiles) {
           mbar_wait(&tfull[0], 0);
           tc_fence_after();
           tmem_ld_32x8(lane_base, va);
           tmem_ld_32x8(lane_base + 16, va + 8);
         }
-        for (; tile < ntiles; tile += gridDim.x, ++t_iter) {
+        for (; unit < ntiles; unit += ustep, ++t_iter) {
+          const int tile = C2 ? pair_tile(unit) : unit;
           const int tm = tile / p.tiles_n, tn = tile - tm * p.tiles_n;
           const int m0 = tm * Cfg::BM + qw * 32;
           const int n0 = tn * BN;
@@ -707,8 +708,8 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
           tmem_ld_wait16(vb);
           tc_fence_before();                                    // the whole chunk has left tensor memory
           __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty[buf]);
-          if (tile + (int)gridDim.x < ntiles) {                 // next tile's half 0 (other buffer) during half 1's GELUs
+          if (lane == 0) { if constexpr (C2) mbar_arrive_cluster(tempty0 + buf * 8); else mbar_arrive(&tempty[buf]); }
+          if (unit + ustep < ntiles) {                          // next tile's half 0 (other buffer) during half 1's GELUs
             mbar_wait(&tfull[buf ^ 1], ((t_iter + 1) >> 1) & 1);
             tc_fence_after();
             tmem_ld_32x8(lane_base + (buf ^ 1) * BN, va);
@@ -992,7 +993,7 @@ static int launch_tc_impl(const CUtensorMap& a1, const CUtensorMap& a2, const CU
     attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
     cfg.attrs = attr;
     cfg.numAttrs = 2;
-    le = cudaLaunchKernelEx(&cfg, igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS, RS, C2>, a1, a2, b, b, b, p);
+    le = cudaLaunchKernelEx(&cfg, igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS, RS, C2>, a1, a2, b, o ? *o : b, b, p);
   } else
   le = launch_pdl(igemm_tc_kernel<BN, BK, EW, GG, O16, UP, SK, TS, RS>, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, st, a1,
                               a2, b, o ? *o : b, r ? *r : b, p);
@@ -1232,6 +1233,21 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
     uint32_t box[2] = {16u, 32u};
     int rc = make_tensor_map_bf16(&tO, d->out, 2, dims, str, box, 32, 2);
     if (rc) return rc;
+    // CTA pair for the GEGLU GEMMs (24 KB instead of 32 KB per 64-deep chunk and CTA): measured r02s and NOT taken by
+    // default — N5120 K640 0.655 -> 0.680 ms (6 launches), N2560 K320 0.673 -> 0.692: these GEMMs are bound by the erf-GELU
+    // epilogue, not by the operand feed, and the pair only adds its synchronisation.  LDMB200_C2_GG_MINK=320 turns it on.
+    static const int c2g_on = getenv("LDMB200_C2") ? atoi(getenv("LDMB200_C2")) : 1;
+    static const int c2g_mink = getenv("LDMB200_C2_GG_MINK") ? atoi(getenv("LDMB200_C2_GG_MINK")) : (1 << 30);
+    if (c2g_on && p.tiles_m % 2 == 0 && p.ctot >= c2g_mink && sm_count() >= 2 && p.tiles_m * p.tiles_n >= 2 * sm_count()) {
+      CUtensorMap tBh;
+      uint64_t bdims[2] = {(uint64_t)p.taps * p.ctot, (uint64_t)d->n};
+      uint64_t bstr[1] = {(uint64_t)p.taps * p.ctot * 2};
+      uint32_t bbox[2] = {(uint32_t)BK, 64u};
+      rc = make_tensor_map_bf16(&tBh, d->w, 2, bdims, bstr, bbox, BK * 2);
+      if (rc) return rc;
+      p.idesc = umma_idesc_f16(256, 128, d->a_dtype == LDMB200_F16 ? 0 : 1);
+      return launch_tc_impl<128, 64, 16, true, true, false, false, true, false, true>(tA1, tA2, tBh, p, st, &tO);
+    }
     return launch_tc_impl<128, 64, 16, true, true, false, false, true>(tA1, tA2, tB, p, st, &tO);
   }
   // ---- CTA pair (cta_group::2, M = 256): the deep reductions (3x3 convolutions, K >= 1280 linears) on 160-wide tiles

@@ -342,7 +342,7 @@ def test_tc_cta_pair(B, H, c1, c2, n, ksize, stride, extras):
         assert K.rel_l2(cs[..., 1], (blk * blk).sum(1).float()) <= 1e-5
 
 
-@pytest.mark.parametrize("rows,cc", [(512, 160), (200, 160), (20480, 320), (64, 640)])
+@pytest.mark.parametrize("rows,cc", [(512, 160), (200, 160), (20480, 320), (64, 640), (10240, 640), (10200, 320)])
 def test_tc_geglu_tma_store(rows, cc):
     """GEGLU epilogue with a 16-bit output (TMA store of each warp's 32 x 16 chunk, 32B-swizzled staging) == the fp32-output
     epilogue (per-lane stores) rounded to the same type, bit for bit; ragged last tile clipped (harness guard rows)."""

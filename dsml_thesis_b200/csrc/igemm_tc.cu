@@ -1265,9 +1265,16 @@ extern "C" int ldmb200_igemm_tc(const ldmb200_gemm_desc* d, void* stream) {
     uint32_t box[2] = {(uint32_t)BK, (uint32_t)(BN / 2)};
     int rc = make_tensor_map_bf16(&tBh, d->w, 2, dims, str, box, BK * 2);
     if (rc) return rc;
-    p.idesc = umma_idesc_f16(256, BN, d->a_dtype == LDMB200_F16 ? 0 : 1);
-    return out16 ? launch_tc_impl<160, 64, 8, false, true, false, false, false, false, true>(tA1, tA2, tBh, p, st)
-                 : launch_tc_impl<160, 64, 8, false, false, false, false, false, false, true>(tA1, tA2, tBh, p, st);
+    static bool c2_unavailable = false;  // a device / partition that cannot co-schedule 2-clusters: single CTAs from then on
+    if (!c2_unavailable) {
+      TcParams p2 = p;
+      p2.idesc = umma_idesc_f16(256, BN, d->a_dtype == LDMB200_F16 ? 0 : 1);
+      rc = out16 ? launch_tc_impl<160, 64, 8, false, true, false, false, false, false, true>(tA1, tA2, tBh, p2, st)
+                 : launch_tc_impl<160, 64, 8, false, false, false, false, false, false, true>(tA1, tA2, tBh, p2, st);
+      if (rc == 0) return 0;
+      cudaGetLastError();   // the launch was refused (nothing ran): clear it and take the single-CTA kernel below
+      c2_unavailable = true;
+    }
   }
   if (BN == 128) return d->geglu ? launch_tc<128, 64, 16, true>(tA1, tA2, tB, p, st) : launch_tc<128, 64, 16>(tA1, tA2, tB, p, st);
   LDM_CHECK_ARG(!d->geglu || d->n % 32 == 0, "igemm_tc: geglu needs n %% 32 == 0 (got n=%d)", d->n);

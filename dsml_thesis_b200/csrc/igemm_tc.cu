@@ -23,6 +23,9 @@
 #ifndef LDM_TC_RES_PREFETCH
 #define LDM_TC_RES_PREFETCH 1
 #endif
+#ifndef LDM_TC_RUNCNT
+#define LDM_TC_RUNCNT 1   // (r02s: -1.7 % on the family, -3..-6 % on the deep convolutions: the per-chunk instruction count of the two service warps is a limiter) running stage / phase counters in the producer and MMA loops instead of it % STAGES, it / STAGES
+#endif
 #ifndef LDM_TC_GG_PIPE
 #define LDM_TC_GG_PIPE 1   // software-pipelined GEGLU epilogue (halves of the chunk; see the epilogue branch)
 #endif
@@ -309,6 +312,8 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     // (a single-thread producer / MMA loop with running stage counters was measured r02l and is SLOWER: big-K convolutions
     // 0.753 -> 0.934 ms at K = 5760, implicit GEMMs 13.6 -> 14.9 ms per eval; the converged-warp form stays)
     uint32_t it = 0;
+    [[maybe_unused]] int rs_ = 0;
+    [[maybe_unused]] uint32_t rp_ = 0;
     [[maybe_unused]] const uint32_t full0 = C2 ? mapa_u32(smem_u32(full), 0) : 0u;   // rank 0's full[] barriers
     for (int unit = unit0; unit < ntiles; unit += ustep) {
       const int tile = C2 ? pair_tile(unit) : SK ? unit / p.splits : unit;
@@ -350,8 +355,14 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
           }
         }
         for (int j = SK ? max(k0 - tap * nchunks, 0) : 0; j < (SK ? min(k1 - tap * nchunks, nchunks) : nchunks); ++j, ++it) {
+#if LDM_TC_RUNCNT
+          const int s = rs_;
+          const uint32_t ph_ = rp_;
+          if (++rs_ == Cfg::STAGES) { rs_ = 0; rp_ ^= 1u; }
+#else
           const int s = it % Cfg::STAGES;
           const uint32_t ph_ = (it / Cfg::STAGES) & 1;
+#endif
           mbar_wait(&empty[s], ph_ ^ 1);
           if (elect_one()) {
             const bool second = j >= p.c1_chunks;
@@ -388,6 +399,8 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
     const uint32_t idesc = p.idesc;
     const int kmax1 = p.c1_tail_k, kmax2 = p.c2_tail_k;
     uint32_t it = 0, t_iter = 0;
+    [[maybe_unused]] int rs_ = 0;
+    [[maybe_unused]] uint32_t rp_ = 0;
     for (int unit = unit0; unit < ntiles; unit += ustep, ++t_iter) {
       const uint32_t buf = t_iter & 1;
       mbar_wait(&tempty[buf], ((t_iter >> 1) & 1) ^ 1);
@@ -398,8 +411,14 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       const int k1 = SK ? min(p.taps * nchunks, k0 + p.kiters_per_split) : p.taps * nchunks;
       for (int tap = SK ? k0 / nchunks : 0; tap < (SK ? (k1 + nchunks - 1) / nchunks : p.taps); ++tap) {
         for (int j = SK ? max(k0 - tap * nchunks, 0) : 0; j < (SK ? min(k1 - tap * nchunks, nchunks) : nchunks); ++j, ++it) {
+#if LDM_TC_RUNCNT
+          const int s = rs_;
+          const uint32_t ph_ = rp_;
+          if (++rs_ == Cfg::STAGES) { rs_ = 0; rp_ ^= 1u; }
+#else
           const int s = it % Cfg::STAGES;
           const uint32_t ph_ = (it / Cfg::STAGES) & 1;
+#endif
           const int kmax = (j == p.c1_chunks - 1) ? kmax1 : (j == nchunks - 1) ? kmax2 : BK / 16;
           mbar_wait(&full[s], ph_);
           tc_fence_after();

@@ -26,6 +26,11 @@
 #ifndef LDM_TC_RUNCNT
 #define LDM_TC_RUNCNT 1   // (r02s: -1.7 % on the family, -3..-6 % on the deep convolutions: the per-chunk instruction count of the two service warps is a limiter) running stage / phase counters in the producer and MMA loops instead of it % STAGES, it / STAGES
 #endif
+#ifndef LDM_TC_SPLITP
+#define LDM_TC_SPLITP 0   // CTA-pair kernels: a second producer warp issues the B (weight) loads, warp 0 the A loads only.  Measured r02s
+                          // (same run, after the running counters): implicit GEMMs 12.47 vs 12.49 ms per eval - the concat convolutions gain
+                          // 2-4 %, the rest is flat: off
+#endif
 #ifndef LDM_TC_GG_PIPE
 #define LDM_TC_GG_PIPE 1   // software-pipelined GEGLU epilogue (halves of the chunk; see the epilogue branch)
 #endif
@@ -78,7 +83,7 @@ struct TcParams {
 // 36 KB per stage through each SM's L2 port, and seven stages instead of five.
 template <int BN, int BK, int EW, bool RS = false, bool C2 = false>
 struct TcCfg {
-  static constexpr int THREADS = 64 + EW * 32;
+  static constexpr int THREADS = 64 + EW * 32 + ((C2 && LDM_TC_SPLITP) ? 32 : 0);
   static constexpr int BM = 128;
   static constexpr int SW = BK * 2;  // swizzle span in bytes == one K-major row
   static constexpr int A_BYTES = BM * BK * 2;
@@ -237,7 +242,7 @@ __device__ __forceinline__ void epi_store(const TcParams& p, const float* st, in
 // C2: CTA-pair main loop (launched as 2-clusters; plain epilogue only): unit = a pair of vertically adjacent M tiles.
 template <int BN, int BK, int EW, bool GG, bool O16, bool UP = false, bool SK = false, bool TS = false, bool RS = false,
           bool C2 = false>
-__global__ void __launch_bounds__(64 + EW * 32, 1)
+__global__ void __launch_bounds__(TcCfg<BN, BK, EW, RS, C2>::THREADS, 1)
 igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmA2,
                 const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
                 const __grid_constant__ CUtensorMap tmR, const TcParams p) {
@@ -375,8 +380,9 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
                 tma_load_5d_pair(sA + s * Cfg::A_BYTES, tm_a, bar, c0, w0 + dw, h0 + dh, plane, n_img);
               else
                 tma_load_5d_pair(sA + s * Cfg::A_BYTES, tm_a, bar, c0, 0, m0, 0, 0);
-              tma_load_2d_pair(sB + s * Cfg::B_BYTES, &tmB, bar, tap * p.ctot + (second ? p.c1 : 0) + c0,
-                               p.b_row0 + tn * BN + crank * (BN / 2));
+              if (!LDM_TC_SPLITP)
+                tma_load_2d_pair(sB + s * Cfg::B_BYTES, &tmB, bar, tap * p.ctot + (second ? p.c1 : 0) + c0,
+                                 p.b_row0 + tn * BN + crank * (BN / 2));
             } else {
             mbar_expect_tx(&full[s], Cfg::TX_BYTES);
             if (p.is_conv)
@@ -386,6 +392,29 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
             tma_load_2d(sB + s * Cfg::B_BYTES, &tmB, &full[s], tap * p.ctot + (second ? p.c1 : 0) + c0, p.b_row0 + tn * BN);
             }
           }
+          __syncwarp();
+        }
+      }
+    }
+  } else if (C2 && LDM_TC_SPLITP && warp == 2 + EW) {
+    // ===================== second producer of the CTA-pair kernels: this CTA's half of the weight tile =====================
+    // (the one-lane instruction stream of a producer that issues A and B — ~80 SASS instructions per 64-deep chunk, most of
+    // them register-to-uniform moves for the TMA coordinates — took as long as the chunk's MMAs: ncu r02t)
+    const uint32_t full0 = mapa_u32(smem_u32(full), 0);
+    int rs_ = 0;
+    uint32_t rp_ = 0;
+    for (int unit = unit0; unit < ntiles; unit += ustep) {
+      const int brow = p.b_row0 + (unit % p.tiles_n) * BN + crank * (BN / 2);
+      for (int tap = 0; tap < p.taps; ++tap) {
+        const int kcol = tap * p.ctot;
+        for (int j = 0; j < nchunks; ++j) {
+          const int s = rs_;
+          const uint32_t ph_ = rp_;
+          if (++rs_ == Cfg::STAGES) { rs_ = 0; rp_ ^= 1u; }
+          mbar_wait(&empty[s], ph_ ^ 1);
+          if (elect_one())
+            tma_load_2d_pair(sB + s * Cfg::B_BYTES, &tmB, full0 + s * 8,
+                             kcol + (j >= p.c1_chunks ? p.c1 + (j - p.c1_chunks) * BK : j * BK), brow);
           __syncwarp();
         }
       }
@@ -449,7 +478,7 @@ igemm_tc_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant_
       }
       __syncwarp();
     }
-  } else if (warp >= 2) {
+  } else if (warp >= 2 && warp < 2 + EW) {
     // ===================== epilogue (EW warps) =====================
     const int ew = warp - 2;
     const int qw = warp & 3;          // TMEM lane quarter accessible to this warp (hardware: warp id % 4)

@@ -91,15 +91,16 @@ def test_training_step_accumulates_and_rezeroes():
     T.p_losses(handle, *args)[0].backward()
     g1 = {n: p.grad.clone() for n, p in unet.named_parameters()}
     T.p_losses(handle, *args)[0].backward()          # grads not zeroed: accumulate like autograd
-    # run-to-run tolerance: weight gradients are summed with fp32 atomics in arbitrary order, and every bf16 cast of the
-    # gradient signal amplifies that last-bit noise up to the bf16 epsilon (0.4 %), so two runs agree to ~1e-2, not 1e-6
+    # run-to-run tolerance: the data-gradient path is deterministic; weight / bias gradients are summed with fp32 atomics
+    # in arbitrary order, so two runs agree to fp32 summation order, not bit for bit — measured (tools/check_train_repro.py)
+    # 4e-7 worst parameter on the TF UNet at 32x32, 9e-5 on this tiny UNet (a bias with heavy cancellation)
     big = lambda t: float(t.norm()) > 1e-5 * t.numel() ** 0.5
     for n, p in unet.named_parameters():
-        assert O.rel_l2(p.grad, 2 * g1[n]) <= 3e-2 or not big(g1[n]), n
+        assert O.rel_l2(p.grad, 2 * g1[n]) <= 2e-3 or not big(g1[n]), n
     unet.zero_grad(set_to_none=True)
     T.p_losses(handle, *args)[0].backward()
     for n, p in unet.named_parameters():
-        assert O.rel_l2(p.grad, g1[n]) <= 3e-2 or not big(g1[n]), n
+        assert O.rel_l2(p.grad, g1[n]) <= 2e-3 or not big(g1[n]), n
 
 
 def test_fused_adamw_ema_step_matches_torch_adamw():

@@ -84,6 +84,7 @@ def test_c2_full_trajectory_vs_reference_golden(precision, golden_c2):
 def test_fr_unet_64_batch4_vs_reference_and_batch_invariance(precision, golden_c2):
     cfg = O.FR_UNET
     m = build(cfg, precision)
+    m.split_k = False          # (the shipped default; explicit so that LDMB200_SPLITK=1 in the environment does not change the test)
     x, ctx = synth_inputs(cfg, 4, 64, 3)
     t = torch.from_numpy(golden_c2["c2/b4/t"])
     with torch.no_grad():
